@@ -1,0 +1,29 @@
+"""CPU oracle for the learner hot path of d3sm0/impala -- TEST INFRASTRUCTURE ONLY.
+
+This package is the *checker*, never the product: only ``tests/``,
+``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl
+reference`` legs may import it.  Nothing under ``impala_b200/`` imports it.
+
+PARITY UNPINNED.  The reference (``/root/reference``) holds no tests, no golden
+vectors and no fixtures, and the arithmetic of its hot path lives
+in third-party packages that are neither vendored nor installed nor pinned:
+
+* ``rlego``  -- ``git+https://github.com/d3sm0/RLego.git`` HEAD, no commit hash
+  (reference ``requirements.txt:7``).  Restated here from the published
+  algorithms its function names mirror one-for-one (DeepMind rlax
+  ``vtrace_td_error_and_advantage`` / ``lambda_returns`` /
+  ``truncated_generalized_advantage_estimation``; Espeholt et al. 2018 sec 4.1;
+  Schulman et al. 2016), anchored on the reference's own call sites
+  (``agents/impala/learning.py:18,150-153``, ``losses.py:106``,
+  ``agents/ppo/learning.py:68``).
+* ``rlmeta`` -- facebookresearch/rlmeta HEAD, unpinned (reference
+  ``Dockerfile:43-47``): ``ReplayBuffer`` / ``CircularBuffer`` /
+  ``UniformSampler``.  Its RNG stream cannot be reproduced (C++ extension
+  absent), so the sampler is *specified* here (Philox4x32-10, pinned by the
+  Random123 known-answer vectors) and the CUDA path must match it bit for bit.
+
+What *is* pinned: the torch arithmetic the reference itself calls
+(``torch.distributions.Categorical`` / ``kl_divergence`` are imported from the
+installed torch, not restated), the op order of the reference's loss code, and
+hand-derived known-answer cases in ``tests/``.
+"""

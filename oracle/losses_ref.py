@@ -1,0 +1,125 @@
+"""Restatement of the reference's loss code (TEST ORACLE, CPU torch, differentiable).
+
+PARITY UNPINNED at the rlego boundary (see ``oracle/__init__.py``).  The
+``torch.distributions`` arithmetic is the installed torch's own, as in the
+reference.  Each function takes the *model outputs* (logits, values) instead of
+``model`` + observations so that the CUDA path can be compared on identical
+tensors; ``*_with_model`` wrappers keep the reference signatures.
+"""
+import torch
+from torch.distributions import Categorical, kl_divergence
+
+from . import rlego_ref
+
+
+def impala_train_loss(logits, values, a, r, discount_t, pi_ref_logits,
+                      entropy_coeff=0.01, lambda_=1.0, clip_rho_threshold=1.0,
+                      clip_pg_rho_threshold=1.0, detach_adv=False, detach_rho=False,
+                      use_vmap=True):
+    """Reference ``ImpalaLearner._train_step`` lines ``agents/impala/learning.py:146-170``.
+
+    Batch-major: ``logits, pi_ref_logits [B,T,A]``, ``values, r, discount_t [B,T]``,
+    ``a [B,T] int64``.  Returns ``(loss, metrics)`` with the reference's metric keys
+    (minus ``train/grad_norm`` which belongs to the optimiser step).
+    ``detach_adv`` / ``detach_rho`` default False = call-site truth (``:148,155``).
+    """
+    pi = Categorical(logits=logits)                                   # :146
+    pi_ref = Categorical(logits=pi_ref_logits)                        # :147
+    rho_tm1 = torch.exp(pi.log_prob(a) - pi_ref.log_prob(a))          # :148
+    rho_in = rho_tm1.detach() if detach_rho else rho_tm1
+    kw = dict(lambda_=lambda_, clip_rho_threshold=clip_rho_threshold,
+              clip_pg_rho_threshold=clip_pg_rho_threshold)
+    args = (values[:, :-1], values[:, 1:], r[:, :-1], discount_t[:, :-1], rho_in[:, :-1])
+    if use_vmap:                                                      # :18
+        adv, err, _ = rlego_ref.batched(rlego_ref.vtrace_td_error_and_advantage, **kw)(*args)
+    else:                                                             # :20-26
+        adv, err, _ = rlego_ref.batched_loop(rlego_ref.vtrace_td_error_and_advantage, *args, **kw)
+    if detach_adv:
+        adv = adv.detach()
+    pg_loss = (pi.log_prob(a)[:, :-1] * adv).mean()                   # :155
+    value_loss = err.pow(2).mean()                                    # :156
+    entropy_loss = pi.entropy().mean()                                # :157
+    loss = -pg_loss + value_loss - entropy_coeff * entropy_loss       # :159
+    metrics = {
+        "train/loss": loss.detach(),
+        "train/entropy": entropy_loss.detach(),
+        "train/td": value_loss.detach(),
+        "train/pg": pg_loss.detach(),
+        "train/kl": kl_divergence(pi, pi_ref).mean().detach(),        # :167
+        "train/ratio": rho_tm1.mean().detach(),                       # :168
+    }
+    return loss, metrics
+
+
+def ppo_loss_from_outputs(logits, v, a, v_target, pi_ref_logits,
+                          entropy_cost=0.01, clip_coeff=0.1):
+    """Reference ``losses.ppo_loss`` lines ``losses.py:134-155`` after ``model(s)``.
+
+    ``logits, pi_ref_logits [N,A]``, ``v [N,1]`` or ``[N]``, ``a [N] int64``,
+    ``v_target [N]``.
+    """
+    pi_tm1 = Categorical(logits=logits)
+    pi_ref = Categorical(logits=pi_ref_logits)
+    ratio = torch.exp(pi_tm1.log_prob(a) - pi_ref.log_prob(a))        # :136
+    adv = v_target - (v.squeeze(-1) if v.dim() > v_target.dim() else v)  # :137
+    td_loss = 0.5 * adv.pow(2).mean()                                 # :138
+    adv = adv.detach()                                                # :139
+    pg_loss_1 = -(adv * ratio)                                        # :140
+    pg_loss_2 = -torch.clamp(ratio, 1 - clip_coeff, 1 + clip_coeff) * adv  # :141
+    pg_loss = torch.max(pg_loss_1, pg_loss_2).mean()                  # :142
+    kl = kl_divergence(pi_tm1, pi_ref).mean().clamp_min(0.)           # :144
+    entropy = pi_tm1.entropy().mean()                                 # :145
+    loss = pg_loss + td_loss - entropy_cost * entropy                 # :146
+    return loss, {
+        "train/loss": loss.detach(),
+        "train/entropy": entropy.detach(),
+        "train/td": td_loss.detach(),
+        "train/pg": pg_loss.detach(),
+        "train/target": v_target.mean().detach(),
+        "train/kl": kl.detach(),
+        "train/ratio": ratio.mean().detach(),
+    }
+
+
+def ppo_loss(model, batch, entropy_cost=0.01, clip_coeff=0.1):
+    """Reference signature, ``losses.py:131``."""
+    s, a, v_target, pi_ref = batch
+    logits, v = model(s)
+    return ppo_loss_from_outputs(logits, v, a, v_target, pi_ref, entropy_cost, clip_coeff)
+
+
+def impala_loss_from_outputs(pi_tm1, v_tm1, a, r, discount_t, lambda_=1.0):
+    """Reference ``losses.impala_loss`` AS WRITTEN (``losses.py:98-128``; WIP, no caller):
+    raw logits gathered (not log-probs), ``ratio = ones``, bootstrap = same-time detached
+    value, one un-batched sequence ``[N,...]``, ``pg = -sum``, entropy disabled.
+    """
+    a = a.squeeze(dim=-1)                                             # :98
+    ratio = torch.ones_like(r).squeeze().float()                      # :99
+    v_t = v_tm1.squeeze(-1).detach()                                  # :105
+    adv, err, _ = rlego_ref.vtrace_td_error_and_advantage(            # :106-108
+        v_tm1.squeeze(-1), v_t, r.squeeze(dim=-1), discount_t.squeeze(dim=-1),
+        ratio.detach(), lambda_=lambda_)
+    td_loss = 0.5 * err.pow(2).mean()                                 # :109
+    pg_loss = -(pi_tm1.gather(1, a.unsqueeze(dim=-1)).squeeze(dim=-1) * adv).sum()  # :116
+    loss = pg_loss + td_loss                                          # :120
+    return loss, {
+        "train/loss": loss.detach(),
+        "train/td": td_loss.detach(),
+        "train/pg": pg_loss.detach(),
+        "train/ratio": ratio.mean().detach(),
+    }
+
+
+def impala_loss(batch, model, lambda_=1., entropy_cost=0.01):
+    """Reference signature, ``losses.py:92`` (note: batch first, unlike ``ppo_loss``)."""
+    s, a, r, discount_t, pi_ref = batch
+    pi_tm1, v_tm1 = model(s)
+    return impala_loss_from_outputs(pi_tm1, v_tm1, a, r, discount_t, lambda_)
+
+
+def ppo_make_targets(r, done, v, gamma=0.99, lambda_=0.95):
+    """Reference ``PPOActorRemote._make_replay`` lines ``agents/ppo/learning.py:67-68``
+    with the evident intent ``values -> v`` (the committed line raises NameError).
+    Per rollout ``[T]`` -> ``[T-1]``."""
+    discount_t = torch.logical_not(done) * gamma
+    return rlego_ref.lambda_returns(r[:-1], discount_t[:-1], v[1:], lambda_)
