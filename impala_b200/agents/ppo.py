@@ -1,0 +1,93 @@
+"""Drop-in for the reference's ``PPOLearner`` (``agents/ppo/learning.py:75-143``) and the actor-side
+target computation (``PPOActorRemote._make_replay``, ``:65-69``)."""
+import time
+from typing import Dict, Optional
+
+import torch
+
+from .. import ops, parallel, vtrace
+
+
+def make_targets(r, done, v, gamma: float = 0.99, lambda_: float = 0.95, time_major: bool = False):
+    """Batched ``_make_replay`` targets: ``lambda_returns(r[:-1], discount[:-1], v[1:], lambda_)`` for
+    every column at once (the reference loops per rollout on the CPU, and its committed line has a
+    NameError -- ``values`` for ``v``).  ``[B,T]`` inputs (``[T,B]`` if ``time_major``) -> ``T-1`` steps."""
+    discount = torch.logical_not(done) * gamma
+    if time_major:
+        return vtrace.lambda_returns(r[:-1], discount[:-1], v[1:], lambda_, time_major=True)
+    return vtrace.lambda_returns(r[:, :-1], discount[:, :-1], v[:, 1:], lambda_)
+
+
+class PPOLearner:
+    def __init__(self, model, replay_buffer, optimizer: torch.optim.Optimizer, batch_size: int = 256,
+                 max_grad_norm: float = 0.5, entropy_coeff: float = 0.01,
+                 learning_starts: Optional[int] = None, model_push_period: int = 8,
+                 clip_coeff: float = 0.1, process_group=None) -> None:
+        self._model = model
+        self._replay_buffer = replay_buffer
+        self._optimizer = optimizer
+        self._batch_size = batch_size
+        self._max_grad_norm = max_grad_norm
+        self._entropy_coeff = entropy_coeff
+        self._learning_starts = learning_starts
+        self._model_push_period = model_push_period
+        self._clip_coeff = clip_coeff
+        self._group = process_group
+        self._device = None
+        self._step_counter = 0
+        self._bucket = None
+        self.can_train = False
+
+    def device(self) -> torch.device:
+        if self._device is None:
+            self._device = next(self._model.parameters()).device
+        return self._device
+
+    def prepare(self):
+        if not self.can_train:
+            self._replay_buffer.warm_up(self._learning_starts)
+        self.can_train = True
+
+    def train_step(self):
+        t0 = time.perf_counter()
+        _, batch, _ = self._replay_buffer.sample(self._batch_size)
+        t1 = time.perf_counter()
+        metrics = self._train_step(batch)
+        t2 = time.perf_counter()
+        self._step_counter += 1
+        update_time = 0
+        if self._step_counter % self._model_push_period == 0 and hasattr(self._model, "push"):
+            start = time.perf_counter()
+            self._model.push()
+            update_time = (time.perf_counter() - start) * 1000
+        metrics["debug/replay_sample_per_second"] = self._batch_size / max((t1 - t0) * 1000, 1e-9)
+        metrics["debug/gradient_per_second"] = self._batch_size / max((t2 - t1) * 1000, 1e-9)
+        metrics["debug/total_time"] = (time.perf_counter() - t0) * 1000
+        metrics["debug/forward_dt"] = (t2 - t1) * 1000
+        metrics["debug/update_time"] = update_time
+        return metrics
+
+    def _train_step(self, batch) -> Dict[str, torch.Tensor]:
+        if self._bucket is None:
+            self._bucket = parallel.GradBucket(self._model.parameters())
+        bucket = self._bucket
+        bucket.attach()
+        dev = self.device()
+        s, a, v_target, pi_ref = (x.to(dev, non_blocking=True) for x in batch)
+        a, v_target = a.reshape(-1), v_target.reshape(-1)
+        _, world_size = parallel.world(self._group)
+        pi, v = self._model(s)
+        scalars, dlogits, dv = ops.ppo_loss_fwdbwd(pi, v, a, v_target, pi_ref, self._entropy_coeff,
+                                                   self._clip_coeff, n_global=pi.shape[0] * world_size)
+        torch.autograd.backward([pi, v], [dlogits, dv.view_as(v)])        # :134
+        bucket.extra.copy_(scalars)
+        bucket.allreduce(self._group)
+        grad_norm = bucket.clip_(self._max_grad_norm)                     # :136-137
+        self._optimizer.step()                                            # :140
+        sc = bucket.extra
+        return {
+            "train/loss": sc[ops.S_LOSS], "train/entropy": sc[ops.S_ENTROPY], "train/td": sc[ops.S_TD],
+            "train/pg": sc[ops.S_PG], "train/target": sc[ops.S_TARGET],
+            "train/kl": sc[ops.S_KL].clamp_min(0.), "train/ratio": sc[ops.S_RATIO],
+            "train_step/grad_norm": grad_norm,
+        }

@@ -1,0 +1,263 @@
+// K1: fused V-trace + IMPALA loss, forward and backward in ONE launch.
+// Replaces reference agents/impala/learning.py:146-160,167-168 (+ rlego V-trace).
+//
+// Work split: a CTA owns a tile of `C` batch columns x all T steps; one thread per
+// (column, step) sample.  The tile's logits and behaviour logits are staged in
+// shared memory by TMA 1-D bulk copies (batch-major: one contiguous copy per tensor;
+// time-major: one copy per step), each thread keeps its A logits in registers, the
+// T-1 step V-trace recursion runs as a register chain in C threads (reference
+// operation order), and d loss/d logits is written back over the staged tile and
+// leaves by a bulk store.  Every input byte is read once, every gradient byte
+// written once: 204 B/sample at A=15.
+#include "softmax.cuh"
+
+namespace b200rl {
+
+struct ImpalaParams {
+    const float *logits, *pi_ref, *rewards, *discounts, *values;
+    const long long *actions;
+    float *dlogits, *dvalues, *scalars;
+    void *workspace;
+    int B, T, A, C, time_major;
+    float lambda_, clip_rho, clip_pg_rho, entropy_coeff, inv_n_pg, inv_n_all;
+    uint32_t flags;
+};
+
+template <int AT>
+__global__ void __launch_bounds__(AT <= 16 ? 512 : 256) impala_loss_kernel(const ImpalaParams p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int T = p.T, A = p.A, C = p.C, NS = C * T;
+    float *sx = reinterpret_cast<float *>(smem_raw);  // [NS*A] logits -> dlogits
+    float *sy = sx + (size_t)NS * A;                  // [NS*A] behaviour logits
+    float *s_td = sy + (size_t)NS * A;                // [NS] clipped TD errors -> V-trace errors e_t
+    float *s_gc = s_td + NS;                          // [NS] discount * c
+    float *s_nx = s_gc + NS;                          // [NS] d loss/d v_{t+1} pushed by step t
+    float *red = s_nx + NS;                           // [5*32]
+    uint64_t *bar = reinterpret_cast<uint64_t *>(red + 5 * 32);
+
+    const int b0 = blockIdx.x * C;
+    const int cols = min(C, p.B - b0);
+    const int s = threadIdx.x;
+    int c, t;
+    if (p.time_major) { t = s / C; c = s - t * C; } else { c = s / T; t = s - c * T; }
+    const bool valid = s < NS && c < cols;
+    const int st_local = p.time_major ? C : 1;  // local index distance between t and t+1
+    const long long n = p.time_major ? (long long)t * p.B + b0 + c : (long long)(b0 + c) * T + t;
+    const long long n_stride_t = p.time_major ? p.B : 1;
+
+    // ---- phase 1: stage the tile ------------------------------------------------------
+    const size_t row_elems = (size_t)(p.time_major ? cols : cols * T) * A;  // contiguous run
+    const int nrows = p.time_major ? T : 1;
+    const size_t g_row0 = (size_t)(p.time_major ? b0 : (size_t)b0 * T) * A;
+    const size_t g_row_stride = (size_t)p.B * A;  // time-major only
+    const size_t s_row_stride = (size_t)C * A;    // time-major only
+    const uint32_t row_bytes = (uint32_t)(row_elems * 4);
+    const bool bulk_ok = (row_bytes % 16 == 0) && ((g_row0 * 4) % 16 == 0) &&
+                         (nrows == 1 || ((g_row_stride * 4) % 16 == 0 && (s_row_stride * 4) % 16 == 0)) &&
+                         ((reinterpret_cast<uintptr_t>(p.logits) | reinterpret_cast<uintptr_t>(p.pi_ref) |
+                           reinterpret_cast<uintptr_t>(p.dlogits)) % 16 == 0);
+    if (bulk_ok) {
+        if (threadIdx.x == 0) {
+            mbar_init(bar, 1);
+            fence_mbar_init();
+            mbar_expect_tx(bar, 2u * row_bytes * nrows);
+            for (int r = 0; r < nrows; ++r) {
+                bulk_g2s(sx + r * s_row_stride, p.logits + g_row0 + r * g_row_stride, row_bytes, bar);
+                bulk_g2s(sy + r * s_row_stride, p.pi_ref + g_row0 + r * g_row_stride, row_bytes, bar);
+            }
+        }
+    } else {
+        for (int r = 0; r < nrows; ++r)
+            for (size_t i = threadIdx.x; i < row_elems; i += blockDim.x) {
+                sx[r * s_row_stride + i] = ld_stream_f32(p.logits + g_row0 + r * g_row_stride + i);
+                sy[r * s_row_stride + i] = ld_stream_f32(p.pi_ref + g_row0 + r * g_row_stride + i);
+            }
+    }
+    long long act = 0;
+    float rew = 0.f, disc = 0.f, v = 0.f, v_next = 0.f;
+    const bool has_next = valid && t < T - 1;
+    if (valid) {
+        act = p.actions[n];
+        rew = p.rewards[n];
+        disc = p.discounts[n];
+        v = p.values[n];
+        if (has_next) v_next = p.values[n + n_stride_t];
+    }
+    __syncthreads();  // mbarrier init visible / cooperative stores done
+    if (bulk_ok) mbar_wait(bar, 0);
+
+    // ---- phase 2: per-sample softmax statistics, TD error, trace coefficient -----------
+    SampleStats<AT> st;
+    float c_pg = 0.f;
+    const bool detach_adv = p.flags & B200RL_DETACH_ADV, detach_rho = p.flags & B200RL_DETACH_RHO;
+    if (valid) {
+        sample_stats<AT>(st, sx + (size_t)s * A, sy + (size_t)s * A, A, act);
+        c_pg = fminf(st.rho, p.clip_pg_rho);
+        if (has_next) {
+            s_td[s] = fminf(st.rho, p.clip_rho) * (rew + disc * v_next - v);
+            s_gc[s] = disc * (fminf(st.rho, 1.0f) * p.lambda_);
+            // adv_t depends on v_{t+1} through the q bootstrap: weight 1 at the last step,
+            // (1 - lambda) elsewhere (the lambda * vs_{t+1} part is a stop-gradient target)
+            const float w = (t == T - 2) ? 1.f : (1.f - p.lambda_);
+            s_nx[s] = detach_adv ? 0.f : -st.lp * c_pg * disc * w * p.inv_n_pg;
+        }
+    }
+    __syncthreads();
+
+    // ---- phase 3: backward-in-time recursion, one register chain per column ------------
+    if (s < cols) {
+        const int sc_local = p.time_major ? 1 : T;
+        float e = 0.f;
+        int idx = s * sc_local + (T - 2) * st_local;
+#pragma unroll 4
+        for (int tt = T - 2; tt >= 0; --tt, idx -= st_local) {
+            e = s_td[idx] + s_gc[idx] * e;
+            s_td[idx] = e;
+        }
+    }
+    __syncthreads();
+
+    // ---- phase 4: losses and gradients -------------------------------------------------
+    float sums[5] = {0.f, 0.f, 0.f, 0.f, 0.f};  // pg, value, entropy, kl, ratio
+    if (valid) {
+        float g_lp = 0.f, dv = 0.f;
+        if (has_next) {
+            const float e = s_td[s];
+            const float tgt = e + v;     // stop-gradient target vs_t
+            const float err = tgt - v;   // rlego "errors"
+            float qb = v_next;
+            if (t < T - 2) {
+                const float e1 = s_td[s + st_local];
+                const float tgt1 = ((e1 + v_next) - v_next) + v_next;
+                qb = p.lambda_ * tgt1 + (1.f - p.lambda_) * v_next;
+            }
+            const float q = rew + disc * qb;
+            const float qmv = q - v;
+            const float adv = c_pg * qmv;
+            sums[0] = st.lp * adv;
+            sums[1] = err * err;
+            float dpg_dlp = adv;  // d(lp*adv)/dlp, adv's own dependence on lp via rho below
+            if (!detach_adv && !detach_rho && st.rho <= p.clip_pg_rho) dpg_dlp += st.lp * st.rho * qmv;
+            g_lp = -dpg_dlp * p.inv_n_pg;
+            dv = -2.f * err * p.inv_n_pg;
+            if (!detach_adv) dv += st.lp * c_pg * p.inv_n_pg;
+        }
+        if (t > 0) dv += s_nx[s - st_local];
+        p.dvalues[n] = dv;
+        sums[2] = st.H;
+        sums[3] = st.kl;
+        sums[4] = st.rho;
+        write_dlogits<AT>(st, sx + (size_t)s * A, A, g_lp, p.entropy_coeff * p.inv_n_all);
+    }
+    if (bulk_ok) fence_proxy_async_smem();
+    __syncthreads();
+    if (bulk_ok) {
+        if (threadIdx.x == 0) {
+            for (int r = 0; r < nrows; ++r)
+                bulk_s2g(p.dlogits + g_row0 + r * g_row_stride, sx + r * s_row_stride, row_bytes);
+            bulk_commit();
+        }
+    } else {
+        for (int r = 0; r < nrows; ++r)
+            for (size_t i = threadIdx.x; i < row_elems; i += blockDim.x)
+                p.dlogits[g_row0 + r * g_row_stride + i] = sx[r * s_row_stride + i];
+    }
+
+    // ---- scalars: deterministic grid reduction -----------------------------------------
+    const float inv_n_pg = p.inv_n_pg, inv_n_all = p.inv_n_all, ec = p.entropy_coeff;
+    float *scalars = p.scalars;
+    grid_reduce<5>(sums, red, p.workspace, [=](const float(&tot)[5]) {
+        const float pg = tot[0] * inv_n_pg, td = tot[1] * inv_n_pg, ent = tot[2] * inv_n_all;
+        scalars[B200RL_S_LOSS] = -pg + td - ec * ent;
+        scalars[B200RL_S_ENTROPY] = ent;
+        scalars[B200RL_S_TD] = td;
+        scalars[B200RL_S_PG] = pg;
+        scalars[B200RL_S_KL] = tot[3] * inv_n_all;
+        scalars[B200RL_S_RATIO] = tot[4] * inv_n_all;
+        scalars[6] = 0.f;
+        scalars[7] = 0.f;
+    });
+    if (bulk_ok && threadIdx.x == 0) bulk_wait_read0();  // smem must outlive the bulk store's reads
+}
+
+}  // namespace b200rl
+
+// ------------------------------------------------------------------------ host side
+namespace b200rl {
+
+int env_int(const char *name, int dflt);
+
+template <int AT>
+static int32_t launch_impala(const ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
+    static bool configured = false;  // opt in to > 48 KB dynamic shared memory once
+    if (!configured || smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(impala_loss_kernel<AT>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        if (e != cudaSuccess) {
+            set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+            return (int32_t)e;
+        }
+        configured = true;
+    }
+    const int grid = (p.B + p.C - 1) / p.C;
+    impala_loss_kernel<AT><<<grid, threads, smem, stream>>>(p);
+    return check_launch("impala_loss_kernel");
+}
+
+}  // namespace b200rl
+
+extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
+    const float *logits, const float *pi_ref, const int64_t *actions, const float *rewards,
+    const float *discounts, const float *values, int64_t B, int64_t T, int64_t A, int64_t stride_b,
+    int64_t stride_t, int64_t n_global_b, float lambda_, float clip_rho, float clip_pg_rho,
+    float entropy_coeff, uint32_t flags, float *dlogits, float *dvalues, float *scalars,
+    void *workspace, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(logits && pi_ref && actions && rewards && discounts && values && dlogits &&
+                       dvalues && scalars && workspace, -1, "impala_loss: null pointer argument");
+    B200RL_REQUIRE(B >= 1 && T >= 2 && A >= 1, -2, "impala_loss: need B>=1, T>=2, A>=1 (got B=%lld T=%lld A=%lld)",
+                   (long long)B, (long long)T, (long long)A);
+    B200RL_REQUIRE(A <= 32, -3, "impala_loss: A=%lld > 32 actions not supported", (long long)A);
+    const int max_threads = A <= 16 ? 512 : 256;  // == __launch_bounds__ of the instantiation
+    B200RL_REQUIRE(T <= max_threads, -3, "impala_loss: T=%lld > %d steps not supported at A=%lld",
+                   (long long)T, max_threads, (long long)A);
+    B200RL_REQUIRE(B * T < (1ll << 31), -3, "impala_loss: B*T too large");
+    const bool batch_major = (stride_t == 1 && stride_b == T);
+    const bool time_major = (stride_b == 1 && stride_t == B);
+    B200RL_REQUIRE(batch_major || time_major, -4,
+                   "impala_loss: strides (%lld,%lld) are neither batch-major (T,1) nor time-major (1,B)",
+                   (long long)stride_b, (long long)stride_t);
+    B200RL_REQUIRE(n_global_b >= B, -2, "impala_loss: n_global_b < B");
+
+    ImpalaParams p;
+    p.logits = logits; p.pi_ref = pi_ref; p.rewards = rewards; p.discounts = discounts; p.values = values;
+    p.actions = reinterpret_cast<const long long *>(actions);
+    p.dlogits = dlogits; p.dvalues = dvalues; p.scalars = scalars; p.workspace = workspace;
+    p.B = (int)B; p.T = (int)T; p.A = (int)A;
+    p.time_major = (time_major && !batch_major) ? 1 : 0;
+    p.lambda_ = lambda_; p.clip_rho = clip_rho; p.clip_pg_rho = clip_pg_rho; p.entropy_coeff = entropy_coeff;
+    p.inv_n_pg = (float)(1.0 / ((double)n_global_b * (double)(T - 1)));
+    p.inv_n_all = (float)(1.0 / ((double)n_global_b * (double)T));
+    p.flags = flags;
+
+    // columns per CTA: ~160-192 samples, a multiple of 4 so time-major rows stay 16-byte aligned
+    int target = env_int("B200RL_K1_SAMPLES", 192);
+    int C = (int)(target / T);
+    if (C >= 4) C &= ~3;
+    if (C < 1) C = 1;
+    if (C > B) C = (int)B;
+    while (C > 1 && C * T > max_threads) C = (C > 4) ? ((C - 1) & ~3) : C - 1;
+    const int a_tile = A <= 8 ? 8 : (A <= 16 ? 16 : 32);
+    auto smem_for = [&](int c) { return (size_t)c * T * (2 * A + 3) * 4 + 5 * 32 * 4 + 16; };
+    while (C > 1 && smem_for(C) > 200 * 1024) C = (C > 4) ? ((C / 2) & ~3) : C - 1;
+    B200RL_REQUIRE(smem_for(C) <= 227 * 1024, -3, "impala_loss: T*A too large for one CTA tile");
+    B200RL_REQUIRE((B + C - 1) / C <= kMaxPartialCtas, -3, "impala_loss: B too large for the partials workspace");
+    p.C = C;
+    const int threads = ((C * (int)T + 31) / 32) * 32;
+    cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+    switch (a_tile) {
+        case 8: return launch_impala<8>(p, threads, smem_for(C), s);
+        case 16: return launch_impala<16>(p, threads, smem_for(C), s);
+        default: return launch_impala<32>(p, threads, smem_for(C), s);
+    }
+}

@@ -1,0 +1,133 @@
+// K4/K5: device-resident replay -- uniform index sampling, row gather, ring append.
+// Replaces rlmeta ReplayBuffer(CircularBuffer, UniformSampler) as used at reference
+// agents/impala/builder.py:30-36 and agents/impala/learning.py:121-123,142 (sample ->
+// RPC -> 5*B host-to-device copies -> torch.stack): storage lives in HBM, indices are
+// drawn on the device and rows are copied HBM -> HBM straight into the [B,...] batch.
+//
+// Sampler stream (specified in oracle/replay_ref.py, pinned by the Random123 KATs):
+// Philox4x32-10, ctr = (lo32(g), hi32(g), stream_id, 0), key = (lo32(seed), hi32(seed)),
+// g = draw_offset + i;  index = mulhi64(out0 | out1 << 32, size).  Integer only: bit exact.
+#include "common.cuh"
+
+namespace b200rl {
+
+__device__ __forceinline__ void philox4x32_10(uint32_t &c0, uint32_t &c1, uint32_t &c2, uint32_t &c3,
+                                              uint32_t k0, uint32_t k1) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+        const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+        const uint32_t n0 = hi1 ^ c1 ^ k0, n2 = hi0 ^ c3 ^ k1;
+        c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+}
+
+__global__ void __launch_bounds__(256) sample_uniform_kernel(uint64_t seed, uint32_t stream_id,
+                                                             uint64_t draw_offset, long long n,
+                                                             uint64_t size, long long *__restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint64_t g = draw_offset + (uint64_t)i;
+    uint32_t c0 = (uint32_t)g, c1 = (uint32_t)(g >> 32), c2 = stream_id, c3 = 0u;
+    philox4x32_10(c0, c1, c2, c3, (uint32_t)seed, (uint32_t)(seed >> 32));
+    const uint64_t x = (uint64_t)c0 | ((uint64_t)c1 << 32);
+    out[i] = (long long)__umul64hi(x, size);
+}
+
+// Row copy with a per-row source or destination index.  The work is flattened over
+// (row, vector) so that consecutive threads move consecutive 16-byte vectors of one row
+// (fully coalesced on both sides) whatever the row size; each thread keeps kUnroll
+// independent vectors in flight.
+//   GATHER : dst[i]                    = src[clamp(idx[i])]
+//   RING   : dst[(count + i) % cap]    = src[i]
+enum { COPY_GATHER = 0, COPY_RING = 1 };
+constexpr int kCopyThreads = 256, kCopyUnroll = 4;
+
+template <typename V, int MODE>
+__global__ void __launch_bounds__(kCopyThreads) row_copy_kernel(
+    const V *__restrict__ src, V *__restrict__ dst, const long long *__restrict__ idx, long long n,
+    long long vec_per_row, long long nrows, long long count) {
+    const long long total = n * vec_per_row;
+    const long long base = ((long long)blockIdx.x * kCopyUnroll) * kCopyThreads + threadIdx.x;
+    V regs[kCopyUnroll];
+    long long d_off[kCopyUnroll];
+#pragma unroll
+    for (int u = 0; u < kCopyUnroll; ++u) {
+        const long long k = base + (long long)u * kCopyThreads;
+        d_off[u] = -1;
+        if (k < total) {
+            const long long row = k / vec_per_row, col = k - row * vec_per_row;
+            long long s_row, d_row;
+            if (MODE == COPY_GATHER) {
+                long long j = __ldg(idx + row);
+                j = j < 0 ? 0 : (j >= nrows ? nrows - 1 : j);
+                s_row = j;
+                d_row = row;
+            } else {
+                s_row = row;
+                d_row = (count + row) % nrows;
+            }
+            regs[u] = __ldcs(src + s_row * vec_per_row + col);  // streaming: touched once
+            d_off[u] = d_row * vec_per_row + col;
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < kCopyUnroll; ++u)
+        if (d_off[u] >= 0) __stcs(dst + d_off[u], regs[u]);
+}
+
+template <int MODE>
+static int32_t launch_row_copy(const void *src, void *dst, const long long *idx, long long n,
+                               long long row_bytes, long long nrows, long long count, cudaStream_t stream) {
+    if (n == 0 || row_bytes == 0) return 0;
+    const uintptr_t align = reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst) | (uintptr_t)row_bytes;
+    const int vec = (align % 16 == 0) ? 16 : (align % 8 == 0) ? 8 : (align % 4 == 0) ? 4 : 1;
+    const long long vpr = row_bytes / vec, total = n * vpr;
+    const long long per_cta = (long long)kCopyThreads * kCopyUnroll;
+    const long long grid = (total + per_cta - 1) / per_cta;
+    B200RL_REQUIRE(grid < (1ll << 31), -3, "row copy: too many elements");
+    switch (vec) {
+        case 16: row_copy_kernel<int4, MODE><<<(unsigned)grid, kCopyThreads, 0, stream>>>((const int4 *)src, (int4 *)dst, idx, n, vpr, nrows, count); break;
+        case 8: row_copy_kernel<int2, MODE><<<(unsigned)grid, kCopyThreads, 0, stream>>>((const int2 *)src, (int2 *)dst, idx, n, vpr, nrows, count); break;
+        case 4: row_copy_kernel<int, MODE><<<(unsigned)grid, kCopyThreads, 0, stream>>>((const int *)src, (int *)dst, idx, n, vpr, nrows, count); break;
+        default: row_copy_kernel<char, MODE><<<(unsigned)grid, kCopyThreads, 0, stream>>>((const char *)src, (char *)dst, idx, n, vpr, nrows, count); break;
+    }
+    return check_launch("row_copy_kernel");
+}
+
+}  // namespace b200rl
+
+extern "C" int32_t b200rl_sample_uniform(uint64_t seed, uint32_t stream_id, uint64_t draw_offset, int64_t n,
+                                         int64_t size, int64_t *out_idx, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(n >= 0, -2, "sample_uniform: n < 0");
+    if (n == 0) return 0;
+    B200RL_REQUIRE(out_idx, -1, "sample_uniform: null output");
+    B200RL_REQUIRE(size >= 1, -2, "sample_uniform: cannot sample from an empty buffer (size=%lld)", (long long)size);
+    sample_uniform_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        seed, stream_id, draw_offset, n, (uint64_t)size, reinterpret_cast<long long *>(out_idx));
+    return check_launch("sample_uniform_kernel");
+}
+
+extern "C" int32_t b200rl_gather_rows(const void *src, int64_t row_bytes, const int64_t *idx, int64_t n,
+                                      int64_t nrows, void *dst, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(n >= 0 && row_bytes >= 0, -2, "gather_rows: negative size");
+    if (n == 0 || row_bytes == 0) return 0;
+    B200RL_REQUIRE(src && idx && dst, -1, "gather_rows: null pointer argument");
+    B200RL_REQUIRE(nrows >= 1, -2, "gather_rows: empty source");
+    return launch_row_copy<COPY_GATHER>(src, dst, reinterpret_cast<const long long *>(idx), n, row_bytes, nrows, 0,
+                                        (cudaStream_t)stream);
+}
+
+extern "C" int32_t b200rl_ring_append(void *storage, int64_t row_bytes, int64_t capacity, int64_t count,
+                                      const void *rows, int64_t n, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(n >= 0 && row_bytes >= 0 && count >= 0, -2, "ring_append: negative size");
+    if (n == 0 || row_bytes == 0) return 0;
+    B200RL_REQUIRE(storage && rows, -1, "ring_append: null pointer argument");
+    B200RL_REQUIRE(capacity >= 1 && n <= capacity, -2, "ring_append: n=%lld exceeds capacity=%lld", (long long)n, (long long)capacity);
+    return launch_row_copy<COPY_RING>(rows, storage, nullptr, n, row_bytes, capacity, count, (cudaStream_t)stream);
+}

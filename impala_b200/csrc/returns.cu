@@ -1,0 +1,160 @@
+// K2: lambda-returns and GAE time scans, batched over columns.
+// Replaces rlego.lambda_returns (reference agents/ppo/learning.py:65-69) and
+// rlego.truncated_generalized_advantage_estimation (losses.py:11).
+//
+// Both are the backward affine recurrence  y_t = b_t + a_t * y_{t+1}:
+//   lambda-returns: a_t = g_t*l,  b_t = r_t + g_t*(1-l)*v_t[t],       y_T = v_t[T-1]
+//   GAE:            a_t = l*g_t,  b_t = r_t + g_t*V[t+1] - V[t],      y_T = 0
+//
+// Time-major kernel (HBM-bound, 16 B/sample): a CTA owns 32 adjacent columns (lane =
+// column, every load a full 128-byte line) and splits T into chunks of L steps, one
+// warp per chunk.  Pass 1: each warp loads its L x 3 values into registers (3L
+// independent loads in flight per thread) and composes its chunk's affine map.  The
+// maps meet in shared memory, each warp folds the later chunks into its carry-in
+// (<= 31 FMAs), then pass 2 re-walks the chunk from registers in the reference's
+// operation order and stores.  No second trip to HBM.
+#include "common.cuh"
+
+namespace b200rl {
+
+enum { MODE_LAMBDA_RETURNS = 0, MODE_GAE = 1 };
+
+struct ScanParams {
+    const float *r, *disc, *v;
+    float *out;
+    int B, T;
+    long long sb, st, vsb, vst;  // element strides of r/disc/out and of v
+    float lambda_;
+};
+
+template <int MODE>
+__device__ __forceinline__ float scan_step(float r, float d, float v0, float v1, float lam, float y) {
+    if (MODE == MODE_LAMBDA_RETURNS) return r + d * ((1.f - lam) * v0 + lam * y);  // v0 = v_t[t]
+    return (r + d * v1 - v0) + lam * d * y;                                         // v0 = V[t], v1 = V[t+1]
+}
+
+template <int MODE, int L>
+__global__ void __launch_bounds__(512) scan_time_major_kernel(const ScanParams p) {
+    __shared__ float sA[16][33], sB[16][33];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, K = blockDim.x >> 5;
+    const int b = blockIdx.x * 32 + lane;
+    const bool col_ok = b < p.B;
+    const int t0 = w * L;
+    float r[L], d[L], v[L + 1];
+#pragma unroll
+    for (int k = 0; k < L; ++k) {
+        const int t = t0 + k;
+        const bool ok = col_ok && t < p.T;
+        const long long i = (long long)t * p.st + (long long)b * p.sb;
+        r[k] = ok ? __ldg(p.r + i) : 0.f;
+        d[k] = ok ? __ldg(p.disc + i) : 0.f;
+        const bool vok = col_ok && t < p.T + (MODE == MODE_GAE ? 1 : 0);  // GAE: V has T+1 steps
+        v[k] = vok ? __ldg(p.v + (long long)t * p.vst + (long long)b * p.vsb) : 0.f;
+    }
+    if (MODE == MODE_GAE) {
+        const int t = t0 + L;  // V[t+1] of the chunk's last step
+        v[L] = (col_ok && t <= p.T) ? __ldg(p.v + (long long)t * p.vst + (long long)b * p.vsb) : 0.f;
+    } else {
+        v[L] = 0.f;
+    }
+    // pass 1: compose the chunk's map y_in -> y_out = Bc + Ac * y_in (steps beyond T are identity)
+    float Ac = 1.f, Bc = 0.f;
+#pragma unroll
+    for (int k = L - 1; k >= 0; --k) {
+        if (t0 + k < p.T) {
+            const float a = p.lambda_ * d[k];
+            const float bb = scan_step<MODE>(r[k], d[k], v[k], v[k + 1], p.lambda_, 0.f);
+            Bc = bb + a * Bc;
+            Ac = a * Ac;
+        }
+    }
+    sA[w][lane] = Ac;
+    sB[w][lane] = Bc;
+    __syncthreads();
+    // carry-in: fold the later chunks, starting from the bootstrap
+    float y = 0.f;
+    if (MODE == MODE_LAMBDA_RETURNS && col_ok)
+        y = __ldg(p.v + (long long)(p.T - 1) * p.vst + (long long)b * p.vsb);
+    for (int k = K - 1; k > w; --k) y = sB[k][lane] + sA[k][lane] * y;
+    // pass 2: the chunk itself, reference operation order, from registers
+#pragma unroll
+    for (int k = L - 1; k >= 0; --k) {
+        const int t = t0 + k;
+        if (col_ok && t < p.T) {
+            y = scan_step<MODE>(r[k], d[k], v[k], v[k + 1], p.lambda_, y);
+            p.out[(long long)t * p.st + (long long)b * p.sb] = y;
+        }
+    }
+}
+
+// Generic layout (batch-major): one thread per column, sequential, reference order.
+template <int MODE>
+__global__ void __launch_bounds__(128) scan_generic_kernel(const ScanParams p) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= p.B) return;
+    const float *vb = p.v + (long long)b * p.vsb;
+    float y = (MODE == MODE_LAMBDA_RETURNS) ? vb[(long long)(p.T - 1) * p.vst] : 0.f;
+    float v1 = (MODE == MODE_GAE) ? vb[(long long)p.T * p.vst] : 0.f;
+    for (int t = p.T - 1; t >= 0; --t) {
+        const long long i = (long long)b * p.sb + (long long)t * p.st;
+        const float v0 = vb[(long long)t * p.vst];
+        y = scan_step<MODE>(p.r[i], p.disc[i], v0, v1, p.lambda_, y);
+        p.out[i] = y;
+        v1 = v0;
+    }
+}
+
+template <int MODE>
+static int32_t launch_scan(const ScanParams &p, cudaStream_t stream) {
+    const bool time_major = (p.sb == 1 && p.vsb == 1);
+    if (time_major && p.T <= 16 * 32) {  // <= 16 chunks (warps) of L steps
+        const int grid = (p.B + 31) / 32;
+        if (p.T <= 16 * 8) {
+            const int K = (p.T + 7) / 8;
+            scan_time_major_kernel<MODE, 8><<<grid, K * 32, 0, stream>>>(p);
+        } else if (p.T <= 16 * 16) {
+            const int K = (p.T + 15) / 16;
+            scan_time_major_kernel<MODE, 16><<<grid, K * 32, 0, stream>>>(p);
+        } else {
+            const int K = (p.T + 31) / 32;
+            scan_time_major_kernel<MODE, 32><<<grid, K * 32, 0, stream>>>(p);
+        }
+        return check_launch("scan_time_major_kernel");
+    }
+    scan_generic_kernel<MODE><<<(p.B + 127) / 128, 128, 0, stream>>>(p);
+    return check_launch("scan_generic_kernel");
+}
+
+static int32_t check_scan_layout(const char *who, int64_t B, int64_t T, int64_t sb, int64_t st) {
+    B200RL_REQUIRE(B >= 1 && T >= 1, -2, "%s: need B>=1 and T>=1 (got B=%lld T=%lld)", who, (long long)B, (long long)T);
+    B200RL_REQUIRE(B * (T + 1) < (1ll << 31), -3, "%s: B*T too large", who);
+    B200RL_REQUIRE((st == 1 && sb >= T) || (sb == 1 && st >= B), -4,
+                   "%s: strides (%lld,%lld) are neither batch-major (>=T,1) nor time-major (1,>=B)", who,
+                   (long long)sb, (long long)st);
+    return 0;
+}
+
+}  // namespace b200rl
+
+extern "C" int32_t b200rl_lambda_returns(const float *r_t, const float *discount_t, const float *v_t,
+                                         int64_t B, int64_t T, int64_t stride_b, int64_t stride_t,
+                                         float lambda_, float *out, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(r_t && discount_t && v_t && out, -1, "lambda_returns: null pointer argument");
+    if (int32_t rc = check_scan_layout("lambda_returns", B, T, stride_b, stride_t)) return rc;
+    ScanParams p{r_t, discount_t, v_t, out, (int)B, (int)T, stride_b, stride_t, stride_b, stride_t, lambda_};
+    return launch_scan<MODE_LAMBDA_RETURNS>(p, (cudaStream_t)stream);
+}
+
+extern "C" int32_t b200rl_gae(const float *r_t, const float *discount_t, const float *values, int64_t B,
+                              int64_t T, int64_t stride_b, int64_t stride_t, int64_t vstride_b,
+                              int64_t vstride_t, float lambda_, float *out, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(r_t && discount_t && values && out, -1, "gae: null pointer argument");
+    if (int32_t rc = check_scan_layout("gae", B, T, stride_b, stride_t)) return rc;
+    B200RL_REQUIRE((vstride_t == 1 && vstride_b >= T + 1) || (vstride_b == 1 && vstride_t >= B), -4,
+                   "gae: value strides (%lld,%lld) unsupported", (long long)vstride_b, (long long)vstride_t);
+    B200RL_REQUIRE((stride_b == 1) == (vstride_b == 1), -4, "gae: values and rewards must share the major order");
+    ScanParams p{r_t, discount_t, values, out, (int)B, (int)T, stride_b, stride_t, vstride_b, vstride_t, lambda_};
+    return launch_scan<MODE_GAE>(p, (cudaStream_t)stream);
+}

@@ -1,0 +1,88 @@
+"""Drop-in for the reference's ``losses.py`` on the learner path (fused CUDA forward+backward).
+
+``ppo_loss(model, batch, entropy_cost, clip_coeff)`` (reference ``losses.py:131``) and
+``impala_loss(batch, model, lambda_, entropy_cost)`` (``losses.py:92``; note the argument order)
+keep their signatures, return ``(loss, metrics)`` with the same metric keys, and ``loss.backward()``
+reaches the model parameters.  The loss value, every metric and d loss/d(model outputs) come out
+of ONE kernel launch; autograd only carries the precomputed gradients into the model.
+"""
+import torch
+
+from . import ops
+
+METRIC_SLOTS = (("train/loss", ops.S_LOSS), ("train/entropy", ops.S_ENTROPY), ("train/td", ops.S_TD),
+                ("train/pg", ops.S_PG), ("train/kl", ops.S_KL), ("train/ratio", ops.S_RATIO))
+
+
+class _FusedLoss(torch.autograd.Function):
+    """loss = f(outputs...) whose gradients were already produced by the fused kernel."""
+
+    @staticmethod
+    def forward(ctx, loss, n_out, *args):
+        outs, grads = args[:n_out], args[n_out:]
+        ctx.save_for_backward(*grads)
+        ctx.shapes = [o.shape for o in outs]
+        return loss.clone()
+
+    @staticmethod
+    def backward(ctx, g):
+        grads = ctx.saved_tensors
+        return (None, None) + tuple((d * g).reshape(s) for d, s in zip(grads, ctx.shapes)) + (None,) * len(grads)
+
+
+def _attach(loss, outputs, grads):
+    if not any(o.requires_grad for o in outputs):
+        return loss
+    return _FusedLoss.apply(loss, len(outputs), *outputs, *grads)
+
+
+def impala_loss_from_outputs(logits, values, a, r, discount_t, pi_ref, entropy_coeff=0.01, lambda_=1.0,
+                             clip_rho_threshold=1.0, clip_pg_rho_threshold=1.0, detach_adv=False,
+                             detach_rho=False, time_major=False, n_global_b=None):
+    """The loss block of ``ImpalaLearner._train_step`` (reference ``agents/impala/learning.py:146-170``)
+    on model outputs ``logits [B,T,A]``, ``values [B,T]``.  Returns ``(loss, metrics)``."""
+    flags = (ops.DETACH_ADV if detach_adv else 0) | (ops.DETACH_RHO if detach_rho else 0)
+    scalars, dlogits, dvalues = ops.impala_loss_fwdbwd(
+        logits, values, a, r, discount_t, pi_ref, entropy_coeff, lambda_, clip_rho_threshold,
+        clip_pg_rho_threshold, flags, n_global_b, time_major)
+    loss = _attach(scalars[ops.S_LOSS], (logits, values), (dlogits, dvalues))
+    metrics = {k: scalars[i] for k, i in METRIC_SLOTS}
+    return loss, metrics
+
+
+def ppo_loss_from_outputs(logits, v, a, v_target, pi_ref, entropy_cost=0.01, clip_coeff=0.1, n_global=None):
+    """Reference ``losses.py:134-155`` on model outputs ``logits [N,A]``, ``v [N,1]``."""
+    scalars, dlogits, dv = ops.ppo_loss_fwdbwd(logits, v, a, v_target, pi_ref, entropy_cost, clip_coeff, n_global)
+    loss = _attach(scalars[ops.S_LOSS], (logits, v), (dlogits, dv))
+    metrics = {k: scalars[i] for k, i in METRIC_SLOTS}
+    metrics["train/target"] = scalars[ops.S_TARGET]
+    metrics["train/kl"] = scalars[ops.S_KL].clamp_min(0.)  # losses.py:144
+    order = ("train/loss", "train/entropy", "train/td", "train/pg", "train/target", "train/kl", "train/ratio")
+    return loss, {k: metrics[k] for k in order}
+
+
+def ppo_loss(model, batch, entropy_cost=0.01, clip_coeff=0.1):
+    """Drop-in for reference ``losses.ppo_loss`` (``losses.py:131-155``)."""
+    s, a, v_target, pi_ref = batch
+    pi_tm1, v_tm1 = model(s)
+    return ppo_loss_from_outputs(pi_tm1, v_tm1, a, v_target, pi_ref, entropy_cost, clip_coeff)
+
+
+def impala_loss(batch, model, lambda_=1., entropy_cost=0.01, as_written=False):
+    """Drop-in for reference ``losses.impala_loss`` (``losses.py:92-128``).
+
+    The committed reference function is work in progress and has no caller (raw logits instead of
+    log-probs, ratio = 1, same-step bootstrap, entropy disabled).  By default this computes the loss
+    the IMPALA learner actually trains with (``agents/impala/learning.py:146-159``) on a ``[B,T,...]``
+    batch; ``as_written=True`` is not offered on the GPU path (see ``oracle/losses_ref.py`` for the
+    literal restatement)."""
+    if as_written:
+        raise RuntimeError("impala_loss(as_written=True) has no CUDA path; the literal WIP semantics "
+                           "live in oracle/losses_ref.py only")
+    s, a, r, discount_t, pi_ref = batch
+    B, T = s.shape[0], s.shape[1]
+    pi, values = model(s.flatten(0, 1))
+    pi = pi.reshape(B, T, -1)
+    values = values.reshape(B, T)
+    sq = lambda x: x.squeeze(-1) if x.dim() == 3 else x  # noqa: E731
+    return impala_loss_from_outputs(pi, values, sq(a), sq(r), sq(discount_t), pi_ref, entropy_cost, lambda_)

@@ -1,0 +1,221 @@
+"""Thin functional wrappers: torch tensors in, C-ABI launches on the current stream."""
+import torch
+
+from . import _cabi
+
+DETACH_ADV, DETACH_RHO, ORDER_RLAX = 1, 2, 4
+S_LOSS, S_ENTROPY, S_TD, S_PG, S_KL, S_RATIO, S_TARGET = range(7)
+
+_workspaces = {}
+
+
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _require_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("impala_b200 ops need CUDA tensors (no CPU fallback); got %s" % t.device)
+
+
+def workspace(device):
+    """Zero-initialised scratch for the fused losses, one per (device, stream)."""
+    key = (device.index if device.index is not None else torch.cuda.current_device(), _stream())
+    ws = _workspaces.get(key)
+    if ws is None:
+        n = _cabi.load().b200rl_loss_workspace_bytes()
+        ws = torch.zeros(n, dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def _f32c(x):
+    return x if (x.dtype == torch.float32 and x.is_contiguous()) else x.float().contiguous()
+
+
+def impala_loss_fwdbwd(logits, values, actions, rewards, discounts, pi_ref, entropy_coeff=0.01,
+                       lambda_=1.0, clip_rho=1.0, clip_pg_rho=1.0, flags=0, n_global_b=None,
+                       time_major=False, out=None):
+    """K1.  Batch-major ``[B,T,A]`` / ``[B,T]`` tensors (or ``[T,B,A]`` / ``[T,B]`` with
+    ``time_major=True``).  Returns ``(scalars[8], dlogits, dvalues)``; nothing is synchronised."""
+    _require_cuda(logits, values, actions, rewards, discounts, pi_ref)
+    logits, pi_ref = _f32c(logits.detach()), _f32c(pi_ref.detach())
+    values, rewards, discounts = _f32c(values.detach()), _f32c(rewards), _f32c(discounts)
+    actions = actions if (actions.dtype == torch.int64 and actions.is_contiguous()) else actions.long().contiguous()
+    if time_major:
+        T, B, A = logits.shape
+        sb, st = 1, B
+    else:
+        B, T, A = logits.shape
+        sb, st = T, 1
+    for name, x in (("values", values), ("actions", actions), ("rewards", rewards), ("discounts", discounts)):
+        if tuple(x.shape) != tuple(logits.shape[:2]):
+            raise RuntimeError("impala_loss: %s has shape %s, expected %s" % (name, tuple(x.shape), tuple(logits.shape[:2])))
+    if pi_ref.shape != logits.shape:
+        raise RuntimeError("impala_loss: pi_ref shape %s != logits shape %s" % (tuple(pi_ref.shape), tuple(logits.shape)))
+    if out is None:
+        scalars = torch.empty(8, dtype=torch.float32, device=logits.device)
+        dlogits = torch.empty_like(logits)
+        dvalues = torch.empty_like(values)
+    else:
+        scalars, dlogits, dvalues = out
+    ws = workspace(logits.device)
+    _cabi.call("b200rl_vtrace_impala_loss_fwdbwd",
+               logits.data_ptr(), pi_ref.data_ptr(), actions.data_ptr(), rewards.data_ptr(),
+               discounts.data_ptr(), values.data_ptr(), B, T, A, sb, st,
+               B if n_global_b is None else n_global_b,
+               lambda_, clip_rho, clip_pg_rho, entropy_coeff, flags,
+               dlogits.data_ptr(), dvalues.data_ptr(), scalars.data_ptr(), ws.data_ptr(), _stream())
+    return scalars, dlogits, dvalues
+
+
+def _major(x):
+    """(B, T, stride_b, stride_t, time_major) of a 2-D [B,T] view in either major order."""
+    B, T = x.shape
+    sb, st = x.stride()
+    if st == 1 and sb >= T:
+        return B, T, sb, st, False
+    if sb == 1 and st >= B:
+        return B, T, sb, st, True
+    if T == 1 or B == 1:
+        return B, T, T, 1, False
+    return None
+
+
+def _same_view(xs):
+    """Make 2-D float32 inputs share one (stride_b, stride_t); copy only when needed."""
+    xs = [x if x.dtype == torch.float32 else x.float() for x in xs]
+    m = [_major(x) for x in xs]
+    if any(v is None for v in m) or len({v[2:] for v in m}) != 1:
+        xs = [x.contiguous() for x in xs]
+        m = [_major(x) for x in xs]
+    return xs, m[0]
+
+
+def _compact_like(B, T, time_major, device):
+    """Compact [B,T] float32 output in the requested major order."""
+    if time_major:
+        return torch.empty((T, B), dtype=torch.float32, device=device).t()
+    return torch.empty((B, T), dtype=torch.float32, device=device)
+
+
+def vtrace_fwd(v_tm1, v_t, r_t, discount_t, rho_tm1, lambda_=1.0, clip_rho=1.0, clip_pg_rho=1.0):
+    """Stand-alone V-trace on ``[B,Tm]`` views -> compact ``(adv, err, q)`` and the layout used."""
+    _require_cuda(v_tm1, v_t, r_t, discount_t, rho_tm1)
+    xs, (B, Tm, sb, st, tm) = _same_view([v_tm1.detach(), v_t.detach(), r_t.detach(),
+                                          discount_t.detach(), rho_tm1.detach()])
+    adv, err, q = (_compact_like(B, Tm, tm, xs[0].device) for _ in range(3))
+    _cabi.call("b200rl_vtrace", *[x.data_ptr() for x in xs], B, Tm, sb, st, lambda_, clip_rho, clip_pg_rho,
+               adv.data_ptr(), err.data_ptr(), q.data_ptr(), _stream())
+    return adv, err, q, xs, (B, Tm, sb, st, tm)
+
+
+def vtrace_bwd(saved, layout, q, g_adv, g_err, g_q, lambda_, clip_pg_rho):
+    v_tm1, _, _, disc, rho = saved
+    B, Tm, sb, st, tm = layout
+
+    def compact(g):
+        if g is None:
+            return None
+        g = g.float()
+        want = (1, B) if tm else (Tm, 1)
+        if g.stride() != want and not (B == 1 or Tm == 1):
+            g = g.t().contiguous().t() if tm else g.contiguous()
+        return g
+
+    g_adv, g_err, g_q = compact(g_adv), compact(g_err), compact(g_q)
+    d_vtm1, d_vt, d_rho = (_compact_like(B, Tm, tm, q.device) for _ in range(3))
+    _cabi.call("b200rl_vtrace_bwd", v_tm1.data_ptr(), disc.data_ptr(), rho.data_ptr(), q.data_ptr(),
+               _cabi.ptr(g_adv), _cabi.ptr(g_err), _cabi.ptr(g_q), B, Tm, sb, st, lambda_, clip_pg_rho,
+               d_vtm1.data_ptr(), d_vt.data_ptr(), d_rho.data_ptr(), _stream())
+    return d_vtm1, d_vt, d_rho
+
+
+def lambda_returns(r_t, discount_t, v_t, lambda_=1.0):
+    """K2.  ``[B,T]`` views (batch- or time-major) -> returns in the same major order."""
+    _require_cuda(r_t, discount_t, v_t)
+    xs, (B, T, sb, st, tm) = _same_view([r_t.detach(), discount_t.detach(), v_t.detach()])
+    if (tm and st != B) or (not tm and sb != T):  # output must be addressable with the input strides
+        xs = [x.t().contiguous().t() if tm else x.contiguous() for x in xs]
+        B, T, sb, st, tm = _major(xs[0])
+    out = _compact_like(B, T, tm, xs[0].device)
+    _cabi.call("b200rl_lambda_returns", *[x.data_ptr() for x in xs], B, T, sb, st, lambda_,
+               out.data_ptr(), _stream())
+    return out
+
+
+def gae(r_t, discount_t, values, lambda_=1.0):
+    """``r_t, discount_t [B,T]``, ``values [B,T+1]`` -> advantages ``[B,T]``."""
+    _require_cuda(r_t, discount_t, values)
+    (r, d), (B, T, sb, st, tm) = _same_view([r_t.detach(), discount_t.detach()])
+    v = values.detach().float()
+    mv = _major(v)
+    if mv is None or mv[4] != tm or (tm and st != B) or (not tm and sb != T):
+        r, d, v = ((x.t().contiguous().t() if tm else x.contiguous()) for x in (r, d, v))
+        B, T, sb, st, tm = _major(r)
+        mv = _major(v)
+    out = _compact_like(B, T, tm, r.device)
+    _cabi.call("b200rl_gae", r.data_ptr(), d.data_ptr(), v.data_ptr(), B, T, sb, st, mv[2], mv[3],
+               lambda_, out.data_ptr(), _stream())
+    return out
+
+
+def ppo_loss_fwdbwd(logits, v, actions, v_target, pi_ref, entropy_cost=0.01, clip_coeff=0.1,
+                    n_global=None, out=None):
+    """K3.  ``logits, pi_ref [N,A]``; ``v, actions, v_target [N]``.  Returns ``(scalars[8], dlogits, dv)``."""
+    _require_cuda(logits, v, actions, v_target, pi_ref)
+    logits, pi_ref = _f32c(logits.detach()), _f32c(pi_ref.detach())
+    v, v_target = _f32c(v.detach().reshape(-1)), _f32c(v_target.reshape(-1))
+    actions = actions.reshape(-1)
+    actions = actions if (actions.dtype == torch.int64 and actions.is_contiguous()) else actions.long().contiguous()
+    N, A = logits.shape
+    if pi_ref.shape != logits.shape or v.numel() != N or v_target.numel() != N or actions.numel() != N:
+        raise RuntimeError("ppo_loss: inconsistent shapes")
+    if out is None:
+        scalars = torch.empty(8, dtype=torch.float32, device=logits.device)
+        dlogits = torch.empty_like(logits)
+        dv = torch.empty_like(v)
+    else:
+        scalars, dlogits, dv = out
+    ws = workspace(logits.device)
+    _cabi.call("b200rl_ppo_loss_fwdbwd", logits.data_ptr(), pi_ref.data_ptr(), actions.data_ptr(),
+               v_target.data_ptr(), v.data_ptr(), N, A, N if n_global is None else n_global,
+               clip_coeff, entropy_cost, 0, dlogits.data_ptr(), dv.data_ptr(), scalars.data_ptr(),
+               ws.data_ptr(), _stream())
+    return scalars, dlogits, dv
+
+
+def sample_uniform(seed, stream_id, draw_offset, n, size, device, out=None):
+    """K4.  ``n`` int64 indices in ``[0,size)`` on ``device``."""
+    if out is None:
+        out = torch.empty(n, dtype=torch.int64, device=device)
+    _require_cuda(out)
+    _cabi.call("b200rl_sample_uniform", seed, stream_id, draw_offset, n, size, out.data_ptr(), _stream())
+    return out
+
+
+def gather_rows(src, idx, out=None):
+    """K5.  ``out[i] = src[idx[i]]`` for a contiguous ``src [nrows, ...]``."""
+    _require_cuda(src, idx)
+    if not src.is_contiguous():
+        raise RuntimeError("gather_rows: storage must be contiguous")
+    idx = idx if (idx.dtype == torch.int64 and idx.is_contiguous()) else idx.long().contiguous()
+    n, nrows = idx.numel(), src.shape[0]
+    row_bytes = src[0].numel() * src.element_size() if nrows else 0
+    if out is None:
+        out = torch.empty((n,) + tuple(src.shape[1:]), dtype=src.dtype, device=src.device)
+    _cabi.call("b200rl_gather_rows", src.data_ptr(), row_bytes, idx.data_ptr(), n, nrows, out.data_ptr(), _stream())
+    return out
+
+
+def ring_append(storage, count, rows):
+    """Rows ``j`` go to slot ``(count + j) % capacity`` of the contiguous ``storage [capacity, ...]``."""
+    _require_cuda(storage, rows)
+    rows = rows.contiguous()
+    if rows.dtype != storage.dtype or tuple(rows.shape[1:]) != tuple(storage.shape[1:]):
+        raise RuntimeError("ring_append: rows %s/%s do not match storage %s/%s"
+                           % (tuple(rows.shape[1:]), rows.dtype, tuple(storage.shape[1:]), storage.dtype))
+    row_bytes = storage[0].numel() * storage.element_size()
+    _cabi.call("b200rl_ring_append", storage.data_ptr(), row_bytes, storage.shape[0], count,
+               rows.data_ptr(), rows.shape[0], _stream())

@@ -1,0 +1,140 @@
+/* b200rl -- C ABI of the B200-native learner hot path (drop-in for d3sm0/impala).
+ *
+ * The reference has no FFI: its "operator API" is plain Python calls (SURVEY.md
+ * sec 8b).  Every entry point below therefore names the reference Python site it
+ * replaces; impala_b200/_cabi.py is the ctypes binding and INTEGRATION.md shows
+ * the stub a reference maintainer would add.
+ *
+ * Conventions
+ *  - all pointers are DEVICE pointers unless named host_*; the caller (PyTorch)
+ *    owns and allocates every buffer, outputs and workspace included; the
+ *    library never allocates, frees or retains a pointer;
+ *  - launches go to `stream` (a cudaStream_t passed as void*), are asynchronous
+ *    and CUDA-graph capturable;
+ *  - return 0 = ok, <0 = argument error (checked on the host before launch),
+ *    >0 = cudaError_t of the launch; text via b200rl_last_error() (thread local);
+ *  - layouts: a [B,T] field is addressed as b*stride_b + t*stride_t (elements);
+ *    supported: batch-major (stride_b=T, stride_t=1, the reference's layout,
+ *    agents/impala/learning.py:142-145) and time-major (stride_b=1, stride_t=B).
+ *    Per-action tensors ([.., A]) use the same sample index times A.
+ *  - there is no CPU fallback and no other backend: sm_100a only.
+ */
+#ifndef B200RL_H
+#define B200RL_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200RL_VERSION 100
+
+/* flags */
+#define B200RL_DETACH_ADV 1u  /* treat pg advantages as constants (textbook IMPALA); reference: not detached, learning.py:155 */
+#define B200RL_DETACH_RHO 2u  /* treat rho as a constant inside V-trace; reference: not detached, learning.py:148 */
+#define B200RL_ORDER_RLAX 4u  /* b200rl_vtrace output order (errors, pg_adv, q) instead of call-site (pg_adv, errors, q) */
+
+/* slots of the float[8] `scalars` output of the fused losses */
+#define B200RL_S_LOSS 0
+#define B200RL_S_ENTROPY 1
+#define B200RL_S_TD 2
+#define B200RL_S_PG 3
+#define B200RL_S_KL 4
+#define B200RL_S_RATIO 5
+#define B200RL_S_TARGET 6 /* PPO only: mean(v_target), losses.py:152 */
+
+int32_t b200rl_version(void);
+const char *b200rl_last_error(void);
+
+/* Bytes of zero-initialised device workspace the fused losses need (zero it ONCE;
+ * every launch leaves it zeroed again). */
+int64_t b200rl_loss_workspace_bytes(void);
+
+/* K1 -- replaces ImpalaLearner._train_step's loss + backward w.r.t. model outputs
+ * (reference agents/impala/learning.py:146-160,167-168) and, inside it,
+ * batched_vtrace = vmap(rlego.vtrace_td_error_and_advantage) (learning.py:15-26).
+ * Inputs [B,T,A] / [B,T] (see layouts); T >= 2.  n_global_b = number of columns of
+ * the GLOBAL batch (== B unless sharded along B across ranks): means are taken
+ * over n_global_b*(T-1) resp. n_global_b*T, so per-rank scalars and gradients sum
+ * to the single-GPU result.  Outputs: dlogits [B,T,A], dvalues [B,T] =
+ * d loss / d logits, d loss / d values; scalars[8] (B200RL_S_*). */
+int32_t b200rl_vtrace_impala_loss_fwdbwd(
+    const float *logits, const float *pi_ref, const int64_t *actions, const float *rewards,
+    const float *discounts, const float *values,
+    int64_t B, int64_t T, int64_t A, int64_t stride_b, int64_t stride_t, int64_t n_global_b,
+    float lambda_, float clip_rho, float clip_pg_rho, float entropy_coeff, uint32_t flags,
+    float *dlogits, float *dvalues, float *scalars, void *workspace, void *stream);
+
+/* Stand-alone drop-in for batched_vtrace(v_tm1, v_t, r_t, discount_t, rho_tm1)
+ * (reference agents/impala/learning.py:18,150-153).  The five inputs are [B,Tm]
+ * views sharing (stride_b, stride_t): batch-major (stride_t=1, stride_b>=Tm -- e.g.
+ * the reference's values[:, :-1] slices of a [B,T] tensor) or time-major
+ * (stride_b=1, stride_t>=B).  Outputs adv, err, q are COMPACT [B,Tm] in the same
+ * major order (order fixed here; the Python wrapper applies B200RL_ORDER_RLAX). */
+int32_t b200rl_vtrace(
+    const float *v_tm1, const float *v_t, const float *r_t, const float *discount_t,
+    const float *rho_tm1, int64_t B, int64_t Tm, int64_t stride_b, int64_t stride_t,
+    float lambda_, float clip_rho, float clip_pg_rho,
+    float *adv, float *err, float *q, void *stream);
+
+/* Backward of b200rl_vtrace under stop_target_gradients=True: given upstream
+ * g_adv, g_err, g_q (compact, any may be NULL = zero) and the saved compact q,
+ * produce compact d v_tm1, d v_t, d rho.  v_tm1, discount_t, rho_tm1 use the
+ * forward's input strides. */
+int32_t b200rl_vtrace_bwd(
+    const float *v_tm1, const float *discount_t, const float *rho_tm1, const float *q,
+    const float *g_adv, const float *g_err, const float *g_q,
+    int64_t B, int64_t Tm, int64_t stride_b, int64_t stride_t,
+    float lambda_, float clip_pg_rho,
+    float *d_v_tm1, float *d_v_t, float *d_rho, void *stream);
+
+/* K2 -- replaces rlego.lambda_returns(r_t, discount_t, v_t, lambda_) per rollout
+ * (reference agents/ppo/learning.py:65-69), batched over B columns.
+ * G_t = r_t + g_t((1-l) v_t[t] + l G_{t+1}), bootstrap v_t[T-1]. */
+int32_t b200rl_lambda_returns(
+    const float *r_t, const float *discount_t, const float *v_t,
+    int64_t B, int64_t T, int64_t stride_b, int64_t stride_t, float lambda_,
+    float *out, void *stream);
+
+/* GAE (rlego.truncated_generalized_advantage_estimation, reference losses.py:11).
+ * values holds T+1 steps per column with its own strides. */
+int32_t b200rl_gae(
+    const float *r_t, const float *discount_t, const float *values,
+    int64_t B, int64_t T, int64_t stride_b, int64_t stride_t,
+    int64_t vstride_b, int64_t vstride_t, float lambda_, float *out, void *stream);
+
+/* K3 -- replaces losses.ppo_loss after model(s) + backward w.r.t. model outputs
+ * (reference losses.py:134-155, caller agents/ppo/learning.py:132-134).
+ * Flat minibatch: logits, pi_ref [N,A]; actions, v_target, v [N].
+ * scalars[B200RL_S_KL] is the UNclamped mean KL (clamp_min(0) belongs after the
+ * cross-rank sum). */
+int32_t b200rl_ppo_loss_fwdbwd(
+    const float *logits, const float *pi_ref, const int64_t *actions, const float *v_target,
+    const float *v, int64_t N, int64_t A, int64_t n_global,
+    float clip_coeff, float entropy_cost, uint32_t flags,
+    float *dlogits, float *dv, float *scalars, void *workspace, void *stream);
+
+/* K4 -- replaces rlmeta UniformSampler (reference agents/impala/builder.py:31-32,
+ * consumer learning.py:121).  Philox4x32-10, see oracle/replay_ref.py for the
+ * stream definition; out_idx[n] int64 in [0,size). */
+int32_t b200rl_sample_uniform(
+    uint64_t seed, uint32_t stream_id, uint64_t draw_offset, int64_t n, int64_t size,
+    int64_t *out_idx, void *stream);
+
+/* K5 -- replaces CircularBuffer.__getitem__ + collate_nested(torch.stack) + .to(device)
+ * (reference agents/impala/learning.py:121-123,142): dst[i] = src[idx[i]], rows of
+ * row_bytes bytes.  Out-of-range indices are clamped into [0,nrows) (never faults). */
+int32_t b200rl_gather_rows(
+    const void *src, int64_t row_bytes, const int64_t *idx, int64_t n, int64_t nrows,
+    void *dst, void *stream);
+
+/* Replaces ReplayBuffer.append/extend storage writes (reference
+ * agents/impala/learning.py:75, agents/ppo/learning.py:63): rows j=0..n-1 go to
+ * slot (count + j) % capacity.  n <= capacity. */
+int32_t b200rl_ring_append(
+    void *storage, int64_t row_bytes, int64_t capacity, int64_t count,
+    const void *rows, int64_t n, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,141 @@
+"""GPU: K1 (fused V-trace + IMPALA loss fwd/bwd) through the C ABI vs the CPU oracle."""
+import os
+
+import pytest
+import torch
+
+from conftest import GOLDEN
+from gpu_util import assert_close, npz_tensors, oracle_impala, to_cuda
+from impala_b200 import losses, ops, synth
+
+pytestmark = pytest.mark.gpu
+KEYS = ("train/loss", "train/entropy", "train/td", "train/pg", "train/kl", "train/ratio")
+SLOTS = (ops.S_LOSS, ops.S_ENTROPY, ops.S_TD, ops.S_PG, ops.S_KL, ops.S_RATIO)
+
+
+def run_k1(d, time_major=False, **kw):
+    g = to_cuda(d)
+    if time_major:
+        g = {k: v.transpose(0, 1).contiguous() for k, v in g.items()}
+    sc, dl, dv = ops.impala_loss_fwdbwd(g["logits"], g["values"], g["a"], g["r"], g["discount"], g["pi_ref"],
+                                        time_major=time_major, **kw)
+    torch.cuda.synchronize()
+    if time_major:
+        dl, dv = dl.transpose(0, 1), dv.transpose(0, 1)
+    return sc.cpu(), dl.cpu(), dv.cpu()
+
+
+def check(d, okw=None, kkw=None, time_major=False):
+    okw, kkw = okw or {}, kkw or {}
+    loss, m, dl_ref, dv_ref = oracle_impala(d, **okw)
+    sc, dl, dv = run_k1(d, time_major, **kkw)
+    for k, s in zip(KEYS, SLOTS):
+        assert_close(sc[s], m[k], k, rtol=2e-5, atol=2e-6)
+    assert_close(dl, dl_ref, "dlogits", rel_to_max=2e-5)
+    assert_close(dv, dv_ref, "dvalues", rel_to_max=2e-5)
+
+
+def test_golden_c1_matches_committed_vectors():
+    d, z = npz_tensors(os.path.join(GOLDEN, "impala_c1.npz"), ("logits", "values", "a", "r", "discount", "pi_ref"))
+    sc, dl, dv = run_k1(d)
+    for i, s in enumerate(SLOTS):
+        assert sc[s].item() == pytest.approx(z["metrics"][i], rel=2e-5, abs=2e-6)
+    assert_close(dl, torch.from_numpy(z["dlogits"]), "dlogits", rel_to_max=2e-5)
+    assert_close(dv, torch.from_numpy(z["dvalues"]), "dvalues", rel_to_max=2e-5)
+
+
+def test_golden_small_lambda_clip_variants():
+    d, z = npz_tensors(os.path.join(GOLDEN, "impala_small_lambda.npz"), ("logits", "values", "a", "r", "discount", "pi_ref"))
+    sc, dl, dv = run_k1(d, lambda_=.9, clip_rho=.8, clip_pg_rho=1.2, entropy_coeff=.05)
+    assert sc[ops.S_LOSS].item() == pytest.approx(z["metrics"][0], rel=2e-5, abs=2e-6)
+    assert_close(dl, torch.from_numpy(z["dlogits"]), "dlogits", rel_to_max=2e-5)
+    assert_close(dv, torch.from_numpy(z["dvalues"]), "dvalues", rel_to_max=2e-5)
+
+
+@pytest.mark.parametrize("B,T,A", [(32, 20, 15), (1, 2, 1), (5, 7, 6), (3, 20, 15), (33, 20, 15), (64, 5, 8),
+                                   (17, 33, 16), (9, 12, 17), (4, 6, 32), (2, 300, 4), (130, 20, 18)])
+@pytest.mark.parametrize("time_major", [False, True])
+def test_parity_shapes(B, T, A, time_major):
+    """Aligned tiles take the TMA bulk path, ragged ones (odd B, A, tail tiles) the cooperative path."""
+    check(synth.impala_rollout(B, T, A, seed=B * 1000 + T * 10 + A), time_major=time_major)
+
+
+@pytest.mark.parametrize("okw,kkw", [
+    (dict(lambda_=.9), dict(lambda_=.9)),
+    (dict(lambda_=0.), dict(lambda_=0.)),
+    (dict(clip_rho_threshold=.7, clip_pg_rho_threshold=1.5), dict(clip_rho=.7, clip_pg_rho=1.5)),
+    (dict(entropy_coeff=.2), dict(entropy_coeff=.2)),
+    (dict(detach_adv=True), dict(flags=ops.DETACH_ADV)),
+    (dict(detach_rho=True, lambda_=.8), dict(flags=ops.DETACH_RHO, lambda_=.8)),
+    (dict(detach_adv=True, detach_rho=True), dict(flags=ops.DETACH_ADV | ops.DETACH_RHO)),
+])
+def test_parity_semantic_switches(okw, kkw):
+    check(synth.impala_rollout(24, 20, 15, seed=7), okw, kkw)
+    check(synth.impala_rollout(7, 11, 6, seed=8), okw, kkw, time_major=True)
+
+
+def test_all_done_and_no_done_and_extreme_rho():
+    d = synth.impala_rollout(16, 20, 15, seed=3)
+    d["discount"] = torch.zeros_like(d["discount"])                  # every step terminal
+    check(d)
+    d["discount"] = torch.full_like(d["discount"], .99)              # no terminal
+    check(d)
+    d["pi_ref"] = d["logits"] + 3. * torch.randn_like(d["logits"])   # rho from ~0 to >> 1
+    check(d)
+    d["pi_ref"] = d["logits"].clone()                                # rho == 1 exactly: the clip tie
+    check(d)
+
+
+def test_full_size_c2_properties():
+    """BASELINE config 2 (T=20, B=4096, A=15): determinism, column-permutation equivariance, and
+    sharded-sum == global (what the multi-GPU path relies on); plus oracle parity at full size."""
+    B, T, A = 4096, 20, 15
+    d = synth.impala_rollout(B, T, A, seed=2000)
+    sc, dl, dv = run_k1(d)
+    sc2, dl2, dv2 = run_k1(d)
+    assert torch.equal(sc, sc2) and torch.equal(dl, dl2) and torch.equal(dv, dv2)
+    perm = torch.randperm(B, generator=torch.Generator().manual_seed(0))
+    scp, dlp, dvp = run_k1({k: v[perm] for k, v in d.items()})
+    assert torch.equal(dlp, dl[perm]) and torch.equal(dvp, dv[perm])
+    assert_close(scp[:6], sc[:6], "permuted scalars", rtol=1e-5, atol=1e-6)
+    parts = [run_k1({k: v[i * 1024:(i + 1) * 1024] for k, v in d.items()}, n_global_b=B) for i in range(4)]
+    assert torch.equal(torch.cat([p[1] for p in parts]), dl) and torch.equal(torch.cat([p[2] for p in parts]), dv)
+    assert_close(sum(p[0] for p in parts)[:6], sc[:6], "sharded scalars", rtol=1e-5, atol=1e-6)
+    check(d)
+
+
+def test_autograd_dropin_and_reference_signature(cuda):
+    d = to_cuda(synth.impala_rollout(8, 20, 15, seed=5))
+    lin = torch.nn.Linear(4, 16).to(cuda)
+    feats = torch.randn(8 * 20, 4, device=cuda)
+
+    def model(s):
+        out = lin(feats)
+        return out[:, :15], out[:, 15:]
+
+    batch = (torch.zeros(8, 20, 1, device=cuda), d["a"].unsqueeze(-1), d["r"].unsqueeze(-1),
+             d["discount"].unsqueeze(-1), d["pi_ref"])
+    loss, m = losses.impala_loss(batch, model, lambda_=1., entropy_cost=.01)
+    assert list(m) == list(KEYS)
+    (2 * loss).backward()
+    g_fused = lin.weight.grad.clone()
+    # same thing through the oracle on the CPU
+    lin_c = torch.nn.Linear(4, 16)
+    lin_c.load_state_dict({k: v.cpu() for k, v in lin.state_dict().items()})
+    out = lin_c(feats.cpu())
+    from oracle import losses_ref
+    c = {k: v.cpu() for k, v in d.items()}
+    l2, _ = losses_ref.impala_train_loss(out[:, :15].reshape(8, 20, 15), out[:, 15:].reshape(8, 20), c["a"], c["r"],
+                                         c["discount"], c["pi_ref"])
+    (2 * l2).backward()
+    assert_close(loss, l2, "loss", rtol=2e-5, atol=2e-6)
+    assert_close(g_fused, lin_c.weight.grad, "dW", rtol=1e-4, atol=1e-6, rel_to_max=1e-4)
+
+
+def test_errors_raise_runtime_error(cuda):
+    d = to_cuda(synth.impala_rollout(4, 20, 40, seed=1))
+    with pytest.raises(RuntimeError, match="32 actions"):
+        ops.impala_loss_fwdbwd(d["logits"], d["values"], d["a"], d["r"], d["discount"], d["pi_ref"])
+    d = to_cuda(synth.impala_rollout(4, 20, 15, seed=1))
+    with pytest.raises(RuntimeError, match="shape"):
+        ops.impala_loss_fwdbwd(d["logits"], d["values"][:, :-1], d["a"], d["r"], d["discount"], d["pi_ref"])

@@ -1,0 +1,163 @@
+"""GPU: K3 (fused PPO loss fwd/bwd), K2 (lambda-returns / GAE scans) and the stand-alone V-trace drop-in
+through the C ABI vs the CPU oracle."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from gpu_util import assert_close, to_cuda
+from impala_b200 import losses, ops, synth, vtrace
+from impala_b200.agents import ppo as ppo_agent
+from oracle import losses_ref, rlego_ref
+
+pytestmark = pytest.mark.gpu
+PPO_KEYS = ("train/loss", "train/entropy", "train/td", "train/pg", "train/target", "train/kl", "train/ratio")
+
+
+def oracle_ppo(d, ec=.01, clip=.1):
+    lg, v = d["logits"].clone().requires_grad_(True), d["v"].clone().requires_grad_(True)
+    loss, m = losses_ref.ppo_loss_from_outputs(lg, v, d["a"], d["v_target"], d["pi_ref"], ec, clip)
+    loss.backward()
+    return m, lg.grad, v.grad
+
+
+@pytest.mark.parametrize("N,A", [(1000, 15), (1, 1), (255, 6), (256, 15), (257, 15), (4099, 8), (513, 17), (300, 32)])
+@pytest.mark.parametrize("ec,clip", [(.01, .1), (0., .3)])
+def test_ppo_parity(N, A, ec, clip):
+    d = synth.ppo_minibatch(N, A, seed=N + A)
+    m, dl_ref, dv_ref = oracle_ppo(d, ec, clip)
+    g = to_cuda(d)
+    lg, v = g["logits"].requires_grad_(True), g["v"].requires_grad_(True)
+    loss, mm = losses.ppo_loss_from_outputs(lg, v, g["a"], g["v_target"], g["pi_ref"], ec, clip)
+    assert list(mm) == list(PPO_KEYS)
+    loss.backward()
+    for k in PPO_KEYS:
+        assert_close(mm[k], m[k], k, rtol=2e-5, atol=2e-6)
+    assert_close(lg.grad, dl_ref, "dlogits", rel_to_max=2e-5)
+    assert_close(v.grad, dv_ref, "dv", rel_to_max=2e-5)
+
+
+def test_ppo_golden_and_clip_branches():
+    z = np.load(os.path.join(GOLDEN, "ppo_small.npz"))
+    d = {k: torch.from_numpy(z[k]) for k in ("logits", "v", "a", "v_target", "pi_ref")}
+    g = to_cuda(d)
+    sc, dl, dv = ops.ppo_loss_fwdbwd(g["logits"], g["v"], g["a"], g["v_target"], g["pi_ref"], .01, .1)
+    assert sc[ops.S_LOSS].item() == pytest.approx(z["metrics"][0], rel=2e-5, abs=2e-6)
+    assert_close(dl, torch.from_numpy(z["dlogits"]), "dlogits", rel_to_max=2e-5)
+    assert_close(dv, torch.from_numpy(z["dv"]).reshape(-1), "dv", rel_to_max=2e-5)
+    # ratio far outside the clip range on both sides, and exactly 1 (the tie inside the range)
+    d2 = synth.ppo_minibatch(2048, 15, seed=9, ref_noise=2.0)
+    d2["pi_ref"][:512] = d2["logits"][:512]
+    m, dl_ref, dv_ref = oracle_ppo(d2)
+    g = to_cuda(d2)
+    sc, dl, dv = ops.ppo_loss_fwdbwd(g["logits"], g["v"], g["a"], g["v_target"], g["pi_ref"], .01, .1)
+    assert_close(sc[ops.S_PG], m["train/pg"], "pg", rtol=2e-5, atol=2e-6)
+    assert_close(dl, dl_ref, "dlogits", rel_to_max=2e-5)
+
+
+def test_ppo_full_size_properties():
+    """One 8-GPU shard of BASELINE config 3 (T=256, B=8192/8 -> N=262,144): determinism, shard-sum == global."""
+    N = 262_144
+    d = to_cuda(synth.ppo_minibatch(N, 15, seed=3000))
+    a = ops.ppo_loss_fwdbwd(d["logits"], d["v"], d["a"], d["v_target"], d["pi_ref"])
+    b = ops.ppo_loss_fwdbwd(d["logits"], d["v"], d["a"], d["v_target"], d["pi_ref"])
+    assert all(torch.equal(x, y) for x, y in zip(a, b))
+    h = N // 2
+    p0 = ops.ppo_loss_fwdbwd(d["logits"][:h], d["v"][:h], d["a"][:h], d["v_target"][:h], d["pi_ref"][:h], n_global=N)
+    p1 = ops.ppo_loss_fwdbwd(d["logits"][h:], d["v"][h:], d["a"][h:], d["v_target"][h:], d["pi_ref"][h:], n_global=N)
+    assert torch.equal(torch.cat([p0[1], p1[1]]), a[1]) and torch.equal(torch.cat([p0[2], p1[2]]), a[2])
+    assert_close((p0[0] + p1[0])[:7], a[0][:7], "scalars", rtol=1e-5, atol=1e-6)
+    m, dl_ref, _ = oracle_ppo({k: v.cpu() for k, v in d.items()})
+    assert_close(a[0][ops.S_LOSS], m["train/loss"], "loss", rtol=2e-5, atol=2e-6)
+    assert_close(a[1], dl_ref, "dlogits", rel_to_max=2e-5)
+
+
+def test_ppo_reference_signature(cuda):
+    d = to_cuda(synth.ppo_minibatch(64, 15, seed=1))
+    w = torch.nn.Parameter(torch.zeros(16, device=cuda))
+    model = lambda s: (d["logits"] + w[:15], d["v"] + w[15:])  # noqa: E731
+    loss, m = losses.ppo_loss(model, (None, d["a"], d["v_target"], d["pi_ref"]), entropy_cost=.01, clip_coeff=.1)
+    loss.backward()
+    c = {k: v.cpu() for k, v in d.items()}
+    wc = torch.zeros(16, requires_grad=True)
+    l2, _ = losses_ref.ppo_loss(lambda s: (c["logits"] + wc[:15], c["v"] + wc[15:]),
+                                (None, c["a"], c["v_target"], c["pi_ref"]))
+    l2.backward()
+    assert_close(w.grad, wc.grad, "dW", rtol=1e-4, atol=1e-6, rel_to_max=1e-4)
+
+
+# ------------------------------------------------------------------ K2 scans
+def oracle_returns(r, d, v, lam):
+    return rlego_ref.batched(rlego_ref.lambda_returns, lambda_=lam)(r, d, v)
+
+
+def oracle_gae(r, d, vals, lam):
+    return rlego_ref.batched(lambda a, b, c: rlego_ref.truncated_generalized_advantage_estimation(a, b, lam, c))(r, d, vals)
+
+
+@pytest.mark.parametrize("B,T", [(64, 256), (1, 1), (33, 7), (5, 128), (31, 129), (40, 300), (3, 600), (100, 20)])
+@pytest.mark.parametrize("lam", [.95, 1.0, 0.0])
+@pytest.mark.parametrize("time_major", [False, True])
+def test_scans_parity(B, T, lam, time_major):
+    x = synth.returns_rollout(B, T + 1, seed=B * 7 + T)
+    r, d, v = x["r"][:, :T], x["discount"][:, :T], x["v"]
+    want_lr, want_gae = oracle_returns(r, d, v[:, 1:], lam), oracle_gae(r, d, v, lam)
+    if time_major:
+        rg, dg, vg = (t.t().contiguous().cuda() for t in (r, d, v))          # [T,B] storage
+        got_lr = vtrace.lambda_returns(rg, dg, vg[1:], lam, time_major=True).t()
+        got_gae = vtrace.truncated_generalized_advantage_estimation(rg, dg, lam, vg, time_major=True).t()
+    else:
+        rg, dg, vg = r.cuda(), d.cuda(), v.cuda()
+        got_lr = vtrace.lambda_returns(rg, dg, vg[:, 1:], lam)
+        got_gae = vtrace.truncated_generalized_advantage_estimation(rg, dg, lam, vg)
+    assert_close(got_lr, want_lr, "lambda_returns", rtol=1e-5, atol=2e-6, rel_to_max=1e-5)
+    assert_close(got_gae, want_gae, "gae", rtol=1e-5, atol=2e-6, rel_to_max=1e-5)
+
+
+def test_scans_golden_identity_and_ppo_targets():
+    z = np.load(os.path.join(GOLDEN, "returns_small.npz"))
+    r, d, v = (torch.from_numpy(z[k]).cuda() for k in ("r", "discount", "v"))
+    lr = vtrace.lambda_returns(r[:, :-1], d[:, :-1], v[:, 1:], .95)
+    gae = vtrace.truncated_generalized_advantage_estimation(r[:, :-1], d[:, :-1], .95, v)
+    assert_close(lr, torch.from_numpy(z["lambda_returns"]), "golden lambda_returns", rel_to_max=1e-5)
+    assert_close(gae, torch.from_numpy(z["gae"]), "golden gae", rel_to_max=1e-5)
+    assert_close(gae + v[:, :-1], lr, "GAE + V == lambda-return", rtol=1e-5, atol=5e-6)
+    # one 8-GPU shard of config 3, time-major: T=256, B=1024
+    x = synth.returns_rollout(1024, 256, seed=3000)
+    done = x["done"].t().contiguous().cuda()
+    rt, vt = x["r"].t().contiguous().cuda(), x["v"].t().contiguous().cuda()
+    tgt = ppo_agent.make_targets(rt, done, vt, .99, .95, time_major=True)
+    assert tgt.shape == (255, 1024)
+    want = torch.stack([losses_ref.ppo_make_targets(x["r"][b], x["done"][b], x["v"][b], .99, .95) for b in range(0, 1024, 64)])
+    assert_close(tgt.t()[::64], want, "ppo targets", rtol=1e-5, atol=2e-6)
+    one = vtrace.lambda_returns(x["r"][0, :-1].cuda(), x["discount"][0, :-1].cuda(), x["v"][0, 1:].cuda(), .95)
+    assert_close(one, want[0], "1-D rollout", rtol=1e-5, atol=2e-6)
+
+
+# ------------------------------------------------------------------ stand-alone V-trace drop-in
+@pytest.mark.parametrize("B,T,lam", [(32, 20, 1.), (7, 5, .9), (1, 2, 0.), (300, 33, .5)])
+def test_batched_vtrace_dropin_forward_backward(B, T, lam):
+    d = synth.impala_rollout(B, T, 4, seed=B + T)
+    rho = torch.exp(.7 * torch.randn(B, T, generator=torch.Generator().manual_seed(1)))
+    kw = dict(lambda_=lam, clip_rho_threshold=.9, clip_pg_rho_threshold=1.1)
+    vc, rc = d["values"].clone().requires_grad_(True), rho.clone().requires_grad_(True)
+    want = rlego_ref.batched(rlego_ref.vtrace_td_error_and_advantage, **kw)(
+        vc[:, :-1], vc[:, 1:], d["r"][:, :-1], d["discount"][:, :-1], rc[:, :-1])
+    wts = [torch.randn(B, T - 1, generator=torch.Generator().manual_seed(i)) for i in range(3)]
+    sum((o * w).sum() for o, w in zip(want, wts)).backward()
+    g = to_cuda(d)
+    vg, rg = g["values"].clone().requires_grad_(True), rho.cuda().requires_grad_(True)
+    got = vtrace.batched_vtrace(vg[:, :-1], vg[:, 1:], g["r"][:, :-1], g["discount"][:, :-1], rg[:, :-1], **kw)
+    sum((o * w.cuda()).sum() for o, w in zip(got, wts)).backward()
+    for name, a, b in zip(("adv", "err", "q"), got, want):
+        assert_close(a, b, name, rtol=1e-5, atol=2e-6, rel_to_max=1e-5)
+    assert_close(vg.grad, vc.grad, "d values", rtol=1e-5, atol=2e-6, rel_to_max=1e-5)
+    assert_close(rg.grad, rc.grad, "d rho", rtol=1e-5, atol=2e-6, rel_to_max=1e-5)
+    e2, a2, _ = vtrace.batched_vtrace(vg[:, :-1], vg[:, 1:], g["r"][:, :-1], g["discount"][:, :-1], rg[:, :-1],
+                                      output_order="rlax", **kw)
+    assert torch.equal(e2, got[1]) and torch.equal(a2, got[0])
+    # per-sequence form, the function the reference vmaps
+    one = vtrace.vtrace_td_error_and_advantage(vg[0, :-1], vg[0, 1:], g["r"][0, :-1], g["discount"][0, :-1], rg[0, :-1], **kw)
+    assert_close(one[0], want[0][0], "per-sequence adv", rtol=1e-5, atol=2e-6)

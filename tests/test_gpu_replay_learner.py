@@ -1,0 +1,178 @@
+"""GPU: K4/K5 (device replay: Philox sampling, row gather, ring append) bit-exact vs the oracle, and the
+ImpalaLearner / PPOLearner drop-ins vs a reference-shaped torch step on the CPU."""
+import copy
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from gpu_util import assert_close
+from impala_b200 import models, ops, replay, synth
+from impala_b200.agents import ImpalaLearner, PPOLearner
+from oracle import c_oracle, losses_ref, replay_ref
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("seed,stream,off,n,size", [(123, 0, 0, 4096, 1_000_000), (2**40 + 7, 5, 2**33, 1000, 3),
+                                                    (0, 0, 0, 17, 1), (9, 1, 10**12, 100_000, 2**40), (1, 0, 0, 0, 5)])
+def test_sampler_bit_exact(cuda, seed, stream, off, n, size):
+    got = ops.sample_uniform(seed, stream, off, n, size, cuda).cpu().numpy()
+    assert np.array_equal(got, replay_ref.sample_uniform(seed, stream, off, n, size))
+    assert np.array_equal(got, c_oracle.sample_uniform(seed, stream, off, n, size))
+
+
+def test_sampler_golden_and_stream_continuity(cuda):
+    z = np.load(os.path.join(GOLDEN, "replay_indices.npz"))
+    s = replay.UniformSampler()
+    s.reset(123)
+    a = torch.cat([s.sample(1000, 1_000_000, cuda), s.sample(3096, 1_000_000, cuda)]).cpu().numpy()
+    assert np.array_equal(a, z["idx_seed123_1M"])
+    s3 = replay.UniformSampler(stream_id=3)
+    s3.reset(123)
+    s3.draws = 10_000_000_000
+    assert np.array_equal(s3.sample(257, 1000, cuda).cpu().numpy(), z["idx_stream3_big_offset"])
+    with pytest.raises(RuntimeError):
+        s.sample(4, 0, cuda)
+
+
+@pytest.mark.parametrize("shape,dtype", [((3, 64, 64), torch.uint8), ((1,), torch.int64), ((1,), torch.float32),
+                                         ((15,), torch.float32), ((7,), torch.uint8), ((3,), torch.int16),
+                                         ((20, 3, 64, 64), torch.uint8)])
+def test_gather_bit_exact(cuda, shape, dtype):
+    nrows, n = 257, 600
+    g = torch.Generator().manual_seed(1)
+    src = (torch.randint(0, 255, (nrows,) + shape, generator=g).to(dtype) if dtype != torch.float32
+           else torch.randn((nrows,) + shape, generator=g))
+    idx = torch.from_numpy(replay_ref.sample_uniform(7, 0, 0, n, nrows))
+    got = ops.gather_rows(src.cuda(), idx.cuda()).cpu()
+    assert torch.equal(got, src.index_select(0, idx))
+    assert np.array_equal(got.numpy(), c_oracle.gather_rows(src.numpy(), idx.numpy()))
+    assert ops.gather_rows(src.cuda(), idx[:0].cuda()).shape == (0,) + shape       # empty batch
+    # unaligned base pointer (odd element offset) -> narrower vector path, same bytes
+    flat = src.cuda().reshape(nrows, -1)
+    if flat.shape[1] > 1:
+        sub = flat[:, 1:].contiguous()
+        assert torch.equal(ops.gather_rows(sub, idx.cuda()).cpu(), sub.cpu().index_select(0, idx))
+
+
+def test_ring_buffer_matches_oracle(cuda):
+    cap = 37
+    rb = replay.ReplayBuffer(replay.CircularBuffer(cap, device=cuda), replay.UniformSampler())
+    rb.sampler.reset(11)
+    ob = replay_ref.ReplayBuffer(replay_ref.CircularBuffer(cap), replay_ref.UniformSampler())
+    ob.sampler.reset(11)
+    g = torch.Generator().manual_seed(0)
+    with pytest.raises(RuntimeError):
+        rb.warm_up(5)
+    for step, n in enumerate([5, 1, 20, 30, 37, 3, 50]):          # wraps, exact fill, n > capacity
+        obs = torch.randint(0, 255, (n, 3, 8, 8), generator=g, dtype=torch.uint8)
+        act = torch.randint(0, 15, (n, 1), generator=g)
+        rew = torch.randn(n, 1, generator=g)
+        if step % 2 == 0:
+            rb.extend((obs, act, rew))
+        else:
+            rb.extend([[obs[i], act[i], rew[i]] for i in range(n)])
+        if n <= cap:
+            ob.extend([obs.numpy(), act.numpy(), rew.numpy()])
+        else:                                                       # oracle: only the survivors matter
+            ob.storage.count += n - cap
+            ob.extend([obs[n - cap:].numpy(), act[n - cap:].numpy(), rew[n - cap:].numpy()])
+        assert rb.size == ob.storage.size and rb.info() == (cap, ob.storage.size)
+        for f, of in zip(rb.storage.fields, ob.storage.fields):
+            occupied = min(rb.storage.count, cap)
+            assert np.array_equal(f.cpu().numpy()[:occupied] if rb.storage.count < cap else f.cpu().numpy(),
+                                  of[:occupied] if rb.storage.count < cap else of)
+        keys, batch, probs = rb.sample(64)
+        okeys, obatch, oprobs = ob.sample(64)
+        assert np.array_equal(keys.cpu().numpy(), okeys)
+        assert all(np.array_equal(b.cpu().numpy(), o) for b, o in zip(batch, obatch))
+        assert np.allclose(probs.cpu().numpy(), oprobs)
+    rb.append([torch.zeros(3, 8, 8, dtype=torch.uint8), torch.zeros(1, dtype=torch.int64), torch.zeros(1)])
+    rb.warm_up(10)
+
+
+def test_config4_shape_gather_roundtrip(cuda):
+    """BASELINE config 4 row shape (64x64x3 u8), capacity scaled to 20k rows: rows are tagged with their
+    index, so a gather is checked by content at any size."""
+    cap, n = 20_000, 4096
+    store = torch.empty(cap, 3, 64, 64, dtype=torch.uint8, device=cuda)
+    tag = torch.arange(cap, device=cuda)
+    store.view(cap, -1)[:, 0] = (tag % 251).to(torch.uint8)
+    store.view(cap, -1)[:, 1] = ((tag // 251) % 251).to(torch.uint8)
+    store.view(cap, -1)[:, -1] = (tag % 13).to(torch.uint8)
+    idx = ops.sample_uniform(123, 0, 0, n, cap, cuda)
+    out = ops.gather_rows(store, idx).view(n, -1)
+    assert torch.equal(out[:, 0].long() + 251 * out[:, 1].long(), idx % (251 * 251))
+    assert torch.equal(out[:, -1].long(), idx % 13)
+    assert torch.equal(out, store.view(cap, -1).index_select(0, idx))
+
+
+def _fill_impala_replay(rb, n_items, T, A, seed):
+    g = torch.Generator().manual_seed(seed)
+    for _ in range(n_items):
+        rb.append([torch.randint(0, 255, (T, 3, 64, 64), generator=g, dtype=torch.uint8),
+                   torch.randint(0, A, (T, 1), generator=g), torch.randn(T, 1, generator=g),
+                   (torch.rand(T, 1, generator=g) > .05).float() * .99, torch.randn(T, A, generator=g)])
+
+
+@pytest.mark.parametrize("body", ["nature", "impala"])
+def test_impala_learner_step_matches_reference_shaped_step(cuda, body):
+    torch.manual_seed(0)
+    T, A, Bsz = 20, 15, 8
+    model = models.ActorCritic((3, 64, 64), A, body=body).to(cuda)
+    ref_model = copy.deepcopy(model).cpu()
+    rb = replay.ReplayBuffer(replay.CircularBuffer(32, device=cuda), replay.UniformSampler())
+    rb.sampler.reset(123)
+    _fill_impala_replay(rb, 12, T, A, seed=5)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4, eps=1e-5)
+    learner = ImpalaLearner(model, rb, opt, batch_size=Bsz, learning_starts=10)
+    learner.prepare()
+    draws0 = rb.sampler.draws
+    metrics = learner.train_step()
+    assert {"train/loss", "train/entropy", "train/td", "train/pg", "train/kl", "train/ratio", "train/grad_norm",
+            "debug/total_time"} <= set(metrics)
+    # the same step as the reference writes it (agents/impala/learning.py:140-177), on the CPU
+    slots = replay_ref.sample_uniform(123, 0, draws0, Bsz, rb.size)
+    s, a, r, d, pi_ref = [f.cpu()[slots] for f in rb.storage.fields]
+    a, r, d = a.squeeze(-1), r.squeeze(-1), d.squeeze(-1)
+    ropt = torch.optim.Adam(ref_model.parameters(), lr=1e-4, eps=1e-5)
+    ropt.zero_grad(set_to_none=True)
+    pi, values = ref_model(s.flatten(0, 1))
+    loss, m = losses_ref.impala_train_loss(pi.reshape(Bsz, T, -1), values.reshape(Bsz, T), a, r, d, pi_ref)
+    loss.backward()
+    gn = torch.nn.utils.clip_grad_norm_(ref_model.parameters(), .5)
+    ropt.step()
+    for k in ("train/loss", "train/entropy", "train/td", "train/pg", "train/kl", "train/ratio"):
+        assert_close(metrics[k], m[k], k, rtol=2e-3, atol=2e-4)       # cuDNN (TF32-free fp32) vs CPU convs
+    assert_close(metrics["train/grad_norm"], gn, "grad_norm", rtol=2e-2, atol=1e-3)
+    for (n1, p), (_, q) in zip(model.named_parameters(), ref_model.named_parameters()):
+        assert_close(p, q, n1, rtol=1e-3, atol=3e-5)                  # one Adam step of lr 1e-4
+
+
+def test_ppo_learner_step(cuda):
+    torch.manual_seed(0)
+    A, N = 15, 256
+    model = models.ActorCritic((3, 64, 64), A).to(cuda)
+    ref_model = copy.deepcopy(model).cpu()
+    rb = replay.ReplayBuffer(replay.CircularBuffer(1000, collate_fn=torch.cat, device=cuda), replay.UniformSampler())
+    rb.sampler.reset(7)
+    g = torch.Generator().manual_seed(1)
+    rb.extend((torch.randint(0, 255, (600, 3, 64, 64), generator=g, dtype=torch.uint8),
+               torch.randint(0, A, (600,), generator=g), torch.randn(600, generator=g), torch.randn(600, A, generator=g)))
+    learner = PPOLearner(model, rb, torch.optim.Adam(model.parameters(), lr=1e-4, eps=1e-5), batch_size=N)
+    learner.prepare()
+    metrics = learner.train_step()
+    slots = replay_ref.sample_uniform(7, 0, 0, N, 600)
+    s, a, vt, pi_ref = [f.cpu()[slots] for f in rb.storage.fields]
+    ropt = torch.optim.Adam(ref_model.parameters(), lr=1e-4, eps=1e-5)
+    loss, m = losses_ref.ppo_loss(ref_model, (s, a, vt, pi_ref), entropy_cost=.01)
+    loss.backward()
+    torch.nn.utils.clip_grad_norm_(ref_model.parameters(), .5)
+    ropt.step()
+    for k in ("train/loss", "train/entropy", "train/td", "train/pg", "train/target", "train/kl", "train/ratio"):
+        assert_close(metrics[k], m[k], k, rtol=2e-3, atol=2e-4)
+    for (n1, p), (_, q) in zip(model.named_parameters(), ref_model.named_parameters()):
+        assert_close(p, q, n1, rtol=1e-3, atol=3e-5)
