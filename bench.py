@@ -1,0 +1,465 @@
+#!/usr/bin/env python
+"""Benchmark of the learner hot path (BASELINE.json metric: learner samples/sec (TxB) for the fused
+V-trace + loss forward/backward; HBM fraction).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload impala_loss|ppo|replay] [--impl reference]
+
+One "step" = one pass of the hot path over one batch of synthetic rollouts.  Default workload =
+BASELINE config 2 (T=20, B=4096, A=15 per GPU; batches are rank-local, weak scaling, no data-path
+collective).  Prints ONE JSON line on rank 0.  See DESIGN.md "Measurement".
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+FALLBACK_HBM_GBS = 6650.0   # /opt/skills/guides/B200_PROFILING.md fallback
+L2_BYTES = 126 * 1024 * 1024
+
+WORKLOADS = {
+    # name: (metric, unit, algorithmic bytes per unit -- SURVEY.md sec 8d / DESIGN.md)
+    "impala_loss": ("learner samples/sec (TxB), fused V-trace + IMPALA loss fwd+bwd", "samples/s", 204),
+    "ppo": ("learner samples/sec (TxB), GAE/lambda-return scan + fused PPO loss fwd+bwd", "samples/s", 216),
+    "replay": ("replay transitions/sec, uniform sample + gather of 64x64x3 u8 rows", "transitions/s", 24584),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=None)
+    ap.add_argument("--warmup", type=int, default=None)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="impala_loss", choices=sorted(WORKLOADS))
+    ap.add_argument("--B", type=int, default=None, help="columns per GPU (default: the BASELINE config)")
+    ap.add_argument("--T", type=int, default=None)
+    ap.add_argument("--A", type=int, default=15)
+    ap.add_argument("--layout", default="batch_major", choices=["batch_major", "time_major"])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def recorded_traffic(workload):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture, if any."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(p):
+        try:
+            return json.load(open(p)).get(workload)
+        except Exception:
+            pass
+    return None
+
+
+class ClockSampler:
+    """Polls NVML for SM clock and throttle reasons while the timed region runs."""
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz, self._stop = [], set(), None, threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv, self.h = pynvml, pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+        self.thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        nv = self.nv
+        names = {"hw_slowdown": 0x8, "sw_power_cap": 0x4, "sw_thermal_slowdown": 0x20,
+                 "hw_thermal_slowdown": 0x40, "hw_power_brake_slowdown": 0x80, "sync_boost": 0x10}
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+                self.reasons |= {k for k, bit in names.items() if r & bit}
+            except Exception:
+                pass
+            time.sleep(0.002)
+
+    def __enter__(self):
+        if self.nv:
+            self.thread.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        if self.nv:
+            self.thread.join(1.0)
+
+    def summary(self):
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": ["nvml unavailable"]}
+        s = sorted(self.samples)
+        return {"sm_mhz": s[len(s) // 2], "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
+                "n_samples": len(s)}
+
+
+# --------------------------------------------------------------------------------------------
+# workloads: each returns (launch(i) -> None, units_per_step, n_kernels_per_step, host_inputs, describe)
+# --------------------------------------------------------------------------------------------
+def n_rotating_sets(bytes_per_set, minimum=4):
+    """Enough distinct input/output sets that a set is evicted from the 126 MB L2 before its reuse."""
+    return max(minimum, int((2.5 * L2_BYTES) // max(bytes_per_set, 1)) + 1)
+
+
+def make_impala_loss(args, device, seed):
+    from impala_b200 import ops, synth
+    B, T, A = args.B or 4096, args.T or 20, args.A
+    tm = args.layout == "time_major"
+    nsets = n_rotating_sets(204 * B * T)
+    sets = []
+    for i in range(nsets):
+        d = synth.impala_rollout(B, T, A, seed=seed + i)
+        if tm:
+            d = {k: v.transpose(0, 1).contiguous() for k, v in d.items()}
+        g = {k: v.to(device) for k, v in d.items()}
+        out = (torch.empty(8, device=device), torch.empty_like(g["logits"]), torch.empty_like(g["values"]))
+        sets.append((g, out))
+    host = {k: v.pin_memory() for k, v in (synth.impala_rollout(B, T, A, seed=seed).items())}
+    if tm:
+        host = {k: v.transpose(0, 1).contiguous().pin_memory() for k, v in host.items()}
+
+    def launch(i):
+        g, out = sets[i % nsets]
+        ops.impala_loss_fwdbwd(g["logits"], g["values"], g["a"], g["r"], g["discount"], g["pi_ref"],
+                               time_major=tm, out=out)
+
+    def e2e_step(dev_in, host_out):
+        sc, _, _ = ops.impala_loss_fwdbwd(dev_in["logits"], dev_in["values"], dev_in["a"], dev_in["r"],
+                                          dev_in["discount"], dev_in["pi_ref"], time_major=tm)
+        host_out.copy_(sc, non_blocking=True)
+
+    desc = {"workload": "IMPALA V-trace + fused loss fwd+bwd (BASELINE config 2)", "T": T, "B_per_gpu": B, "A": A,
+            "layout": args.layout, "l2_policy": "%d rotating input/output sets (%.0f MB > 126 MB L2)"
+            % (nsets, nsets * 204 * B * T / 1e6)}
+    return dict(launch=launch, units=B * T, kernels=1, host=host, e2e_step=e2e_step, desc=desc,
+                check=lambda: sets[0][1][0])
+
+
+def make_ppo(args, device, seed):
+    """BASELINE config 3 per-GPU shard: time-major [T,B] lambda-return scan (K2) then the flat PPO loss (K3)
+    on the T*B samples.  B defaults to 8192 / n_gpus columns."""
+    from impala_b200 import ops, synth
+    T, A = args.T or 256, args.A
+    B = args.B or max(8192 // max(args.gpus, 1), 1)
+    N = T * B
+    nsets = n_rotating_sets(216 * N)
+    sets = []
+    for i in range(nsets):
+        x = synth.returns_rollout(B, T + 1, seed=seed + i)
+        p = synth.ppo_minibatch(N, A, seed=seed + 100 + i)
+        g = dict(r=x["r"][:, :T].t().contiguous().to(device), d=x["discount"][:, :T].t().contiguous().to(device),
+                 vn=x["v"][:, 1:].t().contiguous().to(device),
+                 logits=p["logits"].to(device), pi_ref=p["pi_ref"].to(device), a=p["a"].to(device),
+                 v=p["v"].reshape(-1).to(device))
+        out = (torch.empty(8, device=device), torch.empty_like(g["logits"]), torch.empty_like(g["v"]))
+        sets.append((g, out))
+
+    def launch(i):
+        g, out = sets[i % nsets]
+        target = ops.lambda_returns(g["r"].t(), g["d"].t(), g["vn"].t(), 0.95)       # [B,T] view of [T,B] storage
+        ops.ppo_loss_fwdbwd(g["logits"], g["v"], g["a"], target.t().reshape(-1), g["pi_ref"], 0.0, 0.1, out=out)
+
+    host = {k: v.cpu().pin_memory() for k, v in sets[0][0].items()}
+
+    def e2e_step(dev_in, host_out):
+        target = ops.lambda_returns(dev_in["r"].t(), dev_in["d"].t(), dev_in["vn"].t(), 0.95)
+        sc, _, _ = ops.ppo_loss_fwdbwd(dev_in["logits"], dev_in["v"], dev_in["a"], target.t().reshape(-1),
+                                       dev_in["pi_ref"], 0.0, 0.1)
+        host_out.copy_(sc, non_blocking=True)
+
+    desc = {"workload": "PPO lambda-return scan + clipped-surrogate loss fwd+bwd (BASELINE config 3 shard)",
+            "T": T, "B_per_gpu": B, "A": A, "layout": "time_major scan, flat [T*B,A] loss",
+            "l2_policy": "%d rotating sets (%.0f MB > 126 MB L2)" % (nsets, nsets * 216 * N / 1e6)}
+    return dict(launch=launch, units=N, kernels=2, host=host, e2e_step=e2e_step, desc=desc,
+                check=lambda: sets[0][1][0])
+
+
+def make_replay(args, device, seed):
+    """BASELINE config 4: capacity 1M rows x 12,288 B u8 (12.3 GB in HBM), batch 4096, seed 123."""
+    from impala_b200 import ops
+    cap, n = (args.B or 1_000_000), 4096
+    store = torch.empty(cap, 3, 64, 64, dtype=torch.uint8, device=device)
+    flat = store.view(-1)
+    step = 1 << 28
+    g = torch.Generator(device=device).manual_seed(seed)
+    for off in range(0, flat.numel(), step):        # random bytes, filled on the device in slices
+        m = min(step, flat.numel() - off)
+        flat[off:off + m] = torch.randint(0, 256, (m,), generator=g, device=device, dtype=torch.uint8)
+    nout = 8
+    outs = [torch.empty(n, 3, 64, 64, dtype=torch.uint8, device=device) for _ in range(nout)]
+    idxs = [torch.empty(n, dtype=torch.int64, device=device) for _ in range(nout)]
+    state = {"draws": 0}
+
+    def launch(i):
+        ops.sample_uniform(123, 0, i * n, n, cap, device, out=idxs[i % nout])
+        ops.gather_rows(store, idxs[i % nout], out=outs[i % nout])
+
+    desc = {"workload": "replay uniform sample + gather (BASELINE config 4)", "capacity": cap, "row_bytes": 12288,
+            "batch": n, "l2_policy": "12.3 GB storage >> L2; random rows; %d rotating outputs" % nout}
+    return dict(launch=launch, units=n, kernels=2, host=None, e2e_step=None, desc=desc,
+                check=lambda: idxs[0], state=state)
+
+
+MAKERS = {"impala_loss": make_impala_loss, "ppo": make_ppo, "replay": make_replay}
+
+
+# --------------------------------------------------------------------------------------------
+# timing
+# --------------------------------------------------------------------------------------------
+GRAPH_CHUNK = 1024
+
+
+def build_graphs(launch, steps, stream):
+    """CUDA graphs holding `steps` consecutive steps (launch(i), i = 0..steps-1) in chunks of GRAPH_CHUNK,
+    so the timed region is back-to-back kernels, not Python/ctypes launch latency."""
+    plan, i = [], 0
+    while i < steps:
+        n = min(GRAPH_CHUNK, steps - i)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g, stream=stream):
+            for k in range(i, i + n):
+                launch(k)
+        plan.append(g)
+        i += n
+    return plan
+
+
+def time_device(launch, steps, warmup, device, world_size):
+    """K steps on the device, CUDA events on the launching stream, barrier + synchronize on both sides,
+    max over ranks.  Returns (elapsed ms, clocks summary)."""
+    stream = torch.cuda.Stream(device)
+    with torch.cuda.stream(stream):
+        for i in range(max(warmup, 3)):            # untimed warm-up (also creates workspaces / modules)
+            launch(i)
+    stream.synchronize()
+    plan = build_graphs(launch, steps, stream)
+    with torch.cuda.stream(stream):
+        plan[-1].replay()                          # graph upload
+    stream.synchronize()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world_size > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    with ClockSampler(device.index) as clk:
+        with torch.cuda.stream(stream):
+            start.record(stream)
+            for g in plan:
+                g.replay()
+            stop.record(stream)
+        stop.synchronize()
+    torch.cuda.synchronize()
+    ms = torch.tensor([start.elapsed_time(stop)], dtype=torch.float64, device=device)
+    if world_size > 1:
+        dist.barrier()
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item()), clk.summary()
+
+
+def time_e2e(w, steps, warmup, device, world_size):
+    """Same metric end to end through the public API with HOST inputs: every step copies that step's inputs
+    from pinned host memory (H2D), runs the fused kernel(s) and reads the loss/metric scalars back (D2H).
+    Copies of step i+1 overlap the kernel of step i on a second stream.  Wall clock, synchronised both sides."""
+    host = w["host"]
+    h2d = sum(v.numel() * v.element_size() for v in host.values())
+    copy_s, comp_s = torch.cuda.Stream(device), torch.cuda.Stream(device)
+    dev = [{k: torch.empty_like(v, device=device) for k, v in host.items()} for _ in range(2)]
+    outs = [torch.empty(8, dtype=torch.float32).pin_memory() for _ in range(2)]
+    copied = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
+
+    def run(n):
+        for i in range(n):
+            b = i & 1
+            with torch.cuda.stream(copy_s):
+                if i >= 2:
+                    copy_s.wait_event(consumed[b])
+                for k, v in host.items():
+                    dev[b][k].copy_(v, non_blocking=True)
+                copied[b].record(copy_s)
+            with torch.cuda.stream(comp_s):
+                comp_s.wait_event(copied[b])
+                w["e2e_step"](dev[b], outs[b])
+                consumed[b].record(comp_s)
+        torch.cuda.synchronize()
+
+    run(max(warmup, 3))
+    if world_size > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    run(steps)
+    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=device)
+    if world_size > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    return float(dt.item()), h2d, 32
+
+
+# --------------------------------------------------------------------------------------------
+# CPU legs: the oracle port of the reference's torch path, all host threads
+# --------------------------------------------------------------------------------------------
+def cpu_step_fn(args, B):
+    """One reference-shaped CPU step on B columns (the oracle: eager torch + vmap over the per-sequence loop,
+    exactly the reference's structure, agents/impala/learning.py:18,146-160 / losses.py:131-155)."""
+    from impala_b200 import synth
+    from oracle import losses_ref, rlego_ref
+    if args.workload == "impala_loss":
+        T, A = args.T or 20, args.A
+        d = synth.impala_rollout(B, T, A, seed=2000)
+
+        def step():
+            lg, vv = d["logits"].clone().requires_grad_(True), d["values"].clone().requires_grad_(True)
+            loss, _ = losses_ref.impala_train_loss(lg, vv, d["a"], d["r"], d["discount"], d["pi_ref"])
+            loss.backward()
+            return loss
+        return step, B * T
+    if args.workload == "ppo":
+        T, A = args.T or 256, args.A
+        x = synth.returns_rollout(B, T + 1, seed=3000)
+        p = synth.ppo_minibatch(B * T, A, seed=3100)
+        fn = rlego_ref.batched(rlego_ref.lambda_returns, lambda_=0.95)
+
+        def step():
+            tgt = fn(x["r"][:, :T], x["discount"][:, :T], x["v"][:, 1:])
+            lg, v = p["logits"].clone().requires_grad_(True), p["v"].clone().requires_grad_(True)
+            loss, _ = losses_ref.ppo_loss_from_outputs(lg, v, p["a"], tgt.reshape(-1), p["pi_ref"], 0.0, 0.1)
+            loss.backward()
+            return loss
+        return step, B * T
+    # replay: rlmeta-shaped host path -- draw indices, index the host storage, collate, (no H2D counted)
+    cap = min(args.B or 1_000_000, 100_000)
+    store = torch.randint(0, 256, (cap, 3, 64, 64), dtype=torch.uint8)
+
+    def step():
+        idx = torch.randint(0, cap, (B,))
+        return store.index_select(0, idx)
+    return step, B
+
+
+def time_cpu(args, seconds, steps=None, warmup=2):
+    torch.set_num_threads(os.cpu_count() or 1)
+    full_B = {"impala_loss": args.B or 4096, "ppo": args.B or 8192, "replay": 4096}[args.workload]
+    step, units = cpu_step_fn(args, full_B)
+    t0 = time.perf_counter()
+    step()
+    t_full = time.perf_counter() - t0
+    B = full_B
+    if steps is not None and t_full * (steps + warmup) > seconds:   # shrink the per-step sample to fit the budget
+        B = max(8, int(full_B * seconds / (t_full * (steps + warmup))))
+        step, units = cpu_step_fn(args, B)
+    for _ in range(warmup):
+        step()
+    n, t0 = 0, time.perf_counter()
+    while True:
+        step()
+        n += 1
+        el = time.perf_counter() - t0
+        if (steps is not None and n >= steps) or (steps is None and (el > seconds and n >= 3)) or el > 4 * seconds + 60:
+            break
+    return dict(value=units * n / el, seconds=el, steps=n, cores=torch.get_num_threads(),
+                sample="%d step(s) of %d of %d columns per step, fwd+bwd, torch %d threads" % (n, B, full_B, torch.get_num_threads()))
+
+
+# --------------------------------------------------------------------------------------------
+def run_reference(args, rank, world_size):
+    """`--impl reference`: the reference's own CPU path for this metric.  The reference cannot be imported
+    (rlego / rlmeta / moolib are neither installed nor vendored), so this times the oracle port of
+    its torch code on all host cores.  Rank 0 only; other ranks exit 0."""
+    if rank != 0:
+        return
+    metric, unit, _ = WORKLOADS[args.workload]
+    steps = args.steps if args.steps is not None else 20
+    warmup = args.warmup if args.warmup is not None else 3
+    r = time_cpu(args, seconds=90.0, steps=steps, warmup=min(warmup, 5))
+    line = {
+        "impl": "reference", "metric": metric, "value": r["value"], "unit": unit, "n_gpus": args.gpus,
+        "steps": r["steps"], "warmup": min(warmup, 5), "ms_per_step": 1e3 * r["seconds"] / r["steps"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "sample": r["sample"]},
+        "cpu_baseline": {"value": r["value"], "unit": unit, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+        "e2e": {"value": r["value"], "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        return run_reference(args, rank, world_size)
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU leg")
+    torch.cuda.set_device(local_rank)
+    device = torch.device("cuda", local_rank)
+    if world_size > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=device)
+    metric, unit, bytes_per_unit = WORKLOADS[args.workload]
+    steps = args.steps if args.steps is not None else {"impala_loss": 20000, "ppo": 2000, "replay": 4000}[args.workload]
+    warmup = args.warmup if args.warmup is not None else 50
+    args.gpus = world_size if world_size > 1 else args.gpus
+
+    w = MAKERS[args.workload](args, device, seed=2000 + 1000 * rank)
+    ms, clocks = time_device(w["launch"], steps, warmup, device, world_size)
+    units_total = w["units"] * steps * world_size
+    value = units_total / (ms * 1e-3)
+    peak, peak_src = measured_peak()
+    achieved = bytes_per_unit * w["units"] * steps / (ms * 1e-3) / 1e9     # per GPU, GB/s
+    line = {
+        "metric": metric, "value": value, "unit": unit, "n_gpus": world_size, "steps": steps, "warmup": max(warmup, 3),
+        "ms_per_step": ms / steps, "higher_is_better": True,
+        "scaling": "strong" if (args.workload == "ppo" and args.B is None) else "weak",
+        "vs_baseline": None, "dtype": "f32" if args.workload != "replay" else "u8", "data": "synthetic",
+        "config": dict(w["desc"], parallelism="dp%d (rank-local batches sharded along B, no data-path collective)" % world_size,
+                       timing="CUDA graph of back-to-back steps, CUDA events on the launching stream, max over ranks"),
+        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": recorded_traffic(args.workload), "peak_source": peak_src,
+                     "algorithmic_bytes_per_step": bytes_per_unit * w["units"],
+                     "note": "per GPU; duration = timed region / steps (launch gaps included)"},
+        "clocks": clocks,
+        "gpu_launches": steps * w["kernels"],
+    }
+    if not args.no_e2e and w["e2e_step"] is not None:
+        e_steps = min(steps, 2000)
+        dt, h2d, d2h = time_e2e(w, e_steps, min(warmup, 20), device, world_size)
+        line["e2e"] = {"value": w["units"] * e_steps * world_size / dt, "unit": unit, "h2d_bytes_per_step": h2d,
+                       "d2h_bytes_per_step": d2h, "steps": e_steps,
+                       "note": "pinned host inputs -> H2D -> fused kernel -> D2H of the 8 loss/metric scalars, every step"}
+    elif not args.no_e2e:
+        line["e2e"] = None
+    if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
+        r = time_cpu(args, seconds=args.cpu_seconds)
+        line["cpu_baseline"] = {"value": r["value"], "unit": unit, "cores": r["cores"], "kind": "port",
+                                "sample": r["sample"], "cpu_count": os.cpu_count()}
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world_size > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

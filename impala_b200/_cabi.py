@@ -11,19 +11,19 @@ from . import _build
 
 _lib = None
 
-_vp, _i64, _i32, _u32, _u64, _f = (ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32,
-                                   ctypes.c_uint32, ctypes.c_uint64, ctypes.c_float)
+_vp, _i64, _i32, _u32, _u64, _f, _d = (ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32,
+                                       ctypes.c_uint32, ctypes.c_uint64, ctypes.c_float, ctypes.c_double)
 
 # name -> (restype, argtypes); mirrors include/b200rl.h one to one
 SIGNATURES = {
     "b200rl_version": (_i32, []),
     "b200rl_last_error": (ctypes.c_char_p, []),
     "b200rl_loss_workspace_bytes": (_i64, []),
-    "b200rl_vtrace_impala_loss_fwdbwd": (_i32, [_vp] * 6 + [_i64] * 6 + [_f] * 4 + [_u32] + [_vp] * 5),
-    "b200rl_vtrace": (_i32, [_vp] * 5 + [_i64] * 4 + [_f] * 3 + [_vp] * 4),
-    "b200rl_vtrace_bwd": (_i32, [_vp] * 7 + [_i64] * 4 + [_f] * 2 + [_vp] * 4),
-    "b200rl_lambda_returns": (_i32, [_vp] * 3 + [_i64] * 4 + [_f] + [_vp] * 2),
-    "b200rl_gae": (_i32, [_vp] * 3 + [_i64] * 6 + [_f] + [_vp] * 2),
+    "b200rl_vtrace_impala_loss_fwdbwd": (_i32, [_vp] * 6 + [_i64] * 6 + [_d] + [_f] * 3 + [_u32] + [_vp] * 5),
+    "b200rl_vtrace": (_i32, [_vp] * 5 + [_i64] * 4 + [_d] + [_f] * 2 + [_vp] * 4),
+    "b200rl_vtrace_bwd": (_i32, [_vp] * 7 + [_i64] * 4 + [_d, _f] + [_vp] * 4),
+    "b200rl_lambda_returns": (_i32, [_vp] * 3 + [_i64] * 4 + [_d] + [_vp] * 2),
+    "b200rl_gae": (_i32, [_vp] * 3 + [_i64] * 6 + [_d] + [_vp] * 2),
     "b200rl_ppo_loss_fwdbwd": (_i32, [_vp] * 5 + [_i64] * 3 + [_f] * 2 + [_u32] + [_vp] * 5),
     "b200rl_sample_uniform": (_i32, [_u64, _u32, _u64, _i64, _i64, _vp, _vp]),
     "b200rl_gather_rows": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _vp]),

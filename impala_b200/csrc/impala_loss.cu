@@ -19,7 +19,7 @@ struct ImpalaParams {
     float *dlogits, *dvalues, *scalars;
     void *workspace;
     int B, T, A, C, time_major;
-    float lambda_, clip_rho, clip_pg_rho, entropy_coeff, inv_n_pg, inv_n_all;
+    float lambda_, one_minus_lambda, clip_rho, clip_pg_rho, entropy_coeff, inv_n_pg, inv_n_all;
     uint32_t flags;
 };
 
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(AT <= 16 ? 512 : 256) impala_loss_kernel(const
             s_gc[s] = disc * (fminf(st.rho, 1.0f) * p.lambda_);
             // adv_t depends on v_{t+1} through the q bootstrap: weight 1 at the last step,
             // (1 - lambda) elsewhere (the lambda * vs_{t+1} part is a stop-gradient target)
-            const float w = (t == T - 2) ? 1.f : (1.f - p.lambda_);
+            const float w = (t == T - 2) ? 1.f : p.one_minus_lambda;
             s_nx[s] = detach_adv ? 0.f : -st.lp * c_pg * disc * w * p.inv_n_pg;
         }
     }
@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(AT <= 16 ? 512 : 256) impala_loss_kernel(const
             if (t < T - 2) {
                 const float e1 = s_td[s + st_local];
                 const float tgt1 = ((e1 + v_next) - v_next) + v_next;
-                qb = p.lambda_ * tgt1 + (1.f - p.lambda_) * v_next;
+                qb = p.lambda_ * tgt1 + p.one_minus_lambda * v_next;
             }
             const float q = rew + disc * qb;
             const float qmv = q - v;
@@ -189,15 +189,14 @@ int env_int(const char *name, int dflt);
 
 template <int AT>
 static int32_t launch_impala(const ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
-    static bool configured = false;  // opt in to > 48 KB dynamic shared memory once
-    if (!configured || smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(impala_loss_kernel<AT>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    static size_t configured = 48 * 1024;  // dynamic shared memory already opted in to
+    if (smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(impala_loss_kernel<AT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) {
-            set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+            set_error("cudaFuncSetAttribute(%zu B shared): %s", smem, cudaGetErrorString(e));
             return (int32_t)e;
         }
-        configured = true;
+        configured = smem;
     }
     const int grid = (p.B + p.C - 1) / p.C;
     impala_loss_kernel<AT><<<grid, threads, smem, stream>>>(p);
@@ -209,7 +208,7 @@ static int32_t launch_impala(const ImpalaParams &p, int threads, size_t smem, cu
 extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
     const float *logits, const float *pi_ref, const int64_t *actions, const float *rewards,
     const float *discounts, const float *values, int64_t B, int64_t T, int64_t A, int64_t stride_b,
-    int64_t stride_t, int64_t n_global_b, float lambda_, float clip_rho, float clip_pg_rho,
+    int64_t stride_t, int64_t n_global_b, double lambda_, float clip_rho, float clip_pg_rho,
     float entropy_coeff, uint32_t flags, float *dlogits, float *dvalues, float *scalars,
     void *workspace, void *stream) {
     using namespace b200rl;
@@ -235,7 +234,7 @@ extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
     p.dlogits = dlogits; p.dvalues = dvalues; p.scalars = scalars; p.workspace = workspace;
     p.B = (int)B; p.T = (int)T; p.A = (int)A;
     p.time_major = (time_major && !batch_major) ? 1 : 0;
-    p.lambda_ = lambda_; p.clip_rho = clip_rho; p.clip_pg_rho = clip_pg_rho; p.entropy_coeff = entropy_coeff;
+    p.lambda_ = (float)lambda_; p.one_minus_lambda = (float)(1.0 - lambda_); p.clip_rho = clip_rho; p.clip_pg_rho = clip_pg_rho; p.entropy_coeff = entropy_coeff;
     p.inv_n_pg = (float)(1.0 / ((double)n_global_b * (double)(T - 1)));
     p.inv_n_all = (float)(1.0 / ((double)n_global_b * (double)T));
     p.flags = flags;
@@ -250,7 +249,7 @@ extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
     const int a_tile = A <= 8 ? 8 : (A <= 16 ? 16 : 32);
     auto smem_for = [&](int c) { return (size_t)c * T * (2 * A + 3) * 4 + 5 * 32 * 4 + 16; };
     while (C > 1 && smem_for(C) > 200 * 1024) C = (C > 4) ? ((C / 2) & ~3) : C - 1;
-    B200RL_REQUIRE(smem_for(C) <= 227 * 1024, -3, "impala_loss: T*A too large for one CTA tile");
+    B200RL_REQUIRE(smem_for(C) <= 226 * 1024, -3, "impala_loss: T*A too large for one CTA tile");
     B200RL_REQUIRE((B + C - 1) / C <= kMaxPartialCtas, -3, "impala_loss: B too large for the partials workspace");
     p.C = C;
     const int threads = ((C * (int)T + 31) / 32) * 32;

@@ -115,15 +115,14 @@ __global__ void __launch_bounds__(kPpoTile) ppo_loss_kernel(const PpoParams p) {
 
 template <int AT>
 static int32_t launch_ppo(const PpoParams &p, size_t smem, cudaStream_t stream) {
-    static bool configured = false;
-    if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(ppo_loss_kernel<AT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                             227 * 1024);
+    static size_t configured = 48 * 1024;  // dynamic shared memory already opted in to
+    if (smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(ppo_loss_kernel<AT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) {
-            set_error("cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+            set_error("cudaFuncSetAttribute(%zu B shared): %s", smem, cudaGetErrorString(e));
             return (int32_t)e;
         }
-        configured = true;
+        configured = smem;
     }
     const unsigned grid = (unsigned)((p.N + kPpoTile - 1) / kPpoTile);
     ppo_loss_kernel<AT><<<grid, kPpoTile, smem, stream>>>(p);

@@ -24,13 +24,18 @@ struct ScanParams {
     float *out;
     int B, T;
     long long sb, st, vsb, vst;  // element strides of r/disc/out and of v
-    float lambda_;
+    float lambda_, one_minus_lambda;  // both rounded to fp32 from the double argument
 };
 
+// One step in the reference's operation order with every product and sum rounded separately
+// (no FMA contraction), i.e. exactly what the eager torch ops of the oracle compute; the
+// kernels are HBM-bound, the extra instructions are free.
 template <int MODE>
-__device__ __forceinline__ float scan_step(float r, float d, float v0, float v1, float lam, float y) {
-    if (MODE == MODE_LAMBDA_RETURNS) return r + d * ((1.f - lam) * v0 + lam * y);  // v0 = v_t[t]
-    return (r + d * v1 - v0) + lam * d * y;                                         // v0 = V[t], v1 = V[t+1]
+__device__ __forceinline__ float scan_step(float r, float d, float v0, float v1, float lam, float oml, float y) {
+    if (MODE == MODE_LAMBDA_RETURNS)  // r + d * ((1 - lam) * v_t[t] + lam * y)
+        return __fadd_rn(r, __fmul_rn(d, __fadd_rn(__fmul_rn(oml, v0), __fmul_rn(lam, y))));
+    // (r + d * V[t+1] - V[t]) + lam * d * y
+    return __fadd_rn(__fsub_rn(__fadd_rn(r, __fmul_rn(d, v1)), v0), __fmul_rn(__fmul_rn(lam, d), y));
 }
 
 template <int MODE, int L>
@@ -63,7 +68,7 @@ __global__ void __launch_bounds__(512) scan_time_major_kernel(const ScanParams p
     for (int k = L - 1; k >= 0; --k) {
         if (t0 + k < p.T) {
             const float a = p.lambda_ * d[k];
-            const float bb = scan_step<MODE>(r[k], d[k], v[k], v[k + 1], p.lambda_, 0.f);
+            const float bb = scan_step<MODE>(r[k], d[k], v[k], v[k + 1], p.lambda_, p.one_minus_lambda, 0.f);
             Bc = bb + a * Bc;
             Ac = a * Ac;
         }
@@ -81,7 +86,7 @@ __global__ void __launch_bounds__(512) scan_time_major_kernel(const ScanParams p
     for (int k = L - 1; k >= 0; --k) {
         const int t = t0 + k;
         if (col_ok && t < p.T) {
-            y = scan_step<MODE>(r[k], d[k], v[k], v[k + 1], p.lambda_, y);
+            y = scan_step<MODE>(r[k], d[k], v[k], v[k + 1], p.lambda_, p.one_minus_lambda, y);
             p.out[(long long)t * p.st + (long long)b * p.sb] = y;
         }
     }
@@ -98,7 +103,7 @@ __global__ void __launch_bounds__(128) scan_generic_kernel(const ScanParams p) {
     for (int t = p.T - 1; t >= 0; --t) {
         const long long i = (long long)b * p.sb + (long long)t * p.st;
         const float v0 = vb[(long long)t * p.vst];
-        y = scan_step<MODE>(p.r[i], p.disc[i], v0, v1, p.lambda_, y);
+        y = scan_step<MODE>(p.r[i], p.disc[i], v0, v1, p.lambda_, p.one_minus_lambda, y);
         p.out[i] = y;
         v1 = v0;
     }
@@ -138,23 +143,25 @@ static int32_t check_scan_layout(const char *who, int64_t B, int64_t T, int64_t 
 
 extern "C" int32_t b200rl_lambda_returns(const float *r_t, const float *discount_t, const float *v_t,
                                          int64_t B, int64_t T, int64_t stride_b, int64_t stride_t,
-                                         float lambda_, float *out, void *stream) {
+                                         double lambda_, float *out, void *stream) {
     using namespace b200rl;
     B200RL_REQUIRE(r_t && discount_t && v_t && out, -1, "lambda_returns: null pointer argument");
     if (int32_t rc = check_scan_layout("lambda_returns", B, T, stride_b, stride_t)) return rc;
-    ScanParams p{r_t, discount_t, v_t, out, (int)B, (int)T, stride_b, stride_t, stride_b, stride_t, lambda_};
+    ScanParams p{r_t, discount_t, v_t, out, (int)B, (int)T, stride_b, stride_t, stride_b, stride_t, (float)lambda_,
+                 (float)(1.0 - lambda_)};
     return launch_scan<MODE_LAMBDA_RETURNS>(p, (cudaStream_t)stream);
 }
 
 extern "C" int32_t b200rl_gae(const float *r_t, const float *discount_t, const float *values, int64_t B,
                               int64_t T, int64_t stride_b, int64_t stride_t, int64_t vstride_b,
-                              int64_t vstride_t, float lambda_, float *out, void *stream) {
+                              int64_t vstride_t, double lambda_, float *out, void *stream) {
     using namespace b200rl;
     B200RL_REQUIRE(r_t && discount_t && values && out, -1, "gae: null pointer argument");
     if (int32_t rc = check_scan_layout("gae", B, T, stride_b, stride_t)) return rc;
     B200RL_REQUIRE((vstride_t == 1 && vstride_b >= T + 1) || (vstride_b == 1 && vstride_t >= B), -4,
                    "gae: value strides (%lld,%lld) unsupported", (long long)vstride_b, (long long)vstride_t);
     B200RL_REQUIRE((stride_b == 1) == (vstride_b == 1), -4, "gae: values and rewards must share the major order");
-    ScanParams p{r_t, discount_t, values, out, (int)B, (int)T, stride_b, stride_t, vstride_b, vstride_t, lambda_};
+    ScanParams p{r_t, discount_t, values, out, (int)B, (int)T, stride_b, stride_t, vstride_b, vstride_t, (float)lambda_,
+                 (float)(1.0 - lambda_)};
     return launch_scan<MODE_GAE>(p, (cudaStream_t)stream);
 }

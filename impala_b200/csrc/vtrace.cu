@@ -12,7 +12,7 @@ namespace b200rl {
 __global__ void __launch_bounds__(128) vtrace_fwd_kernel(
     const float *__restrict__ v_tm1, const float *__restrict__ v_t, const float *__restrict__ r_t,
     const float *__restrict__ disc, const float *__restrict__ rho, int B, int Tm, long long sb,
-    long long st, float lambda_, float clip_rho, float clip_pg_rho, float *__restrict__ adv,
+    long long st, float lambda_, float oml, float clip_rho, float clip_pg_rho, float *__restrict__ adv,
     float *__restrict__ err, float *__restrict__ q) {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
     if (b >= B) return;
@@ -27,7 +27,7 @@ __global__ void __launch_bounds__(128) vtrace_fwd_kernel(
         e = td + d * c * e;
         const float tgt = e + vm;
         const float er = tgt - vm;
-        const float qb = (t == Tm - 1) ? vt : lambda_ * tgt_next + (1.f - lambda_) * v_tm1_next;
+        const float qb = (t == Tm - 1) ? vt : lambda_ * tgt_next + oml * v_tm1_next;
         const float qq = r + d * qb;
         err[o] = er;
         q[o] = qq;
@@ -41,7 +41,7 @@ __global__ void __launch_bounds__(128) vtrace_fwd_kernel(
 __global__ void __launch_bounds__(256) vtrace_bwd_kernel(
     const float *__restrict__ v_tm1, const float *__restrict__ disc, const float *__restrict__ rho,
     const float *__restrict__ q, const float *__restrict__ g_adv, const float *__restrict__ g_err,
-    const float *__restrict__ g_q, int B, int Tm, long long sb, long long st, float lambda_,
+    const float *__restrict__ g_q, int B, int Tm, long long sb, long long st, float oml,
     float clip_pg_rho, float *__restrict__ d_v_tm1, float *__restrict__ d_v_t,
     float *__restrict__ d_rho) {
     const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -57,10 +57,10 @@ __global__ void __launch_bounds__(256) vtrace_bwd_kernel(
     const float ga = g_adv ? g_adv[o] : 0.f;
     const float gq = (g_q ? g_q[o] : 0.f) + ga * cpg;  // total upstream on q_t
     float dvm = -(g_err ? g_err[o] : 0.f) - ga * cpg;
-    if (t > 0 && lambda_ != 1.f) {
+    if (t > 0 && oml != 0.f) {
         const long long j = i - st, oj = o - ost;
         const float gq_prev = (g_q ? g_q[oj] : 0.f) + (g_adv ? g_adv[oj] : 0.f) * fminf(rho[j], clip_pg_rho);
-        dvm += gq_prev * disc[j] * (1.f - lambda_);
+        dvm += gq_prev * disc[j] * oml;
     }
     d_v_tm1[o] = dvm;
     d_v_t[o] = (t == Tm - 1) ? gq * disc[i] : 0.f;
@@ -80,22 +80,22 @@ static int32_t check_layout(const char *who, int64_t B, int64_t T, int64_t sb, i
 
 extern "C" int32_t b200rl_vtrace(const float *v_tm1, const float *v_t, const float *r_t,
                                  const float *discount_t, const float *rho_tm1, int64_t B, int64_t Tm,
-                                 int64_t stride_b, int64_t stride_t, float lambda_, float clip_rho,
+                                 int64_t stride_b, int64_t stride_t, double lambda_, float clip_rho,
                                  float clip_pg_rho, float *adv, float *err, float *q, void *stream) {
     using namespace b200rl;
     B200RL_REQUIRE(v_tm1 && v_t && r_t && discount_t && rho_tm1 && adv && err && q, -1, "vtrace: null pointer argument");
     if (int32_t rc = check_layout("vtrace", B, Tm, stride_b, stride_t)) return rc;
     const int threads = 128;
     vtrace_fwd_kernel<<<(unsigned)((B + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
-        v_tm1, v_t, r_t, discount_t, rho_tm1, (int)B, (int)Tm, stride_b, stride_t, lambda_, clip_rho,
-        clip_pg_rho, adv, err, q);
+        v_tm1, v_t, r_t, discount_t, rho_tm1, (int)B, (int)Tm, stride_b, stride_t, (float)lambda_,
+        (float)(1.0 - lambda_), clip_rho, clip_pg_rho, adv, err, q);
     return check_launch("vtrace_fwd_kernel");
 }
 
 extern "C" int32_t b200rl_vtrace_bwd(const float *v_tm1, const float *discount_t, const float *rho_tm1,
                                      const float *q, const float *g_adv, const float *g_err,
                                      const float *g_q, int64_t B, int64_t Tm, int64_t stride_b,
-                                     int64_t stride_t, float lambda_, float clip_pg_rho, float *d_v_tm1,
+                                     int64_t stride_t, double lambda_, float clip_pg_rho, float *d_v_tm1,
                                      float *d_v_t, float *d_rho, void *stream) {
     using namespace b200rl;
     B200RL_REQUIRE(v_tm1 && discount_t && rho_tm1 && q && d_v_tm1 && d_v_t && d_rho, -1, "vtrace_bwd: null pointer argument");
@@ -103,7 +103,7 @@ extern "C" int32_t b200rl_vtrace_bwd(const float *v_tm1, const float *discount_t
     const int threads = 256;
     const long long n = (long long)B * Tm;
     vtrace_bwd_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
-        v_tm1, discount_t, rho_tm1, q, g_adv, g_err, g_q, (int)B, (int)Tm, stride_b, stride_t, lambda_,
-        clip_pg_rho, d_v_tm1, d_v_t, d_rho);
+        v_tm1, discount_t, rho_tm1, q, g_adv, g_err, g_q, (int)B, (int)Tm, stride_b, stride_t,
+        (float)(1.0 - lambda_), clip_pg_rho, d_v_tm1, d_v_t, d_rho);
     return check_launch("vtrace_bwd_kernel");
 }

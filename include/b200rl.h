@@ -17,6 +17,8 @@
  *    supported: batch-major (stride_b=T, stride_t=1, the reference's layout,
  *    agents/impala/learning.py:142-145) and time-major (stride_b=1, stride_t=B).
  *    Per-action tensors ([.., A]) use the same sample index times A.
+ *  - lambda_ is a double so that (1 - lambda_) is rounded to fp32 once, exactly as the
+ *    reference's Python-float arithmetic does (bit-exact scans against the oracle);
  *  - there is no CPU fallback and no other backend: sm_100a only.
  */
 #ifndef B200RL_H
@@ -61,7 +63,7 @@ int32_t b200rl_vtrace_impala_loss_fwdbwd(
     const float *logits, const float *pi_ref, const int64_t *actions, const float *rewards,
     const float *discounts, const float *values,
     int64_t B, int64_t T, int64_t A, int64_t stride_b, int64_t stride_t, int64_t n_global_b,
-    float lambda_, float clip_rho, float clip_pg_rho, float entropy_coeff, uint32_t flags,
+    double lambda_, float clip_rho, float clip_pg_rho, float entropy_coeff, uint32_t flags,
     float *dlogits, float *dvalues, float *scalars, void *workspace, void *stream);
 
 /* Stand-alone drop-in for batched_vtrace(v_tm1, v_t, r_t, discount_t, rho_tm1)
@@ -73,7 +75,7 @@ int32_t b200rl_vtrace_impala_loss_fwdbwd(
 int32_t b200rl_vtrace(
     const float *v_tm1, const float *v_t, const float *r_t, const float *discount_t,
     const float *rho_tm1, int64_t B, int64_t Tm, int64_t stride_b, int64_t stride_t,
-    float lambda_, float clip_rho, float clip_pg_rho,
+    double lambda_, float clip_rho, float clip_pg_rho,
     float *adv, float *err, float *q, void *stream);
 
 /* Backward of b200rl_vtrace under stop_target_gradients=True: given upstream
@@ -84,7 +86,7 @@ int32_t b200rl_vtrace_bwd(
     const float *v_tm1, const float *discount_t, const float *rho_tm1, const float *q,
     const float *g_adv, const float *g_err, const float *g_q,
     int64_t B, int64_t Tm, int64_t stride_b, int64_t stride_t,
-    float lambda_, float clip_pg_rho,
+    double lambda_, float clip_pg_rho,
     float *d_v_tm1, float *d_v_t, float *d_rho, void *stream);
 
 /* K2 -- replaces rlego.lambda_returns(r_t, discount_t, v_t, lambda_) per rollout
@@ -92,7 +94,7 @@ int32_t b200rl_vtrace_bwd(
  * G_t = r_t + g_t((1-l) v_t[t] + l G_{t+1}), bootstrap v_t[T-1]. */
 int32_t b200rl_lambda_returns(
     const float *r_t, const float *discount_t, const float *v_t,
-    int64_t B, int64_t T, int64_t stride_b, int64_t stride_t, float lambda_,
+    int64_t B, int64_t T, int64_t stride_b, int64_t stride_t, double lambda_,
     float *out, void *stream);
 
 /* GAE (rlego.truncated_generalized_advantage_estimation, reference losses.py:11).
@@ -100,7 +102,7 @@ int32_t b200rl_lambda_returns(
 int32_t b200rl_gae(
     const float *r_t, const float *discount_t, const float *values,
     int64_t B, int64_t T, int64_t stride_b, int64_t stride_t,
-    int64_t vstride_b, int64_t vstride_t, float lambda_, float *out, void *stream);
+    int64_t vstride_b, int64_t vstride_t, double lambda_, float *out, void *stream);
 
 /* K3 -- replaces losses.ppo_loss after model(s) + backward w.r.t. model outputs
  * (reference losses.py:134-155, caller agents/ppo/learning.py:132-134).

@@ -112,8 +112,13 @@ def test_scans_parity(B, T, lam, time_major):
         rg, dg, vg = r.cuda(), d.cuda(), v.cuda()
         got_lr = vtrace.lambda_returns(rg, dg, vg[:, 1:], lam)
         got_gae = vtrace.truncated_generalized_advantage_estimation(rg, dg, lam, vg)
-    assert_close(got_lr, want_lr, "lambda_returns", rtol=1e-5, atol=2e-6, rel_to_max=1e-5)
-    assert_close(got_gae, want_gae, "gae", rtol=1e-5, atol=2e-6, rel_to_max=1e-5)
+    # a T-step fp32 recursion whose values reach magnitude M carries rounding error ~ eps * M: the
+    # absolute tolerance scales with M (north_star's atol 1e-6 is for O(1) quantities)
+    for name, got, want in (("lambda_returns", got_lr, want_lr), ("gae", got_gae, want_gae)):
+        M = max(1.0, want.abs().max().item())
+        assert_close(got, want, name, rtol=1e-5, atol=1e-6 * M, rel_to_max=2e-6)
+    if not time_major:  # sequential kernel, same operation order and roundings as the oracle: bit exact
+        assert torch.equal(got_lr.cpu(), want_lr) and torch.equal(got_gae.cpu(), want_gae)
 
 
 def test_scans_golden_identity_and_ppo_targets():
