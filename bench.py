@@ -46,6 +46,12 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--streams", type=int, default=4,
+                    help="issue consecutive (independent) steps round-robin on this many CUDA streams")
+    ap.add_argument("--pipeline", default="independent", choices=["independent", "serial"],
+                    help="independent: consecutive steps use disjoint buffers, so the fused losses are launched with "
+                         "B200RL_INPUTS_STABLE (PDL overlap of launch N+1 with the tail of launch N); serial: every "
+                         "launch waits for the previous kernel before reading anything")
     return ap.parse_args()
 
 
@@ -140,10 +146,12 @@ def make_impala_loss(args, device, seed):
     if tm:
         host = {k: v.transpose(0, 1).contiguous().pin_memory() for k, v in host.items()}
 
+    flags = ops.INPUTS_STABLE if args.pipeline == "independent" else 0
+
     def launch(i):
         g, out = sets[i % nsets]
         ops.impala_loss_fwdbwd(g["logits"], g["values"], g["a"], g["r"], g["discount"], g["pi_ref"],
-                               time_major=tm, out=out)
+                               flags=flags, time_major=tm, out=out)
 
     def e2e_step(dev_in, host_out):
         sc, _, _ = ops.impala_loss_fwdbwd(dev_in["logits"], dev_in["values"], dev_in["a"], dev_in["r"],
@@ -151,7 +159,7 @@ def make_impala_loss(args, device, seed):
         host_out.copy_(sc, non_blocking=True)
 
     desc = {"workload": "IMPALA V-trace + fused loss fwd+bwd (BASELINE config 2)", "T": T, "B_per_gpu": B, "A": A,
-            "layout": args.layout, "l2_policy": "%d rotating input/output sets (%.0f MB > 126 MB L2)"
+            "layout": args.layout, "pipeline": args.pipeline, "l2_policy": "%d rotating input/output sets (%.0f MB > 126 MB L2)"
             % (nsets, nsets * 204 * B * T / 1e6)}
     return dict(launch=launch, units=B * T, kernels=1, host=host, e2e_step=e2e_step, desc=desc,
                 check=lambda: sets[0][1][0])
@@ -231,22 +239,32 @@ MAKERS = {"impala_loss": make_impala_loss, "ppo": make_ppo, "replay": make_repla
 GRAPH_CHUNK = 1024
 
 
-def build_graphs(launch, steps, stream):
+def build_graphs(launch, steps, stream, n_streams=1):
     """CUDA graphs holding `steps` consecutive steps (launch(i), i = 0..steps-1) in chunks of GRAPH_CHUNK,
-    so the timed region is back-to-back kernels, not Python/ctypes launch latency."""
+    so the timed region is back-to-back kernels, not Python/ctypes launch latency.  With n_streams > 1 step i
+    is issued on side stream i % n_streams (fork/join inside the graph): independent steps may overlap."""
+    side = [torch.cuda.Stream(stream.device) for _ in range(n_streams)] if n_streams > 1 else []
     plan, i = [], 0
     while i < steps:
         n = min(GRAPH_CHUNK, steps - i)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g, stream=stream):
+            for s_ in side:
+                s_.wait_stream(stream)
             for k in range(i, i + n):
-                launch(k)
+                if side:
+                    with torch.cuda.stream(side[k % n_streams]):
+                        launch(k)
+                else:
+                    launch(k)
+            for s_ in side:
+                stream.wait_stream(s_)
         plan.append(g)
         i += n
     return plan
 
 
-def time_device(launch, steps, warmup, device, world_size):
+def time_device(launch, steps, warmup, device, world_size, n_streams=1):
     """K steps on the device, CUDA events on the launching stream, barrier + synchronize on both sides,
     max over ranks.  Returns (elapsed ms, clocks summary)."""
     stream = torch.cuda.Stream(device)
@@ -254,7 +272,7 @@ def time_device(launch, steps, warmup, device, world_size):
         for i in range(max(warmup, 3)):            # untimed warm-up (also creates workspaces / modules)
             launch(i)
     stream.synchronize()
-    plan = build_graphs(launch, steps, stream)
+    plan = build_graphs(launch, steps, stream, n_streams)
     with torch.cuda.stream(stream):
         plan[-1].replay()                          # graph upload
     stream.synchronize()
@@ -423,7 +441,7 @@ def main():
     args.gpus = world_size if world_size > 1 else args.gpus
 
     w = MAKERS[args.workload](args, device, seed=2000 + 1000 * rank)
-    ms, clocks = time_device(w["launch"], steps, warmup, device, world_size)
+    ms, clocks = time_device(w["launch"], steps, warmup, device, world_size, args.streams)
     units_total = w["units"] * steps * world_size
     value = units_total / (ms * 1e-3)
     peak, peak_src = measured_peak()
@@ -434,7 +452,7 @@ def main():
         "scaling": "strong" if (args.workload == "ppo" and args.B is None) else "weak",
         "vs_baseline": None, "dtype": "f32" if args.workload != "replay" else "u8", "data": "synthetic",
         "config": dict(w["desc"], parallelism="dp%d (rank-local batches sharded along B, no data-path collective)" % world_size,
-                       timing="CUDA graph of back-to-back steps, CUDA events on the launching stream, max over ranks"),
+                       streams=args.streams, timing="CUDA graph of back-to-back steps, CUDA events on the launching stream, max over ranks"),
         "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": recorded_traffic(args.workload), "peak_source": peak_src,
                      "algorithmic_bytes_per_step": bytes_per_unit * w["units"],

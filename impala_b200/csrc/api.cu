@@ -33,3 +33,4 @@ int env_int(const char *name, int dflt) {
 extern "C" int32_t b200rl_version(void) { return B200RL_VERSION; }
 extern "C" const char *b200rl_last_error(void) { return b200rl::g_err; }
 extern "C" int64_t b200rl_loss_workspace_bytes(void) { return b200rl::kWorkspaceBytes; }
+extern "C" int64_t b200rl_trace_offset_bytes(void) { return b200rl::kTraceOffset; }

@@ -20,10 +20,13 @@ int32_t check_launch(const char *what);
     } while (0)
 
 constexpr int kNumScalars = 8;
-// workspace layout: [0] uint32 ticket counter (self-resetting), pad to 256 B, then
-// per-CTA partial sums [kMaxPartialCtas][8] floats.
+// workspace layout: 256 B reserved, then the published partial sums, uint64 words [8][kMaxPartialCtas]
+// (tag << 32 | float bits), then the trace area.
 constexpr int kMaxPartialCtas = 16384;
-constexpr int64_t kWorkspaceBytes = 256 + (int64_t)kMaxPartialCtas * kNumScalars * 4;
+constexpr int64_t kTraceOffset = 256 + (int64_t)kMaxPartialCtas * kNumScalars * 8;
+// B200RL_TRACE: [kMaxTraceCtas][16] uint64 per CTA: 8 %globaltimer stamps then 8 clock64 stamps (profiling aid)
+constexpr int kMaxTraceCtas = 4096;
+constexpr int64_t kWorkspaceBytes = kTraceOffset + (int64_t)kMaxTraceCtas * 16 * 8;
 
 // ---------------------------------------------------------------- device: PTX
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -77,6 +80,12 @@ __device__ __forceinline__ void fence_proxy_async_smem() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
 
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 __device__ __forceinline__ float ld_stream_f32(const float *p) {
     float v;
     asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
@@ -103,64 +112,121 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
-// Deterministic grid-wide sum of NV per-thread values.  Every CTA writes its
-// partial to workspace, takes a ticket; the last CTA sums all partials in a fixed
-// order, hands them to `finalize(sums)` (thread 0) and resets the ticket.
-// `red` is shared scratch of at least NV * 32 floats.  All threads must call.
-template <int NV, typename Finalize>
+// Programmatic dependent launch (PDL).  Both are no-ops for a launch without the attribute.
+// pdl_launch_dependents: the next kernel in the stream may start being scheduled;
+// pdl_wait: blocks until every kernel this launch depends on has completed and flushed.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+// Deterministic CTA-wide sum of NV per-thread values.  `red` is shared scratch of
+// NV * blockDim.x floats.  Fixed summation order; totals are valid in warp 0 (all lanes).
+// Costs NV stores per thread plus one warp's column sums -- far fewer issue slots than a
+// shuffle tree in every warp.  All threads must call; ends with warp 0 only holding totals.
+template <int NV>
+__device__ __forceinline__ void cta_sum(const float (&vals)[NV], float *red, float (&tot)[NV]) {
+    const int nthr = blockDim.x;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) red[k * nthr + threadIdx.x] = vals[k];
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        // NV independent accumulators: all loads of a row of 32 are in flight together
+#pragma unroll
+        for (int k = 0; k < NV; ++k) tot[k] = 0.f;
+#pragma unroll 2
+        for (int i = threadIdx.x; i < nthr; i += 32) {
+#pragma unroll
+            for (int k = 0; k < NV; ++k) tot[k] += red[k * nthr + i];
+        }
+        // NV interleaved shuffle trees (step outermost: the NV chains hide each other's latency)
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int k = 0; k < NV; ++k) tot[k] += __shfl_xor_sync(0xffffffffu, tot[k], o);
+        }
+    }
+}
+
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u64(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// Deterministic grid-wide sum of NV per-thread values, without fences or atomics.
+//
+// Every CTA reduces its values (cta_sum) and PUBLISHES each partial sum as one 64-bit word
+// (valid tag << 32 | float bits) with a single store: the flag travels with the data, so no
+// fence is needed and the CTA retires immediately.  The CTA with the highest blockIdx -- the
+// last one the hardware dispatches, so every CTA it waits for is already resident or done --
+// collects the words in a fixed order, clears them for the next launch, and hands the totals
+// to `finalize(sums)` (one thread).  workspace: zero-initialised once; left zeroed.
+// `red`: shared scratch of NV * blockDim.x floats.  All threads must call.
+// `before_publish()` runs in every thread right before the workspace is touched (PDL wait).
+// A collector that sees no progress for kSpinLimitCycles gives up and reports NaN sums
+// instead of hanging the GPU.
+constexpr long long kSpinLimitCycles = 1ll << 31;
+
+template <int NV, typename Finalize, typename BeforePublish>
 __device__ __forceinline__ void grid_reduce(float (&vals)[NV], float *red, void *workspace,
-                                            Finalize finalize) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarps = (blockDim.x + 31) >> 5;
-    unsigned int *ticket = reinterpret_cast<unsigned int *>(workspace);
-    float *partials = reinterpret_cast<float *>(reinterpret_cast<char *>(workspace) + 256);
-    __shared__ bool is_last;
+                                            Finalize finalize, BeforePublish before_publish) {
+    static_assert(NV <= kNumScalars, "partials rows");
+    unsigned long long *words =
+        reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(workspace) + 256);
+    float tot[NV];
+    cta_sum<NV>(vals, red, tot);
+    before_publish();
+    const unsigned int n_other = gridDim.x - 1;
+    if (blockIdx.x != n_other) {
 #pragma unroll
-    for (int k = 0; k < NV; ++k) {
-        float s = warp_sum(vals[k]);
-        if (lane == 0) red[k * 32 + warp] = s;
+        for (int k = 0; k < NV; ++k)
+            if (threadIdx.x == k)
+                st_volatile_u64(&words[k * kMaxPartialCtas + blockIdx.x],
+                                (1ull << 32) | (unsigned long long)__float_as_uint(tot[k]));
+        return;
     }
-    __syncthreads();
-    if (warp == 0) {
-#pragma unroll
-        for (int k = 0; k < NV; ++k) {
-            float s = lane < nwarps ? red[k * 32 + lane] : 0.f;
-            s = warp_sum(s);
-            if (lane == 0) partials[(size_t)blockIdx.x * kNumScalars + k] = s;
-        }
-        if (lane == 0) {
-            __threadfence();
-            unsigned int t = atomicAdd(ticket, 1u);
-            is_last = (t == gridDim.x - 1);
-        }
-    }
-    __syncthreads();
-    if (!is_last) return;
-    __threadfence();
-    // fixed-order sum: thread i takes CTAs i, i+blockDim, ... then a block tree
+    // collector
+    constexpr int U = 4;
     float acc[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) acc[k] = 0.f;
-    for (unsigned int c = threadIdx.x; c < gridDim.x; c += blockDim.x) {
+    const long long t0 = clock64();
+    for (unsigned int c0 = threadIdx.x; c0 < n_other; c0 += U * blockDim.x) {
+        unsigned long long w[U][NV];
+        bool all;
+        do {
+            all = true;
 #pragma unroll
-        for (int k = 0; k < NV; ++k) acc[k] += __ldcg(&partials[(size_t)c * kNumScalars + k]);
-    }
+            for (int u = 0; u < U; ++u) {
+                const unsigned int c = c0 + u * blockDim.x;
 #pragma unroll
-    for (int k = 0; k < NV; ++k) {
-        float s = warp_sum(acc[k]);
-        if (lane == 0) red[k * 32 + warp] = s;
-    }
-    __syncthreads();
-    if (warp == 0) {
-        float tot[NV];
+                for (int k = 0; k < NV; ++k) {
+                    w[u][k] = c < n_other ? ld_volatile_u64(&words[k * kMaxPartialCtas + c]) : (1ull << 32);
+                    all = all && (w[u][k] >> 32) != 0ull;
+                }
+            }
+        } while (!all && clock64() - t0 < kSpinLimitCycles);
 #pragma unroll
-        for (int k = 0; k < NV; ++k) {
-            float s = lane < nwarps ? red[k * 32 + lane] : 0.f;
-            tot[k] = warp_sum(s);
+        for (int u = 0; u < U; ++u) {
+            const unsigned int c = c0 + u * blockDim.x;
+#pragma unroll
+            for (int k = 0; k < NV; ++k) {
+                acc[k] += all ? __uint_as_float((unsigned int)w[u][k]) : __int_as_float(0x7fc00000);
+                if (c < n_other) st_volatile_u64(&words[k * kMaxPartialCtas + c], 0ull);
+            }
         }
-        if (lane == 0) {
-            finalize(tot);
-            *ticket = 0u;  // leave the workspace ready for the next launch
-        }
+    }
+    float own[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) own[k] = tot[k];  // valid in warp 0
+    __syncthreads();  // warp 0 is done reading `red` from the first cta_sum
+    cta_sum<NV>(acc, red, tot);
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) tot[k] += own[k];
+        finalize(tot);
     }
 }
 

@@ -13,6 +13,8 @@
 
 namespace b200rl {
 
+constexpr int kWalkMaxT = 48;  // rollouts up to this length use the per-thread column walk
+
 struct ImpalaParams {
     const float *logits, *pi_ref, *rewards, *discounts, *values;
     const long long *actions;
@@ -23,17 +25,26 @@ struct ImpalaParams {
     uint32_t flags;
 };
 
-template <int AT>
-__global__ void __launch_bounds__(AT <= 16 ? 512 : 256) impala_loss_kernel(const ImpalaParams p) {
+template <int AT, bool EXACT>
+__global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(const ImpalaParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int T = p.T, A = p.A, C = p.C, NS = C * T;
-    float *sx = reinterpret_cast<float *>(smem_raw);  // [NS*A] logits -> dlogits
-    float *sy = sx + (size_t)NS * A;                  // [NS*A] behaviour logits
-    float *s_td = sy + (size_t)NS * A;                // [NS] clipped TD errors -> V-trace errors e_t
-    float *s_gc = s_td + NS;                          // [NS] discount * c
-    float *s_nx = s_gc + NS;                          // [NS] d loss/d v_{t+1} pushed by step t
-    float *red = s_nx + NS;                           // [5*32]
-    uint64_t *bar = reinterpret_cast<uint64_t *>(red + 5 * 32);
+    const int T = p.T, A = EXACT ? AT : p.A, C = p.C, NS = C * T;
+    float *sx = reinterpret_cast<float *>(smem_raw);    // [NS*A] logits -> dlogits
+    float *sy = sx + NS * A;                            // [NS*A] behaviour logits
+    float2 *s_tg = reinterpret_cast<float2 *>(sy + NS * A);  // [NS] (clipped TD error, discount * c)
+    float *s_e = reinterpret_cast<float *>(s_tg + NS);  // [NS] V-trace errors e_t
+    float *s_nx = s_e + NS;                             // [NS] d loss/d v_{t+1} pushed by step t
+    float *red = s_nx + NS;                             // [5*blockDim]
+    uint64_t *bar = reinterpret_cast<uint64_t *>(red + 5 * blockDim.x);
+
+    const bool trace = (p.flags & B200RL_TRACE) && threadIdx.x == 0 && blockIdx.x < kMaxTraceCtas;
+    unsigned long long *tr = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(p.workspace) + kTraceOffset) + blockIdx.x * 16;
+#define K1_STAMP(i) do { if (trace) { tr[i] = globaltimer_ns(); tr[8 + i] = (unsigned long long)clock64(); } } while (0)
+    K1_STAMP(0);
+    if (trace) { unsigned int smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid)); tr[7] = smid; }
+    pdl_launch_dependents();
+    const bool late_wait = p.flags & B200RL_INPUTS_STABLE;
+    if (!late_wait) pdl_wait();  // inputs may come from the preceding kernel
 
     const int b0 = blockIdx.x * C;
     const int cols = min(C, p.B - b0);
@@ -42,16 +53,16 @@ __global__ void __launch_bounds__(AT <= 16 ? 512 : 256) impala_loss_kernel(const
     if (p.time_major) { t = s / C; c = s - t * C; } else { c = s / T; t = s - c * T; }
     const bool valid = s < NS && c < cols;
     const int st_local = p.time_major ? C : 1;  // local index distance between t and t+1
-    const long long n = p.time_major ? (long long)t * p.B + b0 + c : (long long)(b0 + c) * T + t;
-    const long long n_stride_t = p.time_major ? p.B : 1;
+    const int n = p.time_major ? t * p.B + b0 + c : (b0 + c) * T + t;
+    const int n_stride_t = p.time_major ? p.B : 1;
 
     // ---- phase 1: stage the tile ------------------------------------------------------
-    const size_t row_elems = (size_t)(p.time_major ? cols : cols * T) * A;  // contiguous run
+    const int row_elems = (p.time_major ? cols : cols * T) * A;  // contiguous run
     const int nrows = p.time_major ? T : 1;
-    const size_t g_row0 = (size_t)(p.time_major ? b0 : (size_t)b0 * T) * A;
+    const size_t g_row0 = (size_t)(p.time_major ? b0 : b0 * T) * A;
     const size_t g_row_stride = (size_t)p.B * A;  // time-major only
-    const size_t s_row_stride = (size_t)C * A;    // time-major only
-    const uint32_t row_bytes = (uint32_t)(row_elems * 4);
+    const int s_row_stride = C * A;               // time-major only
+    const uint32_t row_bytes = (uint32_t)row_elems * 4u;
     const bool bulk_ok = (row_bytes % 16 == 0) && ((g_row0 * 4) % 16 == 0) &&
                          (nrows == 1 || ((g_row_stride * 4) % 16 == 0 && (s_row_stride * 4) % 16 == 0)) &&
                          ((reinterpret_cast<uintptr_t>(p.logits) | reinterpret_cast<uintptr_t>(p.pi_ref) |
@@ -68,7 +79,7 @@ __global__ void __launch_bounds__(AT <= 16 ? 512 : 256) impala_loss_kernel(const
         }
     } else {
         for (int r = 0; r < nrows; ++r)
-            for (size_t i = threadIdx.x; i < row_elems; i += blockDim.x) {
+            for (int i = threadIdx.x; i < row_elems; i += blockDim.x) {
                 sx[r * s_row_stride + i] = ld_stream_f32(p.logits + g_row0 + r * g_row_stride + i);
                 sy[r * s_row_stride + i] = ld_stream_f32(p.pi_ref + g_row0 + r * g_row_stride + i);
             }
@@ -77,25 +88,26 @@ __global__ void __launch_bounds__(AT <= 16 ? 512 : 256) impala_loss_kernel(const
     float rew = 0.f, disc = 0.f, v = 0.f, v_next = 0.f;
     const bool has_next = valid && t < T - 1;
     if (valid) {
-        act = p.actions[n];
-        rew = p.rewards[n];
-        disc = p.discounts[n];
-        v = p.values[n];
-        if (has_next) v_next = p.values[n + n_stride_t];
+        act = __ldg(p.actions + n);
+        rew = __ldg(p.rewards + n);
+        disc = __ldg(p.discounts + n);
+        v = __ldg(p.values + n);
+        if (has_next) v_next = __ldg(p.values + n + n_stride_t);
     }
     __syncthreads();  // mbarrier init visible / cooperative stores done
     if (bulk_ok) mbar_wait(bar, 0);
+    K1_STAMP(1);
 
     // ---- phase 2: per-sample softmax statistics, TD error, trace coefficient -----------
     SampleStats<AT> st;
     float c_pg = 0.f;
     const bool detach_adv = p.flags & B200RL_DETACH_ADV, detach_rho = p.flags & B200RL_DETACH_RHO;
     if (valid) {
-        sample_stats<AT>(st, sx + (size_t)s * A, sy + (size_t)s * A, A, act);
+        sample_stats<AT, EXACT>(st, sx + s * A, sy + s * A, A, act);
         c_pg = fminf(st.rho, p.clip_pg_rho);
         if (has_next) {
-            s_td[s] = fminf(st.rho, p.clip_rho) * (rew + disc * v_next - v);
-            s_gc[s] = disc * (fminf(st.rho, 1.0f) * p.lambda_);
+            s_tg[s] = make_float2(fminf(st.rho, p.clip_rho) * (rew + disc * v_next - v),
+                                  disc * (fminf(st.rho, 1.0f) * p.lambda_));
             // adv_t depends on v_{t+1} through the q bootstrap: weight 1 at the last step,
             // (1 - lambda) elsewhere (the lambda * vs_{t+1} part is a stop-gradient target)
             const float w = (t == T - 2) ? 1.f : p.one_minus_lambda;
@@ -103,31 +115,61 @@ __global__ void __launch_bounds__(AT <= 16 ? 512 : 256) impala_loss_kernel(const
         }
     }
     __syncthreads();
+    K1_STAMP(2);
 
-    // ---- phase 3: backward-in-time recursion, one register chain per column ------------
-    if (s < cols) {
-        const int sc_local = p.time_major ? 1 : T;
-        float e = 0.f;
-        int idx = s * sc_local + (T - 2) * st_local;
+    // ---- phase 3: backward-in-time recursion e_k = td_k + (discount_k c_k) e_{k+1} ----------
+    // Short rollouts (T <= kWalkMaxT): every thread walks its own column from the last step down
+    // to its step -- redundant O(T^2) FMAs per column, but no serial phase, no second barrier;
+    // the chain is the reference's operation order in every thread, so all agree bit for bit.
+    // Long rollouts: one register chain per column, steps fetched 8 at a time.
+    float e_t = 0.f, e_t1 = 0.f;  // e_t, e_{t+1} of this thread's sample
+    if (T <= kWalkMaxT) {
+        const float2 *col = s_tg + (valid ? (p.time_major ? c : c * T) : 0);
 #pragma unroll 4
-        for (int tt = T - 2; tt >= 0; --tt, idx -= st_local) {
-            e = s_td[idx] + s_gc[idx] * e;
-            s_td[idx] = e;
+        for (int k = T - 2; k >= 0; --k) {
+            const float2 q = col[k * st_local];
+            if (k >= t) {
+                e_t1 = e_t;
+                e_t = q.x + q.y * e_t;
+            }
+        }
+    } else {
+        if (s < cols) {
+            const int sc_local = p.time_major ? 1 : T;
+            float e = 0.f;
+            int idx = s * sc_local + (T - 2) * st_local;
+            for (int tt = T - 2; tt >= 0; tt -= 8, idx -= 8 * st_local) {
+                float2 q[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    if (k <= tt) q[k] = s_tg[idx - k * st_local];
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    if (k <= tt) {
+                        e = q[k].x + q[k].y * e;
+                        s_e[idx - k * st_local] = e;
+                    }
+            }
+        }
+        __syncthreads();
+        if (has_next) {
+            e_t = s_e[s];
+            if (t < T - 2) e_t1 = s_e[s + st_local];
         }
     }
-    __syncthreads();
+    K1_STAMP(3);
 
     // ---- phase 4: losses and gradients -------------------------------------------------
     float sums[5] = {0.f, 0.f, 0.f, 0.f, 0.f};  // pg, value, entropy, kl, ratio
     if (valid) {
         float g_lp = 0.f, dv = 0.f;
         if (has_next) {
-            const float e = s_td[s];
+            const float e = e_t;
             const float tgt = e + v;     // stop-gradient target vs_t
             const float err = tgt - v;   // rlego "errors"
             float qb = v_next;
             if (t < T - 2) {
-                const float e1 = s_td[s + st_local];
+                const float e1 = e_t1;
                 const float tgt1 = ((e1 + v_next) - v_next) + v_next;
                 qb = p.lambda_ * tgt1 + p.one_minus_lambda * v_next;
             }
@@ -147,10 +189,11 @@ __global__ void __launch_bounds__(AT <= 16 ? 512 : 256) impala_loss_kernel(const
         sums[2] = st.H;
         sums[3] = st.kl;
         sums[4] = st.rho;
-        write_dlogits<AT>(st, sx + (size_t)s * A, A, g_lp, p.entropy_coeff * p.inv_n_all);
+        write_dlogits<AT, EXACT>(st, sx + s * A, A, g_lp, p.entropy_coeff * p.inv_n_all);
     }
     if (bulk_ok) fence_proxy_async_smem();
     __syncthreads();
+    K1_STAMP(4);
     if (bulk_ok) {
         if (threadIdx.x == 0) {
             for (int r = 0; r < nrows; ++r)
@@ -159,25 +202,31 @@ __global__ void __launch_bounds__(AT <= 16 ? 512 : 256) impala_loss_kernel(const
         }
     } else {
         for (int r = 0; r < nrows; ++r)
-            for (size_t i = threadIdx.x; i < row_elems; i += blockDim.x)
+            for (int i = threadIdx.x; i < row_elems; i += blockDim.x)
                 p.dlogits[g_row0 + r * g_row_stride + i] = sx[r * s_row_stride + i];
     }
 
     // ---- scalars: deterministic grid reduction -----------------------------------------
     const float inv_n_pg = p.inv_n_pg, inv_n_all = p.inv_n_all, ec = p.entropy_coeff;
     float *scalars = p.scalars;
-    grid_reduce<5>(sums, red, p.workspace, [=](const float(&tot)[5]) {
-        const float pg = tot[0] * inv_n_pg, td = tot[1] * inv_n_pg, ent = tot[2] * inv_n_all;
-        scalars[B200RL_S_LOSS] = -pg + td - ec * ent;
-        scalars[B200RL_S_ENTROPY] = ent;
-        scalars[B200RL_S_TD] = td;
-        scalars[B200RL_S_PG] = pg;
-        scalars[B200RL_S_KL] = tot[3] * inv_n_all;
-        scalars[B200RL_S_RATIO] = tot[4] * inv_n_all;
-        scalars[6] = 0.f;
-        scalars[7] = 0.f;
-    });
+    grid_reduce<5>(
+        sums, red, p.workspace,
+        [=](const float(&tot)[5]) {
+            const float pg = tot[0] * inv_n_pg, td = tot[1] * inv_n_pg, ent = tot[2] * inv_n_all;
+            scalars[B200RL_S_LOSS] = -pg + td - ec * ent;
+            scalars[B200RL_S_ENTROPY] = ent;
+            scalars[B200RL_S_TD] = td;
+            scalars[B200RL_S_PG] = pg;
+            scalars[B200RL_S_KL] = tot[3] * inv_n_all;
+            scalars[B200RL_S_RATIO] = tot[4] * inv_n_all;
+            scalars[6] = 0.f;
+            scalars[7] = 0.f;
+        },
+        [=]() { if (late_wait) pdl_wait(); });  // the workspace and scalars are shared with the previous launch
+    K1_STAMP(5);
     if (bulk_ok && threadIdx.x == 0) bulk_wait_read0();  // smem must outlive the bulk store's reads
+    K1_STAMP(6);
+#undef K1_STAMP
 }
 
 }  // namespace b200rl
@@ -187,19 +236,33 @@ namespace b200rl {
 
 int env_int(const char *name, int dflt);
 
-template <int AT>
+template <int AT, bool EXACT>
 static int32_t launch_impala(const ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
     static size_t configured = 48 * 1024;  // dynamic shared memory already opted in to
     if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(impala_loss_kernel<AT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(impala_loss_kernel<AT, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) {
             set_error("cudaFuncSetAttribute(%zu B shared): %s", smem, cudaGetErrorString(e));
             return (int32_t)e;
         }
         configured = smem;
     }
-    const int grid = (p.B + p.C - 1) / p.C;
-    impala_loss_kernel<AT><<<grid, threads, smem, stream>>>(p);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((p.B + p.C - 1) / p.C));
+    cfg.blockDim = dim3((unsigned)threads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // PDL: see pdl_wait() in the kernel
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = env_int("B200RL_PDL", 1) ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, impala_loss_kernel<AT, EXACT>, p);
+    if (e != cudaSuccess) {
+        set_error("impala_loss_kernel launch: %s", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return (int32_t)e;
+    }
     return check_launch("impala_loss_kernel");
 }
 
@@ -217,7 +280,7 @@ extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
     B200RL_REQUIRE(B >= 1 && T >= 2 && A >= 1, -2, "impala_loss: need B>=1, T>=2, A>=1 (got B=%lld T=%lld A=%lld)",
                    (long long)B, (long long)T, (long long)A);
     B200RL_REQUIRE(A <= 32, -3, "impala_loss: A=%lld > 32 actions not supported", (long long)A);
-    const int max_threads = A <= 16 ? 512 : 256;  // == __launch_bounds__ of the instantiation
+    const int max_threads = A <= 16 ? 640 : 256;  // == __launch_bounds__ of the instantiation
     B200RL_REQUIRE(T <= max_threads, -3, "impala_loss: T=%lld > %d steps not supported at A=%lld",
                    (long long)T, max_threads, (long long)A);
     B200RL_REQUIRE(B * T < (1ll << 31), -3, "impala_loss: B*T too large");
@@ -239,24 +302,30 @@ extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
     p.inv_n_all = (float)(1.0 / ((double)n_global_b * (double)T));
     p.flags = flags;
 
-    // columns per CTA: ~160-192 samples, a multiple of 4 so time-major rows stay 16-byte aligned
-    int target = env_int("B200RL_K1_SAMPLES", 192);
+    // columns per CTA: a multiple of 4 so time-major rows stay 16-byte aligned
+    int target = env_int("B200RL_K1_SAMPLES", 160);
     int C = (int)(target / T);
-    if (C >= 4) C &= ~3;
+    if (C >= 4 && time_major && !batch_major) C &= ~3;
     if (C < 1) C = 1;
     if (C > B) C = (int)B;
     while (C > 1 && C * T > max_threads) C = (C > 4) ? ((C - 1) & ~3) : C - 1;
-    const int a_tile = A <= 8 ? 8 : (A <= 16 ? 16 : 32);
-    auto smem_for = [&](int c) { return (size_t)c * T * (2 * A + 3) * 4 + 5 * 32 * 4 + 16; };
+    auto threads_for = [&](int c) { return ((c * (int)T + 31) / 32) * 32; };
+    auto smem_for = [&](int c) { return (size_t)c * T * (2 * A + 4) * 4 + 5 * (size_t)threads_for(c) * 4 + 16; };
     while (C > 1 && smem_for(C) > 200 * 1024) C = (C > 4) ? ((C / 2) & ~3) : C - 1;
     B200RL_REQUIRE(smem_for(C) <= 226 * 1024, -3, "impala_loss: T*A too large for one CTA tile");
     B200RL_REQUIRE((B + C - 1) / C <= kMaxPartialCtas, -3, "impala_loss: B too large for the partials workspace");
     p.C = C;
-    const int threads = ((C * (int)T + 31) / 32) * 32;
+    const int threads = threads_for(C);
+    const size_t smem = smem_for(C);
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    switch (a_tile) {
-        case 8: return launch_impala<8>(p, threads, smem_for(C), s);
-        case 16: return launch_impala<16>(p, threads, smem_for(C), s);
-        default: return launch_impala<32>(p, threads, smem_for(C), s);
+    switch (A) {  // exact-A instantiations (no padding predicates) for the common action spaces
+        case 4: return launch_impala<4, true>(p, threads, smem, s);
+        case 6: return launch_impala<6, true>(p, threads, smem, s);
+        case 15: return launch_impala<15, true>(p, threads, smem, s);
+        case 18: return launch_impala<18, true>(p, threads, smem, s);
+        default: break;
     }
+    if (A <= 8) return launch_impala<8, false>(p, threads, smem, s);
+    if (A <= 16) return launch_impala<16, false>(p, threads, smem, s);
+    return launch_impala<32, false>(p, threads, smem, s);
 }

@@ -20,16 +20,22 @@ struct PpoParams {
     long long N;
     int A;
     float clip_coeff, entropy_cost, inv_n;
+    uint32_t flags;
 };
 
-template <int AT>
+template <int AT, bool EXACT>
 __global__ void __launch_bounds__(kPpoTile) ppo_loss_kernel(const PpoParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int A = p.A;
+    const int A = EXACT ? AT : p.A;
     float *sx = reinterpret_cast<float *>(smem_raw);
     float *sy = sx + (size_t)kPpoTile * A;
-    float *red = sy + (size_t)kPpoTile * A;  // [6*32]
-    uint64_t *bar = reinterpret_cast<uint64_t *>(red + 6 * 32);
+    float *red = sy + (size_t)kPpoTile * A;  // [6*kPpoTile]
+    uint64_t *bar = reinterpret_cast<uint64_t *>(red + 6 * kPpoTile);
+
+    pdl_launch_dependents();
+    const bool late_wait = p.flags & B200RL_INPUTS_STABLE;
+    if (!late_wait) pdl_wait();  // inputs may come from the preceding kernel
+
 
     const long long n0 = (long long)blockIdx.x * kPpoTile;
     const int count = (int)min((long long)kPpoTile, p.N - n0);
@@ -67,7 +73,7 @@ __global__ void __launch_bounds__(kPpoTile) ppo_loss_kernel(const PpoParams p) {
     float sums[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};  // pg, td, entropy, kl, ratio, target
     if (valid) {
         SampleStats<AT> st;
-        sample_stats<AT>(st, sx + (size_t)s * A, sy + (size_t)s * A, A, act);
+        sample_stats<AT, EXACT>(st, sx + s * A, sy + s * A, A, act);
         const float ratio = st.rho;
         const float adv = vt - v;                                   // losses.py:137
         const float lo = 1.f - p.clip_coeff, hi = 1.f + p.clip_coeff;
@@ -85,7 +91,7 @@ __global__ void __launch_bounds__(kPpoTile) ppo_loss_kernel(const PpoParams p) {
         const float g_ratio = (inside || pg1 > pg2) ? -adv : 0.f;
         const float g_lp = g_ratio * ratio * p.inv_n;               // d ratio / d lp = ratio
         p.dv[n0 + s] = -adv * p.inv_n;                              // d(0.5 adv^2)/dv, adv detached in pg
-        write_dlogits<AT>(st, sx + (size_t)s * A, A, g_lp, p.entropy_cost * p.inv_n);
+        write_dlogits<AT, EXACT>(st, sx + s * A, A, g_lp, p.entropy_cost * p.inv_n);
     }
     if (bulk_ok) fence_proxy_async_smem();
     __syncthreads();
@@ -109,23 +115,39 @@ __global__ void __launch_bounds__(kPpoTile) ppo_loss_kernel(const PpoParams p) {
         scalars[B200RL_S_RATIO] = tot[4] * inv_n;
         scalars[B200RL_S_TARGET] = tot[5] * inv_n;
         scalars[7] = 0.f;
-    });
+    }, [=]() { if (late_wait) pdl_wait(); });
     if (bulk_ok && threadIdx.x == 0) bulk_wait_read0();
 }
 
-template <int AT>
+int env_int(const char *name, int dflt);
+
+template <int AT, bool EXACT>
 static int32_t launch_ppo(const PpoParams &p, size_t smem, cudaStream_t stream) {
     static size_t configured = 48 * 1024;  // dynamic shared memory already opted in to
     if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(ppo_loss_kernel<AT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(ppo_loss_kernel<AT, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) {
             set_error("cudaFuncSetAttribute(%zu B shared): %s", smem, cudaGetErrorString(e));
             return (int32_t)e;
         }
         configured = smem;
     }
-    const unsigned grid = (unsigned)((p.N + kPpoTile - 1) / kPpoTile);
-    ppo_loss_kernel<AT><<<grid, kPpoTile, smem, stream>>>(p);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)((p.N + kPpoTile - 1) / kPpoTile));
+    cfg.blockDim = dim3(kPpoTile);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // PDL: see pdl_wait() in the kernel
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = env_int("B200RL_PDL", 1) ? 1 : 0;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, ppo_loss_kernel<AT, EXACT>, p);
+    if (e != cudaSuccess) {
+        set_error("ppo_loss_kernel launch: %s", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return (int32_t)e;
+    }
     return check_launch("ppo_loss_kernel");
 }
 
@@ -137,7 +159,6 @@ extern "C" int32_t b200rl_ppo_loss_fwdbwd(const float *logits, const float *pi_r
                                           uint32_t flags, float *dlogits, float *dv, float *scalars,
                                           void *workspace, void *stream) {
     using namespace b200rl;
-    (void)flags;
     B200RL_REQUIRE(logits && pi_ref && actions && v_target && v && dlogits && dv && scalars && workspace, -1,
                    "ppo_loss: null pointer argument");
     B200RL_REQUIRE(N >= 1 && A >= 1, -2, "ppo_loss: need N>=1, A>=1 (got N=%lld A=%lld)", (long long)N, (long long)A);
@@ -152,9 +173,17 @@ extern "C" int32_t b200rl_ppo_loss_fwdbwd(const float *logits, const float *pi_r
     p.dlogits = dlogits; p.dv = dv; p.scalars = scalars; p.workspace = workspace;
     p.N = N; p.A = (int)A; p.clip_coeff = clip_coeff; p.entropy_cost = entropy_cost;
     p.inv_n = (float)(1.0 / (double)n_global);
-    const size_t smem = (size_t)kPpoTile * A * 8 + 6 * 32 * 4 + 16;
+    p.flags = flags;
+    const size_t smem = (size_t)kPpoTile * A * 8 + 6 * kPpoTile * 4 + 16;
     cudaStream_t s = (cudaStream_t)stream;
-    if (A <= 8) return launch_ppo<8>(p, smem, s);
-    if (A <= 16) return launch_ppo<16>(p, smem, s);
-    return launch_ppo<32>(p, smem, s);
+    switch (A) {
+        case 4: return launch_ppo<4, true>(p, smem, s);
+        case 6: return launch_ppo<6, true>(p, smem, s);
+        case 15: return launch_ppo<15, true>(p, smem, s);
+        case 18: return launch_ppo<18, true>(p, smem, s);
+        default: break;
+    }
+    if (A <= 8) return launch_ppo<8, false>(p, smem, s);
+    if (A <= 16) return launch_ppo<16, false>(p, smem, s);
+    return launch_ppo<32, false>(p, smem, s);
 }

@@ -3,7 +3,7 @@ import torch
 
 from . import _cabi
 
-DETACH_ADV, DETACH_RHO, ORDER_RLAX = 1, 2, 4
+DETACH_ADV, DETACH_RHO, ORDER_RLAX, INPUTS_STABLE, TRACE = 1, 2, 4, 8, 0x80000000
 S_LOSS, S_ENTROPY, S_TD, S_PG, S_KL, S_RATIO, S_TARGET = range(7)
 
 _workspaces = {}

@@ -34,6 +34,19 @@ extern "C" {
 #define B200RL_DETACH_ADV 1u  /* treat pg advantages as constants (textbook IMPALA); reference: not detached, learning.py:155 */
 #define B200RL_DETACH_RHO 2u  /* treat rho as a constant inside V-trace; reference: not detached, learning.py:148 */
 #define B200RL_ORDER_RLAX 4u  /* b200rl_vtrace output order (errors, pg_adv, q) instead of call-site (pg_adv, errors, q) */
+/* Fused losses are launched with programmatic dependent launch (PDL).  By default the kernel waits
+ * for the preceding kernel of the stream before it reads anything.  With B200RL_INPUTS_STABLE the
+ * caller promises that NO buffer of this call except `workspace` and `scalars` is written or read by
+ * the immediately preceding kernel of the stream (e.g. a pipeline over independent rollout batches):
+ * loads, arithmetic and gradient stores then overlap the previous launch's tail and only the
+ * scalar reduction waits. */
+#define B200RL_INPUTS_STABLE 8u
+/* Profiling aid (K1): thread 0 of every CTA < 4096 stamps %globaltimer (ns) at 7 phase boundaries into
+ * workspace + b200rl_trace_offset_bytes(), layout uint64 [cta][16] (slots 0-7 %globaltimer, 8-15 clock64 of the same points;
+ * slot 7/15 = %smid):
+ * 0 start, 1 tile landed in shared memory, 2 softmax statistics done, 3 V-trace recursion done,
+ * 4 gradients written to shared memory, 5 scalar reduction done, 6 bulk store drained from shared memory. */
+#define B200RL_TRACE 0x80000000u
 
 /* slots of the float[8] `scalars` output of the fused losses */
 #define B200RL_S_LOSS 0
@@ -50,6 +63,7 @@ const char *b200rl_last_error(void);
 /* Bytes of zero-initialised device workspace the fused losses need (zero it ONCE;
  * every launch leaves it zeroed again). */
 int64_t b200rl_loss_workspace_bytes(void);
+int64_t b200rl_trace_offset_bytes(void);
 
 /* K1 -- replaces ImpalaLearner._train_step's loss + backward w.r.t. model outputs
  * (reference agents/impala/learning.py:146-160,167-168) and, inside it,

@@ -1,0 +1,48 @@
+"""Per-CTA phase timeline of K1 (B200RL_TRACE): prints where a launch's time goes.  Run on a GPU box."""
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+import torch
+from impala_b200 import ops, synth, _cabi
+
+B, T, A = 4096, 20, 15
+dev = torch.device("cuda", 0)
+sets = []
+for i in range(24):
+    d = synth.impala_rollout(B, T, A, seed=100 + i)
+    g = {k: v.to(dev) for k, v in d.items()}
+    sets.append((g, (torch.empty(8, device=dev), torch.empty_like(g["logits"]), torch.empty_like(g["values"]))))
+off = _cabi.load().b200rl_trace_offset_bytes()
+flags_list = {"serial": ops.TRACE, "independent": ops.TRACE | ops.INPUTS_STABLE}
+names = ["start", "landed", "stats", "scan", "grads", "reduce", "drained"]
+for mode, flags in flags_list.items():
+    def launch(i):
+        g, out = sets[i % len(sets)]
+        ops.impala_loss_fwdbwd(g["logits"], g["values"], g["a"], g["r"], g["discount"], g["pi_ref"], flags=flags, out=out)
+    for i in range(5):
+        launch(i)
+    torch.cuda.synchronize()
+    gr = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(gr):
+        for i in range(20):
+            launch(i)
+    gr.replay(); torch.cuda.synchronize()
+    for w in ops._workspaces.values():
+        w[off:].zero_()
+    torch.cuda.synchronize()
+    gr.replay(); torch.cuda.synchronize()
+    ws = [w for w in ops._workspaces.values() if int(w[off:off + 8].view(torch.int64).item()) > 0][0]
+    tr = ws[off:].view(torch.int64).cpu().numpy().reshape(-1, 16)
+    ncta = int((tr[:, 0] > 0).sum())
+    tr = tr[:ncta]
+    gt, ck, sm = tr[:, :7].astype(np.float64), tr[:, 8:15].astype(np.float64), tr[:, 7]
+    t0 = gt[:, 0].min()
+    print("== %s: last launch of a 20-launch graph, %d CTAs on %d SMs" % (mode, ncta, len(set(sm.tolist()))))
+    print("globaltimer (ns since first CTA start): phase  min  median  max")
+    for i, n in enumerate(names):
+        x = gt[:, i] - t0
+        print("  %-8s %8.0f %8.0f %8.0f" % (n, x.min(), np.median(x), x.max()))
+    print("clock64 deltas per CTA (cycles): phase  min  median  max")
+    for i in range(1, 7):
+        x = ck[:, i] - ck[:, i - 1]
+        print("  %-8s %8.0f %8.0f %8.0f" % (names[i], x.min(), np.median(x), x.max()))
