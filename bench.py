@@ -29,7 +29,20 @@ WORKLOADS = {
     "impala_loss": ("learner samples/sec (TxB), fused V-trace + IMPALA loss fwd+bwd", "samples/s", 204),
     "ppo": ("learner samples/sec (TxB), GAE/lambda-return scan + fused PPO loss fwd+bwd", "samples/s", 216),
     "replay": ("replay transitions/sec, uniform sample + gather of 64x64x3 u8 rows", "transitions/s", 24584),
+    # BASELINE config 5: no HBM-roofline claim (the CNN is compute-bound in cuDNN)
+    "learner": ("learner samples/sec (TxB), full IMPALA learner step (replay gather + IMPALA-CNN fwd/bwd + fused "
+                "V-trace loss + grad allreduce + clip + Adam)", "samples/s", None),
 }
+
+
+WORKLOAD_NAMES = {
+    "impala_loss": "IMPALA V-trace + fused loss fwd+bwd (BASELINE config 2)",
+    "ppo": "PPO lambda-return scan + clipped-surrogate loss fwd+bwd (BASELINE config 3 shard)",
+    "replay": "replay uniform sample + gather (BASELINE config 4)",
+    "learner": "full IMPALA learner step (BASELINE config 5)",
+}
+DEFAULT_T = {"impala_loss": 20, "ppo": 256, "replay": 1, "learner": 20}
+DEFAULT_B = {"impala_loss": 4096, "ppo": 8192, "replay": 1_000_000, "learner": 256}
 
 
 def parse_args():
@@ -230,7 +243,46 @@ def make_replay(args, device, seed):
                 check=lambda: idxs[0], state=state)
 
 
-MAKERS = {"impala_loss": make_impala_loss, "ppo": make_ppo, "replay": make_replay}
+def make_learner(args, device, seed):
+    """BASELINE config 5: the whole learner step through the drop-in ImpalaLearner -- device replay (K4/K5),
+    IMPALA-CNN (630,352 params, cuDNN), K1, ONE NCCL allreduce of the flat gradient bucket (+ scalars), clip, Adam.
+    B=256 rollouts of T=20 per GPU; buffer of 1000 rollouts (reference replay_buffer_size)."""
+    from impala_b200 import models, replay
+    from impala_b200.agents.impala import ImpalaLearner
+    B, T, A = args.B or 256, args.T or 20, args.A
+    torch.manual_seed(seed)
+    model = models.ActorCritic((3, 64, 64), A, body="impala").to(device)
+    if dist.is_initialized():                      # same initial weights on every rank
+        for p in model.parameters():
+            dist.broadcast(p.data, 0)
+    cap = 1000
+    rb = replay.ReplayBuffer(replay.CircularBuffer(cap, device=device), replay.UniformSampler(stream_id=seed % 997))
+    rb.sampler.reset(123)
+    g = torch.Generator(device=device).manual_seed(seed)
+    for lo in range(0, cap, 100):
+        n = min(100, cap - lo)
+        rb.extend((torch.randint(0, 256, (n, T, 3, 64, 64), generator=g, device=device, dtype=torch.uint8),
+                   torch.randint(0, A, (n, T, 1), generator=g, device=device),
+                   torch.randn(n, T, 1, generator=g, device=device).clamp_(-10, 10),
+                   (torch.rand(n, T, 1, generator=g, device=device) > .02).float() * .99,
+                   torch.randn(n, T, A, generator=g, device=device)))
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4, eps=1e-5)     # agents/impala/builder.py:43-44
+    learner = ImpalaLearner(model, rb, opt, batch_size=B, learning_starts=cap)
+    learner.prepare()
+    last = {}
+
+    def launch(i):
+        last["m"] = learner.train_step()
+
+    desc = {"workload": "full IMPALA learner step (BASELINE config 5)", "T": T, "B_per_gpu": B, "A": A,
+            "model": "IMPALA-CNN body + actor-critic head, 630,352 params, fp32 (cuDNN)",
+            "replay": "%d rollouts device-resident (%.0f MB u8), uniform sample + gather on device" % (cap, cap * T * 12288 / 1e6),
+            "l2_policy": "gathered batch 63 MB + activations >> per-step reuse; buffer 246 MB > 126 MB L2"}
+    return dict(launch=launch, units=B * T, kernels=5, host=None, e2e_step=None, desc=desc, graph=False,
+                check=lambda: last["m"]["train/loss"])
+
+
+MAKERS = {"impala_loss": make_impala_loss, "ppo": make_ppo, "replay": make_replay, "learner": make_learner}
 
 
 # --------------------------------------------------------------------------------------------
@@ -244,6 +296,11 @@ def build_graphs(launch, steps, stream, n_streams=1):
     so the timed region is back-to-back kernels, not Python/ctypes launch latency.  With n_streams > 1 step i
     is issued on side stream i % n_streams (fork/join inside the graph): independent steps may overlap."""
     side = [torch.cuda.Stream(stream.device) for _ in range(n_streams)] if n_streams > 1 else []
+    from impala_b200 import ops
+    for s_ in side:                                   # per-stream loss workspaces must exist before capture
+        with torch.cuda.stream(s_):
+            ops.workspace(stream.device)
+    torch.cuda.synchronize()
     plan, i = [], 0
     while i < steps:
         n = min(GRAPH_CHUNK, steps - i)
@@ -262,6 +319,28 @@ def build_graphs(launch, steps, stream, n_streams=1):
         plan.append(g)
         i += n
     return plan
+
+
+def time_eager(launch, steps, warmup, device, world_size):
+    """Eager (no graph) variant for the full learner step: Python drives optimizer / NCCL, timed with CUDA events."""
+    for i in range(max(warmup, 3)):
+        launch(i)
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world_size > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    with ClockSampler(device.index) as clk:
+        start.record()
+        for i in range(steps):
+            launch(i)
+        stop.record()
+        stop.synchronize()
+    torch.cuda.synchronize()
+    ms = torch.tensor([start.elapsed_time(stop)], dtype=torch.float64, device=device)
+    if world_size > 1:
+        dist.barrier()
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    return float(ms.item()), clk.summary()
 
 
 def time_device(launch, steps, warmup, device, world_size, n_streams=1):
@@ -364,6 +443,26 @@ def cpu_step_fn(args, B):
             loss.backward()
             return loss
         return step, B * T
+    if args.workload == "learner":
+        # the reference's whole step on the CPU (agents/impala/learning.py:140-177): host batch -> CNN -> loss -> Adam
+        from impala_b200 import models
+        T, A = args.T or 20, args.A
+        torch.manual_seed(0)
+        model = models.ActorCritic((3, 64, 64), A, body="impala")
+        opt = torch.optim.Adam(model.parameters(), lr=1e-4, eps=1e-5)
+        d = synth.impala_rollout(B, T, A, seed=5000)
+        obs = torch.randint(0, 256, (B, T, 3, 64, 64), dtype=torch.uint8)
+
+        def step():
+            opt.zero_grad(set_to_none=True)
+            pi, v = model(obs.flatten(0, 1))
+            loss, _ = losses_ref.impala_train_loss(pi.reshape(B, T, -1), v.reshape(B, T), d["a"], d["r"],
+                                                   d["discount"], d["pi_ref"])
+            loss.backward()
+            torch.nn.utils.clip_grad_norm_(model.parameters(), 0.5)
+            opt.step()
+            return loss
+        return step, B * T
     # replay: rlmeta-shaped host path -- draw indices, index the host storage, collate, (no H2D counted)
     cap = min(args.B or 1_000_000, 100_000)
     store = torch.randint(0, 256, (cap, 3, 64, 64), dtype=torch.uint8)
@@ -376,7 +475,7 @@ def cpu_step_fn(args, B):
 
 def time_cpu(args, seconds, steps=None, warmup=2):
     torch.set_num_threads(os.cpu_count() or 1)
-    full_B = {"impala_loss": args.B or 4096, "ppo": args.B or 8192, "replay": 4096}[args.workload]
+    full_B = {"impala_loss": args.B or 4096, "ppo": args.B or 8192, "replay": 4096, "learner": args.B or 256}[args.workload]
     step, units = cpu_step_fn(args, full_B)
     t0 = time.perf_counter()
     step()
@@ -413,7 +512,10 @@ def run_reference(args, rank, world_size):
         "impl": "reference", "metric": metric, "value": r["value"], "unit": unit, "n_gpus": args.gpus,
         "steps": r["steps"], "warmup": min(warmup, 5), "ms_per_step": 1e3 * r["seconds"] / r["steps"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "sample": r["sample"]},
+        "config": {"workload": WORKLOAD_NAMES[args.workload], "T": args.T or DEFAULT_T[args.workload], "A": args.A,
+                   "B_per_gpu": args.B or DEFAULT_B[args.workload], "sample": r["sample"],
+                   "note": "reference CPU path = oracle port of the reference's torch code (the reference itself is "
+                           "not importable: rlego/rlmeta/moolib absent and unpinned, DESIGN.md sec 2)"},
         "cpu_baseline": {"value": r["value"], "unit": unit, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
         "e2e": {"value": r["value"], "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -436,24 +538,27 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=device)
     metric, unit, bytes_per_unit = WORKLOADS[args.workload]
-    steps = args.steps if args.steps is not None else {"impala_loss": 20000, "ppo": 2000, "replay": 4000}[args.workload]
+    steps = args.steps if args.steps is not None else {"impala_loss": 20000, "ppo": 2000, "replay": 4000, "learner": 50}[args.workload]
     warmup = args.warmup if args.warmup is not None else 50
     args.gpus = world_size if world_size > 1 else args.gpus
 
     w = MAKERS[args.workload](args, device, seed=2000 + 1000 * rank)
-    ms, clocks = time_device(w["launch"], steps, warmup, device, world_size, args.streams)
+    if w.get("graph", True):
+        ms, clocks = time_device(w["launch"], steps, warmup, device, world_size, args.streams)
+    else:
+        ms, clocks = time_eager(w["launch"], steps, warmup, device, world_size)
     units_total = w["units"] * steps * world_size
     value = units_total / (ms * 1e-3)
     peak, peak_src = measured_peak()
-    achieved = bytes_per_unit * w["units"] * steps / (ms * 1e-3) / 1e9     # per GPU, GB/s
+    achieved = (bytes_per_unit or 0) * w["units"] * steps / (ms * 1e-3) / 1e9     # per GPU, GB/s
     line = {
         "metric": metric, "value": value, "unit": unit, "n_gpus": world_size, "steps": steps, "warmup": max(warmup, 3),
         "ms_per_step": ms / steps, "higher_is_better": True,
         "scaling": "strong" if (args.workload == "ppo" and args.B is None) else "weak",
-        "vs_baseline": None, "dtype": "f32" if args.workload != "replay" else "u8", "data": "synthetic",
+        "vs_baseline": None, "dtype": "u8" if args.workload == "replay" else "f32", "data": "synthetic",
         "config": dict(w["desc"], parallelism="dp%d (rank-local batches sharded along B, no data-path collective)" % world_size,
                        streams=args.streams, timing="CUDA graph of back-to-back steps, CUDA events on the launching stream, max over ranks"),
-        "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        "roofline": None if bytes_per_unit is None else {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": recorded_traffic(args.workload), "peak_source": peak_src,
                      "algorithmic_bytes_per_step": bytes_per_unit * w["units"],
                      "note": "per GPU; duration = timed region / steps (launch gaps included)"},

@@ -24,6 +24,10 @@ def workspace(device):
     key = (device.index if device.index is not None else torch.cuda.current_device(), _stream())
     ws = _workspaces.get(key)
     if ws is None:
+        if torch.cuda.is_current_stream_capturing():
+            raise RuntimeError("impala_b200: the loss workspace of this stream must exist before CUDA-graph capture "
+                               "(call ops.workspace(device) on the capture stream first); allocating it inside the "
+                               "capture would tie it to the graph's private memory pool")
         n = _cabi.load().b200rl_loss_workspace_bytes()
         ws = torch.zeros(n, dtype=torch.uint8, device=device)
         _workspaces[key] = ws
