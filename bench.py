@@ -247,7 +247,7 @@ def make_learner(args, device, seed):
     """BASELINE config 5: the whole learner step through the drop-in ImpalaLearner -- device replay (K4/K5),
     IMPALA-CNN (630,352 params, cuDNN), K1, ONE NCCL allreduce of the flat gradient bucket (+ scalars), clip, Adam.
     B=256 rollouts of T=20 per GPU; buffer of 1000 rollouts (reference replay_buffer_size)."""
-    from impala_b200 import models, replay
+    from impala_b200 import models, optim, replay
     from impala_b200.agents.impala import ImpalaLearner
     B, T, A = args.B or 256, args.T or 20, args.A
     torch.manual_seed(seed)
@@ -266,7 +266,7 @@ def make_learner(args, device, seed):
                    torch.randn(n, T, 1, generator=g, device=device).clamp_(-10, 10),
                    (torch.rand(n, T, 1, generator=g, device=device) > .02).float() * .99,
                    torch.randn(n, T, A, generator=g, device=device)))
-    opt = torch.optim.Adam(model.parameters(), lr=1e-4, eps=1e-5)     # agents/impala/builder.py:43-44
+    opt = optim.FusedClipAdam(model.parameters(), lr=1e-4, eps=1e-5)   # agents/impala/builder.py:43-44, fused with the clip (K6)
     learner = ImpalaLearner(model, rb, opt, batch_size=B, learning_starts=cap)
     learner.prepare()
     last = {}

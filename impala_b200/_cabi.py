@@ -29,6 +29,7 @@ SIGNATURES = {
     "b200rl_sample_uniform": (_i32, [_u64, _u32, _u64, _i64, _i64, _vp, _vp]),
     "b200rl_gather_rows": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _vp]),
     "b200rl_ring_append": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp]),
+    "b200rl_clip_adam_step": (_i32, [_vp] * 4 + [_i64, _f] + [_d] * 4 + [_i64] + [_vp] * 3),
 }
 
 

@@ -4,7 +4,7 @@ from typing import Dict, Optional
 
 import torch
 
-from .. import ops, parallel
+from .. import ops, optim, parallel
 
 
 def make_discount(done: torch.Tensor, gamma: float = 0.99) -> torch.Tensor:
@@ -76,6 +76,9 @@ class ImpalaLearner:
     def _train_step(self, batch) -> Dict[str, torch.Tensor]:
         if self._bucket is None:
             self._bucket = parallel.GradBucket(self._model.parameters())
+            if isinstance(self._optimizer, optim.FusedClipAdam) and \
+                    [id(q) for q in self._bucket.params] != [id(q) for q in self._optimizer.params]:
+                raise RuntimeError("FusedClipAdam must be built from model.parameters() (same order as the gradient bucket)")
         bucket = self._bucket
         bucket.attach()                                                   # == zero_grad (:141)
         s, a, r, discount_t, pi_ref = self._collate(batch)
@@ -92,8 +95,11 @@ class ImpalaLearner:
         torch.autograd.backward([pi, values], [dlogits, dvalues])
         bucket.extra.copy_(scalars)
         bucket.allreduce(self._group)                                     # grads + scalars, one collective
-        grad_norm = bucket.clip_(self._max_grad_norm)                     # :172-173
-        self._optimizer.step()                                            # :176
+        if isinstance(self._optimizer, optim.FusedClipAdam):               # :172-176 in one launch (K6)
+            grad_norm = self._optimizer.step_flat(bucket.grads, self._max_grad_norm)[0]
+        else:
+            grad_norm = bucket.clip_(self._max_grad_norm)                     # :172-173
+            self._optimizer.step()                                            # :176
         sc = bucket.extra
         return {
             "train/loss": sc[ops.S_LOSS], "train/entropy": sc[ops.S_ENTROPY], "train/td": sc[ops.S_TD],

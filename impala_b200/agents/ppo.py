@@ -5,7 +5,7 @@ from typing import Dict, Optional
 
 import torch
 
-from .. import ops, parallel, vtrace
+from .. import ops, optim, parallel, vtrace
 
 
 def make_targets(r, done, v, gamma: float = 0.99, lambda_: float = 0.95, time_major: bool = False):
@@ -70,6 +70,9 @@ class PPOLearner:
     def _train_step(self, batch) -> Dict[str, torch.Tensor]:
         if self._bucket is None:
             self._bucket = parallel.GradBucket(self._model.parameters())
+            if isinstance(self._optimizer, optim.FusedClipAdam) and \
+                    [id(q) for q in self._bucket.params] != [id(q) for q in self._optimizer.params]:
+                raise RuntimeError("FusedClipAdam must be built from model.parameters() (same order as the gradient bucket)")
         bucket = self._bucket
         bucket.attach()
         dev = self.device()
@@ -82,8 +85,11 @@ class PPOLearner:
         torch.autograd.backward([pi, v], [dlogits, dv.view_as(v)])        # :134
         bucket.extra.copy_(scalars)
         bucket.allreduce(self._group)
-        grad_norm = bucket.clip_(self._max_grad_norm)                     # :136-137
-        self._optimizer.step()                                            # :140
+        if isinstance(self._optimizer, optim.FusedClipAdam):               # :136-140 in one launch (K6)
+            grad_norm = self._optimizer.step_flat(bucket.grads, self._max_grad_norm)[0]
+        else:
+            grad_norm = bucket.clip_(self._max_grad_norm)                     # :136-137
+            self._optimizer.step()                                            # :140
         sc = bucket.extra
         return {
             "train/loss": sc[ops.S_LOSS], "train/entropy": sc[ops.S_ENTROPY], "train/td": sc[ops.S_TD],

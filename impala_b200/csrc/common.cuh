@@ -26,7 +26,10 @@ constexpr int kMaxPartialCtas = 16384;
 constexpr int64_t kTraceOffset = 256 + (int64_t)kMaxPartialCtas * kNumScalars * 8;
 // B200RL_TRACE: [kMaxTraceCtas][16] uint64 per CTA: 8 %globaltimer stamps then 8 clock64 stamps (profiling aid)
 constexpr int kMaxTraceCtas = 4096;
-constexpr int64_t kWorkspaceBytes = kTraceOffset + (int64_t)kMaxTraceCtas * 16 * 8;
+// K6 (clip + Adam): 64 B header (uint32 generation) + one published word per CTA
+constexpr int64_t kOptOffset = kTraceOffset + (int64_t)kMaxTraceCtas * 16 * 8;
+constexpr int kMaxOptCtas = 1024;
+constexpr int64_t kWorkspaceBytes = kOptOffset + 64 + (int64_t)kMaxOptCtas * 8;
 
 // ---------------------------------------------------------------- device: PTX
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {

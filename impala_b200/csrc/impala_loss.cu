@@ -67,12 +67,20 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(cons
                          (nrows == 1 || ((g_row_stride * 4) % 16 == 0 && (s_row_stride * 4) % 16 == 0)) &&
                          ((reinterpret_cast<uintptr_t>(p.logits) | reinterpret_cast<uintptr_t>(p.pi_ref) |
                            reinterpret_cast<uintptr_t>(p.dlogits)) % 16 == 0);
+    // The copies are issued by lane 0 of every warp, rows dealt round-robin: a UBLKCP takes tens of
+    // cycles to issue, so one thread issuing 2*T of them (time-major) would delay the last row by
+    // microseconds.  Batch-major has one row per tensor: thread 0 alone, no extra barrier.
+    const int warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
+    const bool issuer = (threadIdx.x & 31) == 0 && warp < nrows;
     if (bulk_ok) {
         if (threadIdx.x == 0) {
             mbar_init(bar, 1);
             fence_mbar_init();
             mbar_expect_tx(bar, 2u * row_bytes * nrows);
-            for (int r = 0; r < nrows; ++r) {
+        }
+        if (nrows > 1) __syncthreads();  // barrier initialised before other warps' copies can complete on it
+        if (issuer) {
+            for (int r = warp; r < nrows; r += nwarps) {
                 bulk_g2s(sx + r * s_row_stride, p.logits + g_row0 + r * g_row_stride, row_bytes, bar);
                 bulk_g2s(sy + r * s_row_stride, p.pi_ref + g_row0 + r * g_row_stride, row_bytes, bar);
             }
@@ -195,8 +203,8 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(cons
     __syncthreads();
     K1_STAMP(4);
     if (bulk_ok) {
-        if (threadIdx.x == 0) {
-            for (int r = 0; r < nrows; ++r)
+        if (issuer) {
+            for (int r = warp; r < nrows; r += nwarps)
                 bulk_s2g(p.dlogits + g_row0 + r * g_row_stride, sx + r * s_row_stride, row_bytes);
             bulk_commit();
         }
@@ -224,7 +232,7 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(cons
         },
         [=]() { if (late_wait) pdl_wait(); });  // the workspace and scalars are shared with the previous launch
     K1_STAMP(5);
-    if (bulk_ok && threadIdx.x == 0) bulk_wait_read0();  // smem must outlive the bulk store's reads
+    if (bulk_ok && issuer) bulk_wait_read0();  // smem must outlive the bulk store's reads
     K1_STAMP(6);
 #undef K1_STAMP
 }

@@ -223,3 +223,20 @@ def ring_append(storage, count, rows):
     row_bytes = storage[0].numel() * storage.element_size()
     _cabi.call("b200rl_ring_append", storage.data_ptr(), row_bytes, storage.shape[0], count,
                rows.data_ptr(), rows.shape[0], _stream())
+
+
+def clip_adam_step(params, grads, exp_avg, exp_avg_sq, step, lr, beta1=0.9, beta2=0.999, eps=1e-8,
+                   max_norm=0.0, total_norm=None):
+    """K6.  Flat fp32 buffers, updated in place; returns the 1-element ``total_norm`` tensor (pre-clip)."""
+    _require_cuda(params, grads, exp_avg, exp_avg_sq)
+    n = params.numel()
+    for name, x in (("params", params), ("grads", grads), ("exp_avg", exp_avg), ("exp_avg_sq", exp_avg_sq)):
+        if x.dtype != torch.float32 or not x.is_contiguous() or x.numel() != n:
+            raise RuntimeError("clip_adam_step: %s must be a contiguous float32 buffer of %d elements" % (name, n))
+    if total_norm is None:
+        total_norm = torch.empty(1, dtype=torch.float32, device=params.device)
+    ws = workspace(params.device)
+    _cabi.call("b200rl_clip_adam_step", params.data_ptr(), grads.data_ptr(), exp_avg.data_ptr(),
+               exp_avg_sq.data_ptr(), n, max_norm, lr, beta1, beta2, eps, step, total_norm.data_ptr(),
+               ws.data_ptr(), _stream())
+    return total_norm

@@ -1,0 +1,70 @@
+"""Fused global-norm clip + Adam over flat buffers (K6).
+
+Drop-in for the optimizer the reference builds at ``agents/impala/builder.py:43-44``
+(``torch.optim.Adam(params, lr=1e-4, eps=1e-5)``) together with the ``clip_grad_norm_`` that precedes every
+``optimizer.step()`` (``agents/impala/learning.py:172-176``, ``agents/ppo/learning.py:136-140``): parameters,
+gradients and both Adam moments live in flat fp32 buffers and one kernel launch does norm -> clip -> update.
+"""
+from typing import Iterable
+
+import torch
+
+from . import ops
+
+
+class FusedClipAdam(torch.optim.Optimizer):
+    """``torch.optim.Adam`` constructor surface (``lr, betas, eps``; no weight decay / amsgrad, as the reference).
+
+    On construction the parameters are re-pointed at views of ONE flat buffer (values preserved).  The
+    learners pass the flat gradient bucket (``parallel.GradBucket``) to ``step_flat``; a plain ``step()``
+    gathers ``p.grad`` first and is there for API compatibility."""
+
+    def __init__(self, params: Iterable[torch.nn.Parameter], lr: float = 1e-3, betas=(0.9, 0.999),
+                 eps: float = 1e-8, max_grad_norm: float = 0.0):
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
+        if len(self.param_groups) != 1:
+            raise RuntimeError("FusedClipAdam: one parameter group only")
+        self.max_grad_norm = float(max_grad_norm)
+        self.params = [p for p in self.param_groups[0]["params"] if p.requires_grad]
+        if not self.params or not all(p.is_cuda and p.dtype == torch.float32 for p in self.params):
+            raise RuntimeError("FusedClipAdam needs float32 CUDA parameters (no CPU fallback)")
+        dev = self.params[0].device
+        n = sum(p.numel() for p in self.params)
+        self.flat = torch.empty(n, dtype=torch.float32, device=dev)
+        off = 0
+        for p in self.params:
+            v = self.flat[off:off + p.numel()].view_as(p)
+            v.copy_(p.data)
+            p.data = v
+            off += p.numel()
+        self.exp_avg = torch.zeros_like(self.flat)
+        self.exp_avg_sq = torch.zeros_like(self.flat)
+        self.total_norm = torch.zeros(1, dtype=torch.float32, device=dev)
+        self.step_count = 0
+        self._own_grads = None
+
+    def step_flat(self, flat_grads: torch.Tensor, max_grad_norm=None) -> torch.Tensor:
+        """One clip + Adam step from a flat gradient buffer laid out like ``self.params``.
+        ``flat_grads`` is clipped in place; returns the pre-clip global norm (1-element tensor)."""
+        g = self.param_groups[0]
+        self.step_count += 1
+        mgn = self.max_grad_norm if max_grad_norm is None else float(max_grad_norm)
+        return ops.clip_adam_step(self.flat, flat_grads, self.exp_avg, self.exp_avg_sq, self.step_count,
+                                  g["lr"], g["betas"][0], g["betas"][1], g["eps"], mgn, self.total_norm)
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        if closure is not None:
+            raise RuntimeError("FusedClipAdam: closures are not supported")
+        if self._own_grads is None:
+            self._own_grads = torch.zeros_like(self.flat)
+        off = 0
+        for p in self.params:
+            n = p.numel()
+            if p.grad is not None and p.grad.data_ptr() != self._own_grads[off:off + n].data_ptr():
+                self._own_grads[off:off + n].copy_(p.grad.reshape(-1))
+            elif p.grad is None:
+                self._own_grads[off:off + n].zero_()
+            off += n
+        self.step_flat(self._own_grads)
+        return None

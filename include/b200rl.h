@@ -150,6 +150,18 @@ int32_t b200rl_ring_append(
     void *storage, int64_t row_bytes, int64_t capacity, int64_t count,
     const void *rows, int64_t n, void *stream);
 
+/* K6 -- replaces clip_grad_norm_(params, max_norm) + optimizer.step() (torch.optim.Adam, no weight decay,
+ * no amsgrad) at reference agents/impala/learning.py:172-176 and agents/ppo/learning.py:136-140 for
+ * parameters, gradients and Adam moments held in FLAT fp32 buffers of n elements.  In place: grads are
+ * scaled by min(1, max_norm / (||g||_2 + 1e-6)) (max_norm <= 0: no clipping), then exp_avg, exp_avg_sq and
+ * params take one Adam step; `step` is the 1-based step number (bias correction).  total_norm[0] receives
+ * ||g||_2 before clipping.  `workspace` is the zero-initialised loss workspace (a separate region of it).
+ * One cooperative launch (grid <= co-resident CTAs; CTAs loop over their chunk, so any n works). */
+int32_t b200rl_clip_adam_step(
+    float *params, float *grads, float *exp_avg, float *exp_avg_sq, int64_t n,
+    float max_norm, double lr, double beta1, double beta2, double eps, int64_t step,
+    float *total_norm, void *workspace, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -28,11 +28,11 @@ for mode, flags in flags_list.items():
             launch(i)
     gr.replay(); torch.cuda.synchronize()
     for w in ops._workspaces.values():
-        w[off:].zero_()
+        w[off:off + 4096 * 128].zero_()
     torch.cuda.synchronize()
     gr.replay(); torch.cuda.synchronize()
     ws = [w for w in ops._workspaces.values() if int(w[off:off + 8].view(torch.int64).item()) > 0][0]
-    tr = ws[off:].view(torch.int64).cpu().numpy().reshape(-1, 16)
+    tr = ws[off:off + 4096 * 128].view(torch.int64).cpu().numpy().reshape(-1, 16)
     ncta = int((tr[:, 0] > 0).sum())
     tr = tr[:ncta]
     gt, ck, sm = tr[:, :7].astype(np.float64), tr[:, 8:15].astype(np.float64), tr[:, 7]

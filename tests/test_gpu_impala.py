@@ -176,7 +176,7 @@ def test_pipelined_launches_match_serial(cuda):
             assert torch.equal(a, b)
     off = _cabi_trace_offset()
     for ws in ops._workspaces.values():
-        assert int(ws[:off].view(torch.int64).abs().sum().item()) == 0      # published words cleared
+        assert int(ws[256:off].view(torch.int64).abs().sum().item()) == 0   # published words cleared
 
 
 def _cabi_trace_offset():
@@ -218,7 +218,7 @@ def test_trace_flag_stamps_phases(cuda):
     for a, b in zip(base, traced):
         assert torch.equal(a, b)
     off = _cabi_trace_offset()
-    tr = ops.workspace(cuda)[off:].view(torch.int64).cpu().view(-1, 16)[:8]        # 64 columns / 8 per CTA
+    tr = ops.workspace(cuda)[off:off + 8 * 16 * 8].view(torch.int64).cpu().view(8, 16)   # 64 columns / 8 per CTA
     assert (tr[:, 0] > 0).all()
     assert ((tr[:, 9:15] - tr[:, 8:14]) >= 0).all()                                # clock64 monotone per CTA
-    ops.workspace(cuda)[off:].zero_()
+    ops.workspace(cuda)[off:off + 8 * 16 * 8].zero_()

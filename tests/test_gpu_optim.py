@@ -1,0 +1,85 @@
+"""GPU: K6 (fused global-norm clip + Adam) through the C ABI vs torch's own clip_grad_norm_ + Adam on the CPU
+(the reference's arithmetic for agents/impala/learning.py:172-176)."""
+import copy
+
+import pytest
+import torch
+
+from gpu_util import assert_close
+from impala_b200 import models, ops, optim
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref_steps(p0, grads, max_norm, lr, betas, eps):
+    p = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.Adam([p], lr=lr, betas=betas, eps=eps)
+    norms, clipped = [], []
+    for g in grads:
+        # clip_grad_norm_ with the norm taken in fp64: torch's fp32 CPU sum of >1e6 squares is itself ~2e-5 off
+        norm = torch.linalg.vector_norm(g.double())
+        coef = min(1.0, max_norm / (norm.item() + 1e-6)) if max_norm > 0 else 1.0
+        p.grad = g * torch.tensor(coef, dtype=torch.float32)
+        norms.append(norm.float())
+        clipped.append(p.grad.clone())
+        opt.step()
+    st = opt.state[p]
+    return p.detach(), st["exp_avg"], st["exp_avg_sq"], norms, clipped
+
+
+@pytest.mark.parametrize("n", [1, 5, 1023, 4096, 630_352, 1_300_001])
+@pytest.mark.parametrize("max_norm,scale", [(0.5, 1.0), (40.0, 1e-3), (0.0, 1.0)])
+def test_clip_adam_matches_torch(cuda, n, max_norm, scale):
+    g = torch.Generator().manual_seed(n)
+    p0 = torch.randn(n, generator=g)
+    grads = [scale * torch.randn(n, generator=g) * (1 + k) for k in range(4)]
+    lr, betas, eps = 1e-4, (0.9, 0.999), 1e-5                 # agents/impala/builder.py:43-44
+    want_p, want_m, want_v, want_norms, want_clipped = _ref_steps(p0, grads, max_norm, lr, betas, eps)
+    p, m, v = p0.to(cuda), torch.zeros(n, device=cuda), torch.zeros(n, device=cuda)
+    for k, gk in enumerate(grads):
+        gd = gk.to(cuda)
+        norm = ops.clip_adam_step(p, gd, m, v, k + 1, lr, betas[0], betas[1], eps, max_norm)
+        assert_close(norm[0], want_norms[k], "norm", rtol=1e-5, atol=0)        # fp32 sum of n squares, different order
+        assert_close(gd, want_clipped[k], "clipped grads", rtol=2e-5, atol=1e-9)
+    assert_close(m, want_m, "exp_avg", rtol=2e-5, atol=1e-8)
+    assert_close(v, want_v, "exp_avg_sq", rtol=4e-5, atol=1e-12)
+    # a parameter moves ~lr per step; 4 steps of lr=1e-4 compared to 1e-7 absolute = 2.5e-4 of the motion
+    assert_close(p, want_p, "params", rtol=1e-6, atol=1e-7)
+
+
+def test_clip_adam_unaligned_and_deterministic(cuda):
+    n = 70_001
+    g = torch.Generator().manual_seed(1)
+    base = [torch.randn(n + 1, generator=g).to(cuda) for _ in range(2)]
+    outs = []
+    for rep in range(2):
+        bufs = [b.clone() for b in base] + [torch.zeros(n + 1, device=cuda), torch.zeros(n + 1, device=cuda)]
+        p, gd, m, v = [b[1:] for b in bufs]                    # 4-byte aligned only: scalar path
+        norm = ops.clip_adam_step(p, gd, m, v, 1, 1e-3, max_norm=0.5)
+        outs.append((p.clone(), gd.clone(), m.clone(), v.clone(), norm.clone()))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+    pa, ga, ma, va = [b.clone() for b in base] + [torch.zeros(n + 1, device=cuda), torch.zeros(n + 1, device=cuda)]
+    norm = ops.clip_adam_step(pa[:n], ga[:n], ma[:n], va[:n], 1, 1e-3, max_norm=0.5)   # aligned: float4 path
+    want_p, want_m, want_v, want_norms, _ = _ref_steps(base[0][:n].cpu(), [base[1][:n].cpu()], 0.5, 1e-3, (0.9, 0.999), 1e-8)
+    assert_close(pa[:n], want_p, "params", rtol=1e-6, atol=1e-7)
+    assert_close(norm[0], want_norms[0], "norm", rtol=1e-5, atol=0)
+
+
+def test_fused_optimizer_class_matches_adam_on_model(cuda):
+    torch.manual_seed(0)
+    model = models.ActorCritic((3, 64, 64), 15, body="nature").to(cuda)
+    ref = copy.deepcopy(model)
+    opt = optim.FusedClipAdam(model.parameters(), lr=1e-4, eps=1e-5, max_grad_norm=0.5)
+    ropt = torch.optim.Adam(ref.parameters(), lr=1e-4, eps=1e-5)
+    obs = torch.randint(0, 256, (16, 3, 64, 64), device=cuda, dtype=torch.uint8)
+    for _ in range(3):
+        for mdl, o in ((model, opt), (ref, ropt)):
+            o.zero_grad(set_to_none=True)
+            pi, v = mdl(obs)
+            (pi.logsumexp(-1).mean() + v.pow(2).mean()).backward()
+            if o is ropt:
+                torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.5)
+            o.step()
+    for (n1, a), (_, b) in zip(model.named_parameters(), ref.named_parameters()):
+        assert_close(a, b, n1, rtol=1e-5, atol=2e-7)

@@ -9,7 +9,7 @@ import torch
 
 from conftest import GOLDEN
 from gpu_util import assert_close
-from impala_b200 import models, ops, replay, synth
+from impala_b200 import models, ops, optim, replay, synth
 from impala_b200.agents import ImpalaLearner, PPOLearner
 from oracle import c_oracle, losses_ref, replay_ref
 
@@ -136,8 +136,8 @@ def _fill_impala_replay(rb, n_items, T, A, seed):
                    (torch.rand(T, 1, generator=g) > .05).float() * .99, torch.randn(T, A, generator=g)])
 
 
-@pytest.mark.parametrize("body", ["nature", "impala"])
-def test_impala_learner_step_matches_reference_shaped_step(cuda, body):
+@pytest.mark.parametrize("body,fused_opt", [("nature", False), ("impala", False), ("impala", True)])
+def test_impala_learner_step_matches_reference_shaped_step(cuda, body, fused_opt):
     torch.manual_seed(0)
     T, A, Bsz = 20, 15, 8
     model = models.ActorCritic((3, 64, 64), A, body=body).to(cuda)
@@ -145,7 +145,7 @@ def test_impala_learner_step_matches_reference_shaped_step(cuda, body):
     rb = replay.ReplayBuffer(replay.CircularBuffer(32, device=cuda), replay.UniformSampler())
     rb.sampler.reset(123)
     _fill_impala_replay(rb, 12, T, A, seed=5)
-    opt = torch.optim.Adam(model.parameters(), lr=1e-4, eps=1e-5)
+    opt = (optim.FusedClipAdam if fused_opt else torch.optim.Adam)(model.parameters(), lr=1e-4, eps=1e-5)
     learner = ImpalaLearner(model, rb, opt, batch_size=Bsz, learning_starts=10)
     learner.prepare()
     draws0 = rb.sampler.draws
