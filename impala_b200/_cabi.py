@@ -14,6 +14,13 @@ _lib = None
 _vp, _i64, _i32, _u32, _u64, _f, _d = (ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32,
                                        ctypes.c_uint32, ctypes.c_uint64, ctypes.c_float, ctypes.c_double)
 
+class Field(ctypes.Structure):
+    """``b200rl_field_t`` (include/b200rl.h)."""
+    _fields_ = [("src", _vp), ("dst", _vp), ("row_bytes", _i64), ("kind", _i32), ("gamma", _f)]
+
+
+FIELD_COPY, FIELD_DONE_TO_DISCOUNT = 0, 1
+
 # name -> (restype, argtypes); mirrors include/b200rl.h one to one
 SIGNATURES = {
     "b200rl_version": (_i32, []),
@@ -24,11 +31,14 @@ SIGNATURES = {
     "b200rl_vtrace": (_i32, [_vp] * 5 + [_i64] * 4 + [_d] + [_f] * 2 + [_vp] * 4),
     "b200rl_vtrace_bwd": (_i32, [_vp] * 7 + [_i64] * 4 + [_d, _f] + [_vp] * 4),
     "b200rl_lambda_returns": (_i32, [_vp] * 3 + [_i64] * 4 + [_d] + [_vp] * 2),
+    "b200rl_n_step_returns": (_i32, [_vp] * 3 + [_i64] * 5 + [_d] + [_vp] * 2),
     "b200rl_gae": (_i32, [_vp] * 3 + [_i64] * 6 + [_d] + [_vp] * 2),
     "b200rl_ppo_loss_fwdbwd": (_i32, [_vp] * 5 + [_i64] * 3 + [_f] * 2 + [_u32] + [_vp] * 5),
     "b200rl_sample_uniform": (_i32, [_u64, _u32, _u64, _i64, _i64, _vp, _vp]),
     "b200rl_gather_rows": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _vp]),
     "b200rl_ring_append": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp]),
+    "b200rl_ring_append_fields": (_i32, [ctypes.POINTER(Field), _i32, _i64, _i64, _i64, _vp]),
+    "b200rl_gather_fields": (_i32, [ctypes.POINTER(Field), _i32, _vp, _i64, _i64, _vp]),
     "b200rl_clip_adam_step": (_i32, [_vp] * 4 + [_i64, _f] + [_d] * 4 + [_i64] + [_vp] * 3),
 }
 

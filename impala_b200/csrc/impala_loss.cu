@@ -13,14 +13,12 @@
 
 namespace b200rl {
 
-constexpr int kWalkMaxT = 48;  // rollouts up to this length use the per-thread column walk
-
 struct ImpalaParams {
     const float *logits, *pi_ref, *rewards, *discounts, *values;
     const long long *actions;
     float *dlogits, *dvalues, *scalars;
     void *workspace;
-    int B, T, A, C, time_major;
+    int B, T, A, C, time_major, walk_max_t;
     float lambda_, one_minus_lambda, clip_rho, clip_pg_rho, entropy_coeff, inv_n_pg, inv_n_all;
     uint32_t flags;
 };
@@ -126,37 +124,47 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(cons
     K1_STAMP(2);
 
     // ---- phase 3: backward-in-time recursion e_k = td_k + (discount_k c_k) e_{k+1} ----------
-    // Short rollouts (T <= kWalkMaxT): every thread walks its own column from the last step down
-    // to its step -- redundant O(T^2) FMAs per column, but no serial phase, no second barrier;
-    // the chain is the reference's operation order in every thread, so all agree bit for bit.
-    // Long rollouts: one register chain per column, steps fetched 8 at a time.
+    // Default: one register chain per column (the column's first thread), steps fetched 4 at a
+    // time and the next 4 prefetched while the chain runs; results go to s_e.
+    // walk_max_t > 0 and T <= walk_max_t: every thread walks its own column from the last step
+    // down to its step instead (redundant O(T^2) FMAs, no second barrier).  Either way every
+    // e_k is produced by the same operation order as the reference's loop.
     float e_t = 0.f, e_t1 = 0.f;  // e_t, e_{t+1} of this thread's sample
-    if (T <= kWalkMaxT) {
+    if (T <= p.walk_max_t) {
         const float2 *col = s_tg + (valid ? (p.time_major ? c : c * T) : 0);
-#pragma unroll 4
-        for (int k = T - 2; k >= 0; --k) {
-            const float2 q = col[k * st_local];
-            if (k >= t) {
-                e_t1 = e_t;
-                e_t = q.x + q.y * e_t;
+        for (int k0 = T - 2; k0 >= 0; k0 -= 4) {
+            float2 q[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) q[j] = col[max(k0 - j, 0) * st_local];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const bool on = (k0 - j) >= t;  // t >= 0, so steps below 0 are never taken
+                const float ne = q[j].x + q[j].y * e_t;
+                e_t1 = on ? e_t : e_t1;
+                e_t = on ? ne : e_t;
             }
         }
     } else {
         if (s < cols) {
-            const int sc_local = p.time_major ? 1 : T;
+            const float2 *__restrict__ col = s_tg + (p.time_major ? s : s * T);
+            float *__restrict__ ecol = s_e + (p.time_major ? s : s * T);
             float e = 0.f;
-            int idx = s * sc_local + (T - 2) * st_local;
-            for (int tt = T - 2; tt >= 0; tt -= 8, idx -= 8 * st_local) {
-                float2 q[8];
+            int k = T - 2;
+            float2 q[4];
 #pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    if (k <= tt) q[k] = s_tg[idx - k * st_local];
+            for (int j = 0; j < 4; ++j) q[j] = col[max(k - j, 0) * st_local];
+            for (; k >= 0; k -= 4) {
+                float2 nq[4];
 #pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    if (k <= tt) {
-                        e = q[k].x + q[k].y * e;
-                        s_e[idx - k * st_local] = e;
+                for (int j = 0; j < 4; ++j) nq[j] = col[max(k - 4 - j, 0) * st_local];  // prefetch the next 4
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    if (k - j >= 0) {
+                        e = q[j].x + q[j].y * e;
+                        ecol[(k - j) * st_local] = e;
                     }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) q[j] = nq[j];
             }
         }
         __syncthreads();
@@ -309,6 +317,7 @@ extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
     p.inv_n_pg = (float)(1.0 / ((double)n_global_b * (double)(T - 1)));
     p.inv_n_all = (float)(1.0 / ((double)n_global_b * (double)T));
     p.flags = flags;
+    p.walk_max_t = env_int("B200RL_K1_WALK_MAXT", 0);
 
     // columns per CTA: a multiple of 4 so time-major rows stay 16-byte aligned
     int target = env_int("B200RL_K1_SAMPLES", 160);

@@ -131,3 +131,141 @@ extern "C" int32_t b200rl_ring_append(void *storage, int64_t row_bytes, int64_t 
     B200RL_REQUIRE(capacity >= 1 && n <= capacity, -2, "ring_append: n=%lld exceeds capacity=%lld", (long long)n, (long long)capacity);
     return launch_row_copy<COPY_RING>(rows, storage, nullptr, n, row_bytes, capacity, count, (cudaStream_t)stream);
 }
+
+// ---------------------------------------------------------------------------------------
+// N2: multi-field ring append in ONE launch, with the actor-side `discount = !done * gamma`
+// (reference ImpalaActor._make_replay, agents/impala/learning.py:77-80) fused into the copy.
+// blockIdx.y selects the field; each field is flattened over (row, 16-byte vector) like
+// row_copy_kernel.  Fields smaller than the widest one simply retire their surplus CTAs.
+namespace b200rl {
+
+constexpr int kMaxFields = 8;
+struct FieldTable {
+    const void *src[kMaxFields];
+    void *dst[kMaxFields];
+    long long row_bytes[kMaxFields];  // bytes per SOURCE row
+    int kind[kMaxFields];             // B200RL_FIELD_*
+    int vec[kMaxFields];              // copy width in bytes (16/8/4/1); discount fields: 1
+    float gamma[kMaxFields];
+    long long n, capacity, count;
+    const long long *idx;  // gather only
+};
+
+// MODE COPY_RING: dst[(count + i) % capacity] = src[i];  COPY_GATHER: dst[i] = src[clamp(idx[i])]
+template <int MODE>
+__global__ void __launch_bounds__(kCopyThreads) fields_copy_kernel(const FieldTable ft) {
+    const int f = blockIdx.y;
+    const long long rb = ft.row_bytes[f];
+    const int vec = ft.vec[f];
+    const long long vpr = rb / vec, total = ft.n * vpr;
+    const long long base = ((long long)blockIdx.x * kCopyUnroll) * kCopyThreads + threadIdx.x;
+    if (base >= total) return;
+    if (MODE == COPY_RING && ft.kind[f] == B200RL_FIELD_DONE_TO_DISCOUNT) {
+        const unsigned char *src = static_cast<const unsigned char *>(ft.src[f]);
+        float *dst = static_cast<float *>(ft.dst[f]);
+        const float g = ft.gamma[f];
+#pragma unroll
+        for (int u = 0; u < kCopyUnroll; ++u) {
+            const long long k = base + (long long)u * kCopyThreads;
+            if (k < total) {
+                const long long row = k / rb, col = k - row * rb;
+                const long long d_row = (ft.count + row) % ft.capacity;
+                dst[d_row * rb + col] = src[k] ? 0.f : g;  // logical_not(done) * gamma
+            }
+        }
+        return;
+    }
+    auto copy = [&](auto tag) {
+        using V = decltype(tag);
+        const V *src = static_cast<const V *>(ft.src[f]);
+        V *dst = static_cast<V *>(ft.dst[f]);
+        V regs[kCopyUnroll];
+        long long d_off[kCopyUnroll];
+#pragma unroll
+        for (int u = 0; u < kCopyUnroll; ++u) {
+            const long long k = base + (long long)u * kCopyThreads;
+            d_off[u] = -1;
+            if (k < total) {
+                const long long row = k / vpr, col = k - row * vpr;
+                if (MODE == COPY_RING) {
+                    regs[u] = __ldcs(src + k);
+                    d_off[u] = ((ft.count + row) % ft.capacity) * vpr + col;
+                } else {
+                    long long j = __ldg(ft.idx + row);
+                    j = j < 0 ? 0 : (j >= ft.capacity ? ft.capacity - 1 : j);
+                    regs[u] = __ldcs(src + j * vpr + col);
+                    d_off[u] = k;
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < kCopyUnroll; ++u)
+            if (d_off[u] >= 0) __stcs(dst + d_off[u], regs[u]);
+    };
+    switch (vec) {
+        case 16: copy(int4{}); break;
+        case 8: copy(int2{}); break;
+        case 4: copy(int{}); break;
+        default: copy(char{}); break;
+    }
+}
+
+}  // namespace b200rl
+
+static int32_t fill_field_table(const char *who, const b200rl_field_t *fields, int32_t n_fields, long long n,
+                                bool allow_discount, b200rl::FieldTable &ft, long long &max_ctas) {
+    using namespace b200rl;
+    max_ctas = 1;
+    for (int f = 0; f < n_fields; ++f) {
+        const b200rl_field_t &x = fields[f];
+        B200RL_REQUIRE(x.src && x.dst, -1, "%s: field %d has a null pointer", who, f);
+        B200RL_REQUIRE(x.row_bytes >= 1, -2, "%s: field %d row_bytes=%lld", who, f, (long long)x.row_bytes);
+        B200RL_REQUIRE(x.kind == B200RL_FIELD_COPY || (allow_discount && x.kind == B200RL_FIELD_DONE_TO_DISCOUNT), -2,
+                       "%s: field %d has unsupported kind %d", who, f, x.kind);
+        ft.src[f] = x.src; ft.dst[f] = x.dst; ft.row_bytes[f] = x.row_bytes; ft.kind[f] = x.kind; ft.gamma[f] = x.gamma;
+        int vec = 1;
+        if (x.kind == B200RL_FIELD_COPY) {
+            const uintptr_t al = reinterpret_cast<uintptr_t>(x.src) | reinterpret_cast<uintptr_t>(x.dst) | (uintptr_t)x.row_bytes;
+            vec = (al % 16 == 0) ? 16 : (al % 8 == 0) ? 8 : (al % 4 == 0) ? 4 : 1;
+        }
+        ft.vec[f] = vec;
+        const long long total = n * (x.row_bytes / vec), per_cta = (long long)kCopyThreads * kCopyUnroll;
+        const long long ctas = (total + per_cta - 1) / per_cta;
+        if (ctas > max_ctas) max_ctas = ctas;
+    }
+    B200RL_REQUIRE(max_ctas < (1ll << 31), -3, "%s: too many elements", who);
+    return 0;
+}
+
+extern "C" int32_t b200rl_ring_append_fields(const b200rl_field_t *fields, int32_t n_fields, int64_t capacity,
+                                             int64_t count, int64_t n, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(n >= 0 && count >= 0, -2, "ring_append_fields: negative size");
+    B200RL_REQUIRE(n_fields >= 1 && n_fields <= kMaxFields, -2, "ring_append_fields: 1..%d fields (got %d)", kMaxFields, n_fields);
+    B200RL_REQUIRE(fields, -1, "ring_append_fields: null field table");
+    if (n == 0) return 0;
+    B200RL_REQUIRE(capacity >= 1 && n <= capacity, -2, "ring_append_fields: n=%lld exceeds capacity=%lld", (long long)n, (long long)capacity);
+    FieldTable ft = {};
+    ft.n = n; ft.capacity = capacity; ft.count = count; ft.idx = nullptr;
+    long long max_ctas;
+    if (int32_t rc = fill_field_table("ring_append_fields", fields, n_fields, n, true, ft, max_ctas)) return rc;
+    fields_copy_kernel<COPY_RING><<<dim3((unsigned)max_ctas, (unsigned)n_fields), kCopyThreads, 0, (cudaStream_t)stream>>>(ft);
+    return check_launch("fields_copy_kernel<ring>");
+}
+
+extern "C" int32_t b200rl_gather_fields(const b200rl_field_t *fields, int32_t n_fields, const int64_t *idx,
+                                        int64_t n, int64_t nrows, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(n >= 0, -2, "gather_fields: negative size");
+    B200RL_REQUIRE(n_fields >= 1 && n_fields <= kMaxFields, -2, "gather_fields: 1..%d fields (got %d)", kMaxFields, n_fields);
+    B200RL_REQUIRE(fields, -1, "gather_fields: null field table");
+    if (n == 0) return 0;
+    B200RL_REQUIRE(idx, -1, "gather_fields: null index");
+    B200RL_REQUIRE(nrows >= 1, -2, "gather_fields: empty source");
+    FieldTable ft = {};
+    ft.n = n; ft.capacity = nrows; ft.count = 0; ft.idx = reinterpret_cast<const long long *>(idx);
+    long long max_ctas;
+    if (int32_t rc = fill_field_table("gather_fields", fields, n_fields, n, false, ft, max_ctas)) return rc;
+    fields_copy_kernel<COPY_GATHER><<<dim3((unsigned)max_ctas, (unsigned)n_fields), kCopyThreads, 0, (cudaStream_t)stream>>>(ft);
+    return check_launch("fields_copy_kernel<gather>");
+}

@@ -130,6 +130,35 @@ static int32_t launch_scan(const ScanParams &p, cudaStream_t stream) {
     return check_launch("scan_generic_kernel");
 }
 
+// N4: n-step bootstrapped returns (rlax / rlego n_step_bootstrapped_returns; reference
+// agents/dqn/learning.py:62,79).  Every output is an independent n-step window, so one thread per
+// (b,t) walks its window backwards with the lambda-returns step (same operation order as the
+// oracle: bit-exact); steps past the end of the rollout are the reference's padding
+// (r = 0, discount = 1, v = v_t[T-1]).  Threads are enumerated in memory order: coalesced for
+// either layout; the window re-reads hit L1.
+__global__ void __launch_bounds__(256) n_step_kernel(const ScanParams p, int n_step) {
+    const long long k = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= (long long)p.B * p.T) return;
+    int b, t;
+    if (p.st == 1) { b = (int)(k / p.T); t = (int)(k - (long long)b * p.T); }
+    else { t = (int)(k / p.B); b = (int)(k - (long long)t * p.B); }
+    const long long base = (long long)b * p.sb;
+    const float v_last = __ldg(p.v + base + (long long)(p.T - 1) * p.st);
+    const int last = t + n_step - 1;
+    float y = last < p.T ? __ldg(p.v + base + (long long)last * p.st) : v_last;
+    for (int i = n_step - 1; i >= 0; --i) {
+        const int kk = t + i;
+        if (kk < p.T) {
+            const long long j = base + (long long)kk * p.st;
+            y = scan_step<MODE_LAMBDA_RETURNS>(__ldg(p.r + j), __ldg(p.disc + j), __ldg(p.v + j), 0.f, p.lambda_,
+                                               p.one_minus_lambda, y);
+        } else {
+            y = scan_step<MODE_LAMBDA_RETURNS>(0.f, 1.f, v_last, 0.f, p.lambda_, p.one_minus_lambda, y);
+        }
+    }
+    p.out[base + (long long)t * p.st] = y;
+}
+
 static int32_t check_scan_layout(const char *who, int64_t B, int64_t T, int64_t sb, int64_t st) {
     B200RL_REQUIRE(B >= 1 && T >= 1, -2, "%s: need B>=1 and T>=1 (got B=%lld T=%lld)", who, (long long)B, (long long)T);
     B200RL_REQUIRE(B * (T + 1) < (1ll << 31), -3, "%s: B*T too large", who);
@@ -164,4 +193,18 @@ extern "C" int32_t b200rl_gae(const float *r_t, const float *discount_t, const f
     ScanParams p{r_t, discount_t, values, out, (int)B, (int)T, stride_b, stride_t, vstride_b, vstride_t, (float)lambda_,
                  (float)(1.0 - lambda_)};
     return launch_scan<MODE_GAE>(p, (cudaStream_t)stream);
+}
+
+extern "C" int32_t b200rl_n_step_returns(const float *r_t, const float *discount_t, const float *v_t, int64_t B,
+                                         int64_t T, int64_t stride_b, int64_t stride_t, int64_t n,
+                                         double lambda_, float *out, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(r_t && discount_t && v_t && out, -1, "n_step_returns: null pointer argument");
+    if (int32_t rc = check_scan_layout("n_step_returns", B, T, stride_b, stride_t)) return rc;
+    B200RL_REQUIRE(n >= 1 && n < (1 << 20), -2, "n_step_returns: n=%lld", (long long)n);
+    ScanParams p{r_t, discount_t, v_t, out, (int)B, (int)T, stride_b, stride_t, stride_b, stride_t, (float)lambda_,
+                 (float)(1.0 - lambda_)};
+    const long long total = B * T;
+    n_step_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p, (int)n);
+    return check_launch("n_step_kernel");
 }

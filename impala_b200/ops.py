@@ -240,3 +240,62 @@ def clip_adam_step(params, grads, exp_avg, exp_avg_sq, step, lr, beta1=0.9, beta
                exp_avg_sq.data_ptr(), n, max_norm, lr, beta1, beta2, eps, step, total_norm.data_ptr(),
                ws.data_ptr(), _stream())
     return total_norm
+
+
+def ring_append_fields(storages, count, rows, done_field=None, gamma=0.99):
+    """N2.  Append ``n`` stacked rows of every field to its ring storage in ONE launch.  ``storages[i]`` is
+    ``[capacity, ...]``, ``rows[i]`` is ``[n, ...]`` (device, same trailing shape and dtype) -- except field
+    ``done_field``: its ``rows`` hold bool/uint8 done flags and its storage receives float32
+    ``logical_not(done) * gamma`` (reference ``agents/impala/learning.py:79``)."""
+    _require_cuda(*storages, *rows)
+    if len(storages) != len(rows) or not storages:
+        raise RuntimeError("ring_append_fields: %d storages vs %d row tensors" % (len(storages), len(rows)))
+    n, cap = rows[0].shape[0], storages[0].shape[0]
+    table = (_cabi.Field * len(rows))()
+    keep = []
+    for i, (st, r) in enumerate(zip(storages, rows)):
+        if r.shape[0] != n or st.shape[0] != cap or tuple(r.shape[1:]) != tuple(st.shape[1:]) or not st.is_contiguous():
+            raise RuntimeError("ring_append_fields: field %d rows %s do not match storage %s" % (i, tuple(r.shape), tuple(st.shape)))
+        r = r.contiguous()
+        if i == done_field:
+            if st.dtype != torch.float32 or r.dtype not in (torch.bool, torch.uint8):
+                raise RuntimeError("ring_append_fields: done field needs bool/uint8 rows and float32 storage")
+            r = r.view(torch.uint8)
+            table[i] = _cabi.Field(r.data_ptr(), st.data_ptr(), r[0].numel() if n else 1, _cabi.FIELD_DONE_TO_DISCOUNT, gamma)
+        else:
+            if r.dtype != st.dtype:
+                raise RuntimeError("ring_append_fields: field %d dtype %s != storage %s" % (i, r.dtype, st.dtype))
+            table[i] = _cabi.Field(r.data_ptr(), st.data_ptr(), (r[0].numel() * r.element_size()) if n else 1, _cabi.FIELD_COPY, 0.0)
+        keep.append(r)
+    _cabi.call("b200rl_ring_append_fields", table, len(rows), cap, count, n, _stream())
+    return keep  # the caller keeps the (possibly re-laid-out) sources alive until the stream has consumed them
+
+
+def gather_fields(storages, idx, outs=None):
+    """Multi-field K5: ``outs[f][i] = storages[f][idx[i]]`` for all fields in ONE launch."""
+    _require_cuda(*storages, idx)
+    idx = idx if (idx.dtype == torch.int64 and idx.is_contiguous()) else idx.long().contiguous()
+    n, nrows = idx.numel(), storages[0].shape[0]
+    if outs is None:
+        outs = [torch.empty((n,) + tuple(st.shape[1:]), dtype=st.dtype, device=st.device) for st in storages]
+    table = (_cabi.Field * len(storages))()
+    for i, (st, o) in enumerate(zip(storages, outs)):
+        if not st.is_contiguous() or st.shape[0] != nrows or not o.is_contiguous():
+            raise RuntimeError("gather_fields: field %d must be contiguous with %d rows" % (i, nrows))
+        table[i] = _cabi.Field(st.data_ptr(), o.data_ptr(), (st[0].numel() * st.element_size()) if nrows else 1,
+                               _cabi.FIELD_COPY, 0.0)
+    _cabi.call("b200rl_gather_fields", table, len(storages), idx.data_ptr(), n, nrows, _stream())
+    return outs
+
+
+def n_step_returns(r_t, discount_t, v_t, n, lambda_=1.0):
+    """N4.  ``[B,T]`` views (batch- or time-major) -> n-step bootstrapped returns, same major order."""
+    _require_cuda(r_t, discount_t, v_t)
+    xs, (B, T, sb, st, tm) = _same_view([r_t.detach(), discount_t.detach(), v_t.detach()])
+    if (tm and st != B) or (not tm and sb != T):
+        xs = [x.t().contiguous().t() if tm else x.contiguous() for x in xs]
+        B, T, sb, st, tm = _major(xs[0])
+    out = _compact_like(B, T, tm, xs[0].device)
+    _cabi.call("b200rl_n_step_returns", *[x.data_ptr() for x in xs], B, T, sb, st, int(n), lambda_,
+               out.data_ptr(), _stream())
+    return out

@@ -63,14 +63,38 @@ class CircularBuffer:
         rows = [r.to(self.device, non_blocking=True) for r in rows]
         if self.fields is None:
             self._alloc(rows)
-        for dst, r in zip(self.fields, rows):
-            ops.ring_append(dst, self.count, r)
+        if len(rows) <= 8:
+            ops.ring_append_fields(self.fields, self.count, rows)           # one launch for all fields
+        else:
+            for dst, r in zip(self.fields, rows):
+                ops.ring_append(dst, self.count, r)
         keys = range(self.count, self.count + n)
         self.count += n
         return keys
 
     def gather(self, slots: torch.Tensor) -> List[torch.Tensor]:
+        if len(self.fields) <= 8:
+            return ops.gather_fields(self.fields, slots)                    # one launch for all fields
         return [ops.gather_rows(f, slots) for f in self.fields]
+
+    def extend_rollouts(self, rows: Sequence[torch.Tensor], done_field: int, gamma: float) -> range:
+        """Device-side ``_make_replay`` + append (reference ``agents/impala/learning.py:71-80``): ``rows`` are the
+        stacked actor outputs ``[n, T, ...]`` with bool ``done`` flags at ``done_field``; the stored field is
+        ``discount_t = logical_not(done) * gamma`` (float32), computed inside the one append launch."""
+        n = rows[0].shape[0]
+        if n > self.capacity:
+            rows = [r[n - self.capacity:] for r in rows]
+            self.count += n - self.capacity
+            n = self.capacity
+        rows = [r.to(self.device, non_blocking=True) for r in rows]
+        if self.fields is None:
+            self.fields = [torch.empty((self.capacity,) + tuple(r.shape[1:]),
+                                       dtype=torch.float32 if i == done_field else r.dtype, device=self.device)
+                           for i, r in enumerate(rows)]
+        ops.ring_append_fields(self.fields, self.count, rows, done_field=done_field, gamma=gamma)
+        keys = range(self.count, self.count + n)
+        self.count += n
+        return keys
 
 
 class ReplayBuffer:
@@ -91,6 +115,11 @@ class ReplayBuffer:
         if len(items) == 0:
             return range(0)
         return self.storage.extend_stacked([torch.stack(f) for f in zip(*items)])
+
+    def extend_rollouts(self, s, a, r, done, pi_ref, gamma: float = 0.99):
+        """Batched ``ImpalaActor._make_replay`` + ``async_append`` for ``n`` stacked rollouts ``[n,T,...]``
+        (reference ``agents/impala/learning.py:71-80``): stores ``[s, a, r, logical_not(done)*gamma, pi_ref]``."""
+        return self.storage.extend_rollouts([s, a, r, done, pi_ref], done_field=3, gamma=gamma)
 
     # -- learner side (reference agents/impala/learning.py:117,121) -------------------------------
     def sample(self, n: int):

@@ -65,3 +65,13 @@ def truncated_generalized_advantage_estimation(r_t, discount_t, lambda_, values,
     if time_major:
         return ops.gae(r_t.t(), discount_t.t(), values.t(), float(lambda_)).t()
     return ops.gae(r_t, discount_t, values, float(lambda_))
+
+
+def n_step_bootstrapped_returns(r_t, discount_t, v_t, n, lambda_t=1.0, time_major=False):
+    """Batched ``rlego.n_step_bootstrapped_returns`` (reference ``agents/dqn/learning.py:62,79``); a 1-D
+    ``[T]`` rollout is accepted as in the reference.  Not differentiable (targets)."""
+    if r_t.dim() == 1:
+        return ops.n_step_returns(r_t[None], discount_t[None], v_t[None], n, float(lambda_t))[0]
+    if time_major:
+        return ops.n_step_returns(r_t.t(), discount_t.t(), v_t.t(), n, float(lambda_t)).t()
+    return ops.n_step_returns(r_t, discount_t, v_t, n, float(lambda_t))

@@ -118,6 +118,14 @@ int32_t b200rl_gae(
     int64_t B, int64_t T, int64_t stride_b, int64_t stride_t,
     int64_t vstride_b, int64_t vstride_t, double lambda_, float *out, void *stream);
 
+/* N4 -- rlego.n_step_bootstrapped_returns(r_t, discount_t, v_t, n, lambda_t) (reference
+ * agents/dqn/learning.py:62,79), batched over B columns; out[b,t] bootstraps from v_t[b, t+n-1]
+ * (v_t[b, T-1] past the end). */
+int32_t b200rl_n_step_returns(
+    const float *r_t, const float *discount_t, const float *v_t,
+    int64_t B, int64_t T, int64_t stride_b, int64_t stride_t, int64_t n, double lambda_,
+    float *out, void *stream);
+
 /* K3 -- replaces losses.ppo_loss after model(s) + backward w.r.t. model outputs
  * (reference losses.py:134-155, caller agents/ppo/learning.py:132-134).
  * Flat minibatch: logits, pi_ref [N,A]; actions, v_target, v [N].
@@ -149,6 +157,30 @@ int32_t b200rl_gather_rows(
 int32_t b200rl_ring_append(
     void *storage, int64_t row_bytes, int64_t capacity, int64_t count,
     const void *rows, int64_t n, void *stream);
+
+/* N2 -- device-side rollout ingestion: replaces ImpalaActor._make_replay + replay.async_append
+ * (reference agents/impala/learning.py:71-80; PPO: agents/ppo/learning.py:59-69): all fields of n stacked
+ * rollouts go to their ring storages (slot (count + j) % capacity) in ONE launch, and a field of kind
+ * B200RL_FIELD_DONE_TO_DISCOUNT converts uint8/bool done flags to float32 `logical_not(done) * gamma`
+ * on the way (row_bytes = flags per row; the destination row holds row_bytes floats).
+ * `fields` is a HOST array (copied into the launch parameters). */
+#define B200RL_FIELD_COPY 0
+#define B200RL_FIELD_DONE_TO_DISCOUNT 1
+typedef struct {
+    const void *src;    /* device, n rows of row_bytes bytes */
+    void *dst;          /* device ring storage of `capacity` rows */
+    int64_t row_bytes;  /* bytes per source row */
+    int32_t kind;       /* B200RL_FIELD_* */
+    float gamma;        /* DONE_TO_DISCOUNT only */
+} b200rl_field_t;
+int32_t b200rl_ring_append_fields(
+    const b200rl_field_t *fields, int32_t n_fields, int64_t capacity, int64_t count, int64_t n, void *stream);
+
+/* Multi-field K5: dst_f[i] = src_f[idx[i]] for every field f in ONE launch (src = ring storage of nrows
+ * rows, dst = the [n, ...] batch tensor; kind must be B200RL_FIELD_COPY).  Replaces the per-field
+ * CircularBuffer.__getitem__ + collate of a sampled batch (reference agents/impala/learning.py:121-123,142). */
+int32_t b200rl_gather_fields(
+    const b200rl_field_t *fields, int32_t n_fields, const int64_t *idx, int64_t n, int64_t nrows, void *stream);
 
 /* K6 -- replaces clip_grad_norm_(params, max_norm) + optimizer.step() (torch.optim.Adam, no weight decay,
  * no amsgrad) at reference agents/impala/learning.py:172-176 and agents/ppo/learning.py:136-140 for

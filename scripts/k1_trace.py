@@ -6,10 +6,13 @@ import torch
 from impala_b200 import ops, synth, _cabi
 
 B, T, A = 4096, 20, 15
+TM = len(sys.argv) > 1 and sys.argv[1] == "time_major"
 dev = torch.device("cuda", 0)
 sets = []
 for i in range(24):
     d = synth.impala_rollout(B, T, A, seed=100 + i)
+    if TM:
+        d = {k: v.transpose(0, 1).contiguous() for k, v in d.items()}
     g = {k: v.to(dev) for k, v in d.items()}
     sets.append((g, (torch.empty(8, device=dev), torch.empty_like(g["logits"]), torch.empty_like(g["values"]))))
 off = _cabi.load().b200rl_trace_offset_bytes()
@@ -18,12 +21,16 @@ names = ["start", "landed", "stats", "scan", "grads", "reduce", "drained"]
 for mode, flags in flags_list.items():
     def launch(i):
         g, out = sets[i % len(sets)]
-        ops.impala_loss_fwdbwd(g["logits"], g["values"], g["a"], g["r"], g["discount"], g["pi_ref"], flags=flags, out=out)
+        ops.impala_loss_fwdbwd(g["logits"], g["values"], g["a"], g["r"], g["discount"], g["pi_ref"], flags=flags, time_major=TM, out=out)
     for i in range(5):
         launch(i)
     torch.cuda.synchronize()
+    cap = torch.cuda.Stream(dev)
+    with torch.cuda.stream(cap):
+        ops.workspace(dev)          # the capture stream's workspace must exist before capture
+    torch.cuda.synchronize()
     gr = torch.cuda.CUDAGraph()
-    with torch.cuda.graph(gr):
+    with torch.cuda.graph(gr, stream=cap):
         for i in range(20):
             launch(i)
     gr.replay(); torch.cuda.synchronize()

@@ -58,6 +58,15 @@ def test_argument_errors_are_reported_without_a_gpu():
     assert lib.b200rl_ring_append(one, 16, 4, 0, one, 5, None) == -2        # n > capacity
     assert lib.b200rl_ppo_loss_fwdbwd(one, one, one, one, one, 0, 15, 0, .1, .01, 0, one, one, one, one, None) == -2
     assert lib.b200rl_lambda_returns(one, one, one, 4, 8, 3, 5, .95, one, None) == -4
+    fields = (_cabi.Field * 2)(_cabi.Field(16, 16, 64, 0, 0.), _cabi.Field(16, 16, 4, 7, 0.))
+    assert lib.b200rl_ring_append_fields(fields, 2, 8, 0, 4, None) == -2 and "kind" in _cabi.last_error()
+    assert lib.b200rl_ring_append_fields(fields, 1, 8, 0, 9, None) == -2            # n > capacity
+    assert lib.b200rl_ring_append_fields(fields, 9, 8, 0, 1, None) == -2            # too many fields
+    disc = (_cabi.Field * 1)(_cabi.Field(16, 16, 4, 1, .99))
+    assert lib.b200rl_gather_fields(disc, 1, one, 4, 8, None) == -2                  # discount kind is append-only
+    assert lib.b200rl_gather_fields(fields, 1, one, 0, 8, None) == 0                 # empty gather is a no-op
+    assert lib.b200rl_clip_adam_step(one, one, one, one, 0, .5, 1e-4, .9, .999, 1e-5, 1, one, one, None) == -2
+    assert lib.b200rl_clip_adam_step(one, one, one, one, 8, .5, 1e-4, .9, .999, 1e-5, 0, one, one, None) == -2
     with pytest.raises(RuntimeError, match="status -2"):
         _cabi.call("b200rl_sample_uniform", 1, 0, 0, 8, 0, 16, None)
 

@@ -166,3 +166,25 @@ def test_batched_vtrace_dropin_forward_backward(B, T, lam):
     # per-sequence form, the function the reference vmaps
     one = vtrace.vtrace_td_error_and_advantage(vg[0, :-1], vg[0, 1:], g["r"][0, :-1], g["discount"][0, :-1], rg[0, :-1], **kw)
     assert_close(one[0], want[0][0], "per-sequence adv", rtol=1e-5, atol=2e-6)
+
+
+@pytest.mark.parametrize("B,T,n", [(64, 20, 3), (1, 1, 1), (5, 7, 1), (33, 129, 5), (4, 6, 6), (3, 5, 9), (100, 256, 3)])
+@pytest.mark.parametrize("lam", [1.0, 0.9])
+@pytest.mark.parametrize("time_major", [False, True])
+def test_n_step_returns_bit_exact(B, T, n, lam, time_major):
+    """N4: rlego.n_step_bootstrapped_returns (reference agents/dqn/learning.py:62), batched; bit-exact vs the oracle."""
+    from oracle import rlego_ref
+    d = synth.returns_rollout(B, T, seed=B * 100 + T + n)
+    want = rlego_ref.batched_loop(rlego_ref.n_step_bootstrapped_returns, d["r"], d["discount"], d["v"], n=n, lambda_t=lam) \
+        if n - 1 <= T else None
+    if want is None:      # rlax pads with min(n-1, T): every target collapses to the padded window
+        pytest.skip("n - 1 > T is outside the oracle restatement")
+    g = {k: v.cuda() for k, v in d.items()}
+    if time_major:
+        got = vtrace.n_step_bootstrapped_returns(g["r"].t().contiguous(), g["discount"].t().contiguous(),
+                                                 g["v"].t().contiguous(), n, lam, time_major=True).t()
+    else:
+        got = vtrace.n_step_bootstrapped_returns(g["r"], g["discount"], g["v"], n, lam)
+    assert torch.equal(got.cpu(), want)
+    one = vtrace.n_step_bootstrapped_returns(g["r"][0], g["discount"][0], g["v"][0], n, lam)   # reference's [T] form
+    assert torch.equal(one.cpu(), want[0])

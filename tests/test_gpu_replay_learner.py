@@ -192,3 +192,45 @@ def test_ppo_learner_step(cuda):
     for k in ("train/loss", "train/entropy", "train/td", "train/pg", "train/target", "train/kl", "train/ratio"):
         assert_close(metrics[k], m[k], k, rtol=1e-4, atol=1e-5)
     _check_step(learner, model, ref_model)
+
+
+def test_rollout_ingestion_fused_discount_and_multifield_gather(cuda):
+    """N2: stacked actor outputs -> ring storage in one launch with discount = logical_not(done) * gamma
+    (reference agents/impala/learning.py:77-80), wrap-around included; then the multi-field gather."""
+    T, A, cap, gamma = 5, 6, 7, 0.99
+    rb = replay.ReplayBuffer(replay.CircularBuffer(cap, device=cuda), replay.UniformSampler())
+    rb.sampler.reset(11)
+    g = torch.Generator().manual_seed(3)
+    want = None
+    total = 0
+    for n in (3, 2, 4, 7, 1):                                   # crosses the end of the ring several times
+        s = torch.randint(0, 256, (n, T, 3, 8, 8), generator=g, dtype=torch.uint8)
+        a = torch.randint(0, A, (n, T, 1), generator=g)
+        r = torch.randn(n, T, 1, generator=g)
+        d = torch.rand(n, T, 1, generator=g) < 0.3
+        pi = torch.randn(n, T, A, generator=g)
+        keys = rb.extend_rollouts(s, a, r, d, pi, gamma)
+        assert list(keys) == list(range(total, total + n))
+        ref_fields = [s, a, r, torch.logical_not(d) * gamma, pi]          # the reference's _make_replay
+        if want is None:
+            want = [torch.zeros((cap,) + tuple(f.shape[1:]), dtype=f.dtype) for f in ref_fields]
+        for j in range(n):
+            for w, f in zip(want, ref_fields):
+                w[(total + j) % cap] = f[j]
+        total += n
+        occupied = min(total, cap)
+        for f, w in zip(rb.storage.fields, want):
+            assert f.dtype == w.dtype
+            got = f.cpu()
+            if total < cap:
+                assert torch.equal(got[:occupied], w[:occupied])
+            else:
+                assert torch.equal(got, w)
+    keys, batch, probs = rb.sample(33)
+    slots = torch.from_numpy(replay_ref.sample_uniform(11, 0, 0, 33, cap).astype(np.int64))
+    for b, w in zip(batch, want):
+        assert torch.equal(b.cpu(), w[slots])
+    # per-field launches and the fused one agree
+    singles = [ops.gather_rows(f, slots.to(cuda)) for f in rb.storage.fields]
+    for b, s1 in zip(batch, singles):
+        assert torch.equal(b, s1)
