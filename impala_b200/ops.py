@@ -299,3 +299,26 @@ def n_step_returns(r_t, discount_t, v_t, n, lambda_=1.0):
     _cabi.call("b200rl_n_step_returns", *[x.data_ptr() for x in xs], B, T, sb, st, int(n), lambda_,
                out.data_ptr(), _stream())
     return out
+
+
+def sumtree_update(tree, idx, value):
+    """N3.  ``tree``: float64 ``[2 * leaves]`` (leaves a power of two); leaf ``idx[i] = value[i]``, sums refreshed."""
+    _require_cuda(tree, idx, value)
+    if tree.dtype != torch.float64 or not tree.is_contiguous():
+        raise RuntimeError("sumtree_update: tree must be a contiguous float64 tensor")
+    idx = idx if (idx.dtype == torch.int64 and idx.is_contiguous()) else idx.long().contiguous()
+    value = value if (value.dtype == torch.float64 and value.is_contiguous()) else value.double().contiguous()
+    if idx.numel() != value.numel():
+        raise RuntimeError("sumtree_update: %d indices vs %d values" % (idx.numel(), value.numel()))
+    _cabi.call("b200rl_sumtree_update", tree.data_ptr(), tree.numel() // 2, idx.data_ptr(), value.data_ptr(),
+               idx.numel(), _stream())
+
+
+def sumtree_sample(tree, size, seed, stream_id, draw_offset, n, with_prob=True):
+    """N3.  ``n`` indices in ``[0,size)`` drawn proportionally to the leaves, and ``leaf / total`` (float32)."""
+    _require_cuda(tree)
+    idx = torch.empty(n, dtype=torch.int64, device=tree.device)
+    prob = torch.empty(n, dtype=torch.float32, device=tree.device) if with_prob else None
+    _cabi.call("b200rl_sumtree_sample", tree.data_ptr(), tree.numel() // 2, size, seed, stream_id, draw_offset, n,
+               idx.data_ptr(), _cabi.ptr(prob), _stream())
+    return idx, prob

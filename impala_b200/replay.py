@@ -36,6 +36,40 @@ class UniformSampler:
         return idx
 
 
+class PrioritizedSampler:
+    """rlmeta ``PrioritizedSampler(priority_exponent)`` (reference ``agents/dqn/builder.py:83-90``): a device
+    sum tree over the buffer slots; ``sample`` draws slots with probability ``p_i^alpha / sum`` and returns
+    those probabilities (the learner turns them into importance weights, ``agents/dqn/learning.py:164-166``)."""
+
+    prioritized = True
+
+    def __init__(self, priority_exponent: float = 1.0, stream_id: int = 0):
+        self.alpha, self.seed, self.stream_id, self.draws = float(priority_exponent), 0, int(stream_id), 0
+        self.tree = None
+
+    def reset(self, seed: int) -> None:
+        self.seed, self.draws = int(seed), 0
+
+    def bind(self, capacity: int, device) -> None:
+        leaves = 1
+        while leaves < capacity:
+            leaves *= 2
+        self.tree = torch.zeros(2 * leaves, dtype=torch.float64, device=device)
+
+    def update(self, slots: torch.Tensor, priorities: torch.Tensor) -> None:
+        value = priorities.to(self.tree.device, torch.float64).reshape(-1)
+        if self.alpha != 1.0:
+            value = value.pow(self.alpha)
+        ops.sumtree_update(self.tree, slots.to(self.tree.device).reshape(-1), value)
+
+    def sample(self, n: int, size: int, device, out=None):
+        if size <= 0:
+            raise RuntimeError("sample from an empty replay buffer")
+        idx, prob = ops.sumtree_sample(self.tree, size, self.seed, self.stream_id, self.draws, n)
+        self.draws += n
+        return idx, prob
+
+
 class CircularBuffer:
     """rlmeta ``CircularBuffer(capacity, collate_fn=None)``: key = append count, slot = key % capacity."""
 
@@ -104,17 +138,49 @@ class ReplayBuffer:
         self.storage, self.sampler, self.with_keys = storage, sampler, with_keys
 
     # -- writer side (reference agents/impala/learning.py:75, agents/ppo/learning.py:63) ----------
-    def append(self, item: Sequence[torch.Tensor]):
-        """One item = one list of per-field tensors (IMPALA: a whole ``[T,...]`` rollout)."""
-        return self.storage.extend_stacked([f.unsqueeze(0) for f in item])
+    def _prioritized(self) -> bool:
+        return getattr(self.sampler, "prioritized", False)
 
-    def extend(self, items):
-        """A list of items (each a list of per-field tensors), or a tuple of stacked fields."""
+    def _set_priorities(self, keys: range, priorities) -> None:
+        if not self._prioritized():
+            return
+        if self.sampler.tree is None:
+            self.sampler.bind(self.storage.capacity, self.storage.device)
+        n = len(keys)
+        if priorities is None:                       # rlmeta: new items enter with priority 1
+            priorities = torch.ones(n, dtype=torch.float64, device=self.storage.device)
+        priorities = torch.as_tensor(priorities).reshape(-1)[-n:]           # rows beyond capacity were dropped
+        slots = torch.arange(keys.start, keys.stop, device=self.storage.device) % self.storage.capacity
+        self.sampler.update(slots, priorities)
+
+    def append(self, item: Sequence[torch.Tensor], priority=None):
+        """One item = one list of per-field tensors (IMPALA: a whole ``[T,...]`` rollout)."""
+        keys = self.storage.extend_stacked([f.unsqueeze(0) for f in item])
+        self._set_priorities(keys, None if priority is None else torch.as_tensor([priority]))
+        return keys
+
+    def extend(self, items, priorities=None):
+        """A list of items (each a list of per-field tensors), or a tuple of stacked fields; ``priorities`` as at
+        reference ``agents/dqn/learning.py:54`` (prioritized sampler only)."""
         if isinstance(items, tuple):
-            return self.storage.extend_stacked(list(items))
-        if len(items) == 0:
+            keys = self.storage.extend_stacked(list(items))
+        elif len(items) == 0:
             return range(0)
-        return self.storage.extend_stacked([torch.stack(f) for f in zip(*items)])
+        else:
+            keys = self.storage.extend_stacked([torch.stack(f) for f in zip(*items)])
+        self._set_priorities(keys, priorities)
+        return keys
+
+    def update(self, keys: torch.Tensor, priorities: torch.Tensor) -> None:
+        """``replay_buffer.update(keys, priorities)`` (reference ``agents/dqn/learning.py:184``): keys of rows
+        that have been overwritten since they were sampled are ignored."""
+        if not self._prioritized():
+            return
+        st = self.storage
+        keys = keys.to(st.device).reshape(-1)
+        live = keys >= max(st.count - st.capacity, 0)
+        slots = torch.where(live, keys % st.capacity, torch.full_like(keys, -1))   # -1: skipped by the kernel
+        self.sampler.update(slots, priorities)
 
     def extend_rollouts(self, s, a, r, done, pi_ref, gamma: float = 0.99):
         """Batched ``ImpalaActor._make_replay`` + ``async_append`` for ``n`` stacked rollouts ``[n,T,...]``
@@ -126,13 +192,17 @@ class ReplayBuffer:
         """``(keys, batch, probabilities)``; ``batch`` = list of stacked ``[n, ...]`` device tensors."""
         st = self.storage
         size = st.size
-        slots = self.sampler.sample(n, size, st.device)
+        if self._prioritized():
+            slots, probs = self.sampler.sample(n, size, st.device)
+        else:
+            slots, probs = self.sampler.sample(n, size, st.device), None
         batch = st.gather(slots)
         if not self.with_keys:
             return slots, batch, None
         oldest = max(st.count - st.capacity, 0)
         keys = oldest + torch.remainder(slots - oldest, st.capacity)
-        probs = torch.full((n,), 1.0 / size, dtype=torch.float32, device=st.device)
+        if probs is None:
+            probs = torch.full((n,), 1.0 / size, dtype=torch.float32, device=st.device)
         return keys, batch, probs
 
     def warm_up(self, learning_starts: Optional[int] = None) -> None:

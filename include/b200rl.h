@@ -182,6 +182,18 @@ int32_t b200rl_ring_append_fields(
 int32_t b200rl_gather_fields(
     const b200rl_field_t *fields, int32_t n_fields, const int64_t *idx, int64_t n, int64_t nrows, void *stream);
 
+/* N3 -- prioritized sampling (replaces rlmeta PrioritizedSampler, reference agents/dqn/builder.py:83-90;
+ * extend/sample/update at agents/dqn/learning.py:54,122,184).  `tree` is a caller-owned, zero-initialised
+ * fp64 array of 2*leaves nodes (leaves = power of two >= capacity; node 1 = root, leaf j at leaves + j).
+ * update: tree leaf idx[i] = value[i] (the already exponentiated priority), ancestors re-summed.
+ * sample: n draws of stream (seed, stream_id) starting at draw_offset -> out_idx in [0,size), out_prob =
+ * leaf / total (may be NULL).  Stream definition: oracle/replay_ref.py (bit-exact). */
+int32_t b200rl_sumtree_update(
+    double *tree, int64_t leaves, const int64_t *idx, const double *value, int64_t n, void *stream);
+int32_t b200rl_sumtree_sample(
+    const double *tree, int64_t leaves, int64_t size, uint64_t seed, uint32_t stream_id, uint64_t draw_offset,
+    int64_t n, int64_t *out_idx, float *out_prob, void *stream);
+
 /* K6 -- replaces clip_grad_norm_(params, max_norm) + optimizer.step() (torch.optim.Adam, no weight decay,
  * no amsgrad) at reference agents/impala/learning.py:172-176 and agents/ppo/learning.py:136-140 for
  * parameters, gradients and Adam moments held in FLAT fp32 buffers of n elements.  In place: grads are

@@ -148,3 +148,50 @@ class ReplayBuffer:
         keys = oldest + ((slots - oldest) % self.storage.capacity)
         probs = np.full(n, 1.0 / size, dtype=np.float32) if n else np.zeros(0, np.float32)
         return keys, self.storage.gather(slots), probs
+
+
+# --------------------------------------------------------------------------------------------
+# Prioritized sampling: specification of the device sum tree.
+# rlmeta PrioritizedSampler (reference agents/dqn/builder.py:83-90) is unobtainable -> PARITY UNPINNED;
+# what is pinned is this specification, reproduced bit for bit by impala_b200/csrc/sumtree.cu.
+# --------------------------------------------------------------------------------------------
+class SumTree:
+    """Complete binary tree of float64 sums over ``leaves`` (power of two) slots; node i = node 2i + node 2i+1."""
+
+    def __init__(self, capacity):
+        self.leaves = 1
+        while self.leaves < capacity:
+            self.leaves *= 2
+        self.tree = np.zeros(2 * self.leaves, dtype=np.float64)
+
+    def update(self, idx, value):
+        idx = np.asarray(idx, dtype=np.int64)
+        self.tree[self.leaves + idx] = np.asarray(value, dtype=np.float64)
+        nodes = np.unique((self.leaves + idx) >> 1)
+        while nodes.size and nodes[0] >= 1:
+            self.tree[nodes] = self.tree[2 * nodes] + self.tree[2 * nodes + 1]
+            if nodes[0] == 1:
+                break
+            nodes = np.unique(nodes >> 1)
+
+    def sample(self, seed, stream_id, draw_offset, n, size):
+        g = np.arange(n, dtype=np.uint64) + np.uint64(draw_offset)
+        o0, o1, _, _ = philox4x32_10_vec(g & np.uint64(MASK32), g >> np.uint64(32),
+                                         np.full(n, stream_id & MASK32, dtype=np.uint64), np.zeros(n, dtype=np.uint64),
+                                         seed & MASK32, (seed >> 32) & MASK32)
+        x64 = o0 | (o1 << np.uint64(32))
+        total = self.tree[1]
+        mass = ((x64 >> np.uint64(11)).astype(np.float64) * 2.0 ** -53) * total
+        out = np.zeros(n, dtype=np.int64)
+        for i in range(n):
+            node, m = 1, mass[i]
+            while node < self.leaves:
+                left = self.tree[2 * node]
+                if m < left:
+                    node = 2 * node
+                else:
+                    m = m - left
+                    node = 2 * node + 1
+            out[i] = min(node - self.leaves, size - 1)
+        prob = (self.tree[self.leaves + out] / total).astype(np.float32)
+        return out, prob

@@ -234,3 +234,57 @@ def test_rollout_ingestion_fused_discount_and_multifield_gather(cuda):
     singles = [ops.gather_rows(f, slots.to(cuda)) for f in rb.storage.fields]
     for b, s1 in zip(batch, singles):
         assert torch.equal(b, s1)
+
+
+def test_sumtree_bit_exact_vs_spec(cuda):
+    """N3: device sum tree + inverse-CDF sampling vs the specification in oracle/replay_ref.py (bit-exact:
+    tree nodes, sampled indices and probabilities), incremental and bulk updates."""
+    rng = np.random.default_rng(0)
+    for cap in (1, 5, 1000, 40_000):
+        ot = replay_ref.SumTree(cap)
+        tree = torch.zeros(2 * ot.leaves, dtype=torch.float64, device=cuda)
+        for n in (min(cap, 7), min(cap, 333), cap):                  # cap = 40,000 > 16,384 takes the bulk path
+            idx = rng.choice(cap, size=n, replace=False).astype(np.int64)
+            val = rng.random(n) ** 3 + 1e-3
+            ot.update(idx, val)
+            ops.sumtree_update(tree, torch.from_numpy(idx).to(cuda), torch.from_numpy(val).to(cuda))
+            assert np.array_equal(tree.cpu().numpy(), ot.tree)
+        size = cap
+        want_idx, want_p = ot.sample(123, 2, 10**9, 4096, size)
+        got_idx, got_p = ops.sumtree_sample(tree, size, 123, 2, 10**9, 4096)
+        assert np.array_equal(got_idx.cpu().numpy(), want_idx)
+        assert np.array_equal(got_p.cpu().numpy(), want_p)
+    # proportionality: slot frequencies follow the priorities
+    tree = torch.zeros(16, dtype=torch.float64, device=cuda)
+    pri = torch.tensor([1., 2., 3., 4., 0., 10.], dtype=torch.float64, device=cuda)
+    ops.sumtree_update(tree, torch.arange(6, device=cuda), pri)
+    idx, p = ops.sumtree_sample(tree, 6, 7, 0, 0, 200_000)
+    freq = torch.bincount(idx, minlength=6).double() / idx.numel()
+    assert torch.allclose(freq, pri / pri.sum(), atol=5e-3) and freq[4] == 0
+    assert torch.allclose(p.double(), (pri / pri.sum())[idx], rtol=1e-6)
+
+
+def test_prioritized_replay_buffer_surface(cuda):
+    """rlmeta surface used by the Ape-X agents (reference agents/dqn/learning.py:54,122,184): extend with
+    priorities, sample -> (keys, batch, probabilities), update(keys, priorities) ignoring evicted keys."""
+    cap = 8
+    rb = replay.ReplayBuffer(replay.CircularBuffer(cap, collate_fn=torch.cat, device=cuda),
+                             replay.PrioritizedSampler(priority_exponent=0.6))
+    rb.sampler.reset(5)
+    obs = torch.arange(12, dtype=torch.float32).reshape(12, 1)
+    keys = rb.extend((obs[:6], torch.arange(6)), priorities=torch.arange(1, 7, dtype=torch.float32))
+    assert list(keys) == list(range(6))
+    ot = replay_ref.SumTree(cap)
+    vals = rb.sampler.tree[rb.sampler.tree.numel() // 2:][:6].cpu().numpy()          # device pow(alpha), as stored
+    assert np.allclose(vals, np.arange(1, 7, dtype=np.float64) ** 0.6, rtol=1e-14)
+    ot.update(np.arange(6), vals)
+    k, batch, probs = rb.sample(64)
+    want_idx, want_p = ot.sample(5, 0, 0, 64, 6)
+    assert np.array_equal(k.cpu().numpy(), want_idx) and np.array_equal(probs.cpu().numpy(), want_p)
+    assert torch.equal(batch[0].cpu(), obs[:6][torch.from_numpy(want_idx)])
+    rb.extend((obs[6:], torch.arange(6, 12)))                                         # wraps: keys 0..3 evicted
+    rb.update(torch.tensor([0, 3, 4, 11]), torch.tensor([100., 100., 2., 3.]))        # 0 and 3 are stale
+    leaves = rb.sampler.tree[rb.sampler.tree.numel() // 2:].cpu().numpy()
+    assert np.allclose(leaves[4], 2. ** 0.6) and np.allclose(leaves[11 % cap], 3. ** 0.6)
+    assert np.allclose(leaves[0], 1.0) and np.allclose(leaves[1], 1.0)                # new rows entered at priority 1; stale keys 0, 3 ignored
+    assert np.isclose(rb.sampler.tree[1].item(), leaves.sum())

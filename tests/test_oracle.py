@@ -226,3 +226,23 @@ def test_golden_vectors_match_oracle():
     zr = np.load(os.path.join(GOLDEN, "replay_indices.npz"))
     assert np.array_equal(zr["idx_seed123_1M"], replay_ref.sample_uniform(123, 0, 0, 4096, 1_000_000))
     assert np.array_equal(zr["idx_stream3_big_offset"], c_oracle.sample_uniform(123, 3, 10_000_000_000, 257, 1000))
+
+
+def test_sumtree_spec_properties():
+    """N3 specification (oracle/replay_ref.SumTree): every node is the sum of its children, the root is the
+    total, sampling is proportional to the leaves and never returns an empty slot or an index >= size."""
+    rng = np.random.default_rng(1)
+    t = replay_ref.SumTree(10)
+    assert t.leaves == 16
+    t.update(np.arange(10), rng.random(10))
+    t.update(np.array([3, 7]), np.array([0.0, 5.0]))
+    for node in range(1, t.leaves):
+        assert t.tree[node] == t.tree[2 * node] + t.tree[2 * node + 1]
+    assert np.isclose(t.tree[1], t.tree[t.leaves:].sum())
+    idx, prob = t.sample(9, 1, 0, 20000, 10)
+    assert idx.min() >= 0 and idx.max() < 10 and not (idx == 3).any()
+    freq = np.bincount(idx, minlength=10) / idx.size
+    assert np.allclose(freq, t.tree[t.leaves:t.leaves + 10] / t.tree[1], atol=1.5e-2)
+    assert np.allclose(prob, (t.tree[t.leaves + idx] / t.tree[1]).astype(np.float32))
+    i2, _ = t.sample(9, 1, 0, 100, 10)
+    assert np.array_equal(i2, idx[:100])                      # counter-based: same draws, same answers
