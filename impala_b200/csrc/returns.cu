@@ -17,6 +17,8 @@
 
 namespace b200rl {
 
+int env_int(const char *name, int dflt);
+
 enum { MODE_LAMBDA_RETURNS = 0, MODE_GAE = 1 };
 
 struct ScanParams {
@@ -92,6 +94,75 @@ __global__ void __launch_bounds__(512) scan_time_major_kernel(const ScanParams p
     }
 }
 
+// Time-major kernel, shared-memory staged (default when the tile fits: T <= kSmemScanMaxT).
+// A CTA owns 32 adjacent columns x all T steps.  The three input tiles go HBM -> shared memory
+// with 16-byte cp.async (LDGSTS: no registers held while the loads fly, so two CTAs fit per SM
+// and one CTA's loads overlap the other's arithmetic and stores).  Then the same two passes as
+// above, but reading shared memory (lane = column: conflict free): pass 1 composes each warp's
+// chunk map, the maps meet in shared memory, pass 2 re-walks the chunk in the reference's
+// operation order and stores 128-byte lines.
+constexpr int kSmemScanMaxT = 256;
+
+__device__ __forceinline__ void cp_async16(void *smem, const void *gmem, int src_bytes) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem)), "l"(gmem), "r"(src_bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+template <int MODE, int kSmemScanWarps>
+__global__ void __launch_bounds__(kSmemScanWarps * 32) scan_smem_kernel(const ScanParams p) {
+    extern __shared__ __align__(16) float smem_scan[];
+    const int T = p.T, TV = T + (MODE == MODE_GAE ? 1 : 0);
+    float *sr = smem_scan;              // [T][32]
+    float *sd = sr + T * 32;            // [T][32]
+    float *sv = sd + T * 32;            // [TV][32]
+    float *sA = sv + TV * 32;           // [kSmemScanWarps][32]
+    float *sB = sA + kSmemScanWarps * 32;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int b0 = blockIdx.x * 32;
+    // ---- stage: chunk = (row, group of 4 columns); rows are st (vst) elements apart in HBM
+    for (int ch = threadIdx.x; ch < TV * 8; ch += kSmemScanWarps * 32) {
+        const int row = ch >> 3, c4 = (ch & 7) * 4;
+        const int remaining = p.B - (b0 + c4);  // columns left from this chunk's first column
+        const int bytes = remaining >= 4 ? 16 : (remaining > 0 ? remaining * 4 : 0);
+        const long long col = remaining > 0 ? b0 + c4 : 0;  // keep the address valid when nothing is read
+        if (row < T) {
+            cp_async16(sr + row * 32 + c4, p.r + (long long)row * p.st + col, bytes);
+            cp_async16(sd + row * 32 + c4, p.disc + (long long)row * p.st + col, bytes);
+        }
+        cp_async16(sv + row * 32 + c4, p.v + (long long)row * p.vst + col, bytes);
+    }
+    cp_async_wait_all();
+    __syncthreads();
+    const int b = b0 + lane;
+    const bool col_ok = b < p.B;
+    const int L = (T + kSmemScanWarps - 1) / kSmemScanWarps;
+    const int t0 = w * L, t1 = min(T, t0 + L);
+    // pass 1: compose the chunk's map y_in -> Bc + Ac * y_in (one warp: nothing to compose, and the
+    // whole column is one chain in the reference's order -- bit exact)
+    float Ac = 1.f, Bc = 0.f;
+    for (int t = (kSmemScanWarps > 1 ? t1 : t0) - 1; t >= t0; --t) {
+        const float d = sd[t * 32 + lane];
+        const float v1 = (MODE == MODE_GAE) ? sv[(t + 1) * 32 + lane] : 0.f;
+        const float a = p.lambda_ * d;
+        const float bb = scan_step<MODE>(sr[t * 32 + lane], d, sv[t * 32 + lane], v1, p.lambda_, p.one_minus_lambda, 0.f);
+        Bc = bb + a * Bc;
+        Ac = a * Ac;
+    }
+    sA[w * 32 + lane] = Ac;
+    sB[w * 32 + lane] = Bc;
+    __syncthreads();
+    // carry-in: fold the later chunks, starting from the bootstrap
+    float y = (MODE == MODE_LAMBDA_RETURNS) ? sv[(T - 1) * 32 + lane] : 0.f;
+    for (int k = kSmemScanWarps - 1; k > w; --k) y = sB[k * 32 + lane] + sA[k * 32 + lane] * y;
+    // pass 2: the chunk itself, reference operation order
+    for (int t = t1 - 1; t >= t0; --t) {
+        const float v1 = (MODE == MODE_GAE) ? sv[(t + 1) * 32 + lane] : 0.f;
+        y = scan_step<MODE>(sr[t * 32 + lane], sd[t * 32 + lane], sv[t * 32 + lane], v1, p.lambda_, p.one_minus_lambda, y);
+        if (col_ok) __stcs(p.out + (long long)t * p.st + b, y);
+    }
+}
+
 // Generic layout (batch-major): one thread per column, sequential, reference order.
 template <int MODE>
 __global__ void __launch_bounds__(128) scan_generic_kernel(const ScanParams p) {
@@ -112,6 +183,33 @@ __global__ void __launch_bounds__(128) scan_generic_kernel(const ScanParams p) {
 template <int MODE>
 static int32_t launch_scan(const ScanParams &p, cudaStream_t stream) {
     const bool time_major = (p.sb == 1 && p.vsb == 1);
+    const bool al16 = ((reinterpret_cast<uintptr_t>(p.r) | reinterpret_cast<uintptr_t>(p.disc) |
+                        reinterpret_cast<uintptr_t>(p.v)) % 16 == 0) && p.st % 4 == 0 && p.vst % 4 == 0;
+    if (time_major && al16 && p.T <= kSmemScanMaxT && p.T >= 32 && env_int("B200RL_K2_SMEM", 1)) {
+        const int TV = p.T + (MODE == MODE_GAE ? 1 : 0);
+        const int nw = env_int("B200RL_K2_WARPS", 8);
+        const size_t smem = (size_t)(2 * p.T + TV + 2 * 8) * 32 * 4;
+        static bool configured = false;
+        if (!configured) {
+            cudaError_t e = cudaFuncSetAttribute(scan_smem_kernel<MODE, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(scan_smem_kernel<MODE, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(scan_smem_kernel<MODE, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
+            if (e == cudaSuccess) e = cudaFuncSetAttribute(scan_smem_kernel<MODE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
+            if (e != cudaSuccess) {
+                set_error("cudaFuncSetAttribute(scan_smem_kernel): %s", cudaGetErrorString(e));
+                return (int32_t)e;
+            }
+            configured = true;
+        }
+        const unsigned grid = (unsigned)((p.B + 31) / 32);
+        switch (nw) {
+            case 1: scan_smem_kernel<MODE, 1><<<grid, 32, smem, stream>>>(p); break;
+            case 2: scan_smem_kernel<MODE, 2><<<grid, 64, smem, stream>>>(p); break;
+            case 4: scan_smem_kernel<MODE, 4><<<grid, 128, smem, stream>>>(p); break;
+            default: scan_smem_kernel<MODE, 8><<<grid, 256, smem, stream>>>(p); break;
+        }
+        return check_launch("scan_smem_kernel");
+    }
     if (time_major && p.T <= 16 * 32) {  // <= 16 chunks (warps) of L steps
         const int grid = (p.B + 31) / 32;
         if (p.T <= 16 * 8) {
