@@ -251,7 +251,10 @@ def make_learner(args, device, seed):
     from impala_b200.agents.impala import ImpalaLearner
     B, T, A = args.B or 256, args.T or 20, args.A
     torch.manual_seed(seed)
-    model = models.ActorCritic((3, 64, 64), A, body="impala").to(device)
+    cl = os.environ.get("B200RL_BENCH_CHANNELS_LAST", "1") == "1"
+    model = models.ActorCritic((3, 64, 64), A, body="impala", channels_last=cl).to(device)
+    if cl:
+        model = model.to(memory_format=torch.channels_last)
     if dist.is_initialized():                      # same initial weights on every rank
         for p in model.parameters():
             dist.broadcast(p.data, 0)
@@ -275,7 +278,8 @@ def make_learner(args, device, seed):
         last["m"] = learner.train_step()
 
     desc = {"workload": "full IMPALA learner step (BASELINE config 5)", "T": T, "B_per_gpu": B, "A": A,
-            "model": "IMPALA-CNN body + actor-critic head, 630,352 params, fp32 (cuDNN)",
+            "model": "IMPALA-CNN body + actor-critic head, 630,352 params, fp32 storage, cuDNN convs with torch's default "
+                     "allow_tf32=True (the reference's torch default too), %s" % ("channels_last" if cl else "NCHW"),
             "replay": "%d rollouts device-resident (%.0f MB u8), uniform sample + gather on device" % (cap, cap * T * 12288 / 1e6),
             "l2_policy": "gathered batch 63 MB + activations >> per-step reuse; buffer 246 MB > 126 MB L2"}
     return dict(launch=launch, units=B * T, kernels=5, host=None, e2e_step=None, desc=desc, graph=False,
