@@ -282,8 +282,26 @@ def make_learner(args, device, seed):
                      "allow_tf32=True (the reference's torch default too), %s" % ("channels_last" if cl else "NCHW"),
             "replay": "%d rollouts device-resident (%.0f MB u8), uniform sample + gather on device" % (cap, cap * T * 12288 / 1e6),
             "l2_policy": "gathered batch 63 MB + activations >> per-step reuse; buffer 246 MB > 126 MB L2"}
+    def breakdown():
+        """Per-phase device time of the learner step (mean of 5 profiled steps after the timed region)."""
+        learner.profile = True
+        tot, names = {}, []
+        for _ in range(5):
+            t0 = torch.cuda.Event(enable_timing=True)
+            t0.record()
+            _, batch, _ = rb.sample(B)
+            t1 = torch.cuda.Event(enable_timing=True)
+            t1.record()
+            learner._train_step(batch)
+            bd = learner.breakdown_ms()
+            bd = dict({"replay sample+gather (K4/K5)": t0.elapsed_time(t1)}, **bd)
+            for k, v in bd.items():
+                tot[k] = tot.get(k, 0.0) + v / 5
+        learner.profile = False
+        return {k: round(v, 4) for k, v in tot.items()}
+
     return dict(launch=launch, units=B * T, kernels=5, host=None, e2e_step=None, desc=desc, graph=False,
-                check=lambda: last["m"]["train/loss"])
+                check=lambda: last["m"]["train/loss"], breakdown=breakdown)
 
 
 MAKERS = {"impala_loss": make_impala_loss, "ppo": make_ppo, "replay": make_replay, "learner": make_learner}
@@ -569,6 +587,8 @@ def main():
         "clocks": clocks,
         "gpu_launches": steps * w["kernels"],
     }
+    if w.get("breakdown"):
+        line["config"]["breakdown_ms"] = w["breakdown"]()
     if not args.no_e2e and w["e2e_step"] is not None:
         e_steps = min(steps, 2000)
         dt, h2d, d2h = time_e2e(w, e_steps, min(warmup, 20), device, world_size)

@@ -80,29 +80,55 @@ class ImpalaLearner:
                     [id(q) for q in self._bucket.params] != [id(q) for q in self._optimizer.params]:
                 raise RuntimeError("FusedClipAdam must be built from model.parameters() (same order as the gradient bucket)")
         bucket = self._bucket
+        mark = self._mark
+        mark("start")
         bucket.attach()                                                   # == zero_grad (:141)
         s, a, r, discount_t, pi_ref = self._collate(batch)
         dev = self.device()
         s, a, r, discount_t, pi_ref = (x.to(dev, non_blocking=True) for x in (s, a, r, discount_t, pi_ref))
         B, T = s.shape[0], s.shape[1]
         _, world_size = parallel.world(self._group)
+        mark("collate+h2d")
         pi, values = self._model.forward(s.flatten(0, 1))                 # :143
         pi = pi.reshape(B, T, -1)
         values = values.reshape(B, T)
+        mark("model fwd")
         scalars, dlogits, dvalues = ops.impala_loss_fwdbwd(               # :146-160 fused
             pi, values, a, r, discount_t, pi_ref, self._entropy_coeff, self._lambda,
             n_global_b=B * world_size)
+        mark("K1 loss fwd+bwd")
         torch.autograd.backward([pi, values], [dlogits, dvalues])
+        mark("model bwd")
         bucket.extra.copy_(scalars)
         bucket.allreduce(self._group)                                     # grads + scalars, one collective
+        mark("grad allreduce")
         if isinstance(self._optimizer, optim.FusedClipAdam):               # :172-176 in one launch (K6)
             grad_norm = self._optimizer.step_flat(bucket.grads, self._max_grad_norm)[0]
         else:
             grad_norm = bucket.clip_(self._max_grad_norm)                     # :172-173
             self._optimizer.step()                                            # :176
+        mark("clip+adam")
         sc = bucket.extra
         return {
             "train/loss": sc[ops.S_LOSS], "train/entropy": sc[ops.S_ENTROPY], "train/td": sc[ops.S_TD],
             "train/pg": sc[ops.S_PG], "train/kl": sc[ops.S_KL], "train/ratio": sc[ops.S_RATIO],
             "train/grad_norm": grad_norm,
         }
+
+    # -- optional per-phase device timing (the reference only has host perf_counter deltas, :133-137) --------
+    profile = False
+
+    def _mark(self, name: str) -> None:
+        if not self.profile:
+            return
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record()
+        if name == "start":
+            self._events = []
+        self._events.append((name, ev))
+
+    def breakdown_ms(self) -> Dict[str, float]:
+        """Device time of each phase of the last profiled ``_train_step`` (synchronises)."""
+        torch.cuda.synchronize()
+        ev = getattr(self, "_events", [])
+        return {n1: e0.elapsed_time(e1) for (_, e0), (n1, e1) in zip(ev, ev[1:])}

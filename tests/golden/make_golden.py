@@ -63,7 +63,35 @@ def replay_case(name):
     np.savez_compressed(os.path.join(HERE, name + ".npz"), idx_seed123_1M=idx, idx_stream3_big_offset=idx2)
 
 
+def next_rows_case(name):
+    """SURVEY sec 8f rows built in round 1: n-step returns (N4), sum-tree draws (N3), clip + Adam (N1)."""
+    d = synth.returns_rollout(8, 24, 4100)
+    ns = rlego_ref.batched_loop(rlego_ref.n_step_bootstrapped_returns, d["r"], d["discount"], d["v"], n=3)
+    rng = np.random.default_rng(7)
+    pri = rng.random(1000) ** 2 + 1e-3
+    tree = replay_ref.SumTree(1000)
+    tree.update(np.arange(1000), pri)
+    idx, prob = tree.sample(123, 0, 0, 512, 1000)
+    g = torch.Generator().manual_seed(11)
+    p0, grads = torch.randn(4099, generator=g), [torch.randn(4099, generator=g) for _ in range(3)]
+    p = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.Adam([p], lr=1e-4, eps=1e-5)                    # reference agents/impala/builder.py:43-44
+    norms = []
+    for gk in grads:
+        p.grad = gk.clone()
+        norms.append(float(torch.nn.utils.clip_grad_norm_([p], 0.5)))  # reference agents/impala/learning.py:172
+        opt.step()
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), r=d["r"].numpy(), discount=d["discount"].numpy(),
+                        v=d["v"].numpy(), n_step3=ns.numpy(), priorities=pri, st_idx=idx, st_prob=prob,
+                        adam_p0=p0.numpy(), adam_grads=torch.stack(grads).numpy(), adam_p=p.detach().numpy(),
+                        adam_m=opt.state[p]["exp_avg"].numpy(), adam_v=opt.state[p]["exp_avg_sq"].numpy(),
+                        adam_norms=np.array(norms))
+
+
 if __name__ == "__main__":
+    if len(sys.argv) > 1 and sys.argv[1] == "next_rows":       # add the new fixture without touching the others
+        next_rows_case("next_rows")
+        sys.exit(0)
     torch.manual_seed(0)
     impala_case("impala_c1", 32, 20, 15, 1000)                       # BASELINE config 1
     impala_case("impala_small_lambda", 5, 7, 6, 1001, lambda_=0.9, clip_rho_threshold=0.8,
@@ -71,4 +99,5 @@ if __name__ == "__main__":
     ppo_case("ppo_small", 1000, 15, 3000)
     returns_case("returns_small", 16, 64, 3100)
     replay_case("replay_indices")
+    next_rows_case("next_rows")
     print("golden vectors written to", HERE)

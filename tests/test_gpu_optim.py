@@ -83,3 +83,26 @@ def test_fused_optimizer_class_matches_adam_on_model(cuda):
             o.step()
     for (n1, a), (_, b) in zip(model.named_parameters(), ref.named_parameters()):
         assert_close(a, b, n1, rtol=1e-5, atol=2e-7)
+
+
+def test_golden_next_rows(cuda):
+    """Committed fixture (tests/golden/next_rows.npz, generated from torch's own Adam / the oracle)."""
+    import os
+    import numpy as np
+    from conftest import GOLDEN
+    from impala_b200 import vtrace
+    z = np.load(os.path.join(GOLDEN, "next_rows.npz"))
+    p = torch.from_numpy(z["adam_p0"]).to(cuda)
+    m, v = torch.zeros_like(p), torch.zeros_like(p)
+    for k in range(3):
+        norm = ops.clip_adam_step(p, torch.from_numpy(z["adam_grads"][k]).to(cuda), m, v, k + 1, 1e-4, eps=1e-5, max_norm=0.5)
+        assert norm.item() == pytest.approx(z["adam_norms"][k], rel=1e-5)
+    assert_close(p, torch.from_numpy(z["adam_p"]), "params", rtol=1e-6, atol=1e-7)
+    assert_close(m, torch.from_numpy(z["adam_m"]), "exp_avg", rtol=2e-5, atol=1e-8)
+    assert_close(v, torch.from_numpy(z["adam_v"]), "exp_avg_sq", rtol=4e-5, atol=1e-12)
+    r, d, vv = (torch.from_numpy(z[k]).to(cuda) for k in ("r", "discount", "v"))
+    assert np.array_equal(vtrace.n_step_bootstrapped_returns(r, d, vv, 3).cpu().numpy(), z["n_step3"])
+    tree = torch.zeros(2048, dtype=torch.float64, device=cuda)
+    ops.sumtree_update(tree, torch.arange(1000, device=cuda), torch.from_numpy(z["priorities"]).to(cuda))
+    idx, prob = ops.sumtree_sample(tree, 1000, 123, 0, 0, 512)
+    assert np.array_equal(idx.cpu().numpy(), z["st_idx"]) and np.array_equal(prob.cpu().numpy(), z["st_prob"])
