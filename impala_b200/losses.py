@@ -86,3 +86,23 @@ def impala_loss(batch, model, lambda_=1., entropy_cost=0.01, as_written=False):
     values = values.reshape(B, T)
     sq = lambda x: x.squeeze(-1) if x.dim() == 3 else x  # noqa: E731
     return impala_loss_from_outputs(pi, values, sq(a), sq(r), sq(discount_t), pi_ref, entropy_cost, lambda_)
+
+
+class _QuantileHuber(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, dist_src, tau_src, dist_target, huber_param):
+        loss, d_src = ops.quantile_huber_fwdbwd(dist_src, tau_src, dist_target, huber_param)
+        ctx.save_for_backward(d_src)
+        ctx.shape = dist_src.shape
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (d_src,) = ctx.saved_tensors
+        return (d_src * g.reshape(-1, 1)).reshape(ctx.shape), None, None, None
+
+
+def quantile_regression_loss(dist_src, tau_src, dist_target, huber_param: float = 1.):
+    """Drop-in for reference ``models/quantile_layers.py:83-93`` (per-sample loss ``[B]``, differentiable w.r.t.
+    ``dist_src``; ``tau_src`` enters only through the detached weights, ``dist_target`` is a target)."""
+    return _QuantileHuber.apply(dist_src, tau_src, dist_target, float(huber_param))

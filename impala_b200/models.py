@@ -109,6 +109,13 @@ class ActorCritic(nn.Module):
     def act(self, obs: torch.Tensor, deterministic_policy: torch.Tensor):
         """Reference ``AtariPPOModel.act`` (``models/distributed_models.py:21-32``): action, full logits, value."""
         logits, v = self.forward(obs.to(next(self.parameters()).device))
-        action = logits.softmax(dim=-1).multinomial(1, replacement=True)
-        action = torch.where(deterministic_policy.to(action.device), logits.argmax(dim=-1, keepdim=True), action)
+        from . import ops           # fused epilogue (N5): softmax -> categorical draw -> argmax select, one launch
+        action = ops.act_epilogue(logits, deterministic_policy, self._act_seed, 0, self._act_draws)   # CUDA only
+        self._act_draws += logits.shape[0]
         return action, logits, v
+
+    _act_seed, _act_draws = 0, 0
+
+    def reset_act_rng(self, seed: int) -> None:
+        """Seed of the actor-side categorical draws (Philox stream; counter = rows drawn so far)."""
+        self._act_seed, self._act_draws = int(seed), 0

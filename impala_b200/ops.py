@@ -322,3 +322,31 @@ def sumtree_sample(tree, size, seed, stream_id, draw_offset, n, with_prob=True):
     _cabi.call("b200rl_sumtree_sample", tree.data_ptr(), tree.numel() // 2, size, seed, stream_id, draw_offset, n,
                idx.data_ptr(), _cabi.ptr(prob), _stream())
     return idx, prob
+
+
+def quantile_huber_fwdbwd(dist_src, tau_src, dist_target, huber_param=1.0):
+    """N4b.  ``dist_src, tau_src [B,N]``, ``dist_target [B,M]`` -> ``(loss [B], d loss_b / d dist_src [B,N])``."""
+    _require_cuda(dist_src, tau_src, dist_target)
+    src, tau, tgt = _f32c(dist_src.detach()), _f32c(tau_src.detach()), _f32c(dist_target.detach())
+    B, N = src.shape
+    if tau.shape != src.shape or tgt.dim() != 2 or tgt.shape[0] != B:
+        raise RuntimeError("quantile_huber: shapes %s %s %s" % (tuple(src.shape), tuple(tau.shape), tuple(tgt.shape)))
+    loss = torch.empty(B, dtype=torch.float32, device=src.device)
+    d_src = torch.empty_like(src)
+    _cabi.call("b200rl_quantile_huber_fwdbwd", src.data_ptr(), tau.data_ptr(), tgt.data_ptr(), B, N, tgt.shape[1],
+               float(huber_param), loss.data_ptr(), d_src.data_ptr(), _stream())
+    return loss, d_src
+
+
+def act_epilogue(logits, deterministic, seed, stream_id, draw_offset):
+    """N5.  ``logits [n,A]`` -> int64 actions ``[n,1]``; ``deterministic``: bool tensor of 1 or n elements."""
+    _require_cuda(logits)
+    logits = _f32c(logits.detach())
+    n, A = logits.shape
+    det = deterministic.to(logits.device).reshape(-1).to(torch.uint8).contiguous()
+    if det.numel() not in (1, n):
+        raise RuntimeError("act_epilogue: deterministic has %d elements for %d rows" % (det.numel(), n))
+    action = torch.empty((n, 1), dtype=torch.int64, device=logits.device)
+    _cabi.call("b200rl_act_epilogue", logits.data_ptr(), n, A, det.data_ptr(), 0 if det.numel() == 1 and n != 1 else 1,
+               seed, stream_id, draw_offset, action.data_ptr(), _stream())
+    return action

@@ -126,6 +126,14 @@ int32_t b200rl_n_step_returns(
     int64_t B, int64_t T, int64_t stride_b, int64_t stride_t, int64_t n, double lambda_,
     float *out, void *stream);
 
+/* N4b -- quantile_regression_loss(dist_src [B,N], tau_src [B,N], dist_target [B,M], huber_param) of reference
+ * models/quantile_layers.py:83-93 (caller agents/dqn/learning.py:209) and its gradient w.r.t. dist_src:
+ * loss [B] = mean_j sum_i |tau_i - 1[delta<0]| * huber(delta_ij), delta_ij = target_j - src_i;
+ * d_src [B,N] = d loss_b / d src_i (the wrapper scales it by the upstream gradient). */
+int32_t b200rl_quantile_huber_fwdbwd(
+    const float *dist_src, const float *tau_src, const float *dist_target, int64_t B, int64_t N, int64_t M,
+    float huber_param, float *loss, float *d_src, void *stream);
+
 /* K3 -- replaces losses.ppo_loss after model(s) + backward w.r.t. model outputs
  * (reference losses.py:134-155, caller agents/ppo/learning.py:132-134).
  * Flat minibatch: logits, pi_ref [N,A]; actions, v_target, v [N].
@@ -193,6 +201,14 @@ int32_t b200rl_sumtree_update(
 int32_t b200rl_sumtree_sample(
     const double *tree, int64_t leaves, int64_t size, uint64_t seed, uint32_t stream_id, uint64_t draw_offset,
     int64_t n, int64_t *out_idx, float *out_prob, void *stream);
+
+/* N5 -- actor epilogue of AtariPPOModel.act (reference models/distributed_models.py:26-31): per row of
+ * logits [n,A]: action = deterministic ? argmax : categorical sample of softmax(logits).  `deterministic` is a
+ * uint8/bool array read with stride 0 (one flag for all rows, as the reference's 1-element tensor) or 1.
+ * Draw specification: oracle/losses_ref.py:act_epilogue (Philox4x32-10, counter word 3 = 1). */
+int32_t b200rl_act_epilogue(
+    const float *logits, int64_t n, int64_t A, const uint8_t *deterministic, int64_t deterministic_stride,
+    uint64_t seed, uint32_t stream_id, uint64_t draw_offset, int64_t *action, void *stream);
 
 /* K6 -- replaces clip_grad_norm_(params, max_norm) + optimizer.step() (torch.optim.Adam, no weight decay,
  * no amsgrad) at reference agents/impala/learning.py:172-176 and agents/ppo/learning.py:136-140 for

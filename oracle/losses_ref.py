@@ -123,3 +123,39 @@ def ppo_make_targets(r, done, v, gamma=0.99, lambda_=0.95):
     Per rollout ``[T]`` -> ``[T-1]``."""
     discount_t = torch.logical_not(done) * gamma
     return rlego_ref.lambda_returns(r[:-1], discount_t[:-1], v[1:], lambda_)
+
+
+def quantile_regression_loss(dist_src, tau_src, dist_target, huber_param=1.):
+    """Reference ``models/quantile_layers.py:83-93`` restated line by line."""
+    delta = dist_target.unsqueeze(1) - dist_src.unsqueeze(2)
+    weight = torch.abs(tau_src.unsqueeze(2) - (delta < 0.).to(torch.float32)).detach()
+    if huber_param == 0:
+        delta = torch.abs(delta)
+    else:
+        abs_delta = torch.abs(delta)
+        quadratic = torch.clamp_max(abs_delta, huber_param)
+        delta = 0.5 * quadratic.pow(2) + huber_param * (abs_delta - quadratic)
+    return (weight * delta).sum(1).mean(-1)
+
+
+def act_epilogue(logits, deterministic, seed, stream_id, draw_offset):
+    """Specification of the fused actor epilogue (reference ``models/distributed_models.py:26-31``
+    draws with ``torch.multinomial`` whose stream cannot be reproduced -- PARITY UNPINNED, distribution identical):
+    returns ``(action [n], lo [n], hi [n])`` where ``lo <= u*total < hi`` are the cumulative-sum brackets of the
+    chosen action, so a GPU result can be accepted when its own bracket contains the same target up to rounding."""
+    import numpy as np
+    from . import replay_ref
+    x = logits.double().numpy()
+    n, A = x.shape
+    g = np.arange(n, dtype=np.uint64) + np.uint64(draw_offset)
+    o0, _, _, _ = replay_ref.philox4x32_10_vec(g & np.uint64(0xFFFFFFFF), g >> np.uint64(32),
+                                                np.full(n, stream_id, dtype=np.uint64), np.ones(n, dtype=np.uint64),
+                                                seed & 0xFFFFFFFF, (seed >> 32) & 0xFFFFFFFF)
+    u = (o0 >> np.uint64(8)).astype(np.float64) * 2.0 ** -24
+    e = np.exp(x - x.max(1, keepdims=True))
+    cum = np.cumsum(e, 1)
+    target = u * cum[:, -1]
+    a = np.minimum((cum > target[:, None]).argmax(1), A - 1)
+    det = np.broadcast_to(np.asarray(deterministic, dtype=bool).reshape(-1), (n,))
+    a = np.where(det, x.argmax(1), a)
+    return a, u, cum / cum[:, -1:]

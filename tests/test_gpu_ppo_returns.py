@@ -188,3 +188,23 @@ def test_n_step_returns_bit_exact(B, T, n, lam, time_major):
     assert torch.equal(got.cpu(), want)
     one = vtrace.n_step_bootstrapped_returns(g["r"][0], g["discount"][0], g["v"][0], n, lam)   # reference's [T] form
     assert torch.equal(one.cpu(), want[0])
+
+
+@pytest.mark.parametrize("B,N,M", [(256, 32, 32), (1, 1, 1), (7, 8, 64), (33, 200, 51), (5, 64, 300)])
+@pytest.mark.parametrize("kappa", [1.0, 0.0, 0.3])
+def test_quantile_huber_fwd_bwd(B, N, M, kappa):
+    """N4b: reference models/quantile_layers.py:83-93, loss and gradient w.r.t. dist_src (as DistributionalApex
+    uses it: .mul(weight).mean().backward(), agents/dqn/learning.py:209-210)."""
+    g = torch.Generator().manual_seed(B * 31 + N + M)
+    src = torch.randn(B, N, generator=g)
+    tau = torch.rand(B, N, generator=g)
+    tgt = torch.randn(B, M, generator=g)
+    wts = torch.rand(B, generator=g)
+    s_ref = src.clone().requires_grad_(True)
+    want = losses_ref.quantile_regression_loss(s_ref, tau, tgt, kappa)
+    want.mul(wts).mean().backward()
+    s_gpu = src.cuda().requires_grad_(True)
+    got = losses.quantile_regression_loss(s_gpu, tau.cuda(), tgt.cuda(), kappa)
+    got.mul(wts.cuda()).mean().backward()
+    assert_close(got, want, "loss", rtol=1e-5, atol=1e-6)
+    assert_close(s_gpu.grad, s_ref.grad, "d dist_src", rtol=1e-5, atol=1e-7, rel_to_max=1e-5)

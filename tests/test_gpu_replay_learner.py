@@ -288,3 +288,30 @@ def test_prioritized_replay_buffer_surface(cuda):
     assert np.allclose(leaves[4], 2. ** 0.6) and np.allclose(leaves[11 % cap], 3. ** 0.6)
     assert np.allclose(leaves[0], 1.0) and np.allclose(leaves[1], 1.0)                # new rows entered at priority 1; stale keys 0, 3 ignored
     assert np.isclose(rb.sampler.tree[1].item(), leaves.sum())
+
+
+def test_act_epilogue_matches_spec(cuda):
+    """N5: fused softmax -> categorical draw -> argmax select (reference models/distributed_models.py:26-31).
+    Deterministic rows are exact argmax; sampled rows must fall in the CDF bracket of the specified uniform
+    (up to fp32 rounding at bracket edges) and follow softmax(logits) in frequency."""
+    g = torch.Generator().manual_seed(0)
+    n, A = 4096, 15
+    logits = 2 * torch.randn(n, A, generator=g)
+    det = torch.rand(n, generator=g) < 0.3
+    got = ops.act_epilogue(logits.to(cuda), det, 99, 0, 12345).cpu().reshape(-1)
+    a, u, cdf = losses_ref.act_epilogue(logits, det.numpy(), 99, 0, 12345)
+    assert torch.equal(got[det], logits.argmax(-1)[det])
+    lo = np.concatenate([np.zeros((n, 1)), cdf[:, :-1]], 1)
+    gi = got.numpy()
+    ok = (lo[np.arange(n), gi] - 1e-5 <= u) & (u <= cdf[np.arange(n), gi] + 1e-5)
+    assert ok[~det.numpy()].all()
+    assert (gi == a).mean() > 0.999
+    one = torch.tensor([[0., 1., 2., 0.5]]).repeat(100_000, 1).to(cuda)
+    draws = ops.act_epilogue(one, torch.tensor([False]), 7, 0, 0).reshape(-1)
+    freq = torch.bincount(draws, minlength=4).double() / draws.numel()
+    assert torch.allclose(freq, one[0].double().softmax(-1), atol=5e-3)
+    assert torch.equal(ops.act_epilogue(one[:8], torch.tensor([True]), 7, 0, 0).reshape(-1), torch.full((8,), 2, device=cuda))
+    model = models.ActorCritic((3, 64, 64), 15).to(cuda)                              # the drop-in act()
+    model.reset_act_rng(3)
+    act, lg, v = model.act(torch.zeros(5, 3, 64, 64, dtype=torch.uint8), torch.tensor([False]))
+    assert act.shape == (5, 1) and act.dtype == torch.int64 and lg.shape == (5, 15) and v.shape == (5, 1)
