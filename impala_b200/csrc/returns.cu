@@ -257,6 +257,45 @@ __global__ void __launch_bounds__(256) n_step_kernel(const ScanParams p, int n_s
     p.out[base + (long long)t * p.st] = y;
 }
 
+// N4, time-major, shared-memory staged: same tile as scan_smem_kernel (32 columns x T steps, 16-byte
+// cp.async), every input byte crosses HBM once; each thread then evaluates the n-step windows of its
+// column for the steps of its warp's chunk out of shared memory (lane = column: conflict free).
+template <int W>
+__global__ void __launch_bounds__(W * 32) n_step_smem_kernel(const ScanParams p, int n_step) {
+    extern __shared__ __align__(16) float smem_scan[];
+    const int T = p.T;
+    float *sr = smem_scan, *sd = sr + T * 32, *sv = sd + T * 32;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int b0 = blockIdx.x * 32;
+    for (int ch = threadIdx.x; ch < T * 8; ch += W * 32) {
+        const int row = ch >> 3, c4 = (ch & 7) * 4;
+        const int remaining = p.B - (b0 + c4);
+        const int bytes = remaining >= 4 ? 16 : (remaining > 0 ? remaining * 4 : 0);
+        const long long col = remaining > 0 ? b0 + c4 : 0;
+        cp_async16(sr + row * 32 + c4, p.r + (long long)row * p.st + col, bytes);
+        cp_async16(sd + row * 32 + c4, p.disc + (long long)row * p.st + col, bytes);
+        cp_async16(sv + row * 32 + c4, p.v + (long long)row * p.vst + col, bytes);
+    }
+    cp_async_wait_all();
+    __syncthreads();
+    const int b = b0 + lane;
+    if (b >= p.B) return;
+    const float v_last = sv[(T - 1) * 32 + lane];
+    for (int t = w; t < T; t += W) {  // interleaved over warps: every warp streams full 128-byte lines
+        const int last = t + n_step - 1;
+        float y = last < T ? sv[last * 32 + lane] : v_last;
+        for (int i = n_step - 1; i >= 0; --i) {
+            const int kk = t + i;
+            if (kk < T)
+                y = scan_step<MODE_LAMBDA_RETURNS>(sr[kk * 32 + lane], sd[kk * 32 + lane], sv[kk * 32 + lane], 0.f,
+                                                   p.lambda_, p.one_minus_lambda, y);
+            else
+                y = scan_step<MODE_LAMBDA_RETURNS>(0.f, 1.f, v_last, 0.f, p.lambda_, p.one_minus_lambda, y);
+        }
+        __stcs(p.out + (long long)t * p.st + b, y);
+    }
+}
+
 static int32_t check_scan_layout(const char *who, int64_t B, int64_t T, int64_t sb, int64_t st) {
     B200RL_REQUIRE(B >= 1 && T >= 1, -2, "%s: need B>=1 and T>=1 (got B=%lld T=%lld)", who, (long long)B, (long long)T);
     B200RL_REQUIRE(B * (T + 1) < (1ll << 31), -3, "%s: B*T too large", who);
@@ -302,6 +341,22 @@ extern "C" int32_t b200rl_n_step_returns(const float *r_t, const float *discount
     B200RL_REQUIRE(n >= 1 && n < (1 << 20), -2, "n_step_returns: n=%lld", (long long)n);
     ScanParams p{r_t, discount_t, v_t, out, (int)B, (int)T, stride_b, stride_t, stride_b, stride_t, (float)lambda_,
                  (float)(1.0 - lambda_)};
+    const bool time_major = (stride_b == 1 && stride_t >= B);
+    const bool al16 = ((reinterpret_cast<uintptr_t>(r_t) | reinterpret_cast<uintptr_t>(discount_t) |
+                        reinterpret_cast<uintptr_t>(v_t)) % 16 == 0) && stride_t % 4 == 0;
+    if (time_major && al16 && T <= kSmemScanMaxT && T >= 8) {
+        static bool configured = false;
+        if (!configured) {
+            cudaError_t e = cudaFuncSetAttribute(n_step_smem_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
+            if (e != cudaSuccess) {
+                set_error("cudaFuncSetAttribute(n_step_smem_kernel): %s", cudaGetErrorString(e));
+                return (int32_t)e;
+            }
+            configured = true;
+        }
+        n_step_smem_kernel<8><<<(unsigned)((B + 31) / 32), 256, (size_t)3 * T * 32 * 4, (cudaStream_t)stream>>>(p, (int)n);
+        return check_launch("n_step_smem_kernel");
+    }
     const long long total = B * T;
     n_step_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(p, (int)n);
     return check_launch("n_step_kernel");
