@@ -103,12 +103,6 @@ __global__ void __launch_bounds__(512) scan_time_major_kernel(const ScanParams p
 // operation order and stores 128-byte lines.
 constexpr int kSmemScanMaxT = 256;
 
-__device__ __forceinline__ void cp_async16(void *smem, const void *gmem, int src_bytes) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem)), "l"(gmem), "r"(src_bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
-
 template <int MODE, int kSmemScanWarps>
 __global__ void __launch_bounds__(kSmemScanWarps * 32) scan_smem_kernel(const ScanParams p) {
     extern __shared__ __align__(16) float smem_scan[];
