@@ -16,6 +16,8 @@
 
 namespace b200rl {
 
+int env_int(const char *name, int dflt);
+
 constexpr int kOptThreads = 256;
 
 struct AdamParams {
@@ -134,7 +136,8 @@ extern "C" int32_t b200rl_clip_adam_step(float *params, float *grads, float *exp
     }
     AdamParams a;
     a.p = params; a.g = grads; a.m = exp_avg; a.v = exp_avg_sq; a.n = n;
-    long long grid = (n + 4 * kOptThreads - 1) / (4 * kOptThreads);  // >= one float4 per thread
+    const long long per_cta = env_int("B200RL_K6_ELEMS", 16 * kOptThreads);  // elements per CTA before the grid is capped (swept: scripts/k6_sweep.py)
+    long long grid = (n + per_cta - 1) / per_cta;
     if (grid > max_grid) grid = max_grid;
     long long chunk = (n + grid - 1) / grid;
     chunk = (chunk + 3) / 4 * 4;  // chunks start on float4 boundaries

@@ -135,8 +135,8 @@ extern "C" int32_t b200rl_ring_append(void *storage, int64_t row_bytes, int64_t 
 // ---------------------------------------------------------------------------------------
 // N2: multi-field ring append in ONE launch, with the actor-side `discount = !done * gamma`
 // (reference ImpalaActor._make_replay, agents/impala/learning.py:77-80) fused into the copy.
-// blockIdx.y selects the field; each field is flattened over (row, 16-byte vector) like
-// row_copy_kernel.  Fields smaller than the widest one simply retire their surplus CTAs.
+// Each field owns a contiguous range of CTAs sized for it and is flattened over (row, 16-byte
+// vector) like row_copy_kernel.
 namespace b200rl {
 
 constexpr int kMaxFields = 8;
@@ -149,16 +149,20 @@ struct FieldTable {
     float gamma[kMaxFields];
     long long n, capacity, count;
     const long long *idx;  // gather only
+    unsigned int cta_end[kMaxFields];  // field f owns CTAs [cta_end[f-1], cta_end[f])
+    int n_fields;
 };
 
 // MODE COPY_RING: dst[(count + i) % capacity] = src[i];  COPY_GATHER: dst[i] = src[clamp(idx[i])]
 template <int MODE>
 __global__ void __launch_bounds__(kCopyThreads) fields_copy_kernel(const FieldTable ft) {
-    const int f = blockIdx.y;
+    int f = 0;
+    while (f < ft.n_fields - 1 && blockIdx.x >= ft.cta_end[f]) ++f;  // every field gets exactly the CTAs it needs
+    const unsigned int cta = blockIdx.x - (f ? ft.cta_end[f - 1] : 0u);
     const long long rb = ft.row_bytes[f];
     const int vec = ft.vec[f];
     const long long vpr = rb / vec, total = ft.n * vpr;
-    const long long base = ((long long)blockIdx.x * kCopyUnroll) * kCopyThreads + threadIdx.x;
+    const long long base = ((long long)cta * kCopyUnroll) * kCopyThreads + threadIdx.x;
     if (base >= total) return;
     if (MODE == COPY_RING && ft.kind[f] == B200RL_FIELD_DONE_TO_DISCOUNT) {
         const unsigned char *src = static_cast<const unsigned char *>(ft.src[f]);
@@ -215,7 +219,8 @@ __global__ void __launch_bounds__(kCopyThreads) fields_copy_kernel(const FieldTa
 static int32_t fill_field_table(const char *who, const b200rl_field_t *fields, int32_t n_fields, long long n,
                                 bool allow_discount, b200rl::FieldTable &ft, long long &max_ctas) {
     using namespace b200rl;
-    max_ctas = 1;
+    max_ctas = 0;  // total CTAs over all fields
+    ft.n_fields = n_fields;
     for (int f = 0; f < n_fields; ++f) {
         const b200rl_field_t &x = fields[f];
         B200RL_REQUIRE(x.src && x.dst, -1, "%s: field %d has a null pointer", who, f);
@@ -230,8 +235,8 @@ static int32_t fill_field_table(const char *who, const b200rl_field_t *fields, i
         }
         ft.vec[f] = vec;
         const long long total = n * (x.row_bytes / vec), per_cta = (long long)kCopyThreads * kCopyUnroll;
-        const long long ctas = (total + per_cta - 1) / per_cta;
-        if (ctas > max_ctas) max_ctas = ctas;
+        max_ctas += (total + per_cta - 1) / per_cta;
+        ft.cta_end[f] = (unsigned int)max_ctas;
     }
     B200RL_REQUIRE(max_ctas < (1ll << 31), -3, "%s: too many elements", who);
     return 0;
@@ -249,7 +254,7 @@ extern "C" int32_t b200rl_ring_append_fields(const b200rl_field_t *fields, int32
     ft.n = n; ft.capacity = capacity; ft.count = count; ft.idx = nullptr;
     long long max_ctas;
     if (int32_t rc = fill_field_table("ring_append_fields", fields, n_fields, n, true, ft, max_ctas)) return rc;
-    fields_copy_kernel<COPY_RING><<<dim3((unsigned)max_ctas, (unsigned)n_fields), kCopyThreads, 0, (cudaStream_t)stream>>>(ft);
+    fields_copy_kernel<COPY_RING><<<(unsigned)max_ctas, kCopyThreads, 0, (cudaStream_t)stream>>>(ft);
     return check_launch("fields_copy_kernel<ring>");
 }
 
@@ -266,6 +271,6 @@ extern "C" int32_t b200rl_gather_fields(const b200rl_field_t *fields, int32_t n_
     ft.n = n; ft.capacity = nrows; ft.count = 0; ft.idx = reinterpret_cast<const long long *>(idx);
     long long max_ctas;
     if (int32_t rc = fill_field_table("gather_fields", fields, n_fields, n, false, ft, max_ctas)) return rc;
-    fields_copy_kernel<COPY_GATHER><<<dim3((unsigned)max_ctas, (unsigned)n_fields), kCopyThreads, 0, (cudaStream_t)stream>>>(ft);
+    fields_copy_kernel<COPY_GATHER><<<(unsigned)max_ctas, kCopyThreads, 0, (cudaStream_t)stream>>>(ft);
     return check_launch("fields_copy_kernel<gather>");
 }

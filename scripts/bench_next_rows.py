@@ -60,9 +60,10 @@ rows = [torch.randint(0, 256, (n, T, 3, 64, 64), dtype=torch.uint8, device=dev),
 row_b = sum(r[0].numel() * r.element_size() for r in rows) + T * 4      # + the float discount written
 report("N2 ingest 256 rollouts (5 fields, fused discount)", timed(lambda i: ops.ring_append_fields(fields, (i * n) % cap, rows, done_field=3), n_streams=1),
        2 * n * row_b, "read + write of every row")
-idx = ops.sample_uniform(1, 0, 0, n, cap, dev)
-outs = [torch.empty((n,) + tuple(f.shape[1:]), dtype=f.dtype, device=dev) for f in fields]
-report("N2 gather 256 rollouts (5 fields, one launch)", timed(lambda i: ops.gather_fields(fields, idx, outs)), 2 * n * row_b)
+idxs = [ops.sample_uniform(1, 0, k * n, n, cap, dev) for k in range(8)]     # 8 x 63 MB of distinct rows > L2
+outs = [[torch.empty((n,) + tuple(f.shape[1:]), dtype=f.dtype, device=dev) for f in fields] for _ in range(4)]
+report("N2 gather 256 rollouts (5 fields, one launch)", timed(lambda i: ops.gather_fields(fields, idxs[i % 8], outs[i % 4])), 2 * n * row_b,
+       "8 rotating index sets over a 1 GB ring, 4 rotating outputs (252 MB)")
 del fields, rows, outs
 # N3: sum tree over 1M slots
 P = 1 << 20
