@@ -251,40 +251,48 @@ __global__ void __launch_bounds__(256) n_step_kernel(const ScanParams p, int n_s
     p.out[base + (long long)t * p.st] = y;
 }
 
-// N4, time-major, shared-memory staged: same tile as scan_smem_kernel (32 columns x T steps, 16-byte
-// cp.async), every input byte crosses HBM once; each thread then evaluates the n-step windows of its
-// column for the steps of its warp's chunk out of shared memory (lane = column: conflict free).
-template <int W>
-__global__ void __launch_bounds__(W * 32) n_step_smem_kernel(const ScanParams p, int n_step) {
+// N4, time-major, shared-memory staged: a CTA owns 32 columns x kNStepRows consecutive steps (+ the
+// n-1 steps of look-ahead), staged with 16-byte cp.async so every input byte crosses HBM once
+// (+ (n-1)/kNStepRows halo).  Windows do not depend on each other, so unlike the scans the time
+// axis tiles freely: many small CTAs per SM, loads / arithmetic / stores of different CTAs overlap.
+constexpr int kNStepRows = 64, kNStepWarps = 4, kNStepMaxHalo = 64;
+
+__global__ void __launch_bounds__(kNStepWarps * 32) n_step_smem_kernel(const ScanParams p, int n_step) {
     extern __shared__ __align__(16) float smem_scan[];
     const int T = p.T;
-    float *sr = smem_scan, *sd = sr + T * 32, *sv = sd + T * 32;
+    const int t0 = blockIdx.y * kNStepRows;
+    const int rows_out = min(kNStepRows, T - t0);
+    const int rows_in = min(T - t0, kNStepRows + n_step - 1);
+    const int R = kNStepRows + n_step - 1;  // allocated rows per array
+    float *sr = smem_scan, *sd = sr + R * 32, *sv = sd + R * 32;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int b0 = blockIdx.x * 32;
-    for (int ch = threadIdx.x; ch < T * 8; ch += W * 32) {
+    for (int ch = threadIdx.x; ch < rows_in * 8; ch += kNStepWarps * 32) {
         const int row = ch >> 3, c4 = (ch & 7) * 4;
         const int remaining = p.B - (b0 + c4);
         const int bytes = remaining >= 4 ? 16 : (remaining > 0 ? remaining * 4 : 0);
         const long long col = remaining > 0 ? b0 + c4 : 0;
-        cp_async16(sr + row * 32 + c4, p.r + (long long)row * p.st + col, bytes);
-        cp_async16(sd + row * 32 + c4, p.disc + (long long)row * p.st + col, bytes);
-        cp_async16(sv + row * 32 + c4, p.v + (long long)row * p.vst + col, bytes);
+        const long long g = (long long)(t0 + row) * p.st + col;
+        cp_async16(sr + row * 32 + c4, p.r + g, bytes);
+        cp_async16(sd + row * 32 + c4, p.disc + g, bytes);
+        cp_async16(sv + row * 32 + c4, p.v + g, bytes);
     }
+    const int b = b0 + lane;
+    const float v_last = b < p.B ? __ldg(p.v + (long long)(T - 1) * p.st + b) : 0.f;
     cp_async_wait_all();
     __syncthreads();
-    const int b = b0 + lane;
     if (b >= p.B) return;
-    const float v_last = sv[(T - 1) * 32 + lane];
-    for (int t = w; t < T; t += W) {  // interleaved over warps: every warp streams full 128-byte lines
-        const int last = t + n_step - 1;
-        float y = last < T ? sv[last * 32 + lane] : v_last;
+    for (int tl = w; tl < rows_out; tl += kNStepWarps) {  // interleaved over warps: full 128-byte lines
+        const int t = t0 + tl, last = t + n_step - 1;
+        float y = last < T ? sv[(last - t0) * 32 + lane] : v_last;
         for (int i = n_step - 1; i >= 0; --i) {
             const int kk = t + i;
-            if (kk < T)
-                y = scan_step<MODE_LAMBDA_RETURNS>(sr[kk * 32 + lane], sd[kk * 32 + lane], sv[kk * 32 + lane], 0.f,
-                                                   p.lambda_, p.one_minus_lambda, y);
-            else
+            if (kk < T) {
+                const int o = (kk - t0) * 32 + lane;
+                y = scan_step<MODE_LAMBDA_RETURNS>(sr[o], sd[o], sv[o], 0.f, p.lambda_, p.one_minus_lambda, y);
+            } else {
                 y = scan_step<MODE_LAMBDA_RETURNS>(0.f, 1.f, v_last, 0.f, p.lambda_, p.one_minus_lambda, y);
+            }
         }
         __stcs(p.out + (long long)t * p.st + b, y);
     }
@@ -338,17 +346,10 @@ extern "C" int32_t b200rl_n_step_returns(const float *r_t, const float *discount
     const bool time_major = (stride_b == 1 && stride_t >= B);
     const bool al16 = ((reinterpret_cast<uintptr_t>(r_t) | reinterpret_cast<uintptr_t>(discount_t) |
                         reinterpret_cast<uintptr_t>(v_t)) % 16 == 0) && stride_t % 4 == 0;
-    if (time_major && al16 && T <= kSmemScanMaxT && T >= 8) {
-        static bool configured = false;
-        if (!configured) {
-            cudaError_t e = cudaFuncSetAttribute(n_step_smem_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
-            if (e != cudaSuccess) {
-                set_error("cudaFuncSetAttribute(n_step_smem_kernel): %s", cudaGetErrorString(e));
-                return (int32_t)e;
-            }
-            configured = true;
-        }
-        n_step_smem_kernel<8><<<(unsigned)((B + 31) / 32), 256, (size_t)3 * T * 32 * 4, (cudaStream_t)stream>>>(p, (int)n);
+    if (time_major && al16 && n - 1 <= kNStepMaxHalo) {
+        const dim3 grid((unsigned)((B + 31) / 32), (unsigned)((T + kNStepRows - 1) / kNStepRows));
+        const size_t smem = (size_t)3 * (kNStepRows + n - 1) * 32 * 4;  // <= 48 KB
+        n_step_smem_kernel<<<grid, kNStepWarps * 32, smem, (cudaStream_t)stream>>>(p, (int)n);
         return check_launch("n_step_smem_kernel");
     }
     const long long total = B * T;
