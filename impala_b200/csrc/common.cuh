@@ -11,6 +11,25 @@ namespace b200rl {
 void set_error(const char *fmt, ...);
 int32_t check_launch(const char *what);
 
+// Dynamic shared memory opt-in, cached per device (one process may drive several GPUs).
+constexpr int kMaxDevices = 64;
+template <typename F>
+inline int32_t ensure_dynamic_smem(F func, size_t bytes, size_t (&cache)[kMaxDevices], const char *what) {
+    if (bytes <= 48 * 1024) return 0;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev = (dev >= 0 && dev < kMaxDevices) ? dev : 0;
+    if (bytes <= cache[dev]) return 0;
+    cudaError_t e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e != cudaSuccess) {
+        set_error("%s: cudaFuncSetAttribute(%zu B shared): %s", what, bytes, cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return (int32_t)e;
+    }
+    cache[dev] = bytes;
+    return 0;
+}
+
 #define B200RL_REQUIRE(cond, code, ...)          \
     do {                                         \
         if (!(cond)) {                           \

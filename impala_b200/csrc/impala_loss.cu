@@ -254,15 +254,8 @@ int env_int(const char *name, int dflt);
 
 template <int AT, bool EXACT>
 static int32_t launch_impala(const ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
-    static size_t configured = 48 * 1024;  // dynamic shared memory already opted in to
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(impala_loss_kernel<AT, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) {
-            set_error("cudaFuncSetAttribute(%zu B shared): %s", smem, cudaGetErrorString(e));
-            return (int32_t)e;
-        }
-        configured = smem;
-    }
+    static size_t smem_cache[kMaxDevices];
+    if (int32_t rc = ensure_dynamic_smem(impala_loss_kernel<AT, EXACT>, smem, smem_cache, "impala_loss")) return rc;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((p.B + p.C - 1) / p.C));
     cfg.blockDim = dim3((unsigned)threads);

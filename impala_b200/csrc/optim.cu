@@ -120,10 +120,12 @@ extern "C" int32_t b200rl_clip_adam_step(float *params, float *grads, float *exp
     B200RL_REQUIRE(step >= 1, -2, "clip_adam_step: step must be >= 1 (got %lld)", (long long)step);
     B200RL_REQUIRE(lr >= 0 && beta1 >= 0 && beta1 < 1 && beta2 >= 0 && beta2 < 1 && eps >= 0, -2,
                    "clip_adam_step: invalid hyper-parameters");
-    static int max_grid = 0;  // co-resident CTAs of this kernel on the current device
+    static int max_grid_dev[kMaxDevices];  // co-resident CTAs of this kernel, per device
+    int dev = 0;
+    cudaGetDevice(&dev);
+    int &max_grid = max_grid_dev[(dev >= 0 && dev < kMaxDevices) ? dev : 0];
     if (max_grid == 0) {
-        int dev = 0, sms = 0, per_sm = 0;
-        cudaGetDevice(&dev);
+        int sms = 0, per_sm = 0;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, clip_adam_kernel<true>, kOptThreads, 0);
         if (sms <= 0 || per_sm <= 0) {

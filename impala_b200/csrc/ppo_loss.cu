@@ -123,15 +123,8 @@ int env_int(const char *name, int dflt);
 
 template <int AT, bool EXACT>
 static int32_t launch_ppo(const PpoParams &p, size_t smem, cudaStream_t stream) {
-    static size_t configured = 48 * 1024;  // dynamic shared memory already opted in to
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(ppo_loss_kernel<AT, EXACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) {
-            set_error("cudaFuncSetAttribute(%zu B shared): %s", smem, cudaGetErrorString(e));
-            return (int32_t)e;
-        }
-        configured = smem;
-    }
+    static size_t smem_cache[kMaxDevices];
+    if (int32_t rc = ensure_dynamic_smem(ppo_loss_kernel<AT, EXACT>, smem, smem_cache, "ppo_loss")) return rc;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((p.N + kPpoTile - 1) / kPpoTile));
     cfg.blockDim = dim3(kPpoTile);

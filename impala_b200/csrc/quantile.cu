@@ -62,15 +62,8 @@ extern "C" int32_t b200rl_quantile_huber_fwdbwd(const float *dist_src, const flo
     B200RL_REQUIRE(huber_param >= 0.f, -2, "quantile_huber: huber_param < 0");
     B200RL_REQUIRE(M <= 4096 && B < (1ll << 31) && N < (1ll << 31), -3, "quantile_huber: M=%lld > 4096 targets not supported", (long long)M);
     const size_t smem = (size_t)kQhWarps * M * 4;
-    static size_t configured = 48 * 1024;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(quantile_huber_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) {
-            set_error("cudaFuncSetAttribute(%zu B shared): %s", smem, cudaGetErrorString(e));
-            return (int32_t)e;
-        }
-        configured = smem;
-    }
+    static size_t smem_cache[kMaxDevices];
+    if (int32_t rc = ensure_dynamic_smem(quantile_huber_kernel, smem, smem_cache, "quantile_huber")) return rc;
     quantile_huber_kernel<<<(unsigned)((B + kQhWarps - 1) / kQhWarps), kQhWarps * 32, smem, (cudaStream_t)stream>>>(
         dist_src, tau_src, dist_target, (int)B, (int)N, (int)M, huber_param, loss, d_src);
     return check_launch("quantile_huber_kernel");

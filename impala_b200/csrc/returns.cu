@@ -183,18 +183,15 @@ static int32_t launch_scan(const ScanParams &p, cudaStream_t stream) {
         const int TV = p.T + (MODE == MODE_GAE ? 1 : 0);
         const int nw = env_int("B200RL_K2_WARPS", 8);
         const size_t smem = (size_t)(2 * p.T + TV + 2 * 8) * 32 * 4;
-        static bool configured = false;
-        if (!configured) {
-            cudaError_t e = cudaFuncSetAttribute(scan_smem_kernel<MODE, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
-            if (e == cudaSuccess) e = cudaFuncSetAttribute(scan_smem_kernel<MODE, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
-            if (e == cudaSuccess) e = cudaFuncSetAttribute(scan_smem_kernel<MODE, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
-            if (e == cudaSuccess) e = cudaFuncSetAttribute(scan_smem_kernel<MODE, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 110 * 1024);
-            if (e != cudaSuccess) {
-                set_error("cudaFuncSetAttribute(scan_smem_kernel): %s", cudaGetErrorString(e));
-                return (int32_t)e;
-            }
-            configured = true;
+        static size_t c8[kMaxDevices], c4[kMaxDevices], c2[kMaxDevices], c1[kMaxDevices];
+        int32_t rc = 0;
+        switch (nw) {
+            case 1: rc = ensure_dynamic_smem(scan_smem_kernel<MODE, 1>, smem, c1, "scan"); break;
+            case 2: rc = ensure_dynamic_smem(scan_smem_kernel<MODE, 2>, smem, c2, "scan"); break;
+            case 4: rc = ensure_dynamic_smem(scan_smem_kernel<MODE, 4>, smem, c4, "scan"); break;
+            default: rc = ensure_dynamic_smem(scan_smem_kernel<MODE, 8>, smem, c8, "scan"); break;
         }
+        if (rc) return rc;
         const unsigned grid = (unsigned)((p.B + 31) / 32);
         switch (nw) {
             case 1: scan_smem_kernel<MODE, 1><<<grid, 32, smem, stream>>>(p); break;
