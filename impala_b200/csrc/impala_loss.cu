@@ -19,11 +19,13 @@ struct ImpalaParams {
     float *dlogits, *dvalues, *scalars;
     void *workspace;
     int B, T, A, C, time_major, walk_max_t;
+    int bulk_full, bulk_last;  // tiles that can use TMA bulk copies (alignment), see the launcher
+    unsigned int inv_div;  // ceil(2^32 / T) batch-major, ceil(2^32 / C) time-major
     float lambda_, one_minus_lambda, clip_rho, clip_pg_rho, entropy_coeff, inv_n_pg, inv_n_all;
     uint32_t flags;
 };
 
-template <int AT, bool EXACT>
+template <int AT, bool EXACT, bool TRACE>
 __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(const ImpalaParams p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int T = p.T, A = EXACT ? AT : p.A, C = p.C, NS = C * T;
@@ -35,9 +37,10 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(cons
     float *red = s_nx + NS;                             // [5*blockDim]
     uint64_t *bar = reinterpret_cast<uint64_t *>(red + 5 * blockDim.x);
 
-    const bool trace = (p.flags & B200RL_TRACE) && threadIdx.x == 0 && blockIdx.x < kMaxTraceCtas;
+    // B200RL_TRACE selects a separate instantiation: the production kernel carries no stamp code
+    const bool trace = TRACE && threadIdx.x == 0 && blockIdx.x < kMaxTraceCtas;
     unsigned long long *tr = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(p.workspace) + kTraceOffset) + blockIdx.x * 16;
-#define K1_STAMP(i) do { if (trace) { tr[i] = globaltimer_ns(); tr[8 + i] = (unsigned long long)clock64(); } } while (0)
+#define K1_STAMP(i) do { if (TRACE && trace) { tr[i] = globaltimer_ns(); tr[8 + i] = (unsigned long long)clock64(); } } while (0)
     K1_STAMP(0);
     if (trace) { unsigned int smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid)); tr[7] = smid; }
     pdl_launch_dependents();
@@ -48,7 +51,9 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(cons
     const int cols = min(C, p.B - b0);
     const int s = threadIdx.x;
     int c, t;
-    if (p.time_major) { t = s / C; c = s - t * C; } else { c = s / T; t = s - c * T; }
+    // s / T (resp. s / C) by one IMAD.HI with the host-computed ceil(2^32 / divisor): exact for s * divisor < 2^32
+    if (p.time_major) { t = C == 1 ? s : (int)__umulhi((unsigned)s, p.inv_div); c = s - t * C; }
+    else { c = (int)__umulhi((unsigned)s, p.inv_div); t = s - c * T; }
     const bool valid = s < NS && c < cols;
     const int st_local = p.time_major ? C : 1;  // local index distance between t and t+1
     const int n = p.time_major ? t * p.B + b0 + c : (b0 + c) * T + t;
@@ -61,10 +66,9 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(cons
     const size_t g_row_stride = (size_t)p.B * A;  // time-major only
     const int s_row_stride = C * A;               // time-major only
     const uint32_t row_bytes = (uint32_t)row_elems * 4u;
-    const bool bulk_ok = (row_bytes % 16 == 0) && ((g_row0 * 4) % 16 == 0) &&
-                         (nrows == 1 || ((g_row_stride * 4) % 16 == 0 && (s_row_stride * 4) % 16 == 0)) &&
-                         ((reinterpret_cast<uintptr_t>(p.logits) | reinterpret_cast<uintptr_t>(p.pi_ref) |
-                           reinterpret_cast<uintptr_t>(p.dlogits)) % 16 == 0);
+    // TMA bulk copies need 16-byte aligned addresses and sizes: decided on the host (full tiles / the ragged
+    // last tile), since every term depends on launch arguments only
+    const bool bulk_ok = (cols == C) ? p.bulk_full : p.bulk_last;
     // The copies are issued by lane 0 of every warp, rows dealt round-robin: a UBLKCP takes tens of
     // cycles to issue, so one thread issuing 2*T of them (time-major) would delay the last row by
     // microseconds.  Batch-major has one row per tensor: thread 0 alone, no extra barrier.
@@ -125,7 +129,7 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(cons
 
     // ---- phase 3: backward-in-time recursion e_k = td_k + (discount_k c_k) e_{k+1} ----------
     // Default: one register chain per column (the column's first thread), steps fetched 4 at a
-    // time and the next 4 prefetched while the chain runs; results go to s_e.
+    // time; results go to s_e.
     // walk_max_t > 0 and T <= walk_max_t: every thread walks its own column from the last step
     // down to its step instead (redundant O(T^2) FMAs, no second barrier).  Either way every
     // e_k is produced by the same operation order as the reference's loop.
@@ -146,25 +150,23 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(cons
         }
     } else {
         if (s < cols) {
-            const float2 *__restrict__ col = s_tg + (p.time_major ? s : s * T);
-            float *__restrict__ ecol = s_e + (p.time_major ? s : s * T);
+            const int base = p.time_major ? s : s * T;
+            const float2 *__restrict__ qp = s_tg + base + (T - 2) * st_local;  // step k
+            float *__restrict__ ep = s_e + base + (T - 2) * st_local;
+            const int st4 = 4 * st_local;
             float e = 0.f;
             int k = T - 2;
-            float2 q[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) q[j] = col[max(k - j, 0) * st_local];
-            for (; k >= 0; k -= 4) {
-                float2 nq[4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j) nq[j] = col[max(k - 4 - j, 0) * st_local];  // prefetch the next 4
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    if (k - j >= 0) {
-                        e = q[j].x + q[j].y * e;
-                        ecol[(k - j) * st_local] = e;
-                    }
-#pragma unroll
-                for (int j = 0; j < 4; ++j) q[j] = nq[j];
+            for (; k >= 3; k -= 4, qp -= st4, ep -= st4) {  // 4 independent loads, then 4 chained FMAs
+                const float2 q0 = qp[0], q1 = qp[-st_local], q2 = qp[-2 * st_local], q3 = qp[-3 * st_local];
+                e = q0.x + q0.y * e; ep[0] = e;
+                e = q1.x + q1.y * e; ep[-st_local] = e;
+                e = q2.x + q2.y * e; ep[-2 * st_local] = e;
+                e = q3.x + q3.y * e; ep[-3 * st_local] = e;
+            }
+            for (; k >= 0; --k, qp -= st_local, ep -= st_local) {
+                const float2 q = *qp;
+                e = q.x + q.y * e;
+                *ep = e;
             }
         }
         __syncthreads();
@@ -252,10 +254,10 @@ namespace b200rl {
 
 int env_int(const char *name, int dflt);
 
-template <int AT, bool EXACT>
-static int32_t launch_impala(const ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
+template <int AT, bool EXACT, bool TRACE>
+static int32_t launch_impala_t(const ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
     static size_t smem_cache[kMaxDevices];
-    if (int32_t rc = ensure_dynamic_smem(impala_loss_kernel<AT, EXACT>, smem, smem_cache, "impala_loss")) return rc;
+    if (int32_t rc = ensure_dynamic_smem(impala_loss_kernel<AT, EXACT, TRACE>, smem, smem_cache, "impala_loss")) return rc;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)((p.B + p.C - 1) / p.C));
     cfg.blockDim = dim3((unsigned)threads);
@@ -266,13 +268,19 @@ static int32_t launch_impala(const ImpalaParams &p, int threads, size_t smem, cu
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = env_int("B200RL_PDL", 1) ? 1 : 0;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, impala_loss_kernel<AT, EXACT>, p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, impala_loss_kernel<AT, EXACT, TRACE>, p);
     if (e != cudaSuccess) {
         set_error("impala_loss_kernel launch: %s", cudaGetErrorString(e));
         (void)cudaGetLastError();
         return (int32_t)e;
     }
     return check_launch("impala_loss_kernel");
+}
+
+template <int AT, bool EXACT>
+static int32_t launch_impala(const ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
+    if (p.flags & B200RL_TRACE) return launch_impala_t<AT, EXACT, true>(p, threads, smem, stream);
+    return launch_impala_t<AT, EXACT, false>(p, threads, smem, stream);
 }
 
 }  // namespace b200rl
@@ -325,6 +333,21 @@ extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
     B200RL_REQUIRE(smem_for(C) <= 226 * 1024, -3, "impala_loss: T*A too large for one CTA tile");
     B200RL_REQUIRE((B + C - 1) / C <= kMaxPartialCtas, -3, "impala_loss: B too large for the partials workspace");
     p.C = C;
+    {   // alignment of the bulk copies: row start, row size, row strides (time-major), base pointers
+        const bool tm = p.time_major != 0;
+        const bool ptrs = ((reinterpret_cast<uintptr_t>(logits) | reinterpret_cast<uintptr_t>(pi_ref) |
+                            reinterpret_cast<uintptr_t>(dlogits)) % 16) == 0;
+        auto ok = [&](long long cols) {
+            const long long row_bytes = (tm ? cols : cols * T) * A * 4;
+            const long long tile_step = (tm ? (long long)C : (long long)C * T) * A * 4;  // distance between tiles' first rows
+            bool a = ptrs && row_bytes % 16 == 0 && tile_step % 16 == 0;
+            if (tm) a = a && ((long long)B * A * 4) % 16 == 0 && ((long long)C * A * 4) % 16 == 0;
+            return a ? 1 : 0;
+        };
+        p.bulk_full = ok(C);
+        p.bulk_last = (B % C) ? ok(B % C) : p.bulk_full;
+    }
+    p.inv_div = (unsigned int)(((1ull << 32) + (unsigned)(p.time_major ? C : (int)T) - 1) / (unsigned)(p.time_major ? C : (int)T));
     const int threads = threads_for(C);
     const size_t smem = smem_for(C);
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);

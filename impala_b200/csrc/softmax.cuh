@@ -5,12 +5,12 @@
 //
 // The kernels are issue-slot bound at BASELINE sizes (16.7 MB per launch), so the
 // arithmetic is arranged for the fewest instructions per logit.  With
-//   d_j = x_j - max x,  e_j = exp(d_j),  se = sum e,  p_j = e_j / se,  dbar = sum p_j d_j
-// everything the losses need follows from three running sums:
-//   log p_j            = d_j - ln se
-//   entropy H          = ln se - dbar                         (torch Categorical.entropy)
+//   m = max x,  e_j = exp(x_j - m),  se = sum e,  p_j = e_j / se,  lse = m + ln se,  xbar = sum p_j x_j
+// everything the losses need follows from three running sums (no per-logit log-probability is formed):
+//   log p_j            = x_j - lse
+//   entropy H          = lse - xbar                           (torch Categorical.entropy)
 //   KL(p || p_ref)     = sum p_j (x_j - y_j) - lse_x + lse_y  (torch kl_divergence)
-//   -c dH/dx_j         = c p_j (log p_j + H) = c p_j (d_j - dbar)
+//   -c dH/dx_j         = c p_j (log p_j + H) = c p_j (x_j - xbar)
 #pragma once
 #include "common.cuh"
 
@@ -18,10 +18,10 @@ namespace b200rl {
 
 template <int AT>
 struct SampleStats {
-    float d[AT];   // x_j - max x
-    float e[AT];   // exp(d_j)
+    float d[AT];   // x_j (the logits, register copy)
+    float e[AT];   // exp(x_j - max x)
     float inv_se;  // 1 / sum e
-    float dbar;    // sum p_j d_j
+    float dbar;    // xbar = sum p_j x_j
     float H;       // entropy
     float kl;      // KL(p || p_ref)
     float lp;      // log pi(a)
@@ -55,13 +55,11 @@ __device__ __forceinline__ void sample_stats(SampleStats<AT> &st, const float *s
     for (int j = 0; j < AT; ++j) {
         if (EXACT || j < A) {
             const float x = st.d[j];
-            const float dj = x - m;
             const float ej = fast_exp2(fmaf(x, kLog2e, -mk));
             se += ej;
             ser += fast_exp2(fmaf(y[j], kLog2e, -mrk));
-            s1 = fmaf(ej, dj, s1);
+            s1 = fmaf(ej, x, s1);
             s2 = fmaf(ej, x - y[j], s2);
-            st.d[j] = dj;
             st.e[j] = ej;
         } else {
             st.e[j] = 0.f;
@@ -72,7 +70,7 @@ __device__ __forceinline__ void sample_stats(SampleStats<AT> &st, const float *s
     const float lnse = __fmul_rn(fast_log2(se), kLn2), lnser = __fmul_rn(fast_log2(ser), kLn2);
     st.inv_se = __fdividef(1.f, se);
     st.dbar = s1 * st.inv_se;
-    st.H = lnse - st.dbar;
+    st.H = (m + lnse) - st.dbar;
     st.kl = fmaf(s2, st.inv_se, (mr - m) + (lnser - lnse));
     int a = (int)action;
     a = a < 0 ? 0 : (a >= A ? A - 1 : a);  // never index outside the row
@@ -83,7 +81,7 @@ __device__ __forceinline__ void sample_stats(SampleStats<AT> &st, const float *s
 }
 
 // d loss / d logits for one sample, written over its shared-memory row:
-//   g_lp * (onehot(a) - p) + c_ent * p * (log p + H)  =  e_j * (c1 * d_j + k1)  (+ g_lp at j = a)
+//   g_lp * (onehot(a) - p) + c_ent * p * (log p + H)  =  e_j * (c1 * x_j + k1)  (+ g_lp at j = a)
 // (c_ent = entropy_coeff / N; the second term is -c_ent * dH/dlogits.)
 template <int AT, bool EXACT>
 __device__ __forceinline__ void write_dlogits(const SampleStats<AT> &st, float *srow, int A_rt,
