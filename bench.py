@@ -59,7 +59,7 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--streams", type=int, default=4,
+    ap.add_argument("--streams", type=int, default=6,
                     help="issue consecutive (independent) steps round-robin on this many CUDA streams")
     ap.add_argument("--pipeline", default="independent", choices=["independent", "serial"],
                     help="independent: consecutive steps use disjoint buffers, so the fused losses are launched with "
