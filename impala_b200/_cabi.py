@@ -34,6 +34,7 @@ SIGNATURES = {
     "b200rl_n_step_returns": (_i32, [_vp] * 3 + [_i64] * 5 + [_d] + [_vp] * 2),
     "b200rl_gae": (_i32, [_vp] * 3 + [_i64] * 6 + [_d] + [_vp] * 2),
     "b200rl_ppo_loss_fwdbwd": (_i32, [_vp] * 5 + [_i64] * 3 + [_f] * 2 + [_u32] + [_vp] * 5),
+    "b200rl_ppo_is_loss_fwdbwd": (_i32, [_vp] * 7 + [_i64] * 4 + [_f, _d] + [_f] * 4 + [_u32] + [_vp] * 5),
     "b200rl_sample_uniform": (_i32, [_u64, _u32, _u64, _i64, _i64, _vp, _vp]),
     "b200rl_gather_rows": (_i32, [_vp, _i64, _vp, _i64, _i64, _vp, _vp]),
     "b200rl_ring_append": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp]),

@@ -68,6 +68,35 @@ def ppo_loss(model, batch, entropy_cost=0.01, clip_coeff=0.1):
     return ppo_loss_from_outputs(pi_tm1, v_tm1, a, v_target, pi_ref, entropy_cost, clip_coeff)
 
 
+def ppo_is_loss_from_outputs(logits, v_tm1, v_boot, a, r, d, pi_ref, entropy_cost=0.01, clip_coeff=0.1,
+                             lambda_=0.95, gamma=0.99, n_global_b=None):
+    """Reference ``losses.py:64-89`` on model outputs ``logits [B,T,A]``, ``v_tm1 [B,T]`` and the bootstrap
+    value ``v_boot [B]`` of ``s1[:, -1]``."""
+    scalars, dlogits, dv = ops.ppo_is_loss_fwdbwd(logits, v_tm1, v_boot, a, r, d, pi_ref, entropy_cost, clip_coeff,
+                                                  lambda_, gamma, n_global_b=n_global_b)
+    loss = _attach(scalars[ops.S_LOSS], (logits, v_tm1), (dlogits, dv))
+    metrics = {k: scalars[i] for k, i in METRIC_SLOTS}
+    metrics["train/kl"] = scalars[ops.S_KL].clamp_min(0.)  # losses.py:79
+    return loss, metrics
+
+
+def ppo_loss_is(batch, model, entropy_cost=0.01, clip_coeff=0.1, lambda_=0.95, gamma=0.99):
+    """Drop-in for reference ``losses.ppo_loss_is`` (``losses.py:62-89``): same signature, ``(loss, metrics)``
+    return and metric keys.  The committed function cannot run (``functorch`` is not imported, ``batched_vtrace``
+    is undefined there); this computes what it spells out.  ``functorch.vmap(model)(s)`` becomes one model call
+    on the flattened ``[B*T,...]`` batch; the bootstrap call on ``s1[:, -1:]`` runs under ``no_grad`` (``:70-72``)."""
+    s, a, r, s1, d, pi_ref = batch
+    B, T = s.shape[0], s.shape[1]
+    pi, v = model(s.flatten(0, 1))
+    pi = pi.reshape(B, T, -1)
+    v = v.reshape(B, T)
+    with torch.no_grad():
+        _, v_boot = model(s1[:, -1])
+    sq = lambda x: x.squeeze(-1) if x.dim() == 3 else x  # noqa: E731
+    return ppo_is_loss_from_outputs(pi, v, v_boot.reshape(B), sq(a), sq(r), sq(d), pi_ref, entropy_cost, clip_coeff,
+                                    lambda_, gamma)
+
+
 def impala_loss(batch, model, lambda_=1., entropy_cost=0.01, as_written=False):
     """Drop-in for reference ``losses.impala_loss`` (``losses.py:92-128``).
 

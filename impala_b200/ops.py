@@ -190,6 +190,39 @@ def ppo_loss_fwdbwd(logits, v, actions, v_target, pi_ref, entropy_cost=0.01, cli
     return scalars, dlogits, dv
 
 
+def ppo_is_loss_fwdbwd(logits, values, v_boot, actions, rewards, done, pi_ref, entropy_cost=0.01, clip_coeff=0.1,
+                       lambda_=0.95, gamma=0.99, clip_rho=1.0, clip_pg_rho=1.0, flags=0, n_global_b=None, out=None):
+    """K7 (reference ``losses.py:62-89`` intent).  ``logits, pi_ref [B,T,A]``; ``values, actions, rewards, done
+    [B,T]``; ``v_boot [B]``.  Returns ``(scalars[8], dlogits, dvalues)``."""
+    _require_cuda(logits, values, v_boot, actions, rewards, done, pi_ref)
+    logits, pi_ref = _f32c(logits.detach()), _f32c(pi_ref.detach())
+    values, rewards, v_boot = _f32c(values.detach()), _f32c(rewards), _f32c(v_boot.detach().reshape(-1))
+    if logits.dim() != 3:
+        raise RuntimeError("ppo_is_loss: logits must be [B,T,A]")
+    B, T, A = logits.shape
+    actions = actions if (actions.dtype == torch.int64 and actions.is_contiguous()) else actions.long().contiguous()
+    if done.dtype == torch.bool and done.is_contiguous():
+        done = done.view(torch.uint8)
+    elif done.dtype != torch.uint8 or not done.is_contiguous():
+        done = (done != 0).contiguous().view(torch.uint8)
+    if pi_ref.shape != logits.shape or v_boot.numel() != B or \
+            any(tuple(x.shape) != (B, T) for x in (values, actions, rewards, done)):
+        raise RuntimeError("ppo_is_loss: inconsistent shapes")
+    if out is None:
+        scalars = torch.empty(8, dtype=torch.float32, device=logits.device)
+        dlogits = torch.empty_like(logits)
+        dvalues = torch.empty_like(values)
+    else:
+        scalars, dlogits, dvalues = out
+    ws = workspace(logits.device)
+    _cabi.call("b200rl_ppo_is_loss_fwdbwd", logits.data_ptr(), pi_ref.data_ptr(), actions.data_ptr(),
+               rewards.data_ptr(), done.data_ptr(), values.data_ptr(), v_boot.data_ptr(), B, T, A,
+               B if n_global_b is None else n_global_b, gamma, lambda_, clip_rho, clip_pg_rho, clip_coeff,
+               entropy_cost, flags, dlogits.data_ptr(), dvalues.data_ptr(), scalars.data_ptr(), ws.data_ptr(),
+               _stream())
+    return scalars, dlogits, dvalues
+
+
 def sample_uniform(seed, stream_id, draw_offset, n, size, device, out=None):
     """K4.  ``n`` int64 indices in ``[0,size)`` on ``device``."""
     if out is None:

@@ -16,6 +16,16 @@ def impala_rollout(B=32, T=20, A=15, seed=1000, ref_noise=0.3, p_done=0.02, gamm
     return dict(logits=logits, values=values, a=a, r=r, discount=discount.float(), pi_ref=pi_ref)
 
 
+def ppo_is_rollout(B=32, T=20, A=15, seed=3200, ref_noise=0.3, p_done=0.1):
+    """Inputs of ``ppo_loss_is`` (reference ``losses.py:62``): an IMPALA-shaped rollout plus done flags and a
+    bootstrap value per rollout."""
+    d = impala_rollout(B, T, A, seed, ref_noise)
+    g = torch.Generator().manual_seed(seed + 77)
+    done = torch.rand(B, T, generator=g) < p_done
+    return dict(logits=d["logits"], pi_ref=d["pi_ref"], a=d["a"], r=d["r"], values=d["values"], done=done,
+                v_boot=torch.randn(B, generator=g))
+
+
 def ppo_minibatch(N=2048, A=15, seed=3000, ref_noise=0.3):
     """Flat PPO minibatch: logits/pi_ref ``[N,A]``, v ``[N,1]``, a, v_target ``[N]``."""
     g = torch.Generator().manual_seed(seed)

@@ -145,6 +145,23 @@ int32_t b200rl_ppo_loss_fwdbwd(
     float clip_coeff, float entropy_cost, uint32_t flags,
     float *dlogits, float *dv, float *scalars, void *workspace, void *stream);
 
+/* K7 -- restates the intent of reference losses.py:62-89 (`ppo_loss_is`: the PPO clip on
+ * V-trace advantages; not executable as committed -- functorch is not imported and
+ * batched_vtrace is undefined in that module) after the two model calls, plus its backward.
+ * Batch-major [B,T,...]: logits, pi_ref [B,T,A]; actions i64, rewards f32, done u8 (0/1),
+ * values (= v_tm1) f32 [B,T]; v_boot [B] = the value of s1[:, -1] (no gradient).  In-kernel:
+ * discount = (1-done)*gamma (:65), mask = roll(1-done, 1, dim=1) (:64), v_t = cat(values[:,1:],
+ * v_boot) (:70-72), V-trace with rho detached over all T steps (:73), td = 0.5 mean (mask err)^2
+ * (:74), pg = mean max(-adv rho, -clamp(rho, 1-c, 1+c) adv) with adv = (adv mask).detach()
+ * (:75-78), loss = pg + td - entropy_cost * H (:81).  Means run over n_global_b * T samples.
+ * scalars[B200RL_S_KL] is the UNclamped mean KL as in K3. */
+int32_t b200rl_ppo_is_loss_fwdbwd(
+    const float *logits, const float *pi_ref, const int64_t *actions, const float *rewards,
+    const uint8_t *done, const float *values, const float *v_boot, int64_t B, int64_t T, int64_t A,
+    int64_t n_global_b, float gamma, double lambda_, float clip_rho, float clip_pg_rho,
+    float clip_coeff, float entropy_cost, uint32_t flags,
+    float *dlogits, float *dvalues, float *scalars, void *workspace, void *stream);
+
 /* K4 -- replaces rlmeta UniformSampler (reference agents/impala/builder.py:31-32,
  * consumer learning.py:121).  Philox4x32-10, see oracle/replay_ref.py for the
  * stream definition; out_idx[n] int64 in [0,size). */

@@ -88,6 +88,56 @@ def ppo_loss(model, batch, entropy_cost=0.01, clip_coeff=0.1):
     return ppo_loss_from_outputs(logits, v, a, v_target, pi_ref, entropy_cost, clip_coeff)
 
 
+def ppo_is_loss_from_outputs(logits, v_tm1, v_boot, a, r, d, pi_ref_logits, entropy_cost=0.01,
+                             clip_coeff=0.1, lambda_=0.95, gamma=0.99):
+    """Reference ``losses.ppo_loss_is`` lines ``losses.py:64-89`` after the two model calls.  The
+    committed function is not executable (``functorch`` not imported ``:1,66``, ``batched_vtrace``
+    undefined ``:10,73``, ``1 - d`` on a bool tensor); this restates what it spells out, with
+    ``batched_vtrace`` = the per-rollout loop over ``rlego_ref.vtrace_td_error_and_advantage``.
+
+    ``logits, pi_ref_logits [B,T,A]``, ``v_tm1 [B,T]``, ``v_boot [B]`` (value of ``s1[:, -1]``, no
+    gradient), ``a [B,T] int64``, ``r [B,T]``, ``d [B,T]`` done flags.
+    """
+    df = d.to(v_tm1.dtype)
+    mask = (1 - df).roll(shifts=1, dims=1)                            # :64
+    discount_t = (1 - df) * gamma                                     # :65
+    pi_tm1 = Categorical(logits=logits)
+    pi_ref = Categorical(logits=pi_ref_logits)
+    ratio = torch.exp(pi_tm1.log_prob(a) - pi_ref.log_prob(a))        # :69
+    with torch.no_grad():                                             # :70-72
+        v_t = torch.cat([v_tm1[:, 1:], v_boot.reshape(-1, 1)], dim=1)
+    adv, err, _ = rlego_ref.batched_loop(rlego_ref.vtrace_td_error_and_advantage, v_tm1, v_t, r,
+                                         discount_t, ratio.detach(), lambda_=lambda_)   # :73
+    td_loss = 0.5 * (mask * err).pow(2).mean()                        # :74
+    adv = (adv * mask).detach()                                       # :75
+    pg_loss_1 = -(adv * ratio)                                        # :76
+    pg_loss_2 = -torch.clamp(ratio, 1 - clip_coeff, 1 + clip_coeff) * adv  # :77
+    pg_loss = torch.max(pg_loss_1, pg_loss_2).mean()                  # :78
+    kl = kl_divergence(pi_tm1, pi_ref).mean().clamp_min(0.)           # :79
+    entropy = pi_tm1.entropy().mean()                                 # :80
+    loss = pg_loss + td_loss - entropy_cost * entropy                 # :81
+    return loss, {
+        "train/loss": loss.detach(),
+        "train/entropy": entropy.detach(),
+        "train/td": td_loss.detach(),
+        "train/pg": pg_loss.detach(),
+        "train/kl": kl.detach(),
+        "train/ratio": ratio.mean().detach(),
+    }
+
+
+def ppo_loss_is(batch, model, entropy_cost=0.01, clip_coeff=0.1, lambda_=0.95, gamma=0.99):
+    """Reference signature, ``losses.py:62``; ``functorch.vmap(model)(s)`` = the model applied per rollout."""
+    s, a, r, s1, d, pi_ref = batch
+    B, T = s.shape[0], s.shape[1]
+    logits, v = model(s.flatten(0, 1))
+    with torch.no_grad():
+        _, v_boot = model(s1[:, -1])
+    sq = lambda x: x.squeeze(-1) if x.dim() == 3 else x  # noqa: E731
+    return ppo_is_loss_from_outputs(logits.reshape(B, T, -1), v.reshape(B, T), v_boot.reshape(B), sq(a), sq(r),
+                                    sq(d), pi_ref, entropy_cost, clip_coeff, lambda_, gamma)
+
+
 def impala_loss_from_outputs(pi_tm1, v_tm1, a, r, discount_t, lambda_=1.0):
     """Reference ``losses.impala_loss`` AS WRITTEN (``losses.py:98-128``; WIP, no caller):
     raw logits gathered (not log-probs), ``ratio = ones``, bootstrap = same-time detached

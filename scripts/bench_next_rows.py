@@ -87,3 +87,22 @@ report("N4b quantile-Huber B=256 N=M=64", timed(lambda i: ops.quantile_huber_fwd
 lg = torch.randn(128, 15, device=dev)
 det = torch.tensor([False], device=dev)
 report("N5 act epilogue 128 rows", timed(lambda i: ops.act_epilogue(lg, det, 1, 0, i * 128)), 0, "launch-latency bound (reference inference batch 128)")
+
+# K7: ppo_loss_is (losses.py:62-89) at the C2 shape, 201 B/sample; rotating sets > L2
+from impala_b200 import synth
+B, T, A = 4096, 20, 15
+nsets = int(2.5 * 126e6 // (201 * B * T)) + 1
+sets = []
+for i in range(nsets):
+    d = {k: v.to(dev) for k, v in synth.ppo_is_rollout(B, T, A, seed=i).items()}
+    sets.append((d, (torch.empty(8, device=dev), torch.empty_like(d["logits"]), torch.empty_like(d["values"]))))
+
+
+def k7(i):
+    d, out = sets[i % nsets]
+    ops.ppo_is_loss_fwdbwd(d["logits"], d["values"], d["v_boot"], d["a"], d["r"], d["done"], d["pi_ref"],
+                           flags=ops.INPUTS_STABLE, out=out)
+
+
+report("K7 ppo_loss_is T=20 B=4096 A=15", timed(k7, steps=400, n_streams=6), 201 * B * T + 4 * B,
+       "6 streams, INPUTS_STABLE; 201 B/sample + 4 B/rollout bootstrap")

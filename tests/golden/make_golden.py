@@ -88,9 +88,24 @@ def next_rows_case(name):
                         adam_norms=np.array(norms))
 
 
+def ppo_is_case(name, B, T, A, seed):
+    d = synth.ppo_is_rollout(B, T, A, seed)
+    logits = d["logits"].clone().requires_grad_(True)
+    v = d["values"].clone().requires_grad_(True)
+    loss, m = losses_ref.ppo_is_loss_from_outputs(logits, v, d["v_boot"], d["a"], d["r"], d["done"], d["pi_ref"])
+    loss.backward()
+    keys = ("train/loss", "train/entropy", "train/td", "train/pg", "train/kl", "train/ratio")
+    np.savez_compressed(os.path.join(HERE, name + ".npz"), **{k: t.numpy() for k, t in d.items()},
+                        dlogits=logits.grad.numpy(), dvalues=v.grad.numpy(),
+                        metrics=np.array([m[k].item() for k in keys], dtype=np.float64))
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "next_rows":       # add the new fixture without touching the others
         next_rows_case("next_rows")
+        sys.exit(0)
+    if len(sys.argv) > 1 and sys.argv[1] == "ppo_is":
+        ppo_is_case("ppo_is_small", 12, 20, 15, 3200)
         sys.exit(0)
     torch.manual_seed(0)
     impala_case("impala_c1", 32, 20, 15, 1000)                       # BASELINE config 1
@@ -100,4 +115,5 @@ if __name__ == "__main__":
     returns_case("returns_small", 16, 64, 3100)
     replay_case("replay_indices")
     next_rows_case("next_rows")
+    ppo_is_case("ppo_is_small", 12, 20, 15, 3200)
     print("golden vectors written to", HERE)

@@ -208,3 +208,102 @@ def test_quantile_huber_fwd_bwd(B, N, M, kappa):
     got.mul(wts.cuda()).mean().backward()
     assert_close(got, want, "loss", rtol=1e-5, atol=1e-6)
     assert_close(s_gpu.grad, s_ref.grad, "d dist_src", rtol=1e-5, atol=1e-7, rel_to_max=1e-5)
+
+
+# ---- K7: ppo_loss_is (reference losses.py:62-89) ---------------------------------------------------------------
+IS_KEYS = ("train/loss", "train/entropy", "train/td", "train/pg", "train/kl", "train/ratio")
+
+
+def oracle_ppo_is(d, **kw):
+    lg, v = d["logits"].clone().requires_grad_(True), d["values"].clone().requires_grad_(True)
+    loss, m = losses_ref.ppo_is_loss_from_outputs(lg, v, d["v_boot"], d["a"], d["r"], d["done"], d["pi_ref"], **kw)
+    loss.backward()
+    return m, lg.grad, v.grad
+
+
+@pytest.mark.parametrize("B,T,A", [(12, 20, 15), (1, 1, 1), (7, 1, 6), (33, 20, 15), (5, 33, 8), (9, 64, 17), (3, 256, 4),
+                                   (300, 20, 32), (64, 7, 18)])
+@pytest.mark.parametrize("kw", [{}, dict(entropy_cost=0., clip_coeff=.3, lambda_=1., gamma=.9)])
+def test_ppo_is_parity(B, T, A, kw):
+    d = synth.ppo_is_rollout(B, T, A, seed=B + T + A)
+    m, dl_ref, dv_ref = oracle_ppo_is(d, **kw)
+    g = to_cuda(d)
+    lg, v = g["logits"].requires_grad_(True), g["values"].requires_grad_(True)
+    loss, mm = losses.ppo_is_loss_from_outputs(lg, v, g["v_boot"], g["a"], g["r"], g["done"], g["pi_ref"], **kw)
+    assert list(mm) == list(IS_KEYS)
+    loss.backward()
+    for k in IS_KEYS:
+        assert_close(mm[k], m[k], k, rtol=2e-5, atol=2e-6)
+    assert_close(lg.grad, dl_ref, "dlogits", rel_to_max=2e-5)
+    assert_close(v.grad, dv_ref, "dv", rel_to_max=2e-5)
+
+
+def test_ppo_is_golden_edges_and_wrapper():
+    z = np.load(os.path.join(GOLDEN, "ppo_is_small.npz"))
+    d = {k: torch.from_numpy(z[k]) for k in ("logits", "values", "v_boot", "a", "r", "done", "pi_ref")}
+    g = to_cuda(d)
+    sc, dl, dv = ops.ppo_is_loss_fwdbwd(g["logits"], g["values"], g["v_boot"], g["a"], g["r"], g["done"], g["pi_ref"])
+    for i, slot in enumerate((ops.S_LOSS, ops.S_ENTROPY, ops.S_TD, ops.S_PG, ops.S_KL, ops.S_RATIO)):
+        assert sc[slot].item() == pytest.approx(z["metrics"][i], rel=2e-5, abs=2e-6)
+    assert_close(dl, torch.from_numpy(z["dlogits"]), "dlogits", rel_to_max=2e-5)
+    assert_close(dv, torch.from_numpy(z["dvalues"]), "dv", rel_to_max=2e-5)
+    # every step done / never done / identical policies (ratio == 1: the tie inside the clip range) / far off-policy
+    for name, edit in (("all_done", lambda x: x["done"].fill_(True)), ("no_done", lambda x: x["done"].fill_(False)),
+                       ("on_policy", lambda x: x["pi_ref"].copy_(x["logits"])),
+                       ("off_policy", lambda x: x["pi_ref"].add_(torch.randn_like(x["pi_ref"]) * 2))):
+        d2 = synth.ppo_is_rollout(40, 20, 15, seed=11)
+        edit(d2)
+        m, dl_ref, dv_ref = oracle_ppo_is(d2)
+        g2 = to_cuda(d2)
+        sc, dl, dv = ops.ppo_is_loss_fwdbwd(g2["logits"], g2["values"], g2["v_boot"], g2["a"], g2["r"], g2["done"], g2["pi_ref"])
+        assert_close(sc[ops.S_LOSS], m["train/loss"], name + " loss", rtol=2e-5, atol=2e-6)
+        assert_close(dl, dl_ref, name + " dlogits", rel_to_max=2e-5)
+        assert_close(dv, dv_ref, name + " dv", rel_to_max=2e-5)
+        if name == "on_policy":
+            assert sc[ops.S_RATIO].item() == 1.0
+    # float / uint8 done flags are accepted like the bool ones; shards add up to the global batch
+    d3 = synth.ppo_is_rollout(64, 20, 15, seed=12)
+    g3 = to_cuda(d3)
+    args = lambda x, sl: (x["logits"][sl], x["values"][sl], x["v_boot"][sl], x["a"][sl], x["r"][sl])  # noqa: E731
+    full = ops.ppo_is_loss_fwdbwd(*args(g3, slice(None)), g3["done"], g3["pi_ref"])
+    f2 = ops.ppo_is_loss_fwdbwd(*args(g3, slice(None)), g3["done"].float(), g3["pi_ref"])
+    assert all(torch.equal(x, y) for x, y in zip(full, f2))
+    lo, hi = slice(0, 24), slice(24, 64)
+    p0 = ops.ppo_is_loss_fwdbwd(*args(g3, lo), g3["done"][lo], g3["pi_ref"][lo], n_global_b=64)
+    p1 = ops.ppo_is_loss_fwdbwd(*args(g3, hi), g3["done"][hi], g3["pi_ref"][hi], n_global_b=64)
+    assert torch.equal(torch.cat([p0[1], p1[1]]), full[1]) and torch.equal(torch.cat([p0[2], p1[2]]), full[2])
+    assert_close((p0[0] + p1[0])[:6], full[0][:6], "scalars", rtol=1e-5, atol=1e-6)
+    # reference signature: ppo_loss_is(batch, model, ...) with loss.backward() reaching the parameters
+    B, T, A = 6, 5, 4
+    torch.manual_seed(0)
+    net = torch.nn.Linear(8, A + 1).cuda()
+    model = lambda s: (lambda o: (o[:, :A], o[:, A:]))(net(s))  # noqa: E731
+    s, s1 = torch.randn(B, T, 8, device="cuda"), torch.randn(B, T, 8, device="cuda")
+    d4 = to_cuda(synth.ppo_is_rollout(B, T, A, seed=13))
+    batch = (s, d4["a"][..., None], d4["r"][..., None], s1, d4["done"], d4["pi_ref"])
+    loss, mm = losses.ppo_loss_is(batch, model)
+    loss.backward()
+    gw = net.weight.grad.clone()
+    net.zero_grad()
+    cpu_net = torch.nn.Linear(8, A + 1)
+    cpu_net.load_state_dict({k: v.cpu() for k, v in net.state_dict().items()})
+    cmodel = lambda s: (lambda o: (o[:, :A], o[:, A:]))(cpu_net(s))  # noqa: E731
+    l_ref, m_ref = losses_ref.ppo_loss_is(tuple(x.cpu() for x in batch), cmodel)
+    l_ref.backward()
+    assert_close(loss, l_ref, "loss", rtol=2e-5, atol=2e-6)
+    assert_close(gw, cpu_net.weight.grad, "dW", rel_to_max=5e-5)
+
+
+def test_ppo_is_full_size_properties():
+    """T=20, B=4096, A=15 (the C2 shape): determinism, oracle parity of the scalars and of a slice of the gradients."""
+    d = synth.ppo_is_rollout(4096, 20, 15, seed=14)
+    g = to_cuda(d)
+    a = ops.ppo_is_loss_fwdbwd(g["logits"], g["values"], g["v_boot"], g["a"], g["r"], g["done"], g["pi_ref"])
+    b = ops.ppo_is_loss_fwdbwd(g["logits"], g["values"], g["v_boot"], g["a"], g["r"], g["done"], g["pi_ref"],
+                               flags=ops.INPUTS_STABLE)
+    assert all(torch.equal(x, y) for x, y in zip(a, b))
+    m, dl_ref, dv_ref = oracle_ppo_is(d)
+    for k, slot in zip(IS_KEYS, (ops.S_LOSS, ops.S_ENTROPY, ops.S_TD, ops.S_PG, ops.S_KL, ops.S_RATIO)):
+        assert_close(a[0][slot], m[k], k, rtol=2e-5, atol=2e-6)
+    assert_close(a[1], dl_ref, "dlogits", rel_to_max=2e-5)
+    assert_close(a[2], dv_ref, "dv", rel_to_max=2e-5)

@@ -261,3 +261,50 @@ def test_golden_next_rows_match_oracle():
     tree.update(np.arange(1000), z["priorities"])
     idx, prob = tree.sample(123, 0, 0, 512, 1000)
     assert np.array_equal(idx, z["st_idx"]) and np.array_equal(prob, z["st_prob"])
+
+
+def test_ppo_loss_is_restatement():
+    """Reference ``losses.ppo_loss_is`` (``losses.py:62-89``) as restated in the oracle: golden fixture, the rolled
+    mask, and the degenerate cases that can be worked out by hand."""
+    z = np.load(os.path.join(GOLDEN, "ppo_is_small.npz"))
+    t = {k: torch.from_numpy(z[k]) for k in ("logits", "values", "v_boot", "a", "r", "done", "pi_ref")}
+    lg, vv = t["logits"].clone().requires_grad_(True), t["values"].clone().requires_grad_(True)
+    loss, m = losses_ref.ppo_is_loss_from_outputs(lg, vv, t["v_boot"], t["a"], t["r"], t["done"], t["pi_ref"])
+    loss.backward()
+    assert list(m) == ["train/loss", "train/entropy", "train/td", "train/pg", "train/kl", "train/ratio"]
+    np.testing.assert_allclose(np.array([m[k].item() for k in m]), z["metrics"], rtol=1e-5)
+    np.testing.assert_allclose(lg.grad.numpy(), z["dlogits"], rtol=1e-5, atol=1e-8)
+    np.testing.assert_allclose(vv.grad.numpy(), z["dvalues"], rtol=1e-5, atol=1e-8)
+    # on-policy, never done, lambda = 1: err_t is the discounted sum of one-step TD errors up to the bootstrap,
+    # the advantage equals it, and d loss / d v = -err / N
+    B, T, A = 3, 6, 4
+    d = synth.ppo_is_rollout(B, T, A, seed=5, p_done=0.)
+    v = d["values"].clone().requires_grad_(True)
+    loss, m = losses_ref.ppo_is_loss_from_outputs(d["logits"], v, d["v_boot"], d["a"], d["r"], d["done"], d["logits"],
+                                                  entropy_cost=0., lambda_=1., gamma=.9)
+    loss.backward()
+    vt = torch.cat([d["values"][:, 1:], d["v_boot"][:, None]], 1)
+    delta = d["r"] + .9 * vt - d["values"]
+    err = torch.zeros(B, T)
+    e = torch.zeros(B)
+    for k in reversed(range(T)):
+        e = delta[:, k] + .9 * e
+        err[:, k] = e
+    assert m["train/ratio"].item() == 1.0 and m["train/kl"].item() == 0.0
+    assert m["train/td"].item() == pytest.approx(.5 * err.pow(2).mean().item(), rel=1e-5)
+    assert m["train/pg"].item() == pytest.approx(-err.mean().item(), rel=1e-4, abs=1e-6)
+    np.testing.assert_allclose(v.grad.numpy(), (-err / (B * T)).numpy(), rtol=1e-4, atol=1e-7)
+    # the mask is the not-done flag rolled by one step (wrapping): a done at the last step masks step 0
+    done = torch.zeros(B, T, dtype=torch.bool)
+    done[1, T - 1] = True
+    done[2, 2] = True
+    v2 = d["values"].clone().requires_grad_(True)
+    losses_ref.ppo_is_loss_from_outputs(d["logits"], v2, d["v_boot"], d["a"], d["r"], done, d["pi_ref"])[0].backward()
+    assert v2.grad[1, 0].item() == 0. and v2.grad[2, 3].item() == 0. and (v2.grad != 0).sum().item() == B * T - 2
+    # reference signature
+    model = lambda s: (d["logits"].reshape(-1, A), d["values"].reshape(-1, 1)) if s.shape[0] == B * T \
+        else (None, d["v_boot"][:, None])  # noqa: E731
+    s = torch.zeros(B, T, 1)
+    l2, _ = losses_ref.ppo_loss_is((s, d["a"][..., None], d["r"][..., None], s, done, d["pi_ref"]), model)
+    l3, _ = losses_ref.ppo_is_loss_from_outputs(d["logits"], d["values"], d["v_boot"], d["a"], d["r"], done, d["pi_ref"])
+    assert l2.item() == l3.item()
