@@ -106,3 +106,16 @@ def k7(i):
 
 report("K7 ppo_loss_is T=20 B=4096 A=15", timed(k7, steps=400, n_streams=6), 201 * B * T + 4 * B,
        "6 streams, INPUTS_STABLE; 201 B/sample + 4 B/rollout bootstrap")
+
+# K1 in the same harness and on the same rollouts, for comparison with K7 (204 B/sample)
+disc = [(~d["done"]).float() * 0.99 for d, _ in sets]
+
+
+def k1(i):
+    d, out = sets[i % nsets]
+    ops.impala_loss_fwdbwd(d["logits"], d["values"], d["a"], d["r"], disc[i % nsets], d["pi_ref"], flags=ops.INPUTS_STABLE, out=out)
+
+
+report("K1 impala_loss T=20 B=4096 A=15 (same harness)", timed(k1, steps=400, n_streams=6), 204 * B * T, "6 streams, INPUTS_STABLE")
+report("K1 impala_loss T=20 B=4096 A=15 (same harness, 4000 steps)", timed(k1, steps=4000, n_streams=6), 204 * B * T, "6 streams, INPUTS_STABLE")
+report("K7 ppo_loss_is (4000 steps)", timed(k7, steps=4000, n_streams=6), 201 * B * T + 4 * B, "6 streams, INPUTS_STABLE")
