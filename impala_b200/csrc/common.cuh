@@ -1,5 +1,6 @@
 // Shared device/host helpers for the b200rl kernels (sm_100a only).
 #pragma once
+#include <cuda.h>  // CUtensorMap (types only: the encoder is fetched through cudaGetDriverEntryPoint, libcuda is not linked)
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -10,6 +11,8 @@ namespace b200rl {
 // ---------------------------------------------------------------- host: errors
 void set_error(const char *fmt, ...);
 int32_t check_launch(const char *what);
+bool encode_tmap_2d_f32(CUtensorMap *map, const void *base, uint64_t inner, uint64_t rows, uint64_t pitch_bytes,
+                        uint32_t box_inner, uint32_t box_rows);  // api.cu
 
 // Dynamic shared memory opt-in, cached per device (one process may drive several GPUs).
 constexpr int kMaxDevices = 64;
@@ -100,6 +103,22 @@ __device__ __forceinline__ void bulk_wait_read0() {
 // make generic-proxy smem writes visible to the async proxy (before bulk_s2g)
 __device__ __forceinline__ void fence_proxy_async_smem() {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// TMA 2-D tiled copies through a tensor map (SASS: UTMALDG / UTMASTG).  x = innermost coordinate (elements),
+// y = row.  Shared-memory tiles are dense [box_rows][box_inner] and 128-byte aligned; elements of the box
+// that fall outside the tensor are zero-filled on load and dropped on store.
+__device__ __forceinline__ void tma_load_2d(void *dst_smem, const CUtensorMap *map, int x, int y, uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::
+            "r"(smem_u32(dst_smem)),
+        "l"(map), "r"(x), "r"(y), "r"(smem_u32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap *map, const void *src_smem, int x, int y) {
+    asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%1, %2}], [%3];" ::"l"(map), "r"(x),
+                 "r"(y), "r"(smem_u32(src_smem))
+                 : "memory");
 }
 
 // 16-byte cp.async (LDGSTS), L1-bypassing; src_bytes < 16 zero-fills the rest (0: nothing is read)

@@ -13,7 +13,17 @@
 
 namespace b200rl {
 
+// Tensor maps of the time-major instantiation ([T rows][B*A] tensors, box = T x C*A); a separate kernel
+// parameter so that batch-major launches do not carry 384 bytes of unused maps.
+template <bool TM>
+struct TileMaps {};
+template <>
+struct TileMaps<true> {
+    CUtensorMap logits, pi_ref, dlogits;
+};
+
 struct ImpalaParams {
+    int use_tmap;
     const float *logits, *pi_ref, *rewards, *discounts, *values;
     const long long *actions;
     float *dlogits, *dvalues, *scalars;
@@ -28,12 +38,13 @@ struct ImpalaParams {
 // TM: time-major [T,B,...] layout.  A template parameter so that the batch-major kernel carries no stride
 // arithmetic and no per-row copy loop (it executes ~10% fewer instructions than a run-time switch).
 template <int AT, bool EXACT, bool TRACE, bool TM>
-__global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(const ImpalaParams p) {
+__global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(const __grid_constant__ ImpalaParams p, const __grid_constant__ TileMaps<TM> maps) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int T = p.T, A = EXACT ? AT : p.A, C = p.C, NS = C * T;
     float *sx = reinterpret_cast<float *>(smem_raw);    // [NS*A] logits -> dlogits
-    float *sy = sx + NS * A;                            // [NS*A] behaviour logits
-    float2 *s_tg = reinterpret_cast<float2 *>(sy + NS * A);  // [NS] (clipped TD error, discount * c)
+    const int tile_elems = TM ? ((NS * A + 31) & ~31) : NS * A;  // tensor-map tiles start 128-byte aligned
+    float *sy = sx + tile_elems;                        // [NS*A] behaviour logits
+    float2 *s_tg = reinterpret_cast<float2 *>(sy + tile_elems);  // [NS] (clipped TD error, discount * c)
     float *s_e = reinterpret_cast<float *>(s_tg + NS);  // [NS] V-trace errors e_t
     float *s_nx = s_e + NS;                             // [NS] d loss/d v_{t+1} pushed by step t
     float *red = s_nx + NS;                             // [5*blockDim]
@@ -70,19 +81,29 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(cons
     const uint32_t row_bytes = (uint32_t)row_elems * 4u;
     // TMA bulk copies need 16-byte aligned addresses and sizes: decided on the host (full tiles / the ragged
     // last tile), since every term depends on launch arguments only
-    const bool bulk_ok = (cols == C) ? p.bulk_full : p.bulk_last;
+    // time-major with a tensor map: ONE 2-D tiled copy per tensor (T rows x C*A floats; the ragged last tile
+    // is zero-filled / clipped by the TMA unit) instead of T row copies
+    const bool tmap = TM && p.use_tmap;
+    const bool bulk_ok = tmap || ((cols == C) ? p.bulk_full : p.bulk_last);
     // The copies are issued by lane 0 of every warp, rows dealt round-robin: a UBLKCP takes tens of
     // cycles to issue, so one thread issuing 2*T of them (time-major) would delay the last row by
     // microseconds.  Batch-major has one row per tensor: thread 0 alone, no extra barrier.
     const int warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const bool issuer = TM ? ((threadIdx.x & 31) == 0 && warp < nrows) : threadIdx.x == 0;
+    const bool issuer = (TM && !tmap) ? ((threadIdx.x & 31) == 0 && warp < nrows) : threadIdx.x == 0;
     if (bulk_ok) {
         if (threadIdx.x == 0) {
             mbar_init(bar, 1);
             fence_mbar_init();
-            mbar_expect_tx(bar, 2u * row_bytes * nrows);
+            mbar_expect_tx(bar, tmap ? 2u * (uint32_t)(NS * A) * 4u : 2u * row_bytes * nrows);
         }
-        if (TM) {
+        if constexpr (TM) {
+            if (tmap && threadIdx.x == 0) {
+                tma_load_2d(sx, &maps.logits, b0 * A, 0, bar);
+                tma_load_2d(sy, &maps.pi_ref, b0 * A, 0, bar);
+            }
+        }
+        if (tmap) {
+        } else if (TM) {
             __syncthreads();  // barrier initialised before other warps' copies can complete on it
             if (issuer) {
                 for (int r = warp; r < nrows; r += nwarps) {
@@ -202,7 +223,9 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(cons
     K1_STAMP(4);
     if (bulk_ok) {
         if (issuer) {
-            if (TM) {
+            if (tmap) {
+                if constexpr (TM) tma_store_2d(&maps.dlogits, sx, b0 * A, 0);
+            } else if (TM) {
                 for (int r = warp; r < nrows; r += nwarps)
                     bulk_s2g(p.dlogits + g_row0 + r * g_row_stride, sx + r * s_row_stride, row_bytes);
             } else {
@@ -247,7 +270,17 @@ namespace b200rl {
 int env_int(const char *name, int dflt);
 
 template <int AT, bool EXACT, bool TRACE, bool TM>
-static int32_t launch_impala_t(const ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
+static int32_t launch_impala_t(ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
+    TileMaps<TM> maps;
+    if constexpr (TM) {
+        if (env_int("B200RL_K1_TMAP", 1)) {
+            const uint64_t inner = (uint64_t)p.B * p.A, pitch = inner * 4;
+            const uint32_t bi = (uint32_t)(p.C * p.A), br = (uint32_t)p.T;
+            p.use_tmap = encode_tmap_2d_f32(&maps.logits, p.logits, inner, br, pitch, bi, br) &&
+                         encode_tmap_2d_f32(&maps.pi_ref, p.pi_ref, inner, br, pitch, bi, br) &&
+                         encode_tmap_2d_f32(&maps.dlogits, p.dlogits, inner, br, pitch, bi, br);
+        }
+    }
     static size_t smem_cache[kMaxDevices];
     if (int32_t rc = ensure_dynamic_smem(impala_loss_kernel<AT, EXACT, TRACE, TM>, smem, smem_cache, "impala_loss")) return rc;
     cudaLaunchConfig_t cfg = {};
@@ -260,7 +293,7 @@ static int32_t launch_impala_t(const ImpalaParams &p, int threads, size_t smem, 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = env_int("B200RL_PDL", 1) ? 1 : 0;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, impala_loss_kernel<AT, EXACT, TRACE, TM>, p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, impala_loss_kernel<AT, EXACT, TRACE, TM>, p, maps);
     if (e != cudaSuccess) {
         set_error("impala_loss_kernel launch: %s", cudaGetErrorString(e));
         (void)cudaGetLastError();
@@ -270,7 +303,7 @@ static int32_t launch_impala_t(const ImpalaParams &p, int threads, size_t smem, 
 }
 
 template <int AT, bool EXACT>
-static int32_t launch_impala(const ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
+static int32_t launch_impala(ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
     if (p.flags & B200RL_TRACE) {  // stamped instantiations (scripts/k1_trace.py)
         if (p.time_major) return launch_impala_t<AT, EXACT, true, true>(p, threads, smem, stream);
         return launch_impala_t<AT, EXACT, true, false>(p, threads, smem, stream);
@@ -323,7 +356,7 @@ extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
     if (C > B) C = (int)B;
     while (C > 1 && C * T > max_threads) C = (C > 4) ? ((C - 1) & ~3) : C - 1;
     auto threads_for = [&](int c) { return ((c * (int)T + 31) / 32) * 32; };
-    auto smem_for = [&](int c) { return (size_t)c * T * (2 * A + 4) * 4 + 5 * (size_t)threads_for(c) * 4 + 16; };
+    auto smem_for = [&](int c) { return (size_t)c * T * (2 * A + 4) * 4 + 5 * (size_t)threads_for(c) * 4 + 16 + 256; };
     while (C > 1 && smem_for(C) > 200 * 1024) C = (C > 4) ? ((C / 2) & ~3) : C - 1;
     B200RL_REQUIRE(smem_for(C) <= 226 * 1024, -3, "impala_loss: T*A too large for one CTA tile");
     B200RL_REQUIRE((B + C - 1) / C <= kMaxPartialCtas, -3, "impala_loss: B too large for the partials workspace");
@@ -342,6 +375,7 @@ extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
         p.bulk_full = ok(C);
         p.bulk_last = (B % C) ? ok(B % C) : p.bulk_full;
     }
+    p.use_tmap = 0;  // set by the time-major launcher
     p.inv_div = (unsigned int)(((1ull << 32) + (unsigned)(p.time_major ? C : (int)T) - 1) / (unsigned)(p.time_major ? C : (int)T));
     const int threads = threads_for(C);
     const size_t smem = smem_for(C);
