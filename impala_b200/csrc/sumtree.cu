@@ -25,27 +25,77 @@ __device__ __forceinline__ void philox4x32_10_st(uint32_t &c0, uint32_t &c1, uin
     }
 }
 
-// Leaves first, then the touched ancestors level by level.  One CTA: the n updates of a learner
-// step (a few thousand) share most ancestors, and a CTA-wide barrier per level is all the
-// ordering the tree needs.  Duplicate indices: one of their values wins (in the learner's use --
-// keys sampled with replacement -- duplicates carry the same priority, so the choice is immaterial).
-__global__ void __launch_bounds__(1024) sumtree_update_kernel(double *tree, long long P, const long long *idx,
-                                                              const double *value, long long n) {
-    for (long long i = threadIdx.x; i < n; i += blockDim.x) {
-        long long j = idx[i];
-        if (j < 0 || j >= P) continue;
-        tree[P + j] = value[i];
+// Update = set n leaves, refresh their ancestors.  A learner step updates a few thousand leaves of a tree
+// with ~10^6; one SM cannot issue the scattered loads fast enough (measured: 71 us for 4096 of 1M from one
+// CTA), and a level-by-level walk is a chain of dependent L2 round trips.  So:
+//   * the tree is cut into G subtrees (roots = nodes [G, 2G)); CTA c scans all n indices, keeps those that
+//     fall under its root (n/G on average) and refreshes only its own subtree -- no cross-CTA ordering;
+//   * inside a subtree the levels wider than kSub are walked level by level (children fetched with one
+//     16-byte load); the kSub-wide level is then read ONCE into shared memory and everything above it is
+//     reduced there (recomputing an untouched node reproduces its value bit for bit, since
+//     node = left + right always holds);
+//   * a second one-CTA launch reduces the top log2(G) levels the same way from one read of level G.
+// Duplicate indices: one of their values wins (in the learner's use -- keys sampled with replacement --
+// duplicates carry the same priority, so the choice is immaterial).
+constexpr int kSub = 512;           // widest level of a subtree held in shared memory
+constexpr int kUpdThreads = 256;
+constexpr int kUpdMax = 8192;       // updates per launch of this path
+constexpr int kMaxSubtrees = 128;   // <= kSub so that the top launch fits the same shared array
+
+// Reduce the subtree rooted at `root` above its `sb`-wide level (sb <= kSub, a power of two; that level is
+// final in global memory) in shared memory and write every node above that level back.
+__device__ __forceinline__ void sumtree_reduce_top(double *tree, long long root, int sb, double *s_top) {
+    const int tid = threadIdx.x;
+    const long long first = root * sb;  // the sb-wide level of this subtree: nodes [root*sb, (root+1)*sb)
+    for (int i = tid; i < sb; i += blockDim.x) s_top[sb + i] = __ldcg(tree + first + i);
+    __syncthreads();
+    for (int w = sb >> 1; w >= 1; w >>= 1) {
+        for (int i = tid; i < w; i += blockDim.x) s_top[w + i] = s_top[2 * (w + i)] + s_top[2 * (w + i) + 1];
+        __syncthreads();
+    }
+    for (int q = 1 + tid; q < sb; q += blockDim.x) {
+        const int l = 31 - __clz(q);  // local level of local node q in [2^l, 2^(l+1))
+        tree[(root << l) + (q - (1 << l))] = s_top[q];
+    }
+}
+
+__global__ void __launch_bounds__(kUpdThreads) sumtree_update_kernel(double *tree, long long P, int G, const long long *idx,
+                                                                     const double *value, int n) {
+    __shared__ int s_leaf[kUpdMax];
+    __shared__ double s_top[2 * kSub];
+    __shared__ int s_count;
+    const int tid = threadIdx.x;
+    const long long S = P / G;              // leaves per subtree
+    const long long lo = (long long)blockIdx.x * S;
+    if (tid == 0) s_count = 0;
+    __syncthreads();
+    for (int i = tid; i < n; i += kUpdThreads) {
+        const long long j = __ldg(idx + i);
+        if (j >= lo && j < lo + S && j >= 0 && j < P) {
+            s_leaf[atomicAdd(&s_count, 1)] = (int)j;
+            __stcg(tree + P + j, value[i]);
+        }
     }
     __syncthreads();
-    for (long long width = P >> 1, shift = 1; width >= 1; width >>= 1, ++shift) {
-        for (long long i = threadIdx.x; i < n; i += blockDim.x) {
-            const long long j = idx[i];
-            if (j < 0 || j >= P) continue;
-            const long long node = (P + j) >> shift;
-            tree[node] = tree[2 * node] + tree[2 * node + 1];  // duplicates recompute the same value
+    const int m = s_count;
+    const int sb = S < kSub ? (int)S : kSub;
+    if (m == 0) return;                     // untouched subtree: every node already equals the sum of its children
+    int shift = 1;
+    for (long long width = S >> 1; width >= sb; width >>= 1, ++shift) {
+        for (int i = tid; i < m; i += kUpdThreads) {
+            const long long node = (P + s_leaf[i]) >> shift;
+            const double2 ch = __ldcg(reinterpret_cast<const double2 *>(tree + 2 * node));
+            __stcg(tree + node, ch.x + ch.y);  // duplicates recompute the same value
         }
         __syncthreads();
     }
+    sumtree_reduce_top(tree, (long long)G + blockIdx.x, sb, s_top);
+}
+
+// Top of the tree: nodes [G, 2G) are final; reduce the log2(G) levels above them.
+__global__ void __launch_bounds__(kUpdThreads) sumtree_top_kernel(double *tree, int G) {
+    __shared__ double s_top[2 * kSub];
+    sumtree_reduce_top(tree, 1, G, s_top);
 }
 
 // Full rebuild of one level from the level below (used for bulk loads): node in [width, 2*width).
@@ -103,8 +153,13 @@ extern "C" int32_t b200rl_sumtree_update(double *tree, int64_t leaves, const int
     B200RL_REQUIRE(tree && idx && value, -1, "sumtree_update: null pointer argument");
     B200RL_REQUIRE(is_pow2(leaves), -2, "sumtree_update: leaves=%lld is not a power of two", (long long)leaves);
     cudaStream_t s = (cudaStream_t)stream;
-    if (n <= 16384) {
-        sumtree_update_kernel<<<1, 1024, 0, s>>>(tree, leaves, reinterpret_cast<const long long *>(idx), value, n);
+    B200RL_REQUIRE(leaves <= (1ll << 30), -3, "sumtree_update: leaves=%lld > 2^30", (long long)leaves);
+    B200RL_REQUIRE(reinterpret_cast<uintptr_t>(tree) % 16 == 0, -4, "sumtree_update: tree must be 16-byte aligned");
+    if (n <= kUpdMax) {
+        int G = 1;
+        while (G < kMaxSubtrees && leaves / (2 * G) >= kSub) G *= 2;  // subtrees of at least kSub leaves
+        sumtree_update_kernel<<<G, kUpdThreads, 0, s>>>(tree, leaves, G, reinterpret_cast<const long long *>(idx), value, (int)n);
+        if (G > 1) sumtree_top_kernel<<<1, kUpdThreads, 0, s>>>(tree, G);
         return check_launch("sumtree_update_kernel");
     }
     // bulk load: set the leaves, then rebuild every level

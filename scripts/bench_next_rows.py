@@ -71,7 +71,7 @@ tree = torch.zeros(2 * P, dtype=torch.float64, device=dev)
 ops.sumtree_update(tree, torch.arange(1_000_000, device=dev), torch.rand(1_000_000, device=dev, dtype=torch.float64) + 1e-3)
 ui = torch.randint(0, 1_000_000, (4096,), device=dev)
 uv = torch.rand(4096, device=dev, dtype=torch.float64)
-report("N3 sumtree update 4096 of 1M", timed(lambda i: ops.sumtree_update(tree, ui, uv), n_streams=1), 0, "one CTA, 20 levels, latency-bound")
+report("N3 sumtree update 4096 of 1M", timed(lambda i: ops.sumtree_update(tree, ui, uv), n_streams=1), 0, "128 subtree CTAs + one top CTA, latency-bound")
 oi, op_ = torch.empty(4096, dtype=torch.int64, device=dev), torch.empty(4096, device=dev)
 from impala_b200 import _cabi
 report("N3 sumtree sample 4096 of 1M", timed(lambda i: _cabi.call("b200rl_sumtree_sample", tree.data_ptr(), P, 1_000_000, 1, 0, i * 4096,

@@ -240,12 +240,16 @@ def test_sumtree_bit_exact_vs_spec(cuda):
     """N3: device sum tree + inverse-CDF sampling vs the specification in oracle/replay_ref.py (bit-exact:
     tree nodes, sampled indices and probabilities), incremental and bulk updates."""
     rng = np.random.default_rng(0)
-    for cap in (1, 5, 1000, 40_000):
+    # leaves 1..2^20: one subtree CTA, 2, 16 and 128 subtree CTAs (with and without level-by-level part)
+    for cap in (1, 5, 600, 1000, 5000, 40_000, 1_000_000):
         ot = replay_ref.SumTree(cap)
         tree = torch.zeros(2 * ot.leaves, dtype=torch.float64, device=cuda)
-        for n in (min(cap, 7), min(cap, 333), cap):                  # cap = 40,000 > 16,384 takes the bulk path
+        for n in (min(cap, 7), min(cap, 333), min(cap, 4096), min(cap, 8192), cap):   # n > 8192 takes the bulk path
             idx = rng.choice(cap, size=n, replace=False).astype(np.int64)
             val = rng.random(n) ** 3 + 1e-3
+            if n == 4096:                                             # duplicates (same priority, as the learner's)
+                idx[100:200] = idx[:100]
+                val[100:200] = val[:100]
             ot.update(idx, val)
             ops.sumtree_update(tree, torch.from_numpy(idx).to(cuda), torch.from_numpy(val).to(cuda))
             assert np.array_equal(tree.cpu().numpy(), ot.tree)
