@@ -38,7 +38,12 @@ __device__ __forceinline__ float adam_update(float &p, float &g, float &m, float
     return p;
 }
 
-template <bool VEC>
+// VEC: 16-byte aligned buffers.  RESIDENT (VEC only): the chunk is at most kResident float4 per thread, so p, g, m and v
+// are all fetched BEFORE the grid barrier and stay in registers across it -- after the barrier there is only
+// arithmetic and stores (the small-bucket case: 630,352 parameters are 154 such chunks).
+constexpr int kResident = 4;
+
+template <bool VEC, bool RESIDENT>
 __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams a) {
     __shared__ float red[kOptThreads];
     __shared__ float s_total;
@@ -51,7 +56,21 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams
     }
     // ---- phase 1: partial sum of squares, fixed order ----
     float ss[1] = {0.f};
-    if (VEC) {
+    float4 rp[kResident], rg[kResident], rm[kResident], rv[kResident];
+    if (RESIDENT) {
+        const float4 *p4 = reinterpret_cast<const float4 *>(a.p), *g4 = reinterpret_cast<const float4 *>(a.g);
+        const float4 *m4 = reinterpret_cast<const float4 *>(a.m), *v4 = reinterpret_cast<const float4 *>(a.v);
+#pragma unroll
+        for (int k = 0; k < kResident; ++k) {
+            const long long i = lo / 4 + threadIdx.x + (long long)k * kOptThreads;
+            if (i < hi / 4) { rg[k] = g4[i]; rp[k] = p4[i]; rm[k] = m4[i]; rv[k] = v4[i]; }
+            else rg[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int k = 0; k < kResident; ++k)  // same per-thread order as the streaming path
+            ss[0] += (rg[k].x * rg[k].x + rg[k].y * rg[k].y) + (rg[k].z * rg[k].z + rg[k].w * rg[k].w);
+        for (long long i = (hi / 4) * 4 + threadIdx.x; i < hi; i += kOptThreads) ss[0] += a.g[i] * a.g[i];  // tail of n
+    } else if (VEC) {
         const float4 *g4 = reinterpret_cast<const float4 *>(a.g);
         for (long long i = lo / 4 + threadIdx.x; i < hi / 4; i += kOptThreads) {
             const float4 x = g4[i];
@@ -88,10 +107,29 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams
         *reinterpret_cast<volatile unsigned int *>(a.gen) = tag;  // every CTA has read the old value (barrier above)
     }
     // ---- phase 2: clip + Adam ----
-    if (VEC) {
+    if (RESIDENT) {
         float4 *p4 = reinterpret_cast<float4 *>(a.p), *g4 = reinterpret_cast<float4 *>(a.g);
         float4 *m4 = reinterpret_cast<float4 *>(a.m), *v4 = reinterpret_cast<float4 *>(a.v);
-        for (long long i = lo / 4 + threadIdx.x; i < hi / 4; i += kOptThreads) {
+#pragma unroll
+        for (int k = 0; k < kResident; ++k) {
+            const long long i = lo / 4 + threadIdx.x + (long long)k * kOptThreads;
+            if (i < hi / 4) {
+                adam_update(rp[k].x, rg[k].x, rm[k].x, rv[k].x, coef, a);
+                adam_update(rp[k].y, rg[k].y, rm[k].y, rv[k].y, coef, a);
+                adam_update(rp[k].z, rg[k].z, rm[k].z, rv[k].z, coef, a);
+                adam_update(rp[k].w, rg[k].w, rm[k].w, rv[k].w, coef, a);
+                p4[i] = rp[k]; g4[i] = rg[k]; m4[i] = rm[k]; v4[i] = rv[k];
+            }
+        }
+        for (long long i = (hi / 4) * 4 + threadIdx.x; i < hi; i += kOptThreads)
+            adam_update(a.p[i], a.g[i], a.m[i], a.v[i], coef, a);
+    } else if (VEC) {
+        float4 *p4 = reinterpret_cast<float4 *>(a.p), *g4 = reinterpret_cast<float4 *>(a.g);
+        float4 *m4 = reinterpret_cast<float4 *>(a.m), *v4 = reinterpret_cast<float4 *>(a.v);
+        // backwards: the end of the chunk is what phase 1 read last, so it is the part of g most likely still in L2
+        const long long first = lo / 4, count = hi / 4 - first;
+        for (long long r = count - 1 - threadIdx.x; r >= 0; r -= kOptThreads) {
+            const long long i = first + r;
             float4 p = p4[i], g = g4[i], m = m4[i], v = v4[i];
             adam_update(p.x, g.x, m.x, v.x, coef, a);
             adam_update(p.y, g.y, m.y, v.y, coef, a);
@@ -121,13 +159,14 @@ extern "C" int32_t b200rl_clip_adam_step(float *params, float *grads, float *exp
     B200RL_REQUIRE(lr >= 0 && beta1 >= 0 && beta1 < 1 && beta2 >= 0 && beta2 < 1 && eps >= 0, -2,
                    "clip_adam_step: invalid hyper-parameters");
     static int max_grid_dev[kMaxDevices];  // co-resident CTAs of this kernel, per device
+    static int max_grid_res_dev[kMaxDevices];  // same for the register-resident instantiation
     int dev = 0;
     cudaGetDevice(&dev);
     int &max_grid = max_grid_dev[(dev >= 0 && dev < kMaxDevices) ? dev : 0];
     if (max_grid == 0) {
         int sms = 0, per_sm = 0;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, clip_adam_kernel<true>, kOptThreads, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, clip_adam_kernel<true, false>, kOptThreads, 0);
         if (sms <= 0 || per_sm <= 0) {
             (void)cudaGetLastError();
             set_error("clip_adam_step: occupancy query failed (no CUDA device?)");
@@ -135,6 +174,9 @@ extern "C" int32_t b200rl_clip_adam_step(float *params, float *grads, float *exp
         }
         max_grid = sms * (per_sm > 4 ? 4 : per_sm);
         if (max_grid > kMaxOptCtas) max_grid = kMaxOptCtas;
+        int per_sm_res = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_res, clip_adam_kernel<true, true>, kOptThreads, 0);
+        max_grid_res_dev[(dev >= 0 && dev < kMaxDevices) ? dev : 0] = sms * (per_sm_res > 0 ? per_sm_res : 0);
     }
     AdamParams a;
     a.p = params; a.g = grads; a.m = exp_avg; a.v = exp_avg_sq; a.n = n;
@@ -167,7 +209,11 @@ extern "C" int32_t b200rl_clip_adam_step(float *params, float *grads, float *exp
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaError_t e = vec ? cudaLaunchKernelEx(&cfg, clip_adam_kernel<true>, a) : cudaLaunchKernelEx(&cfg, clip_adam_kernel<false>, a);
+    const bool resident = vec && chunk <= (long long)kResident * 4 * kOptThreads &&
+                          grid <= max_grid_res_dev[(dev >= 0 && dev < kMaxDevices) ? dev : 0] && env_int("B200RL_K6_RESIDENT", 1);
+    cudaError_t e = resident ? cudaLaunchKernelEx(&cfg, clip_adam_kernel<true, true>, a)
+                    : vec    ? cudaLaunchKernelEx(&cfg, clip_adam_kernel<true, false>, a)
+                             : cudaLaunchKernelEx(&cfg, clip_adam_kernel<false, false>, a);
     if (e != cudaSuccess) {
         set_error("clip_adam_kernel launch: %s", cudaGetErrorString(e));
         (void)cudaGetLastError();
