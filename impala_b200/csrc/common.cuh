@@ -121,6 +121,27 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap *map, const void 
                  : "memory");
 }
 
+// Thread-block clusters: rank of this CTA, cluster-wide barrier, and a 16-byte read of another CTA's shared
+// memory (distributed shared memory: mapa translates a local shared address to the peer's window).
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float4 ld_dsmem_f4(const void *local_smem, uint32_t rank) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(local_smem)), "r"(rank));
+    float4 v;
+    asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+                 : "r"(remote)
+                 : "memory");
+    return v;
+}
+
 // 16-byte cp.async (LDGSTS), L1-bypassing; src_bytes < 16 zero-fills the rest (0: nothing is read)
 __device__ __forceinline__ void cp_async16(void *smem, const void *gmem, int src_bytes) {
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem)), "l"(gmem), "r"(src_bytes)

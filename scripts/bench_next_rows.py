@@ -81,6 +81,12 @@ report("N3 sumtree sample 4096 of 1M", timed(lambda i: _cabi.call("b200rl_sumtre
 T, B = 256, 8192
 xs = [[torch.randn(T, B, device=dev) for _ in range(3)] for _ in range(6)]
 report("N4 n-step returns n=3, T=256 B=8192", timed(lambda i: ops.n_step_returns(*[x.t() for x in xs[i % 6]], 3)), 16 * T * B)
+outs2 = [torch.empty(T, B, device=dev) for _ in range(6)]
+report("K2 lambda-returns T=256 B=8192 (alone)", timed(lambda i: ops.lambda_returns(*[x.t() for x in xs[i % 6]], 0.95)), 16 * T * B)
+report("K2 lambda-returns T=256 B=8192 (alone, 1 stream)", timed(lambda i: ops.lambda_returns(*[x.t() for x in xs[i % 6]], 0.95), n_streams=1), 16 * T * B)
+xs5 = [[torch.randn(512, 4096, device=dev) for _ in range(3)] for _ in range(6)]
+report("K2 lambda-returns T=512 B=4096 (alone)", timed(lambda i: ops.lambda_returns(*[x.t() for x in xs5[i % 6]], 0.95)), 16 * 512 * 4096)
+del xs5
 # N4b: quantile Huber, B=256 N=M=64 ; N5: act epilogue 128 rows
 src, tau, tgt = torch.randn(256, 64, device=dev), torch.rand(256, 64, device=dev), torch.randn(256, 64, device=dev)
 report("N4b quantile-Huber B=256 N=M=64", timed(lambda i: ops.quantile_huber_fwdbwd(src, tau, tgt)), 0, "launch-latency bound (262 KB)")
