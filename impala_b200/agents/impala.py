@@ -75,7 +75,8 @@ class ImpalaLearner:
 
     def _train_step(self, batch) -> Dict[str, torch.Tensor]:
         if self._bucket is None:
-            self._bucket = parallel.GradBucket(self._model.parameters())
+            self._bucket = parallel.make_bucket(self._model.parameters(), self._group,
+                                                isinstance(self._optimizer, optim.FusedClipAdam))
             if isinstance(self._optimizer, optim.FusedClipAdam) and \
                     [id(q) for q in self._bucket.params] != [id(q) for q in self._optimizer.params]:
                 raise RuntimeError("FusedClipAdam must be built from model.parameters() (same order as the gradient bucket)")
@@ -100,15 +101,20 @@ class ImpalaLearner:
         torch.autograd.backward([pi, values], [dlogits, dvalues])
         mark("model bwd")
         bucket.extra.copy_(scalars)
-        bucket.allreduce(self._group)                                     # grads + scalars, one collective
-        mark("grad allreduce")
-        if isinstance(self._optimizer, optim.FusedClipAdam):               # :172-176 in one launch (K6)
-            grad_norm = self._optimizer.step_flat(bucket.grads, self._max_grad_norm)[0]
+        if isinstance(bucket, parallel.PeerGradBucket):                   # allreduce + :172-176 in one launch (K8)
+            mark("grad allreduce")
+            grad_norm = self._optimizer.step_peer(bucket, self._max_grad_norm)[0]
+            sc = bucket.extra_reduced
         else:
-            grad_norm = bucket.clip_(self._max_grad_norm)                     # :172-173
-            self._optimizer.step()                                            # :176
+            bucket.allreduce(self._group)                                 # grads + scalars, one collective
+            mark("grad allreduce")
+            if isinstance(self._optimizer, optim.FusedClipAdam):           # :172-176 in one launch (K6)
+                grad_norm = self._optimizer.step_flat(bucket.grads, self._max_grad_norm)[0]
+            else:
+                grad_norm = bucket.clip_(self._max_grad_norm)                 # :172-173
+                self._optimizer.step()                                        # :176
+            sc = bucket.extra
         mark("clip+adam")
-        sc = bucket.extra
         return {
             "train/loss": sc[ops.S_LOSS], "train/entropy": sc[ops.S_ENTROPY], "train/td": sc[ops.S_TD],
             "train/pg": sc[ops.S_PG], "train/kl": sc[ops.S_KL], "train/ratio": sc[ops.S_RATIO],

@@ -69,7 +69,8 @@ class PPOLearner:
 
     def _train_step(self, batch) -> Dict[str, torch.Tensor]:
         if self._bucket is None:
-            self._bucket = parallel.GradBucket(self._model.parameters())
+            self._bucket = parallel.make_bucket(self._model.parameters(), self._group,
+                                                isinstance(self._optimizer, optim.FusedClipAdam))
             if isinstance(self._optimizer, optim.FusedClipAdam) and \
                     [id(q) for q in self._bucket.params] != [id(q) for q in self._optimizer.params]:
                 raise RuntimeError("FusedClipAdam must be built from model.parameters() (same order as the gradient bucket)")
@@ -84,13 +85,17 @@ class PPOLearner:
                                                    self._clip_coeff, n_global=pi.shape[0] * world_size)
         torch.autograd.backward([pi, v], [dlogits, dv.view_as(v)])        # :134
         bucket.extra.copy_(scalars)
-        bucket.allreduce(self._group)
-        if isinstance(self._optimizer, optim.FusedClipAdam):               # :136-140 in one launch (K6)
-            grad_norm = self._optimizer.step_flat(bucket.grads, self._max_grad_norm)[0]
+        if isinstance(bucket, parallel.PeerGradBucket):                   # allreduce + :136-140 in one launch (K8)
+            grad_norm = self._optimizer.step_peer(bucket, self._max_grad_norm)[0]
+            sc = bucket.extra_reduced
         else:
-            grad_norm = bucket.clip_(self._max_grad_norm)                     # :136-137
-            self._optimizer.step()                                            # :140
-        sc = bucket.extra
+            bucket.allreduce(self._group)
+            if isinstance(self._optimizer, optim.FusedClipAdam):           # :136-140 in one launch (K6)
+                grad_norm = self._optimizer.step_flat(bucket.grads, self._max_grad_norm)[0]
+            else:
+                grad_norm = bucket.clip_(self._max_grad_norm)                 # :136-137
+                self._optimizer.step()                                        # :140
+            sc = bucket.extra
         return {
             "train/loss": sc[ops.S_LOSS], "train/entropy": sc[ops.S_ENTROPY], "train/td": sc[ops.S_TD],
             "train/pg": sc[ops.S_PG], "train/target": sc[ops.S_TARGET],

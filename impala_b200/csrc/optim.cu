@@ -29,6 +29,77 @@ struct AdamParams {
     unsigned long long *words;
 };
 
+// ---- K8: the same kernel with the gradient ALLREDUCE fused in (PEER = true) ----------------------------------
+// Every rank's flat gradient bucket is mapped into every other rank's address space (CUDA IPC over NVLink /
+// NVSwitch peer access).  Instead of reading its own gradient, a CTA reads its chunk from ALL ranks' buckets
+// with system-scope loads and adds them in rank order 0..W-1 -- every rank computes bit-identical sums -- then
+// norm, clip and Adam proceed as in K6.  Two flag exchanges bracket the peer reads: "my gradients are final"
+// before them, "I have finished reading yours" after them (the kernel does not exit before every peer has
+// said so, so stream order protects the next backward pass that overwrites the bucket).  Flags carry the step
+// number: monotonic, never reset.
+constexpr int kMaxPeers = 8;
+constexpr long long kPeerSpinLimitCycles = 1ll << 35;  // ~18 s: ranks may be skewed by a whole learner step
+
+struct PeerParams {
+    const float *g[kMaxPeers];      // every rank's bucket: n gradients followed by n_extra floats
+    unsigned int *flags[kMaxPeers];  // every rank's flag area: ready[kMaxPeers], done[kMaxPeers]
+    float *extra_out;                // [n_extra] sums of the buckets' tails (loss / metric scalars)
+    int world, rank, n_extra;
+    unsigned int gen;
+};
+
+__device__ __forceinline__ void st_release_sys_u32(unsigned int *p, unsigned int v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys_u32(const unsigned int *p) {
+    unsigned int v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 ld_sys_f4(const float4 *p) {
+    float4 v;
+    asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ float ld_sys_f32(const float *p) {
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+    return v;
+}
+// wait until peer `t`'s word in this rank's flag area reaches `gen`; false on timeout
+__device__ __forceinline__ bool peer_wait(const unsigned int *word, unsigned int gen) {
+    const long long t0 = clock64();
+    while ((int)(ld_acquire_sys_u32(word) - gen) < 0)
+        if (clock64() - t0 > kPeerSpinLimitCycles) return false;
+    return true;
+}
+template <bool PEER>
+__device__ __forceinline__ float4 load_grad4(const AdamParams &a, const PeerParams &pp, long long i) {
+    if constexpr (!PEER) {
+        return reinterpret_cast<const float4 *>(a.g)[i];
+    } else {
+    float4 v[kMaxPeers];
+#pragma unroll
+    for (int r = 0; r < kMaxPeers; ++r)
+        if (r < pp.world) v[r] = ld_sys_f4(reinterpret_cast<const float4 *>(pp.g[r]) + i);
+    float4 s = v[0];
+#pragma unroll
+    for (int r = 1; r < kMaxPeers; ++r)
+        if (r < pp.world) { s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w; }
+    return s;
+    }
+}
+template <bool PEER>
+__device__ __forceinline__ float load_grad1(const AdamParams &a, const PeerParams &pp, long long i) {
+    if constexpr (!PEER) {
+        return a.g[i];
+    } else {
+        float s = ld_sys_f32(pp.g[0] + i);
+        for (int r = 1; r < pp.world; ++r) s += ld_sys_f32(pp.g[r] + i);
+        return s;
+    }
+}
+
 __device__ __forceinline__ float adam_update(float &p, float &g, float &m, float &v, float coef, const AdamParams &a) {
     g = g * coef;
     m = m + a.one_minus_beta1 * (g - m);                  // exp_avg.lerp_(grad, 1 - beta1)
@@ -43,13 +114,24 @@ __device__ __forceinline__ float adam_update(float &p, float &g, float &m, float
 // arithmetic and stores (the small-bucket case: 630,352 parameters are 154 such chunks).
 constexpr int kResident = 4;
 
-template <bool VEC, bool RESIDENT>
-__global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams a) {
+template <bool VEC, bool RESIDENT, bool PEER>
+__global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams a, const PeerParams pp) {
     __shared__ float red[kOptThreads];
     __shared__ float s_total;
     const long long lo = (long long)blockIdx.x * a.chunk;
     const long long hi = min(a.n, lo + a.chunk);
     __shared__ unsigned int s_tag;
+    __shared__ int s_peer_ok;
+    if (PEER) {
+        // "my gradients are final" to every rank (they were written by earlier kernels of this stream), then wait
+        // for every rank's word in this rank's flag area
+        if (threadIdx.x == 0) s_peer_ok = 1;
+        __syncthreads();
+        if (blockIdx.x == 0 && threadIdx.x < pp.world) st_release_sys_u32(pp.flags[threadIdx.x] + pp.rank, pp.gen);
+        if (threadIdx.x < pp.world && !peer_wait(pp.flags[pp.rank] + threadIdx.x, pp.gen)) s_peer_ok = 0;
+        __syncthreads();
+        if (blockIdx.x == 0 && threadIdx.x < pp.n_extra) pp.extra_out[threadIdx.x] = load_grad1<true>(a, pp, a.n + threadIdx.x);
+    }
     if (threadIdx.x == 0) {
         unsigned int t = *reinterpret_cast<volatile unsigned int *>(a.gen) + 1u;
         s_tag = t ? t : 1u;  // 0 is the "never written" tag of a zeroed workspace
@@ -58,27 +140,40 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams
     float ss[1] = {0.f};
     float4 rp[kResident], rg[kResident], rm[kResident], rv[kResident];
     if (RESIDENT) {
-        const float4 *p4 = reinterpret_cast<const float4 *>(a.p), *g4 = reinterpret_cast<const float4 *>(a.g);
+        const float4 *p4 = reinterpret_cast<const float4 *>(a.p);
         const float4 *m4 = reinterpret_cast<const float4 *>(a.m), *v4 = reinterpret_cast<const float4 *>(a.v);
 #pragma unroll
         for (int k = 0; k < kResident; ++k) {
             const long long i = lo / 4 + threadIdx.x + (long long)k * kOptThreads;
-            if (i < hi / 4) { rg[k] = g4[i]; rp[k] = p4[i]; rm[k] = m4[i]; rv[k] = v4[i]; }
+            if (i < hi / 4) { rg[k] = load_grad4<PEER>(a, pp, i); rp[k] = p4[i]; rm[k] = m4[i]; rv[k] = v4[i]; }
             else rg[k] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
 #pragma unroll
         for (int k = 0; k < kResident; ++k)  // same per-thread order as the streaming path
             ss[0] += (rg[k].x * rg[k].x + rg[k].y * rg[k].y) + (rg[k].z * rg[k].z + rg[k].w * rg[k].w);
-        for (long long i = (hi / 4) * 4 + threadIdx.x; i < hi; i += kOptThreads) ss[0] += a.g[i] * a.g[i];  // tail of n
+        for (long long i = (hi / 4) * 4 + threadIdx.x; i < hi; i += kOptThreads) {  // tail of n
+            const float x = load_grad1<PEER>(a, pp, i);
+            if (PEER) a.g[i] = x;
+            ss[0] += x * x;
+        }
     } else if (VEC) {
-        const float4 *g4 = reinterpret_cast<const float4 *>(a.g);
+        float4 *g4 = reinterpret_cast<float4 *>(a.g);
         for (long long i = lo / 4 + threadIdx.x; i < hi / 4; i += kOptThreads) {
-            const float4 x = g4[i];
+            const float4 x = load_grad4<PEER>(a, pp, i);
+            if (PEER) g4[i] = x;  // the reduced gradient, re-read by phase 2
             ss[0] += (x.x * x.x + x.y * x.y) + (x.z * x.z + x.w * x.w);
         }
-        for (long long i = (hi / 4) * 4 + threadIdx.x; i < hi; i += kOptThreads) ss[0] += a.g[i] * a.g[i];  // tail of n
+        for (long long i = (hi / 4) * 4 + threadIdx.x; i < hi; i += kOptThreads) {  // tail of n
+            const float x = load_grad1<PEER>(a, pp, i);
+            if (PEER) a.g[i] = x;
+            ss[0] += x * x;
+        }
     } else {
-        for (long long i = lo + threadIdx.x; i < hi; i += kOptThreads) ss[0] += a.g[i] * a.g[i];
+        for (long long i = lo + threadIdx.x; i < hi; i += kOptThreads) {
+            const float x = load_grad1<PEER>(a, pp, i);
+            if (PEER) a.g[i] = x;
+            ss[0] += x * x;
+        }
     }
     float tot[1];
     cta_sum<1>(ss, red, tot);
@@ -99,7 +194,9 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams
     cta_sum<1>(acc, red, tot);
     if (threadIdx.x == 0) s_total = tot[0];
     __syncthreads();
-    const float norm = sqrtf(s_total);
+    if (PEER && blockIdx.x == 0 && threadIdx.x < pp.world)  // every CTA of this rank has consumed its peer reads
+        st_release_sys_u32(pp.flags[threadIdx.x] + kMaxPeers + pp.rank, pp.gen);
+    const float norm = (PEER && !s_peer_ok) ? __int_as_float(0x7fc00000) : sqrtf(s_total);  // a peer never arrived: NaN
     float coef = 1.f;
     if (a.max_norm > 0.f) coef = fminf(a.max_norm / (norm + 1e-6f), 1.f);  // torch clip_grad_norm_
     if (blockIdx.x == 0 && threadIdx.x == 0) {
@@ -143,40 +240,40 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams
         for (long long i = lo + threadIdx.x; i < hi; i += kOptThreads)
             adam_update(a.p[i], a.g[i], a.m[i], a.v[i], coef, a);
     }
+    if (PEER && blockIdx.x == 0 && threadIdx.x < pp.world)  // nobody still reads this rank's bucket once the kernel is done
+        (void)peer_wait(pp.flags[pp.rank] + kMaxPeers + threadIdx.x, pp.gen);
 }
 
-}  // namespace b200rl
-
-extern "C" int32_t b200rl_clip_adam_step(float *params, float *grads, float *exp_avg, float *exp_avg_sq,
-                                         int64_t n, float max_norm, double lr, double beta1, double beta2,
-                                         double eps, int64_t step, float *total_norm, void *workspace,
-                                         void *stream) {
-    using namespace b200rl;
-    B200RL_REQUIRE(params && grads && exp_avg && exp_avg_sq && total_norm && workspace, -1,
-                   "clip_adam_step: null pointer argument");
-    B200RL_REQUIRE(n >= 1, -2, "clip_adam_step: n=%lld", (long long)n);
-    B200RL_REQUIRE(step >= 1, -2, "clip_adam_step: step must be >= 1 (got %lld)", (long long)step);
+// Shared host side of K6 (peer == nullptr) and K8.
+static int32_t launch_clip_adam(const char *who, float *params, float *grads, float *exp_avg, float *exp_avg_sq, int64_t n,
+                                float max_norm, double lr, double beta1, double beta2, double eps, int64_t step,
+                                float *total_norm, void *workspace, void *stream, const PeerParams *peer) {
+    B200RL_REQUIRE(params && grads && exp_avg && exp_avg_sq && total_norm && workspace, -1, "%s: null pointer argument", who);
+    B200RL_REQUIRE(n >= 1, -2, "%s: n=%lld", who, (long long)n);
+    B200RL_REQUIRE(step >= 1, -2, "%s: step must be >= 1 (got %lld)", who, (long long)step);
     B200RL_REQUIRE(lr >= 0 && beta1 >= 0 && beta1 < 1 && beta2 >= 0 && beta2 < 1 && eps >= 0, -2,
-                   "clip_adam_step: invalid hyper-parameters");
-    static int max_grid_dev[kMaxDevices];  // co-resident CTAs of this kernel, per device
-    static int max_grid_res_dev[kMaxDevices];  // same for the register-resident instantiation
+                   "%s: invalid hyper-parameters", who);
+    static int max_grid_dev[kMaxDevices];      // co-resident CTAs of the streaming kernel, per device
+    static int max_grid_res_dev[kMaxDevices];  // same for the register-resident instantiations
     int dev = 0;
     cudaGetDevice(&dev);
-    int &max_grid = max_grid_dev[(dev >= 0 && dev < kMaxDevices) ? dev : 0];
+    const int di = (dev >= 0 && dev < kMaxDevices) ? dev : 0;
+    int &max_grid = max_grid_dev[di];
     if (max_grid == 0) {
-        int sms = 0, per_sm = 0;
+        int sms = 0, per_sm = 0, per_sm_res = 0, per_sm_peer = 0;
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, clip_adam_kernel<true, false>, kOptThreads, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, clip_adam_kernel<true, false, true>, kOptThreads, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_res, clip_adam_kernel<true, true, false>, kOptThreads, 0);
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_peer, clip_adam_kernel<true, true, true>, kOptThreads, 0);
         if (sms <= 0 || per_sm <= 0) {
             (void)cudaGetLastError();
-            set_error("clip_adam_step: occupancy query failed (no CUDA device?)");
+            set_error("%s: occupancy query failed (no CUDA device?)", who);
             return (int32_t)cudaErrorUnknown;
         }
         max_grid = sms * (per_sm > 4 ? 4 : per_sm);
         if (max_grid > kMaxOptCtas) max_grid = kMaxOptCtas;
-        int per_sm_res = 0;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_res, clip_adam_kernel<true, true>, kOptThreads, 0);
-        max_grid_res_dev[(dev >= 0 && dev < kMaxDevices) ? dev : 0] = sms * (per_sm_res > 0 ? per_sm_res : 0);
+        if (per_sm_peer < per_sm_res) per_sm_res = per_sm_peer;
+        max_grid_res_dev[di] = sms * (per_sm_res > 0 ? per_sm_res : 0);
     }
     AdamParams a;
     a.p = params; a.g = grads; a.m = exp_avg; a.v = exp_avg_sq; a.n = n;
@@ -198,8 +295,14 @@ extern "C" int32_t b200rl_clip_adam_step(float *params, float *grads, float *exp
     a.total_norm = total_norm;
     a.gen = reinterpret_cast<unsigned int *>(reinterpret_cast<char *>(workspace) + kOptOffset);
     a.words = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(workspace) + kOptOffset + 64);
-    const bool vec = ((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads) |
-                       reinterpret_cast<uintptr_t>(exp_avg) | reinterpret_cast<uintptr_t>(exp_avg_sq)) % 16) == 0;
+    uintptr_t align = reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(grads) |
+                      reinterpret_cast<uintptr_t>(exp_avg) | reinterpret_cast<uintptr_t>(exp_avg_sq);
+    PeerParams pp = {};
+    if (peer) {
+        pp = *peer;
+        for (int r = 0; r < pp.world; ++r) align |= reinterpret_cast<uintptr_t>(pp.g[r]);
+    }
+    const bool vec = (align % 16) == 0;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3(kOptThreads);
@@ -209,15 +312,56 @@ extern "C" int32_t b200rl_clip_adam_step(float *params, float *grads, float *exp
     attr[0].val.cooperative = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    const bool resident = vec && chunk <= (long long)kResident * 4 * kOptThreads &&
-                          grid <= max_grid_res_dev[(dev >= 0 && dev < kMaxDevices) ? dev : 0] && env_int("B200RL_K6_RESIDENT", 1);
-    cudaError_t e = resident ? cudaLaunchKernelEx(&cfg, clip_adam_kernel<true, true>, a)
-                    : vec    ? cudaLaunchKernelEx(&cfg, clip_adam_kernel<true, false>, a)
-                             : cudaLaunchKernelEx(&cfg, clip_adam_kernel<false, false>, a);
+    const bool resident = vec && chunk <= (long long)kResident * 4 * kOptThreads && grid <= max_grid_res_dev[di] &&
+                          env_int("B200RL_K6_RESIDENT", 1);
+    cudaError_t e;
+    if (peer)
+        e = resident ? cudaLaunchKernelEx(&cfg, clip_adam_kernel<true, true, true>, a, pp)
+            : vec    ? cudaLaunchKernelEx(&cfg, clip_adam_kernel<true, false, true>, a, pp)
+                     : cudaLaunchKernelEx(&cfg, clip_adam_kernel<false, false, true>, a, pp);
+    else
+        e = resident ? cudaLaunchKernelEx(&cfg, clip_adam_kernel<true, true, false>, a, pp)
+            : vec    ? cudaLaunchKernelEx(&cfg, clip_adam_kernel<true, false, false>, a, pp)
+                     : cudaLaunchKernelEx(&cfg, clip_adam_kernel<false, false, false>, a, pp);
     if (e != cudaSuccess) {
         set_error("clip_adam_kernel launch: %s", cudaGetErrorString(e));
         (void)cudaGetLastError();
         return (int32_t)e;
     }
     return check_launch("clip_adam_kernel");
+}
+
+}  // namespace b200rl
+
+extern "C" int32_t b200rl_clip_adam_step(float *params, float *grads, float *exp_avg, float *exp_avg_sq,
+                                         int64_t n, float max_norm, double lr, double beta1, double beta2,
+                                         double eps, int64_t step, float *total_norm, void *workspace,
+                                         void *stream) {
+    return b200rl::launch_clip_adam("clip_adam_step", params, grads, exp_avg, exp_avg_sq, n, max_norm, lr, beta1, beta2, eps,
+                                    step, total_norm, workspace, stream, nullptr);
+}
+
+extern "C" int32_t b200rl_peer_allreduce_clip_adam_step(
+    float *params, const float *const *peer_buckets, uint32_t *const *peer_flags, int32_t world, int32_t rank,
+    float *grads_out, float *extra_out, int64_t n_extra, float *exp_avg, float *exp_avg_sq, int64_t n, float max_norm,
+    double lr, double beta1, double beta2, double eps, int64_t step, float *total_norm, void *workspace, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(peer_buckets && peer_flags && grads_out, -1, "peer_allreduce_clip_adam_step: null pointer argument");
+    B200RL_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, -2,
+                   "peer_allreduce_clip_adam_step: world=%d rank=%d (at most %d ranks)", world, rank, kMaxPeers);
+    B200RL_REQUIRE(n_extra >= 0 && n_extra <= kOptThreads && (n_extra == 0 || extra_out), -2,
+                   "peer_allreduce_clip_adam_step: n_extra=%lld", (long long)n_extra);
+    B200RL_REQUIRE(step >= 1 && step < (1ll << 31), -2, "peer_allreduce_clip_adam_step: step=%lld", (long long)step);
+    PeerParams pp = {};
+    for (int r = 0; r < world; ++r) {
+        B200RL_REQUIRE(peer_buckets[r] && peer_flags[r], -1, "peer_allreduce_clip_adam_step: rank %d pointer is null", r);
+        B200RL_REQUIRE(peer_buckets[r] != grads_out, -2, "peer_allreduce_clip_adam_step: grads_out must not alias a bucket");
+        pp.g[r] = peer_buckets[r];
+        pp.flags[r] = peer_flags[r];
+    }
+    pp.extra_out = extra_out;
+    pp.world = world; pp.rank = rank; pp.n_extra = (int)n_extra;
+    pp.gen = (unsigned int)step;
+    return launch_clip_adam("peer_allreduce_clip_adam_step", params, grads_out, exp_avg, exp_avg_sq, n, max_norm, lr, beta1,
+                            beta2, eps, step, total_norm, workspace, stream, &pp);
 }

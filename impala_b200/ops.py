@@ -1,4 +1,6 @@
 """Thin functional wrappers: torch tensors in, C-ABI launches on the current stream."""
+import ctypes
+
 import torch
 
 from . import _cabi
@@ -273,6 +275,52 @@ def clip_adam_step(params, grads, exp_avg, exp_avg_sq, step, lr, beta1=0.9, beta
                exp_avg_sq.data_ptr(), n, max_norm, lr, beta1, beta2, eps, step, total_norm.data_ptr(),
                ws.data_ptr(), _stream())
     return total_norm
+
+
+def peer_allreduce_clip_adam_step(params, peer_bucket_ptrs, peer_flag_ptrs, rank, grads_out, extra_out, exp_avg,
+                                  exp_avg_sq, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, max_norm=0.0,
+                                  total_norm=None):
+    """K8.  ``peer_bucket_ptrs`` / ``peer_flag_ptrs``: device addresses (ints) of every rank's bucket and flag area as
+    mapped into THIS process (``parallel.PeerGradBucket``).  Returns the 1-element pre-clip norm of the reduced gradient."""
+    _require_cuda(params, grads_out, exp_avg, exp_avg_sq)
+    n, world = params.numel(), len(peer_bucket_ptrs)
+    for name, x in (("params", params), ("grads_out", grads_out), ("exp_avg", exp_avg), ("exp_avg_sq", exp_avg_sq)):
+        if x.dtype != torch.float32 or not x.is_contiguous() or x.numel() != n:
+            raise RuntimeError("peer_allreduce_clip_adam_step: %s must be a contiguous float32 buffer of %d elements" % (name, n))
+    if len(peer_flag_ptrs) != world:
+        raise RuntimeError("peer_allreduce_clip_adam_step: %d buckets vs %d flag areas" % (world, len(peer_flag_ptrs)))
+    n_extra = 0 if extra_out is None else extra_out.numel()
+    if total_norm is None:
+        total_norm = torch.empty(1, dtype=torch.float32, device=params.device)
+    buckets = (ctypes.c_void_p * world)(*peer_bucket_ptrs)
+    flags = (ctypes.c_void_p * world)(*peer_flag_ptrs)
+    ws = workspace(params.device)
+    _cabi.call("b200rl_peer_allreduce_clip_adam_step", params.data_ptr(), ctypes.addressof(buckets), ctypes.addressof(flags),
+               world, rank, grads_out.data_ptr(), 0 if extra_out is None else extra_out.data_ptr(), n_extra,
+               exp_avg.data_ptr(), exp_avg_sq.data_ptr(), n, max_norm, lr, beta1, beta2, eps, step,
+               total_norm.data_ptr(), ws.data_ptr(), _stream())
+    return total_norm
+
+
+def ipc_export(tensor):
+    """``(handle: bytes[64], offset: int)`` naming ``tensor``'s memory for another process (K8 plumbing)."""
+    _require_cuda(tensor)
+    handle = ctypes.create_string_buffer(64)
+    offset = ctypes.c_int64(0)
+    _cabi.call("b200rl_ipc_export", tensor.data_ptr(), ctypes.addressof(handle), ctypes.addressof(offset))
+    return handle.raw, offset.value
+
+
+def ipc_import(handle, offset):
+    """Device address (int) of a peer's buffer in this process (the mapping lives until ``ipc_close`` / exit)."""
+    buf = ctypes.create_string_buffer(bytes(handle), 64)
+    out = ctypes.c_void_p(0)
+    _cabi.call("b200rl_ipc_import", ctypes.addressof(buf), offset, ctypes.addressof(out))
+    return out.value
+
+
+def ipc_close(ptr, offset):
+    _cabi.call("b200rl_ipc_close", ptr, offset)
 
 
 def ring_append_fields(storages, count, rows, done_field=None, gamma=0.99):

@@ -52,6 +52,17 @@ class FusedClipAdam(torch.optim.Optimizer):
         return ops.clip_adam_step(self.flat, flat_grads, self.exp_avg, self.exp_avg_sq, self.step_count,
                                   g["lr"], g["betas"][0], g["betas"][1], g["eps"], mgn, self.total_norm)
 
+    def step_peer(self, bucket, max_grad_norm=None) -> torch.Tensor:
+        """K8: allreduce (over the peer-mapped buckets of ``parallel.PeerGradBucket``) + clip + Adam in ONE launch, no
+        NCCL call.  The reduced, clipped gradient lands in ``bucket.reduced``, the summed scalar tail in
+        ``bucket.extra_reduced``; returns the pre-clip global norm.  Every rank must call it once per step."""
+        g = self.param_groups[0]
+        self.step_count += 1
+        mgn = self.max_grad_norm if max_grad_norm is None else float(max_grad_norm)
+        return ops.peer_allreduce_clip_adam_step(self.flat, bucket.bucket_ptrs, bucket.flag_ptrs, bucket.rank, bucket.reduced,
+                                                 bucket.extra_reduced, self.exp_avg, self.exp_avg_sq, self.step_count,
+                                                 g["lr"], g["betas"][0], g["betas"][1], g["eps"], mgn, self.total_norm)
+
     @torch.no_grad()
     def step(self, closure=None):
         if closure is not None:

@@ -6,6 +6,8 @@ independent per batch column (the reference itself writes that as ``vmap`` over 
 the only exchange is ONE allreduce per step: the flattened model gradient with the 8 loss/metric
 scalars riding in its tail (NCCL over NVLink/NVSwitch on GPUs, gloo in the CPU tests).
 """
+import os
+import warnings
 from typing import Iterable, Optional
 
 import torch
@@ -29,11 +31,12 @@ class GradBucket:
     """All parameter gradients as views into one flat fp32 buffer + ``n_extra`` tail floats, so a step
     needs exactly one allreduce (630,352 params = 2.52 MB for the IMPALA-CNN: latency-bound, one bucket)."""
 
-    def __init__(self, params: Iterable[torch.nn.Parameter], n_extra: int = 8):
+    def __init__(self, params: Iterable[torch.nn.Parameter], n_extra: int = 8, reserve: int = 0):
         self.params = [p for p in params if p.requires_grad]
         n = sum(p.numel() for p in self.params)
         dev = self.params[0].device
-        self.flat = torch.zeros(n + n_extra, dtype=torch.float32, device=dev)
+        self.store = torch.zeros(n + n_extra + reserve, dtype=torch.float32, device=dev)  # reserve: see PeerGradBucket
+        self.flat = self.store[:n + n_extra]
         self.n, self.n_extra = n, n_extra
         self.views, off = [], 0
         for p in self.params:
@@ -66,3 +69,71 @@ class GradBucket:
         total = torch.linalg.vector_norm(g)
         g.mul_(torch.clamp(max_norm / (total + 1e-6), max=1.0))
         return total
+
+
+class PeerGradBucket(GradBucket):
+    """A ``GradBucket`` whose buffer is mapped into every rank's address space (CUDA IPC, NVLink / NVSwitch peer
+    access), for the fused allreduce + clip + Adam kernel (K8, ``ops.peer_allreduce_clip_adam_step``): no NCCL call on
+    the step.  Buffer layout: ``n`` gradients, ``n_extra`` scalars, padding to 16 bytes, 16 flag words."""
+
+    FLAG_WORDS = 16
+
+    def __init__(self, params: Iterable[torch.nn.Parameter], n_extra: int = 8, group=None):
+        from . import ops
+        plist = [p for p in params if p.requires_grad]
+        n = sum(p.numel() for p in plist)
+        pad = (-(n + n_extra)) % 4
+        super().__init__(plist, n_extra, reserve=pad + self.FLAG_WORDS)
+        if not self.store.is_cuda:
+            raise RuntimeError("PeerGradBucket needs CUDA parameters (peer memory is a GPU feature)")
+        self.group = group
+        self.rank, self.world_size = world(group)
+        if self.world_size > 8:
+            raise RuntimeError("PeerGradBucket: at most 8 ranks (one NVSwitch box)")
+        self.flag_offset_bytes = (n + n_extra + pad) * 4
+        mine = ops.ipc_export(self.store)
+        gathered = [None] * self.world_size
+        if self.world_size > 1:
+            dist.all_gather_object(gathered, mine, group=group)
+        else:
+            gathered[0] = mine
+        self._imports = []
+        self.bucket_ptrs = []
+        for r, (handle, offset) in enumerate(gathered):
+            if r == self.rank:
+                self.bucket_ptrs.append(self.store.data_ptr())
+            else:
+                ptr = ops.ipc_import(handle, offset)
+                self._imports.append((ptr, offset))
+                self.bucket_ptrs.append(ptr)
+        self.flag_ptrs = [p + self.flag_offset_bytes for p in self.bucket_ptrs]
+        self.reduced = torch.zeros(self.n, dtype=torch.float32, device=self.store.device)   # reduced, clipped gradient
+        self.extra_reduced = torch.zeros(n_extra, dtype=torch.float32, device=self.store.device)
+        if self.world_size > 1:
+            dist.barrier(group=group)   # every rank has mapped every bucket before the first kernel touches one
+
+    def allreduce(self, group=None) -> None:
+        raise RuntimeError("PeerGradBucket: the allreduce is fused into FusedClipAdam.step_peer (K8)")
+
+    def close(self) -> None:
+        from . import ops
+        for ptr, offset in self._imports:
+            ops.ipc_close(ptr, offset)
+        self._imports = []
+
+
+def make_bucket(params, group=None, fused_optimizer: bool = False, n_extra: int = 8) -> GradBucket:
+    """The learners' gradient bucket: peer-mapped (K8) when the optimizer is ``FusedClipAdam``, more than one rank runs
+    on CUDA and ``B200RL_PEER_ALLREDUCE`` is not ``0``; otherwise the plain bucket (one NCCL / gloo allreduce per step).
+    ``B200RL_PEER_ALLREDUCE=1`` makes a failed IPC mapping an error instead of a warning + NCCL."""
+    plist = [p for p in params if p.requires_grad]
+    mode = os.environ.get("B200RL_PEER_ALLREDUCE", "auto")
+    _, ws = world(group)
+    if fused_optimizer and ws > 1 and plist[0].is_cuda and mode != "0":
+        try:
+            return PeerGradBucket(plist, n_extra, group)
+        except RuntimeError as e:   # export / import failures are symmetric across ranks (same allocator, same box)
+            if mode == "1":
+                raise
+            warnings.warn("peer-mapped gradient bucket unavailable (%s); using the NCCL allreduce" % e)
+    return GradBucket(plist, n_extra)

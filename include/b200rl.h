@@ -239,6 +239,29 @@ int32_t b200rl_clip_adam_step(
     float max_norm, double lr, double beta1, double beta2, double eps, int64_t step,
     float *total_norm, void *workspace, void *stream);
 
+/* K8 -- K6 with the gradient allreduce fused in (SURVEY sec 8f N1 "fused with the allreduce epilogue"; replaces the
+ * dist.all_reduce + clip_grad_norm_ + optimizer.step() of a data-parallel learner step).  One process per GPU;
+ * every rank's bucket (n gradients followed by n_extra floats, e.g. the loss scalars) and flag area
+ * (2 * 8 uint32, zeroed once) are mapped into every rank (b200rl_ipc_export / _import below).  The kernel
+ * exchanges "gradients final" flags, reads its chunk from ALL buckets over NVLink with system-scope loads, adds
+ * them in rank order (bit-identical on every rank), then norm -> clip -> Adam as K6; grads_out receives the
+ * reduced, clipped gradient (must not alias a bucket), extra_out the n_extra tail sums.  The kernel returns only
+ * after every peer has finished reading this rank's bucket.  `step` doubles as the flag generation: all ranks
+ * must pass the same, strictly increasing value.  A rank that never arrives turns total_norm into NaN after
+ * ~18 s instead of hanging.  peer_buckets / peer_flags are HOST arrays of `world` device pointers (<= 8). */
+int32_t b200rl_peer_allreduce_clip_adam_step(
+    float *params, const float *const *peer_buckets, uint32_t *const *peer_flags, int32_t world, int32_t rank,
+    float *grads_out, float *extra_out, int64_t n_extra, float *exp_avg, float *exp_avg_sq, int64_t n,
+    float max_norm, double lr, double beta1, double beta2, double eps, int64_t step,
+    float *total_norm, void *workspace, void *stream);
+
+/* CUDA IPC plumbing for K8.  export: 64-byte handle of the cudaMalloc block `ptr` lives in + its byte offset in
+ * that block.  import: map a peer's block (peer access enabled lazily) and return the peer's buffer address.
+ * close: unmap (pass the pointer and offset import returned / was given). */
+int32_t b200rl_ipc_export(const void *ptr, void *handle64, int64_t *offset);
+int32_t b200rl_ipc_import(const void *handle64, int64_t offset, void **out_ptr);
+int32_t b200rl_ipc_close(void *ptr, int64_t offset);
+
 #ifdef __cplusplus
 }
 #endif
