@@ -245,7 +245,8 @@ def make_replay(args, device, seed):
 
 def make_learner(args, device, seed):
     """BASELINE config 5: the whole learner step through the drop-in ImpalaLearner -- device replay (K4/K5),
-    IMPALA-CNN (630,352 params, cuDNN), K1, ONE NCCL allreduce of the flat gradient bucket (+ scalars), clip, Adam.
+    IMPALA-CNN (630,352 params, cuDNN), K1, then the gradient allreduce fused into clip + Adam over peer memory (K8;
+    B200RL_PEER_ALLREDUCE=0: ONE NCCL allreduce of the flat gradient bucket (+ scalars), then K6).
     B=256 rollouts of T=20 per GPU; buffer of 1000 rollouts (reference replay_buffer_size)."""
     from impala_b200 import models, optim, replay
     from impala_b200.agents.impala import ImpalaLearner
@@ -282,8 +283,17 @@ def make_learner(args, device, seed):
                      "allow_tf32=True (the reference's torch default too), %s" % ("channels_last" if cl else "NCHW"),
             "replay": "%d rollouts device-resident (%.0f MB u8), uniform sample + gather on device" % (cap, cap * T * 12288 / 1e6),
             "l2_policy": "gathered batch 63 MB + activations >> per-step reuse; buffer 246 MB > 126 MB L2"}
+    def grad_exchange():
+        from impala_b200 import parallel
+        if not dist.is_initialized() or dist.get_world_size() == 1:
+            return "none (one rank)"
+        if isinstance(learner._bucket, parallel.PeerGradBucket):
+            return "K8: allreduce fused into clip+Adam, peer buckets read over NVLink (CUDA IPC), no NCCL call on the step"
+        return "one NCCL allreduce of the flat gradient bucket (+ 8 scalars), then K6 clip+Adam"
+
     def breakdown():
         """Per-phase device time of the learner step (mean of 5 profiled steps after the timed region)."""
+        desc["grad_exchange"] = grad_exchange()
         learner.profile = True
         tot, names = {}, []
         for _ in range(5):
@@ -614,6 +624,8 @@ def main():
         del w2
     if w.get("breakdown"):
         line["config"]["breakdown_ms"] = w["breakdown"]()
+        if "grad_exchange" in w["desc"]:
+            line["config"]["grad_exchange"] = w["desc"]["grad_exchange"]
     if not args.no_e2e and w["e2e_step"] is not None:
         e_steps = min(steps, 2000)
         dt, h2d, d2h = time_e2e(w, e_steps, min(warmup, 20), device, world_size)
