@@ -37,14 +37,21 @@ struct AdamParams {
 // before them, "I have finished reading yours" after them (the kernel does not exit before every peer has
 // said so, so stream order protects the next backward pass that overwrites the bucket).  Flags carry the step
 // number: monotonic, never reset.
+// Two routes.  ONE-SHOT (2 ranks): every rank reads every bucket in full -- (W-1) n floats over NVLink per rank,
+// one flag round trip.  TWO-SHOT (more ranks): CTA c of rank r reduces only the r-th part of chunk c
+// (reduce-scatter: (W-1)/W n floats read per rank) and stores the sums into the `reduced` buffer of EVERY rank
+// (all-gather: (W-1)/W n floats written), then the W CTAs "c" of the ranks exchange per-CTA flags and each reads
+// its now complete local chunk.  A sum is formed once, by one rank, in rank order: bit-identical everywhere.
 constexpr int kMaxPeers = 8;
 constexpr long long kPeerSpinLimitCycles = 1ll << 35;  // ~18 s: ranks may be skewed by a whole learner step
 
 struct PeerParams {
     const float *g[kMaxPeers];      // every rank's bucket: n gradients followed by n_extra floats
     unsigned int *flags[kMaxPeers];  // every rank's flag area: ready[kMaxPeers], done[kMaxPeers]
+    float *red[kMaxPeers];           // two-shot: every rank's reduced-gradient buffer (red[rank] == AdamParams::g)
+    unsigned int *cflags[kMaxPeers]; // two-shot: every rank's per-CTA flag area [kMaxOptCtas][kMaxPeers]
     float *extra_out;                // [n_extra] sums of the buckets' tails (loss / metric scalars)
-    int world, rank, n_extra;
+    int world, rank, n_extra, two_shot;
     unsigned int gen;
 };
 
@@ -60,6 +67,9 @@ __device__ __forceinline__ float4 ld_sys_f4(const float4 *p) {
     float4 v;
     asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
     return v;
+}
+__device__ __forceinline__ void st_sys_f4(float4 *p, float4 v) {
+    asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 __device__ __forceinline__ float ld_sys_f32(const float *p) {
     float v;
@@ -78,6 +88,7 @@ __device__ __forceinline__ float4 load_grad4(const AdamParams &a, const PeerPara
     if constexpr (!PEER) {
         return reinterpret_cast<const float4 *>(a.g)[i];
     } else {
+    if (pp.two_shot) return __ldcg(reinterpret_cast<const float4 *>(a.g) + i);  // complete after the exchange phase
     float4 v[kMaxPeers];
 #pragma unroll
     for (int r = 0; r < kMaxPeers; ++r)
@@ -131,6 +142,33 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams
         if (threadIdx.x < pp.world && !peer_wait(pp.flags[pp.rank] + threadIdx.x, pp.gen)) s_peer_ok = 0;
         __syncthreads();
         if (blockIdx.x == 0 && threadIdx.x < pp.n_extra) pp.extra_out[threadIdx.x] = load_grad1<true>(a, pp, a.n + threadIdx.x);
+        if (pp.two_shot) {
+            // reduce-scatter + all-gather of this CTA's chunk: this rank sums part `rank`, writes it to every rank
+            const long long lo4 = lo / 4, cnt = hi / 4 - lo4;
+            const long long ps = (cnt + pp.world - 1) / pp.world;
+            const long long b = lo4 + pp.rank * ps, e = min(hi / 4, b + ps);
+            for (long long i = b + threadIdx.x; i < e; i += kOptThreads) {
+                float4 v[kMaxPeers];
+#pragma unroll
+                for (int r = 0; r < kMaxPeers; ++r)
+                    if (r < pp.world) v[r] = ld_sys_f4(reinterpret_cast<const float4 *>(pp.g[r]) + i);
+                float4 sum = v[0];
+#pragma unroll
+                for (int r = 1; r < kMaxPeers; ++r)
+                    if (r < pp.world) { sum.x += v[r].x; sum.y += v[r].y; sum.z += v[r].z; sum.w += v[r].w; }
+#pragma unroll
+                for (int r = 0; r < kMaxPeers; ++r)
+                    if (r < pp.world) st_sys_f4(reinterpret_cast<float4 *>(pp.red[r]) + i, sum);
+            }
+            __threadfence_system();
+            __syncthreads();
+            if (threadIdx.x < pp.world)
+                st_release_sys_u32(pp.cflags[threadIdx.x] + (long long)blockIdx.x * kMaxPeers + pp.rank, pp.gen);
+            if (threadIdx.x < pp.world &&
+                !peer_wait(pp.cflags[pp.rank] + (long long)blockIdx.x * kMaxPeers + threadIdx.x, pp.gen))
+                s_peer_ok = 0;
+            __syncthreads();
+        }
     }
     if (threadIdx.x == 0) {
         unsigned int t = *reinterpret_cast<volatile unsigned int *>(a.gen) + 1u;
@@ -160,7 +198,7 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams
         float4 *g4 = reinterpret_cast<float4 *>(a.g);
         for (long long i = lo / 4 + threadIdx.x; i < hi / 4; i += kOptThreads) {
             const float4 x = load_grad4<PEER>(a, pp, i);
-            if (PEER) g4[i] = x;  // the reduced gradient, re-read by phase 2
+            if (PEER && !pp.two_shot) g4[i] = x;  // the reduced gradient, re-read by phase 2
             ss[0] += (x.x * x.x + x.y * x.y) + (x.z * x.z + x.w * x.w);
         }
         for (long long i = (hi / 4) * 4 + threadIdx.x; i < hi; i += kOptThreads) {  // tail of n
@@ -342,9 +380,10 @@ extern "C" int32_t b200rl_clip_adam_step(float *params, float *grads, float *exp
 }
 
 extern "C" int32_t b200rl_peer_allreduce_clip_adam_step(
-    float *params, const float *const *peer_buckets, uint32_t *const *peer_flags, int32_t world, int32_t rank,
-    float *grads_out, float *extra_out, int64_t n_extra, float *exp_avg, float *exp_avg_sq, int64_t n, float max_norm,
-    double lr, double beta1, double beta2, double eps, int64_t step, float *total_norm, void *workspace, void *stream) {
+    float *params, const float *const *peer_buckets, uint32_t *const *peer_flags, float *const *peer_reduced,
+    uint32_t *const *peer_cta_flags, int32_t world, int32_t rank, float *grads_out, float *extra_out, int64_t n_extra,
+    float *exp_avg, float *exp_avg_sq, int64_t n, float max_norm, double lr, double beta1, double beta2, double eps,
+    int64_t step, float *total_norm, void *workspace, void *stream) {
     using namespace b200rl;
     B200RL_REQUIRE(peer_buckets && peer_flags && grads_out, -1, "peer_allreduce_clip_adam_step: null pointer argument");
     B200RL_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, -2,
@@ -358,6 +397,23 @@ extern "C" int32_t b200rl_peer_allreduce_clip_adam_step(
         B200RL_REQUIRE(peer_buckets[r] != grads_out, -2, "peer_allreduce_clip_adam_step: grads_out must not alias a bucket");
         pp.g[r] = peer_buckets[r];
         pp.flags[r] = peer_flags[r];
+    }
+    // route: B200RL_K8_TWO_SHOT=1/0 forces it, default two-shot for more than 2 ranks (needs the shared reduced buffers)
+    const int want = env_int("B200RL_K8_TWO_SHOT", -1);
+    pp.two_shot = (peer_reduced && peer_cta_flags && (want == 1 || (want < 0 && world > 2))) ? 1 : 0;
+    if (pp.two_shot) {
+        uintptr_t al = 0;
+        for (int r = 0; r < world; ++r) {
+            B200RL_REQUIRE(peer_reduced[r] && peer_cta_flags[r], -1, "peer_allreduce_clip_adam_step: rank %d pointer is null", r);
+            pp.red[r] = peer_reduced[r];
+            pp.cflags[r] = peer_cta_flags[r];
+            al |= reinterpret_cast<uintptr_t>(peer_reduced[r]) | reinterpret_cast<uintptr_t>(peer_buckets[r]);
+        }
+        B200RL_REQUIRE(peer_reduced[rank] == grads_out, -2,
+                       "peer_allreduce_clip_adam_step: grads_out must be this rank's shared reduced buffer");
+        if (al % 16 || ((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(exp_avg) |
+                         reinterpret_cast<uintptr_t>(exp_avg_sq)) % 16))
+            pp.two_shot = 0;  // unaligned buffers take the scalar one-shot route
     }
     pp.extra_out = extra_out;
     pp.world = world; pp.rank = rank; pp.n_extra = (int)n_extra;

@@ -61,7 +61,8 @@ class FusedClipAdam(torch.optim.Optimizer):
         mgn = self.max_grad_norm if max_grad_norm is None else float(max_grad_norm)
         return ops.peer_allreduce_clip_adam_step(self.flat, bucket.bucket_ptrs, bucket.flag_ptrs, bucket.rank, bucket.reduced,
                                                  bucket.extra_reduced, self.exp_avg, self.exp_avg_sq, self.step_count,
-                                                 g["lr"], g["betas"][0], g["betas"][1], g["eps"], mgn, self.total_norm)
+                                                 g["lr"], g["betas"][0], g["betas"][1], g["eps"], mgn, self.total_norm,
+                                                 bucket.reduced_ptrs, bucket.cta_flag_ptrs)
 
     @torch.no_grad()
     def step(self, closure=None):

@@ -74,16 +74,19 @@ class GradBucket:
 class PeerGradBucket(GradBucket):
     """A ``GradBucket`` whose buffer is mapped into every rank's address space (CUDA IPC, NVLink / NVSwitch peer
     access), for the fused allreduce + clip + Adam kernel (K8, ``ops.peer_allreduce_clip_adam_step``): no NCCL call on
-    the step.  Buffer layout: ``n`` gradients, ``n_extra`` scalars, padding to 16 bytes, 16 flag words."""
+    the step.  Buffer layout: ``n`` gradients, ``n_extra`` scalars, padding to 16 bytes, 16 flag words, 8,192 per-CTA
+    flag words and the ``n``-float reduced-gradient buffer the ranks write into each other (two-shot route)."""
 
     FLAG_WORDS = 16
+    CTA_FLAG_WORDS = 1024 * 8          # two-shot route: per-CTA flags, [kMaxOptCtas][8]
 
     def __init__(self, params: Iterable[torch.nn.Parameter], n_extra: int = 8, group=None):
         from . import ops
         plist = [p for p in params if p.requires_grad]
         n = sum(p.numel() for p in plist)
         pad = (-(n + n_extra)) % 4
-        super().__init__(plist, n_extra, reserve=pad + self.FLAG_WORDS)
+        n_pad = n + ((-n) % 4)
+        super().__init__(plist, n_extra, reserve=pad + self.FLAG_WORDS + self.CTA_FLAG_WORDS + n_pad)
         if not self.store.is_cuda:
             raise RuntimeError("PeerGradBucket needs CUDA parameters (peer memory is a GPU feature)")
         self.group = group
@@ -107,7 +110,11 @@ class PeerGradBucket(GradBucket):
                 self._imports.append((ptr, offset))
                 self.bucket_ptrs.append(ptr)
         self.flag_ptrs = [p + self.flag_offset_bytes for p in self.bucket_ptrs]
-        self.reduced = torch.zeros(self.n, dtype=torch.float32, device=self.store.device)   # reduced, clipped gradient
+        cta_flag_off = self.flag_offset_bytes + self.FLAG_WORDS * 4
+        reduced_off = cta_flag_off + self.CTA_FLAG_WORDS * 4
+        self.cta_flag_ptrs = [p + cta_flag_off for p in self.bucket_ptrs]
+        self.reduced_ptrs = [p + reduced_off for p in self.bucket_ptrs]
+        self.reduced = self.store[reduced_off // 4: reduced_off // 4 + self.n]   # reduced, clipped gradient (peer-written in two-shot)
         self.extra_reduced = torch.zeros(n_extra, dtype=torch.float32, device=self.store.device)
         if self.world_size > 1:
             dist.barrier(group=group)   # every rank has mapped every bucket before the first kernel touches one

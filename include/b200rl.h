@@ -248,9 +248,15 @@ int32_t b200rl_clip_adam_step(
  * reduced, clipped gradient (must not alias a bucket), extra_out the n_extra tail sums.  The kernel returns only
  * after every peer has finished reading this rank's bucket.  `step` doubles as the flag generation: all ranks
  * must pass the same, strictly increasing value.  A rank that never arrives turns total_norm into NaN after
- * ~18 s instead of hanging.  peer_buckets / peer_flags are HOST arrays of `world` device pointers (<= 8). */
+ * ~18 s instead of hanging.  peer_buckets / peer_flags are HOST arrays of `world` device pointers (<= 8).
+ * Routes: one-shot (every rank reads every bucket in full; default for 2 ranks) and two-shot (reduce-scatter +
+ * all-gather through every rank's peer-mapped reduced buffer; default for more ranks).  Two-shot needs
+ * peer_reduced (every rank's reduced-gradient buffer of n floats, peer_reduced[rank] == grads_out) and
+ * peer_cta_flags (every rank's per-CTA flag area, 1024 * 8 uint32, zeroed once); pass NULL for both to force
+ * one-shot (grads_out is then any local buffer). */
 int32_t b200rl_peer_allreduce_clip_adam_step(
-    float *params, const float *const *peer_buckets, uint32_t *const *peer_flags, int32_t world, int32_t rank,
+    float *params, const float *const *peer_buckets, uint32_t *const *peer_flags, float *const *peer_reduced,
+    uint32_t *const *peer_cta_flags, int32_t world, int32_t rank,
     float *grads_out, float *extra_out, int64_t n_extra, float *exp_avg, float *exp_avg_sq, int64_t n,
     float max_norm, double lr, double beta1, double beta2, double eps, int64_t step,
     float *total_norm, void *workspace, void *stream);

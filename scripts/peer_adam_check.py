@@ -20,7 +20,9 @@ def main():
     dev = torch.device("cuda", torch.cuda.current_device())
     dist.init_process_group("nccl", device_id=dev)
     results = {}
-    for n in (630_352, 1001, 3_000_000):                     # the reference model, a ragged tiny one, a streaming-path one
+    for route, n in [(r, n) for r in ("one_shot", "two_shot") for n in (630_352, 1001, 3_000_000)]:
+        # the reference model, a ragged tiny one, a streaming-path one; both exchange routes
+        os.environ["B200RL_K8_TWO_SHOT"] = "1" if route == "two_shot" else "0"
         torch.manual_seed(0)
         pa = [torch.nn.Parameter(torch.randn(n - 7, device=dev)), torch.nn.Parameter(torch.randn(7, device=dev))]
         pb = [torch.nn.Parameter(p.detach().clone()) for p in pa]
@@ -71,7 +73,7 @@ def main():
             dist.all_reduce(ref.flat)
             opt_b.step_flat(ref.grads, 0.5)
 
-        results[n] = {"k8_us": round(timed(lambda: opt_a.step_peer(bucket, 0.5)), 2), "nccl_plus_k6_us": round(timed(nccl_route), 2)}
+        results["%s n=%d" % (route, n)] = {"k8_us": round(timed(lambda: opt_a.step_peer(bucket, 0.5)), 2), "nccl_plus_k6_us": round(timed(nccl_route), 2)}
         dist.barrier()
         bucket.close()
     if rank == 0:

@@ -14,8 +14,10 @@ pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
+@pytest.mark.parametrize("route", ["0", "1"])      # one-shot / two-shot exchange (B200RL_K8_TWO_SHOT)
 @pytest.mark.parametrize("n", [1001, 630_352, 3_000_000])
-def test_peer_path_world1_equals_k6(n):
+def test_peer_path_world1_equals_k6(n, route, monkeypatch):
+    monkeypatch.setenv("B200RL_K8_TWO_SHOT", route)
     dev = torch.device("cuda", 0)
     torch.manual_seed(1)
     pa = [torch.nn.Parameter(torch.randn(n - 5, device=dev)), torch.nn.Parameter(torch.randn(5, device=dev))]
