@@ -555,7 +555,8 @@ def run_reference(args, rank, world_size):
     line = {
         "impl": "reference", "metric": metric, "value": r["value"], "unit": unit, "n_gpus": args.gpus,
         "steps": r["steps"], "warmup": min(warmup, 5), "ms_per_step": 1e3 * r["seconds"] / r["steps"],
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u8" if args.workload == "replay" else "f32", "data": "synthetic",
         "config": {"workload": WORKLOAD_NAMES[args.workload], "T": args.T or DEFAULT_T[args.workload], "A": args.A,
                    "B_per_gpu": args.B or DEFAULT_B[args.workload], "sample": r["sample"],
                    "note": "reference CPU path = oracle port of the reference's torch code (the reference itself is "
@@ -605,7 +606,7 @@ def main():
         "roofline": None if bytes_per_unit is None else {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                      "traffic": recorded_traffic(args.workload), "peak_source": peak_src,
                      "algorithmic_bytes_per_step": bytes_per_unit * w["units"],
-                     "note": "per GPU; duration = timed region / steps (launch gaps included)"},
+                     "note": "per GPU; duration = timed region / steps (launch gaps included); the measured peak is a copy (half reads, half writes) -- a read-heavy kernel can exceed it"},
         "clocks": clocks,
         "gpu_launches": steps * w["kernels"],
     }

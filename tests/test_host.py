@@ -90,3 +90,18 @@ def test_sharded_sum_equals_global_gloo():
     assert flat[A].item() == pytest.approx(dv.sum().item(), abs=1e-6)
     assert flat[A + 1].item() == pytest.approx(m["pg"].item(), abs=1e-6)
     assert flat[A + 2].item() == pytest.approx(m["entropy"].item(), abs=1e-6)
+
+
+def test_make_bucket_routes_on_cpu(monkeypatch):
+    """``parallel.make_bucket``: CPU parameters / one rank / B200RL_PEER_ALLREDUCE=0 give the plain bucket; the
+    peer-mapped bucket (K8) is a CUDA feature and says so."""
+    from impala_b200 import parallel
+    ps = [torch.nn.Parameter(torch.randn(5)), torch.nn.Parameter(torch.randn(3, 2))]
+    b = parallel.make_bucket(ps, None, fused_optimizer=True)
+    assert type(b) is parallel.GradBucket and b.flat.numel() == 11 + 8 and b.store.numel() == b.flat.numel()
+    b.attach()
+    assert all(p.grad.data_ptr() == v.data_ptr() for p, v in zip(b.params, b.views))
+    monkeypatch.setenv("B200RL_PEER_ALLREDUCE", "0")
+    assert type(parallel.make_bucket(ps, None, fused_optimizer=True)) is parallel.GradBucket
+    with pytest.raises(RuntimeError):
+        parallel.PeerGradBucket(ps)
