@@ -42,6 +42,8 @@ struct AdamParams {
 // (reduce-scatter: (W-1)/W n floats read per rank) and stores the sums into the `reduced` buffer of EVERY rank
 // (all-gather: (W-1)/W n floats written), then the W CTAs "c" of the ranks exchange per-CTA flags and each reads
 // its now complete local chunk.  A sum is formed once, by one rank, in rank order: bit-identical everywhere.
+// NVLS (two-shot with multicast addresses of the same buffers): the part is fetched with ONE multimem.ld_reduce --
+// the NVSwitch adds the W ranks' values -- and broadcast with ONE multimem.st: n/W floats each way per rank.
 constexpr int kMaxPeers = 8;
 constexpr long long kPeerSpinLimitCycles = 1ll << 35;  // ~18 s: ranks may be skewed by a whole learner step
 
@@ -50,6 +52,8 @@ struct PeerParams {
     unsigned int *flags[kMaxPeers];  // every rank's flag area: ready[kMaxPeers], done[kMaxPeers]
     float *red[kMaxPeers];           // two-shot: every rank's reduced-gradient buffer (red[rank] == AdamParams::g)
     unsigned int *cflags[kMaxPeers]; // two-shot: every rank's per-CTA flag area [kMaxOptCtas][kMaxPeers]
+    const float *mc_g;               // NVLS: multicast address of the buckets (nullptr: unicast loads / stores)
+    float *mc_red;                   // NVLS: multicast address of the reduced buffers
     float *extra_out;                // [n_extra] sums of the buckets' tails (loss / metric scalars)
     int world, rank, n_extra, two_shot;
     unsigned int gen;
@@ -70,6 +74,15 @@ __device__ __forceinline__ float4 ld_sys_f4(const float4 *p) {
 }
 __device__ __forceinline__ void st_sys_f4(float4 *p, float4 v) {
     asm volatile("st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float4 *mc) {  // sum over the multicast group, formed in the switch
+    float4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_st_f4(float4 *mc, float4 v) {  // one store, delivered to every rank
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
 }
 __device__ __forceinline__ float ld_sys_f32(const float *p) {
     float v;
@@ -147,6 +160,11 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams
             const long long lo4 = lo / 4, cnt = hi / 4 - lo4;
             const long long ps = (cnt + pp.world - 1) / pp.world;
             const long long b = lo4 + pp.rank * ps, e = min(hi / 4, b + ps);
+            if (pp.mc_g) {
+                for (long long i = b + threadIdx.x; i < e; i += kOptThreads)
+                    multimem_st_f4(reinterpret_cast<float4 *>(pp.mc_red) + i,
+                                   multimem_ld_reduce_f4(reinterpret_cast<const float4 *>(pp.mc_g) + i));
+            } else
             for (long long i = b + threadIdx.x; i < e; i += kOptThreads) {
                 float4 v[kMaxPeers];
 #pragma unroll
@@ -381,9 +399,9 @@ extern "C" int32_t b200rl_clip_adam_step(float *params, float *grads, float *exp
 
 extern "C" int32_t b200rl_peer_allreduce_clip_adam_step(
     float *params, const float *const *peer_buckets, uint32_t *const *peer_flags, float *const *peer_reduced,
-    uint32_t *const *peer_cta_flags, int32_t world, int32_t rank, float *grads_out, float *extra_out, int64_t n_extra,
-    float *exp_avg, float *exp_avg_sq, int64_t n, float max_norm, double lr, double beta1, double beta2, double eps,
-    int64_t step, float *total_norm, void *workspace, void *stream) {
+    uint32_t *const *peer_cta_flags, const float *mc_buckets, float *mc_reduced, int32_t world, int32_t rank,
+    float *grads_out, float *extra_out, int64_t n_extra, float *exp_avg, float *exp_avg_sq, int64_t n, float max_norm,
+    double lr, double beta1, double beta2, double eps, int64_t step, float *total_norm, void *workspace, void *stream) {
     using namespace b200rl;
     B200RL_REQUIRE(peer_buckets && peer_flags && grads_out, -1, "peer_allreduce_clip_adam_step: null pointer argument");
     B200RL_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, -2,
@@ -414,6 +432,11 @@ extern "C" int32_t b200rl_peer_allreduce_clip_adam_step(
         if (al % 16 || ((reinterpret_cast<uintptr_t>(params) | reinterpret_cast<uintptr_t>(exp_avg) |
                          reinterpret_cast<uintptr_t>(exp_avg_sq)) % 16))
             pp.two_shot = 0;  // unaligned buffers take the scalar one-shot route
+    }
+    if (pp.two_shot && mc_buckets && mc_reduced && env_int("B200RL_K8_NVLS", 1) &&
+        ((reinterpret_cast<uintptr_t>(mc_buckets) | reinterpret_cast<uintptr_t>(mc_reduced)) % 16) == 0) {
+        pp.mc_g = mc_buckets;
+        pp.mc_red = mc_reduced;
     }
     pp.extra_out = extra_out;
     pp.world = world; pp.rank = rank; pp.n_extra = (int)n_extra;

@@ -279,7 +279,8 @@ def clip_adam_step(params, grads, exp_avg, exp_avg_sq, step, lr, beta1=0.9, beta
 
 def peer_allreduce_clip_adam_step(params, peer_bucket_ptrs, peer_flag_ptrs, rank, grads_out, extra_out, exp_avg,
                                   exp_avg_sq, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, max_norm=0.0,
-                                  total_norm=None, peer_reduced_ptrs=None, peer_cta_flag_ptrs=None):
+                                  total_norm=None, peer_reduced_ptrs=None, peer_cta_flag_ptrs=None, mc_bucket_ptr=0,
+                                  mc_reduced_ptr=0):
     """K8.  ``peer_bucket_ptrs`` / ``peer_flag_ptrs``: device addresses (ints) of every rank's bucket and flag area as
     mapped into THIS process (``parallel.PeerGradBucket``).  Returns the 1-element pre-clip norm of the reduced gradient."""
     _require_cuda(params, grads_out, exp_avg, exp_avg_sq)
@@ -299,7 +300,8 @@ def peer_allreduce_clip_adam_step(params, peer_bucket_ptrs, peer_flag_ptrs, rank
     cfl = (ctypes.c_void_p * world)(*peer_cta_flag_ptrs) if two else None
     ws = workspace(params.device)
     _cabi.call("b200rl_peer_allreduce_clip_adam_step", params.data_ptr(), ctypes.addressof(buckets), ctypes.addressof(flags),
-               ctypes.addressof(red) if two else 0, ctypes.addressof(cfl) if two else 0, world, rank, grads_out.data_ptr(), 0 if extra_out is None else extra_out.data_ptr(), n_extra,
+               ctypes.addressof(red) if two else 0, ctypes.addressof(cfl) if two else 0, mc_bucket_ptr or 0,
+               mc_reduced_ptr or 0, world, rank, grads_out.data_ptr(), 0 if extra_out is None else extra_out.data_ptr(), n_extra,
                exp_avg.data_ptr(), exp_avg_sq.data_ptr(), n, max_norm, lr, beta1, beta2, eps, step,
                total_norm.data_ptr(), ws.data_ptr(), _stream())
     return total_norm

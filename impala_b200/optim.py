@@ -62,7 +62,8 @@ class FusedClipAdam(torch.optim.Optimizer):
         return ops.peer_allreduce_clip_adam_step(self.flat, bucket.bucket_ptrs, bucket.flag_ptrs, bucket.rank, bucket.reduced,
                                                  bucket.extra_reduced, self.exp_avg, self.exp_avg_sq, self.step_count,
                                                  g["lr"], g["betas"][0], g["betas"][1], g["eps"], mgn, self.total_norm,
-                                                 bucket.reduced_ptrs, bucket.cta_flag_ptrs)
+                                                 bucket.reduced_ptrs, bucket.cta_flag_ptrs, bucket.mc_bucket_ptr,
+                                                 bucket.mc_reduced_ptr)
 
     @torch.no_grad()
     def step(self, closure=None):

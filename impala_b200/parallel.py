@@ -31,11 +31,12 @@ class GradBucket:
     """All parameter gradients as views into one flat fp32 buffer + ``n_extra`` tail floats, so a step
     needs exactly one allreduce (630,352 params = 2.52 MB for the IMPALA-CNN: latency-bound, one bucket)."""
 
-    def __init__(self, params: Iterable[torch.nn.Parameter], n_extra: int = 8, reserve: int = 0):
+    def __init__(self, params: Iterable[torch.nn.Parameter], n_extra: int = 8, reserve: int = 0, store=None):
         self.params = [p for p in params if p.requires_grad]
         n = sum(p.numel() for p in self.params)
         dev = self.params[0].device
-        self.store = torch.zeros(n + n_extra + reserve, dtype=torch.float32, device=dev)  # reserve: see PeerGradBucket
+        # reserve / store: see PeerGradBucket (extra floats behind the bucket; a pre-allocated symmetric buffer)
+        self.store = torch.zeros(n + n_extra + reserve, dtype=torch.float32, device=dev) if store is None else store
         self.flat = self.store[:n + n_extra]
         self.n, self.n_extra = n, n_extra
         self.views, off = [], 0
@@ -72,9 +73,11 @@ class GradBucket:
 
 
 class PeerGradBucket(GradBucket):
-    """A ``GradBucket`` whose buffer is mapped into every rank's address space (CUDA IPC, NVLink / NVSwitch peer
-    access), for the fused allreduce + clip + Adam kernel (K8, ``ops.peer_allreduce_clip_adam_step``): no NCCL call on
-    the step.  Buffer layout: ``n`` gradients, ``n_extra`` scalars, padding to 16 bytes, 16 flag words, 8,192 per-CTA
+    """A ``GradBucket`` whose buffer is mapped into every rank's address space (NVLink / NVSwitch peer access), for the
+    fused allreduce + clip + Adam kernel (K8, ``ops.peer_allreduce_clip_adam_step``): no NCCL call on the step.
+    Transport (``B200RL_PEER_TRANSPORT`` = ``auto`` | ``symm`` | ``ipc``): torch symmetric memory when available -- it
+    also yields the NVLS multicast address the kernel's ``multimem`` route needs -- else CUDA IPC handles exchanged
+    through ``all_gather_object`` (unicast peer loads / stores only).  Buffer layout: ``n`` gradients, ``n_extra`` scalars, padding to 16 bytes, 16 flag words, 8,192 per-CTA
     flag words and the ``n``-float reduced-gradient buffer the ranks write into each other (two-shot route)."""
 
     FLAG_WORDS = 16
@@ -86,34 +89,56 @@ class PeerGradBucket(GradBucket):
         n = sum(p.numel() for p in plist)
         pad = (-(n + n_extra)) % 4
         n_pad = n + ((-n) % 4)
-        super().__init__(plist, n_extra, reserve=pad + self.FLAG_WORDS + self.CTA_FLAG_WORDS + n_pad)
-        if not self.store.is_cuda:
+        reserve = pad + self.FLAG_WORDS + self.CTA_FLAG_WORDS + n_pad
+        if not plist[0].is_cuda:
             raise RuntimeError("PeerGradBucket needs CUDA parameters (peer memory is a GPU feature)")
         self.group = group
         self.rank, self.world_size = world(group)
         if self.world_size > 8:
             raise RuntimeError("PeerGradBucket: at most 8 ranks (one NVSwitch box)")
+        transport = os.environ.get("B200RL_PEER_TRANSPORT", "auto")
+        store, self._symm, self.mc_ptr = None, None, 0
+        if self.world_size > 1 and transport != "ipc":
+            try:
+                import torch.distributed._symmetric_memory as symm_mem
+                store = symm_mem.empty(n + n_extra + reserve, dtype=torch.float32, device=plist[0].device)
+                store.zero_()
+                self._symm = symm_mem.rendezvous(store, group if group is not None else dist.group.WORLD)
+                self.mc_ptr = int(self._symm.multicast_ptr or 0)
+            except Exception as e:   # noqa: BLE001 -- any failure here is symmetric across ranks (same build, same box)
+                if transport == "symm":
+                    raise RuntimeError("symmetric-memory transport unavailable: %s" % e)
+                store, self._symm, self.mc_ptr = None, None, 0
+        super().__init__(plist, n_extra, reserve=reserve, store=store)
+        self.transport = "symm" if self._symm is not None else "ipc"
         self.flag_offset_bytes = (n + n_extra + pad) * 4
-        mine = ops.ipc_export(self.store)
-        gathered = [None] * self.world_size
-        if self.world_size > 1:
-            dist.all_gather_object(gathered, mine, group=group)
-        else:
-            gathered[0] = mine
         self._imports = []
-        self.bucket_ptrs = []
-        for r, (handle, offset) in enumerate(gathered):
-            if r == self.rank:
-                self.bucket_ptrs.append(self.store.data_ptr())
+        if self._symm is not None:
+            self.bucket_ptrs = [int(p) for p in self._symm.buffer_ptrs]
+            if self.bucket_ptrs[self.rank] != self.store.data_ptr():
+                raise RuntimeError("symmetric memory: local buffer pointer mismatch")
+        else:
+            mine = ops.ipc_export(self.store)
+            gathered = [None] * self.world_size
+            if self.world_size > 1:
+                dist.all_gather_object(gathered, mine, group=group)
             else:
-                ptr = ops.ipc_import(handle, offset)
-                self._imports.append((ptr, offset))
-                self.bucket_ptrs.append(ptr)
+                gathered[0] = mine
+            self.bucket_ptrs = []
+            for r, (handle, offset) in enumerate(gathered):
+                if r == self.rank:
+                    self.bucket_ptrs.append(self.store.data_ptr())
+                else:
+                    ptr = ops.ipc_import(handle, offset)
+                    self._imports.append((ptr, offset))
+                    self.bucket_ptrs.append(ptr)
         self.flag_ptrs = [p + self.flag_offset_bytes for p in self.bucket_ptrs]
         cta_flag_off = self.flag_offset_bytes + self.FLAG_WORDS * 4
         reduced_off = cta_flag_off + self.CTA_FLAG_WORDS * 4
         self.cta_flag_ptrs = [p + cta_flag_off for p in self.bucket_ptrs]
         self.reduced_ptrs = [p + reduced_off for p in self.bucket_ptrs]
+        self.mc_bucket_ptr = self.mc_ptr                                    # NVLS multicast views of the same offsets
+        self.mc_reduced_ptr = self.mc_ptr + reduced_off if self.mc_ptr else 0
         self.reduced = self.store[reduced_off // 4: reduced_off // 4 + self.n]   # reduced, clipped gradient (peer-written in two-shot)
         self.extra_reduced = torch.zeros(n_extra, dtype=torch.float32, device=self.store.device)
         if self.world_size > 1:

@@ -253,10 +253,14 @@ int32_t b200rl_clip_adam_step(
  * all-gather through every rank's peer-mapped reduced buffer; default for more ranks).  Two-shot needs
  * peer_reduced (every rank's reduced-gradient buffer of n floats, peer_reduced[rank] == grads_out) and
  * peer_cta_flags (every rank's per-CTA flag area, 1024 * 8 uint32, zeroed once); pass NULL for both to force
- * one-shot (grads_out is then any local buffer). */
+ * one-shot (grads_out is then any local buffer).  NVLS: when the buffers come from a multicast-capable symmetric
+ * allocation, mc_buckets / mc_reduced are the MULTICAST addresses of the buckets / reduced buffers; the two-shot
+ * route then fetches each part with one multimem.ld_reduce (the NVSwitch adds) and broadcasts it with one
+ * multimem.st.  The switch's summation order is its own: results are identical on all ranks but equal the
+ * rank-ordered sum only to rounding.  Pass NULL for unicast loads / stores. */
 int32_t b200rl_peer_allreduce_clip_adam_step(
     float *params, const float *const *peer_buckets, uint32_t *const *peer_flags, float *const *peer_reduced,
-    uint32_t *const *peer_cta_flags, int32_t world, int32_t rank,
+    uint32_t *const *peer_cta_flags, const float *mc_buckets, float *mc_reduced, int32_t world, int32_t rank,
     float *grads_out, float *extra_out, int64_t n_extra, float *exp_avg, float *exp_avg_sq, int64_t n,
     float max_norm, double lr, double beta1, double beta2, double eps, int64_t step,
     float *total_norm, void *workspace, void *stream);

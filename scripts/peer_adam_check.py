@@ -20,15 +20,20 @@ def main():
     dev = torch.device("cuda", torch.cuda.current_device())
     dist.init_process_group("nccl", device_id=dev)
     results = {}
-    for route, n in [(r, n) for r in ("one_shot", "two_shot") for n in (630_352, 1001, 3_000_000)]:
-        # the reference model, a ragged tiny one, a streaming-path one; both exchange routes
-        os.environ["B200RL_K8_TWO_SHOT"] = "1" if route == "two_shot" else "0"
+    for route, n in [(r, n) for r in ("one_shot", "two_shot", "nvls") for n in (630_352, 1001, 3_000_000)]:
+        # the reference model, a ragged tiny one, a streaming-path one; every exchange route
+        os.environ["B200RL_K8_TWO_SHOT"] = "0" if route == "one_shot" else "1"
+        os.environ["B200RL_K8_NVLS"] = "1" if route == "nvls" else "0"
+        os.environ["B200RL_PEER_TRANSPORT"] = "auto" if route == "nvls" else "ipc"
         torch.manual_seed(0)
         pa = [torch.nn.Parameter(torch.randn(n - 7, device=dev)), torch.nn.Parameter(torch.randn(7, device=dev))]
         pb = [torch.nn.Parameter(p.detach().clone()) for p in pa]
         opt_a = optim.FusedClipAdam(pa, lr=1e-2, eps=1e-5)
         opt_b = optim.FusedClipAdam(pb, lr=1e-2, eps=1e-5)
         bucket = parallel.PeerGradBucket(pa, n_extra=8)
+        nvls = route == "nvls" and bucket.mc_ptr != 0          # the switch's summation order is its own: compare to rounding
+        if route == "nvls" and not nvls and rank == 0:
+            print("no multicast address (transport %s): the nvls rows below are the unicast two-shot route" % bucket.transport)
         ref = parallel.GradBucket(pb, n_extra=8)
         g = torch.Generator(device=dev).manual_seed(100 + rank)
         for step in range(4):
@@ -45,10 +50,16 @@ def main():
             norm_b = opt_b.step_flat(ref.grads, 0.5).clone()
             norm_a = opt_a.step_peer(bucket, 0.5).clone()
             torch.cuda.synchronize()
-            assert torch.equal(norm_a, norm_b), (n, step, norm_a, norm_b)
-            assert torch.equal(opt_a.flat, opt_b.flat), (n, step, "params")
-            assert torch.equal(opt_a.exp_avg, opt_b.exp_avg) and torch.equal(opt_a.exp_avg_sq, opt_b.exp_avg_sq)
-            assert torch.equal(bucket.reduced, ref.grads), (n, step, "reduced clipped gradient")
+            if nvls:
+                torch.testing.assert_close(norm_a, norm_b, rtol=1e-5, atol=1e-6)
+                torch.testing.assert_close(bucket.reduced, ref.grads, rtol=1e-5, atol=1e-6)
+                torch.testing.assert_close(opt_a.flat, opt_b.flat, rtol=1e-5, atol=1e-5)
+                opt_b.flat.copy_(opt_a.flat); opt_b.exp_avg.copy_(opt_a.exp_avg); opt_b.exp_avg_sq.copy_(opt_a.exp_avg_sq)
+            else:
+                assert torch.equal(norm_a, norm_b), (n, step, norm_a, norm_b)
+                assert torch.equal(opt_a.flat, opt_b.flat), (n, step, "params")
+                assert torch.equal(opt_a.exp_avg, opt_b.exp_avg) and torch.equal(opt_a.exp_avg_sq, opt_b.exp_avg_sq)
+                assert torch.equal(bucket.reduced, ref.grads), (n, step, "reduced clipped gradient")
             assert torch.equal(bucket.extra_reduced, want[n:]), (n, step, "scalar tail")
             everyone = [torch.empty_like(opt_a.flat) for _ in range(world)]
             dist.all_gather(everyone, opt_a.flat)
