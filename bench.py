@@ -288,7 +288,9 @@ def make_learner(args, device, seed):
         if not dist.is_initialized() or dist.get_world_size() == 1:
             return "none (one rank)"
         if isinstance(learner._bucket, parallel.PeerGradBucket):
-            return "K8: allreduce fused into clip+Adam, peer buckets read over NVLink (CUDA IPC), no NCCL call on the step"
+            b = learner._bucket
+            return "K8: allreduce fused into clip+Adam over NVLink peer memory (transport: %s%s), no NCCL call on the step" % (
+                b.transport, ", NVLS multicast address available" if b.mc_ptr else "")
         return "one NCCL allreduce of the flat gradient bucket (+ 8 scalars), then K6 clip+Adam"
 
     def breakdown():
