@@ -1,10 +1,13 @@
 // Stand-alone V-trace (drop-in for batched_vtrace, reference agents/impala/learning.py:15-26,
 // 150-153; algorithm: rlax vtrace_td_error_and_advantage) and its backward.
 //
-// Forward: one thread per column walks the T-1 steps backwards in registers.  Time-major
-// inputs are coalesced across the warp; batch-major inputs are read a 128-byte line per
-// thread which then serves the next 32 steps out of L1.  (The learner's hot path does not
-// come through here -- K1 fuses this recursion into the loss kernel.)
+// Forward (Tm <= 256): K1's tiling without the softmax -- a CTA owns C columns x all Tm steps, one thread per
+// (column, step) in MEMORY order so every load and store is coalesced for either layout; the (td, discount*c)
+// pairs meet in shared memory, the column's first thread runs the recursion as a register chain, and every
+// thread then finishes its own step.  The first version (one thread per column walking global memory, 32 CTAs
+// for B = 4096) took 48 us for the 2.5 MB of BASELINE config 2; this one is launch-bound.  Longer sequences keep
+// the one-thread-per-column kernel.  (The learner's hot path does not come through here -- K1 fuses this
+// recursion into the loss kernel.)
 #include "common.cuh"
 
 namespace b200rl {
@@ -35,6 +38,55 @@ __global__ void __launch_bounds__(128) vtrace_fwd_kernel(
         tgt_next = er + vm;
         v_tm1_next = vm;
     }
+}
+
+constexpr int kVtThreads = 256;
+
+template <bool TM>
+__global__ void __launch_bounds__(kVtThreads) vtrace_fwd_tiled_kernel(
+    const float *__restrict__ v_tm1, const float *__restrict__ v_t, const float *__restrict__ r_t,
+    const float *__restrict__ disc, const float *__restrict__ rho, int B, int Tm, int C, long long sb,
+    long long st, float lambda_, float oml, float clip_rho, float clip_pg_rho, float *__restrict__ adv,
+    float *__restrict__ err, float *__restrict__ q) {
+    __shared__ float2 s_tg[kVtThreads];
+    __shared__ float s_e[kVtThreads], s_vm[kVtThreads];
+    const int s = threadIdx.x, b0 = blockIdx.x * C, cols = min(C, B - b0);
+    int c, t;
+    if (TM) { t = s / C; c = s - t * C; } else { c = s / Tm; t = s - c * Tm; }
+    const bool valid = s < C * Tm && c < cols;
+    const int stl = TM ? C : 1;  // local distance between steps t and t+1
+    float rh = 0.f, vm = 0.f, vt = 0.f, r = 0.f, d = 0.f;
+    if (valid) {
+        const long long i = (long long)(b0 + c) * sb + (long long)t * st;
+        rh = rho[i]; vm = v_tm1[i]; vt = v_t[i]; r = r_t[i]; d = disc[i];
+        const float cc = fminf(rh, 1.0f) * lambda_;
+        s_tg[s] = make_float2(fminf(rh, clip_rho) * (r + d * vt - vm), d * cc);
+        s_vm[s] = vm;
+    }
+    __syncthreads();
+    if (s < cols) {
+        int k = (TM ? s : s * Tm) + (Tm - 1) * stl;
+        float e = 0.f;
+        for (int j = Tm - 1; j >= 0; --j, k -= stl) {
+            const float2 x = s_tg[k];
+            e = x.x + x.y * e;
+            s_e[k] = e;
+        }
+    }
+    __syncthreads();
+    if (!valid) return;
+    const float er = (s_e[s] + vm) - vm;
+    float qb = vt;
+    if (t < Tm - 1) {
+        const float vm1 = s_vm[s + stl];
+        const float tgt1 = ((s_e[s + stl] + vm1) - vm1) + vm1;
+        qb = lambda_ * tgt1 + oml * vm1;
+    }
+    const float qq = r + d * qb;
+    const long long o = TM ? (long long)t * B + b0 + c : (long long)(b0 + c) * Tm + t;  // outputs are compact
+    err[o] = er;
+    q[o] = qq;
+    adv[o] = fminf(rh, clip_pg_rho) * (qq - vm);
 }
 
 // Elementwise backward (stop_target_gradients=True: vs targets are constants).
@@ -85,6 +137,21 @@ extern "C" int32_t b200rl_vtrace(const float *v_tm1, const float *v_t, const flo
     using namespace b200rl;
     B200RL_REQUIRE(v_tm1 && v_t && r_t && discount_t && rho_tm1 && adv && err && q, -1, "vtrace: null pointer argument");
     if (int32_t rc = check_layout("vtrace", B, Tm, stride_b, stride_t)) return rc;
+    if (Tm <= kVtThreads) {
+        const bool tm = !(stride_t == 1 && stride_b >= Tm);
+        int C = kVtThreads / (int)Tm;
+        if (C > B) C = (int)B;
+        const unsigned grid = (unsigned)((B + C - 1) / C);
+        if (tm)
+            vtrace_fwd_tiled_kernel<true><<<grid, kVtThreads, 0, (cudaStream_t)stream>>>(
+                v_tm1, v_t, r_t, discount_t, rho_tm1, (int)B, (int)Tm, C, stride_b, stride_t, (float)lambda_,
+                (float)(1.0 - lambda_), clip_rho, clip_pg_rho, adv, err, q);
+        else
+            vtrace_fwd_tiled_kernel<false><<<grid, kVtThreads, 0, (cudaStream_t)stream>>>(
+                v_tm1, v_t, r_t, discount_t, rho_tm1, (int)B, (int)Tm, C, stride_b, stride_t, (float)lambda_,
+                (float)(1.0 - lambda_), clip_rho, clip_pg_rho, adv, err, q);
+        return check_launch("vtrace_fwd_tiled_kernel");
+    }
     const int threads = 128;
     vtrace_fwd_kernel<<<(unsigned)((B + threads - 1) / threads), threads, 0, (cudaStream_t)stream>>>(
         v_tm1, v_t, r_t, discount_t, rho_tm1, (int)B, (int)Tm, stride_b, stride_t, (float)lambda_,

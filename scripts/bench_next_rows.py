@@ -125,3 +125,10 @@ def k1(i):
 report("K1 impala_loss T=20 B=4096 A=15 (same harness)", timed(k1, steps=400, n_streams=6), 204 * B * T, "6 streams, INPUTS_STABLE")
 report("K1 impala_loss T=20 B=4096 A=15 (same harness, 4000 steps)", timed(k1, steps=4000, n_streams=6), 204 * B * T, "6 streams, INPUTS_STABLE")
 report("K7 ppo_loss_is (4000 steps)", timed(k7, steps=4000, n_streams=6), 201 * B * T + 4 * B, "6 streams, INPUTS_STABLE")
+
+# stand-alone V-trace (A1 drop-in, b200rl_vtrace) at the C2 shape: 5 inputs + 3 outputs = 32 B per step
+Bv, Tv = 4096, 19
+vs = [[torch.randn(Bv, Tv, device=dev) for _ in range(4)] + [torch.rand(Bv, Tv, device=dev) * 2] for _ in range(60)]
+report("A1 stand-alone V-trace fwd B=4096 T-1=19 (batch-major)", timed(lambda i: ops.vtrace_fwd(*vs[i % 60])), 32 * Bv * Tv,
+       "20 B read + 12 B written per step; 2.5 MB per launch: launch-bound")
+del vs

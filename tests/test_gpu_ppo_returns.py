@@ -159,7 +159,8 @@ def test_scans_golden_identity_and_ppo_targets():
 
 
 # ------------------------------------------------------------------ stand-alone V-trace drop-in
-@pytest.mark.parametrize("B,T,lam", [(32, 20, 1.), (7, 5, .9), (1, 2, 0.), (300, 33, .5)])
+@pytest.mark.parametrize("B,T,lam", [(32, 20, 1.), (7, 5, .9), (1, 2, 0.), (300, 33, .5), (4096, 20, 1.), (5, 300, .95),
+                                     (3, 257, 1.)])
 def test_batched_vtrace_dropin_forward_backward(B, T, lam):
     d = synth.impala_rollout(B, T, 4, seed=B + T)
     rho = torch.exp(.7 * torch.randn(B, T, generator=torch.Generator().manual_seed(1)))
@@ -183,6 +184,20 @@ def test_batched_vtrace_dropin_forward_backward(B, T, lam):
     # per-sequence form, the function the reference vmaps
     one = vtrace.vtrace_td_error_and_advantage(vg[0, :-1], vg[0, 1:], g["r"][0, :-1], g["discount"][0, :-1], rg[0, :-1], **kw)
     assert_close(one[0], want[0][0], "per-sequence adv", rtol=1e-5, atol=2e-6)
+
+
+@pytest.mark.parametrize("B,T", [(64, 20), (5, 3), (1000, 20), (7, 300)])
+def test_vtrace_forward_time_major(B, T):
+    """The stand-alone V-trace on time-major storage ([T,B] tensors handed over as [B,T] views) equals the batch-major call."""
+    d = to_cuda(synth.impala_rollout(B, T, 4, seed=B + T))
+    rho = torch.exp(.7 * torch.randn(B, T, generator=torch.Generator().manual_seed(2))).cuda()
+    args = (d["values"][:, :-1], d["values"][:, 1:], d["r"][:, :-1], d["discount"][:, :-1], rho[:, :-1])
+    want = ops.vtrace_fwd(*args, lambda_=.9, clip_rho=.9, clip_pg_rho=1.1)[:3]
+    tm_args = [x.t().contiguous().t() for x in args]                  # same values, strides (1, B)
+    got = ops.vtrace_fwd(*tm_args, lambda_=.9, clip_rho=.9, clip_pg_rho=1.1)[:3]
+    for name, a, b in zip(("adv", "err", "q"), got, want):
+        assert a.stride() == (1, B) or B == 1 or T == 2
+        assert torch.equal(a.contiguous(), b.contiguous()), name
 
 
 @pytest.mark.parametrize("B,T,n", [(64, 20, 3), (1, 1, 1), (5, 7, 1), (33, 129, 5), (4, 6, 6), (3, 5, 9), (100, 256, 3)])
