@@ -9,6 +9,7 @@ of ONE kernel launch; autograd only carries the precomputed gradients into the m
 import torch
 
 from . import ops
+from . import vtrace as _vtrace
 
 METRIC_SLOTS = (("train/loss", ops.S_LOSS), ("train/entropy", ops.S_ENTROPY), ("train/td", ops.S_TD),
                 ("train/pg", ops.S_PG), ("train/kl", ops.S_KL), ("train/ratio", ops.S_RATIO))
@@ -103,11 +104,9 @@ def impala_loss(batch, model, lambda_=1., entropy_cost=0.01, as_written=False):
     The committed reference function is work in progress and has no caller (raw logits instead of
     log-probs, ratio = 1, same-step bootstrap, entropy disabled).  By default this computes the loss
     the IMPALA learner actually trains with (``agents/impala/learning.py:146-159``) on a ``[B,T,...]``
-    batch; ``as_written=True`` is not offered on the GPU path (see ``oracle/losses_ref.py`` for the
-    literal restatement)."""
+    batch; ``as_written=True`` computes the committed function literally (``_impala_loss_as_written``)."""
     if as_written:
-        raise RuntimeError("impala_loss(as_written=True) has no CUDA path; the literal WIP semantics "
-                           "live in oracle/losses_ref.py only")
+        return _impala_loss_as_written(batch, model, lambda_)
     s, a, r, discount_t, pi_ref = batch
     B, T = s.shape[0], s.shape[1]
     pi, values = model(s.flatten(0, 1))
@@ -115,6 +114,27 @@ def impala_loss(batch, model, lambda_=1., entropy_cost=0.01, as_written=False):
     values = values.reshape(B, T)
     sq = lambda x: x.squeeze(-1) if x.dim() == 3 else x  # noqa: E731
     return impala_loss_from_outputs(pi, values, sq(a), sq(r), sq(discount_t), pi_ref, entropy_cost, lambda_)
+
+
+def _impala_loss_as_written(batch, model, lambda_):
+    """Reference ``losses.impala_loss`` literally (``losses.py:92-128``): ONE un-batched sequence ``[N,...]``, raw
+    logits gathered instead of log-probs (``:116``), ``ratio = ones`` (``:99``), the bootstrap is the same-step
+    detached value (``:105``), ``td = 0.5 mean err^2`` (``:109``), ``pg = -sum`` (``:116``), entropy disabled
+    (``:120``).  The V-trace call (``:106-108``) is the CUDA kernel behind ``vtrace.batched_vtrace`` (differentiable:
+    ``adv`` is not detached here either); the gather and the two reductions around it are the three torch ops the
+    reference itself spells out."""
+    s, a, r, discount_t, pi_ref = batch
+    pi_tm1, v_tm1 = model(s)
+    a = a.squeeze(dim=-1)
+    ratio = torch.ones_like(r).squeeze().float()
+    v = v_tm1.squeeze(-1)
+    adv, err, _ = _vtrace.vtrace_td_error_and_advantage(v, v.detach(), r.squeeze(dim=-1), discount_t.squeeze(dim=-1),
+                                                        ratio, lambda_=lambda_)
+    td_loss = 0.5 * err.pow(2).mean()
+    pg_loss = -(pi_tm1.gather(1, a.unsqueeze(dim=-1)).squeeze(dim=-1) * adv).sum()
+    loss = pg_loss + td_loss
+    return loss, {"train/loss": loss.detach(), "train/td": td_loss.detach(), "train/pg": pg_loss.detach(),
+                  "train/ratio": ratio.mean().detach()}
 
 
 class _QuantileHuber(torch.autograd.Function):
