@@ -4,7 +4,7 @@ This package is the *checker*, never the product: only ``tests/``,
 ``__graft_entry__.smoke()`` and ``bench.py``'s ``cpu_baseline`` / ``--impl
 reference`` legs may import it.  Nothing under ``impala_b200/`` imports it.
 
-PARITY UNPINNED.  The reference (``/root/reference``) holds no tests, no golden
+PARITY UNPINNED for the rlego / rlmeta arithmetic (pinned for the rest, see the end of this note).  The reference (``/root/reference``) holds no tests, no golden
 vectors and no fixtures, and the arithmetic of its hot path lives
 in third-party packages that are neither vendored nor installed nor pinned:
 
@@ -24,6 +24,12 @@ in third-party packages that are neither vendored nor installed nor pinned:
 
 What *is* pinned: the torch arithmetic the reference itself calls
 (``torch.distributions.Categorical`` / ``kl_divergence`` are imported from the
-installed torch, not restated), the op order of the reference's loss code, and
-hand-derived known-answer cases in ``tests/``.
+installed torch, not restated), and -- by fixtures produced by RUNNING the
+reference's own files with import shims for the absent third-party names
+(``tests/golden/make_golden_from_reference.py`` -> ``tests/golden/ref_*.npz``;
+checked in ``tests/test_reference_golden.py``) -- ``losses.ppo_loss``,
+``quantile_regression_loss``, the whole of ``ImpalaLearner._train_step`` around
+the rlego call (slices, means, signs, no-detach, clip, Adam) and
+``losses.impala_loss`` as committed.  The rlego recursions themselves are
+covered by hand-derived known-answer cases in ``tests/`` only.
 """
