@@ -16,6 +16,8 @@ fixture                reference code that ran                                 t
                        (``agents/impala/learning.py:140-177``) incl. the       (shim = ``oracle/rlego_ref.py``; the V-trace
                        reference's ``functorch.vmap`` wrapper (``:15-18``),     recursion itself stays UNPINNED), everything
                        ``clip_grad_norm_`` and ``Adam.step``                    else is the reference's own op sequence
+``ref_ppo_step``       ``PPOLearner._train_step``                              none -> **pinned by the reference itself**
+                       (``agents/ppo/learning.py:130-143``) incl. clip + Adam
 ``ref_impala_loss``    ``losses.impala_loss`` (``losses.py:92-128``)           same shim
 ``ref_make_replay``    ``ImpalaActor._make_replay``                            none (``moolib.Batcher`` shim only hands the
                        (``agents/impala/learning.py:77-80``)                   stacked tensors back)
@@ -116,6 +118,7 @@ def install_shims():
     _pkg("models", os.path.join(REF, "models"))
     _pkg("agents", os.path.join(REF, "agents"))
     _pkg("agents.impala", os.path.join(REF, "agents", "impala"))
+    _pkg("agents.ppo", os.path.join(REF, "agents", "ppo"))
     sys.path.insert(0, REF)
     sys.modules["models.distributed_models"] = _mod("models.distributed_models")   # only get_muesli (dead) uses it
 
@@ -186,6 +189,34 @@ def ref_impala_step(learning):
               logits_after=model.logits.detach(), values_after=model.values.detach())
 
 
+def ref_ppo_step(ppo_learning):
+    """``PPOLearner._train_step`` (``agents/ppo/learning.py:130-143``): ``losses.ppo_loss`` -> backward -> clip -> Adam."""
+    N, A = 256, 15                                                            # batch_size default, :81
+    d = synth.ppo_minibatch(N, A, 4600)
+    model = OutputsModel(d["logits"], d["v"])
+    opt = torch.optim.Adam(model.parameters(), lr=1e-4, eps=1e-5)             # agents/ppo/builder.py
+    learner = ppo_learning.PPOLearner(model, None, opt, batch_size=N)
+    captured = {}
+    clip = torch.nn.utils.clip_grad_norm_
+
+    def spy(params, max_norm, *a, **k):
+        params = list(params)
+        captured["dlogits"], captured["dv"] = params[0].grad.clone(), params[1].grad.clone()
+        return clip(params, max_norm, *a, **k)
+
+    torch.nn.utils.clip_grad_norm_ = spy
+    try:
+        m = learner._train_step((torch.zeros(N, 1), d["a"], d["v_target"], d["pi_ref"]))
+    finally:
+        torch.nn.utils.clip_grad_norm_ = clip
+    keys = ("train/loss", "train/entropy", "train/td", "train/pg", "train/target", "train/kl", "train/ratio",
+            "train_step/grad_norm")
+    assert set(m) == set(keys)
+    _save("ref_ppo_step", **d, dlogits=captured["dlogits"], dv=captured["dv"],
+          metrics=np.array([float(m[k]) for k in keys], dtype=np.float64),
+          logits_after=model.logits.detach(), v_after=model.values.detach())
+
+
 def ref_impala_loss(losses):
     T, A = 24, 15
     d = synth.impala_rollout(1, T, A, 4400)
@@ -244,6 +275,7 @@ def main():
     ref_ppo_loss(losses)
     ref_quantile(ql)
     ref_impala_step(learning)
+    ref_ppo_step(importlib.import_module("agents.ppo.learning"))
     ref_impala_loss(losses)
     ref_make_replay(learning)
     ref_models()

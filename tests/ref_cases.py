@@ -5,6 +5,7 @@ import torch
 
 IMPALA_STEP_KEYS = ("train/loss", "train/entropy", "train/td", "train/pg", "train/kl", "train/ratio", "train/grad_norm")
 PPO_KEYS = ("train/loss", "train/entropy", "train/td", "train/pg", "train/target", "train/kl", "train/ratio")
+PPO_STEP_KEYS = PPO_KEYS + ("train_step/grad_norm",)
 IMPALA_LOSS_KEYS = ("train/loss", "train/td", "train/pg", "train/ratio")
 IMPALA_FIELDS = ("logits", "values", "a", "r", "discount", "pi_ref")
 PPO_FIELDS = ("logits", "v", "a", "v_target", "pi_ref")

@@ -12,7 +12,8 @@ from conftest import GOLDEN
 from gpu_util import assert_close
 from impala_b200 import losses, ops, optim
 from impala_b200.agents.impala import ImpalaLearner
-from ref_cases import (IMPALA_FIELDS, IMPALA_LOSS_KEYS, IMPALA_STEP_KEYS, PPO_FIELDS, PPO_KEYS, OutputsModel,
+from impala_b200.agents.ppo import PPOLearner
+from ref_cases import (IMPALA_FIELDS, IMPALA_LOSS_KEYS, IMPALA_STEP_KEYS, PPO_FIELDS, PPO_KEYS, PPO_STEP_KEYS, OutputsModel,
                        impala_batch_list, impala_loss_batch)
 
 pytestmark = pytest.mark.gpu
@@ -78,6 +79,25 @@ def test_impala_learner_dropin_equals_reference_train_step(cuda, name, fused_opt
     assert_close(model.values, torch.from_numpy(z["values_after"]), "values after Adam", rtol=1e-6, atol=2e-7)
     # the step really moved the parameters (lr 1e-4 * g/(|g|+eps))
     assert (model.logits.detach().cpu() - d["logits"].cpu()).abs().max().item() > 1e-5
+
+
+@pytest.mark.parametrize("fused_opt", [True, False])
+def test_ppo_learner_dropin_equals_reference_train_step(cuda, fused_opt):
+    """agents/ppo/learning.py:130-143 ran here unmodified; K3 + K6 (or torch's Adam) must leave the same metrics,
+    gradient norm and parameters."""
+    d, z = load("ref_ppo_step", PPO_FIELDS, cuda)
+    model = OutputsModel(d["logits"], d["v"]).to(cuda)
+    if fused_opt:
+        opt = optim.FusedClipAdam(model.parameters(), lr=1e-4, eps=1e-5)
+    else:
+        opt = torch.optim.Adam(model.parameters(), lr=1e-4, eps=1e-5)
+    learner = PPOLearner(model, None, opt, batch_size=len(d["a"]))
+    m = learner._train_step((torch.zeros(len(d["a"]), 1, device=cuda), d["a"], d["v_target"], d["pi_ref"]))
+    assert set(m) == set(PPO_STEP_KEYS)
+    for i, k in enumerate(PPO_STEP_KEYS):
+        assert float(m[k]) == pytest.approx(z["metrics"][i], rel=2e-5, abs=2e-6), k
+    assert_close(model.logits, torch.from_numpy(z["logits_after"]), "logits after Adam", rtol=1e-6, atol=2e-7)
+    assert_close(model.values, torch.from_numpy(z["v_after"]), "v after Adam", rtol=1e-6, atol=2e-7)
 
 
 def test_impala_loss_as_written_equals_reference_run(cuda):

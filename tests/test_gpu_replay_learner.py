@@ -128,6 +128,37 @@ def test_config4_shape_gather_roundtrip(cuda):
     assert torch.equal(out, store.view(cap, -1).index_select(0, idx))
 
 
+def test_config4_full_size_gather_and_append(cuda):
+    """BASELINE config 4 at FULL size: 1,000,000 rows x 12,288 B = 12.29 GB ring, batch 4,096, seed 123.  Byte offsets
+    pass 2^32 from row 349,526 on, which only this size exercises.  Size-independent checks: every gathered row
+    carries its own index tag; the whole batch equals torch's index_select; appending the batch back (ring wrap
+    included) and re-gathering is the identity; the index stream equals the committed golden stream."""
+    import numpy as np
+    from conftest import GOLDEN
+    cap, row, n = 1_000_000, 3 * 64 * 64, 4096
+    free, _ = torch.cuda.mem_get_info()
+    if free < 14 * 2**30:
+        pytest.skip("needs 14 GB of free HBM")
+    store = torch.empty(cap, row, dtype=torch.uint8, device=cuda)
+    store.view(torch.int32).random_()                                   # arbitrary bytes everywhere
+    store[:, :8] = torch.arange(cap, device=cuda).view(cap, 1).view(torch.uint8).view(cap, 8)   # little-endian tag
+    idx = ops.sample_uniform(123, 0, 0, n, cap, cuda)
+    z = np.load(os.path.join(GOLDEN, "replay_indices.npz"))
+    assert np.array_equal(idx.cpu().numpy(), z["idx_seed123_1M"])
+    assert (idx > 349_526).any() and int(idx.max()) < cap
+    out = ops.gather_rows(store, idx)
+    assert torch.equal(out[:, :8].contiguous().view(torch.int64).view(-1), idx)
+    assert torch.equal(out, store.index_select(0, idx))
+    # ring append of the batch across the wrap point: count = cap - 100 -> rows land in slots cap-100.., 0..n-101
+    count = cap - 100
+    ops.ring_append(store, count, out)
+    slots = (torch.arange(n, device=cuda) + count) % cap
+    back = ops.gather_rows(store, slots)
+    assert torch.equal(back, out)
+    del store, out, back
+    torch.cuda.empty_cache()
+
+
 def _fill_impala_replay(rb, n_items, T, A, seed):
     g = torch.Generator().manual_seed(seed)
     for _ in range(n_items):

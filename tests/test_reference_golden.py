@@ -69,6 +69,20 @@ def test_oracle_impala_train_loss_equals_reference_learner_step(name):
     assert np.array_equal(p[1].detach().numpy(), z["values_after"])
 
 
+def test_oracle_ppo_loss_plus_clip_adam_equals_reference_ppo_learner_step():
+    """``PPOLearner._train_step`` (agents/ppo/learning.py:130-143) is reference code end to end (no rlego)."""
+    d, z = load("ref_ppo_step", PPO_FIELDS)
+    p = [d["logits"].clone().requires_grad_(True), d["v"].clone().requires_grad_(True)]
+    loss, m = losses_ref.ppo_loss_from_outputs(p[0], p[1], d["a"], d["v_target"], d["pi_ref"], 0.01, 0.1)
+    loss.backward()
+    assert np.array_equal(p[0].grad.numpy(), z["dlogits"]) and np.array_equal(p[1].grad.numpy(), z["dv"])
+    assert [m[k].item() for k in PPO_KEYS] == list(z["metrics"][:-1])
+    norm = torch.nn.utils.clip_grad_norm_(p, 0.5)
+    torch.optim.Adam(p, lr=1e-4, eps=1e-5).step()
+    assert norm.item() == z["metrics"][-1]
+    assert np.array_equal(p[0].detach().numpy(), z["logits_after"]) and np.array_equal(p[1].detach().numpy(), z["v_after"])
+
+
 def test_oracle_impala_loss_as_written_equals_reference_run():
     z = np.load(os.path.join(GOLDEN, "ref_impala_loss.npz"))
     model = OutputsModel(torch.from_numpy(z["logits"]), torch.from_numpy(z["values"]))
