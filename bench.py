@@ -253,7 +253,8 @@ def make_learner(args, device, seed):
     B, T, A = args.B or 256, args.T or 20, args.A
     torch.manual_seed(seed)
     cl = os.environ.get("B200RL_BENCH_CHANNELS_LAST", "1") == "1"
-    model = models.ActorCritic((3, 64, 64), A, body="impala", channels_last=cl).to(device)
+    fused = cl and os.environ.get("B200RL_BENCH_FUSED_GLUE", "1") == "1"
+    model = models.ActorCritic((3, 64, 64), A, body="impala", channels_last=cl, fused_glue=fused).to(device)
     if cl:
         model = model.to(memory_format=torch.channels_last)
     if dist.is_initialized():                      # same initial weights on every rank
@@ -280,7 +281,8 @@ def make_learner(args, device, seed):
 
     desc = {"workload": "full IMPALA learner step (BASELINE config 5)", "T": T, "B_per_gpu": B, "A": A,
             "model": "IMPALA-CNN body + actor-critic head, 630,352 params, fp32 storage, cuDNN convs with torch's default "
-                     "allow_tf32=True (the reference's torch default too), %s" % ("channels_last" if cl else "NCHW"),
+                     "allow_tf32=True (the reference's torch default too), %s%s" % ("channels_last" if cl else "NCHW", ", bias/ReLU/residual/max-pool glue "
+                     "and its backward in the K9 kernels (convolutions bias-free in cuDNN)" if fused else ""),
             "replay": "%d rollouts device-resident (%.0f MB u8), uniform sample + gather on device" % (cap, cap * T * 12288 / 1e6),
             "l2_policy": "gathered batch 63 MB + activations >> per-step reuse; buffer 246 MB > 126 MB L2"}
     def grad_exchange():

@@ -50,6 +50,11 @@ SIGNATURES = {
     "b200rl_ipc_export": (_i32, [_vp, _vp, _vp]),
     "b200rl_ipc_import": (_i32, [_vp, _i64, _vp]),
     "b200rl_ipc_close": (_i32, [_vp, _i64]),
+    "b200rl_obs_u8_to_f32_nhwc": (_i32, [_vp, _vp, _i64, _i64, _i64, _i64, _f, _vp]),
+    "b200rl_maxpool3x3s2_fwd": (_i32, [_vp] * 5 + [_i64] * 4 + [_vp]),
+    "b200rl_maxpool3x3s2_bwd": (_i32, [_vp] * 3 + [_i64] * 4 + [_vp]),
+    "b200rl_bias_act_fwd": (_i32, [_vp] * 5 + [_i64] * 3 + [_vp]),
+    "b200rl_relu_bwd_add": (_i32, [_vp] * 5 + [_i64] * 3 + [_vp]),
 }
 
 

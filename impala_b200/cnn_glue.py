@@ -1,0 +1,70 @@
+"""Autograd pieces of the fused IMPALA-CNN glue (K9, ``csrc/cnn_glue.cu``).
+
+The reference's body (``models/common.py:8-83``) is ``conv -> max_pool -> 2 x [relu -> conv -> relu -> conv -> +x]``
+per stage; the convolutions stay in cuDNN (bias-free here), and everything between them -- bias adds, ReLUs, residual
+adds, the pools, and in the backward pass the ReLU masks, gradient joins and bias gradients -- runs in the kernels
+below, one pass each, instead of ~10 eager elementwise / pooling launches per block.
+"""
+import torch
+
+from . import ops
+
+_CL = torch.channels_last
+
+
+def _cl(g):
+    return None if g is None else g.contiguous(memory_format=_CL)
+
+
+class PoolBias(torch.autograd.Function):
+    """``p = max_pool2d(u + bias, 3, 2, 1)`` and ``r = relu(p)`` (``ImpalaCNNBlock.forward``, ``models/common.py:53-55``,
+    plus the ReLU that opens the first residual block, ``:30``)."""
+
+    @staticmethod
+    def forward(ctx, u, bias):
+        p, r, code = ops.maxpool3x3s2_fwd(u, bias, with_relu=True)
+        ctx.save_for_backward(code, r)
+        ctx.in_shape = tuple(u.shape)
+        return p, r
+
+    @staticmethod
+    def backward(ctx, dp, dr):
+        code, r = ctx.saved_tensors
+        g, db = ops.relu_bwd_add(_cl(dp), _cl(dr), r)           # gradient w.r.t. p, joined; its channel sums = d bias
+        return ops.maxpool3x3s2_bwd(g, code, ctx.in_shape), db
+
+
+class BiasAct(torch.autograd.Function):
+    """``v = u + bias (+ res)``; outputs ``v`` and/or ``relu(v)``:
+    ``relu(conv0(.))`` (``models/common.py:31-32``) is ``(want_y, want_r) = (False, True)`` without ``res``;
+    ``conv1(.) + inputs`` (``:33-34``) has ``res`` and also emits the ReLU that opens the next block / closes the body."""
+
+    @staticmethod
+    def forward(ctx, u, bias, res, want_y, want_r):
+        y, r = ops.bias_act_fwd(u, bias, res, want_y, want_r)
+        ctx.save_for_backward(r) if want_r else ctx.save_for_backward()
+        ctx.flags = (res is not None, want_y, want_r)
+        return tuple(t for t in (y, r) if t is not None)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        has_res, want_y, want_r = ctx.flags
+        grads = list(grads)
+        dy = _cl(grads.pop(0)) if want_y else None
+        dr = _cl(grads.pop(0)) if want_r else None
+        r = ctx.saved_tensors[0] if want_r else None
+        g, db = ops.relu_bwd_add(dy, dr, r)
+        return g, db, (g if has_res else None), None, None
+
+
+def pool_bias(u, bias):
+    return PoolBias.apply(u, bias)
+
+
+def bias_relu(u, bias):
+    return BiasAct.apply(u, bias, None, False, True)[0]
+
+
+def bias_add(u, bias, res, want_y=True, want_r=False):
+    out = BiasAct.apply(u, bias, res, want_y, want_r)
+    return out if len(out) > 1 else out[0]

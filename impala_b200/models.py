@@ -53,7 +53,11 @@ class _ImpalaStage(nn.Module):
 
 
 class ImpalaCNN(nn.Module):
-    """16-32-32 IMPALA-CNN; 64x64 input -> 32*8*8 = 2048 features."""
+    """16-32-32 IMPALA-CNN; 64x64 input -> 32*8*8 = 2048 features.
+
+    ``forward_fused`` computes the same function with the cuDNN convolutions called bias-free and everything between
+    them (bias, ReLU, residual add, max-pool, and their backward passes incl. the bias gradients) in the K9 glue
+    kernels (``cnn_glue.py``): CUDA float32 channels_last tensors only, same parameters, same state dict."""
 
     def __init__(self, obs_shape: Tuple[int, int, int]):
         super().__init__()
@@ -66,6 +70,23 @@ class ImpalaCNN(nn.Module):
 
     def forward(self, x):
         return self.body(x)
+
+    def forward_fused(self, x):
+        from . import cnn_glue as G
+        stages = [m for m in self.body if isinstance(m, _ImpalaStage)]
+        for si, st in enumerate(stages):
+            u = F.conv2d(x, st.conv.weight, None, padding=1)
+            p, r = G.pool_bias(u, st.conv.bias)                            # max_pool(conv + b), relu of it
+            for bi, blk in enumerate((st.res_block0, st.res_block1)):
+                r1 = G.bias_relu(F.conv2d(r, blk.conv0.weight, None, padding=1), blk.conv0.bias)
+                u1 = F.conv2d(r1, blk.conv1.weight, None, padding=1)
+                if bi == 0:                                                # block output + the next block's opening ReLU
+                    p, r = G.bias_add(u1, blk.conv1.bias, p, want_y=True, want_r=True)
+                elif si + 1 < len(stages):                                 # feeds the next stage's convolution
+                    x = G.bias_add(u1, blk.conv1.bias, p, want_y=True, want_r=False)
+                else:                                                      # the body's closing ReLU
+                    x = G.bias_add(u1, blk.conv1.bias, p, want_y=False, want_r=True)
+        return x.flatten(1)
 
 
 class NatureCNN(nn.Module):
@@ -89,7 +110,7 @@ class ActorCritic(nn.Module):
     """``x/255 -> body -> LayerNorm -> Linear(.,256) -> GELU -> {actor Linear(256,A), critic Linear(256,1)}``."""
 
     def __init__(self, obs_shape: Tuple[int, int, int], action_dim: int = 15, h_dim: int = 256,
-                 body: str = "nature", channels_last: bool = False):
+                 body: str = "nature", channels_last: bool = False, fused_glue: bool = False):
         super().__init__()
         self.body = ImpalaCNN(obs_shape) if body == "impala" else NatureCNN(obs_shape)
         d = self.body.output_dim
@@ -97,8 +118,19 @@ class ActorCritic(nn.Module):
         self.actor = _trunc_init(nn.Linear(h_dim, action_dim))
         self.critic = _trunc_init(nn.Linear(h_dim, 1))
         self.channels_last = channels_last
+        if fused_glue and not (channels_last and body == "impala"):
+            raise RuntimeError("fused_glue needs body='impala' and channels_last=True")
+        self.fused_glue = fused_glue
 
     def forward(self, obs: torch.Tensor):
+        if self.fused_glue:                                  # K9: CUDA only, raises otherwise (no silent fallback)
+            from . import ops
+            if obs.dtype == torch.uint8:
+                x = ops.obs_to_f32_nhwc(obs.contiguous())    # obs.float() / 255 + NCHW -> NHWC in one pass
+            else:
+                x = (obs.float() / 255.).contiguous(memory_format=torch.channels_last)
+            h = self.projection(self.body.forward_fused(x))
+            return self.actor(h), self.critic(h)
         x = obs.float() / 255.
         if self.channels_last:
             x = x.contiguous(memory_format=torch.channels_last)

@@ -436,3 +436,97 @@ def act_epilogue(logits, deterministic, seed, stream_id, draw_offset):
     _cabi.call("b200rl_act_epilogue", logits.data_ptr(), n, A, det.data_ptr(), 0 if det.numel() == 1 and n != 1 else 1,
                seed, stream_id, draw_offset, action.data_ptr(), _stream())
     return action
+
+
+# ---- K9: memory-bound glue of the IMPALA-CNN (fp32 NHWC = torch channels_last) ------------------------------------
+GLUE_MAX_CTAS = 148 * 8          # grid of the two grid-stride glue kernels: 8 CTAs of 256 threads per SM
+
+
+def _nhwc(x, name):
+    if x.dim() != 4 or x.dtype != torch.float32 or not x.is_contiguous(memory_format=torch.channels_last):
+        raise RuntimeError("%s: expected a float32 channels_last [N,C,H,W] tensor, got %s %s strides %s"
+                           % (name, tuple(x.shape), x.dtype, x.stride()))
+    return x
+
+
+def _empty_nhwc(N, C, H, W, device, dtype=torch.float32):
+    return torch.empty((N, C, H, W), dtype=dtype, device=device, memory_format=torch.channels_last)
+
+
+def _glue_ctas(n_float4):
+    return max(1, min(GLUE_MAX_CTAS, (n_float4 + 255) // 256))
+
+
+def obs_to_f32_nhwc(obs, divisor=255.0):
+    """``obs.float() / divisor`` (reference ``models/models.py:73``) for uint8 ``[N,3,H,W]`` NCHW frames, written
+    directly in channels_last memory order: one pass instead of cast + divide + layout copy."""
+    _require_cuda(obs)
+    if obs.dtype != torch.uint8 or obs.dim() != 4 or not obs.is_contiguous():
+        raise RuntimeError("obs_to_f32_nhwc: expected contiguous uint8 [N,C,H,W], got %s %s" % (tuple(obs.shape), obs.dtype))
+    N, C, H, W = obs.shape
+    out = _empty_nhwc(N, C, H, W, obs.device)
+    _cabi.call("b200rl_obs_u8_to_f32_nhwc", obs.data_ptr(), out.data_ptr(), N, C, H, W, float(divisor), _stream())
+    return out
+
+
+def maxpool3x3s2_fwd(u, bias=None, with_relu=False):
+    """``p = max_pool2d(u + bias, 3, 2, 1)``; returns ``(p, relu(p) or None, code)`` (``code``: uint8 argmax tap)."""
+    _require_cuda(u)
+    _nhwc(u, "maxpool3x3s2_fwd")
+    N, C, H, W = u.shape
+    OH, OW = (H - 1) // 2 + 1, (W - 1) // 2 + 1
+    p = _empty_nhwc(N, C, OH, OW, u.device)
+    r = _empty_nhwc(N, C, OH, OW, u.device) if with_relu else None
+    code = _empty_nhwc(N, C, OH, OW, u.device, torch.uint8)
+    b = None if bias is None else _f32c(bias.detach())
+    _cabi.call("b200rl_maxpool3x3s2_fwd", u.data_ptr(), _cabi.ptr(b), p.data_ptr(), _cabi.ptr(r), code.data_ptr(),
+               N, H, W, C, _stream())
+    return p, r, code
+
+
+def maxpool3x3s2_bwd(g, code, in_shape):
+    """Gradient w.r.t. the pool input ``[N,C,H,W]`` from ``g`` (pooled size) and the forward's ``code``."""
+    _require_cuda(g, code)
+    _nhwc(g, "maxpool3x3s2_bwd")
+    N, C, H, W = in_shape
+    du = _empty_nhwc(N, C, H, W, g.device)
+    _cabi.call("b200rl_maxpool3x3s2_bwd", g.data_ptr(), code.data_ptr(), du.data_ptr(), N, H, W, C, _stream())
+    return du
+
+
+def bias_act_fwd(u, bias, res=None, want_y=True, want_r=False):
+    """``v = u + bias[c] (+ res)``; returns ``(v or None, relu(v) or None)`` as requested."""
+    _require_cuda(u, bias)
+    _nhwc(u, "bias_act_fwd")
+    if res is not None:
+        _nhwc(res, "bias_act_fwd res")
+        if res.shape != u.shape:
+            raise RuntimeError("bias_act_fwd: res %s vs u %s" % (tuple(res.shape), tuple(u.shape)))
+    if not (want_y or want_r):
+        raise RuntimeError("bias_act_fwd: nothing to compute")
+    N, C, H, W = u.shape
+    y = torch.empty_like(u) if want_y else None
+    r = torch.empty_like(u) if want_r else None
+    b = _f32c(bias.detach())
+    _cabi.call("b200rl_bias_act_fwd", u.data_ptr(), b.data_ptr(), _cabi.ptr(res), _cabi.ptr(y), _cabi.ptr(r),
+               N * H * W, C, _glue_ctas(N * H * W * C // 4), _stream())
+    return y, r
+
+
+def relu_bwd_add(dy, dr, r):
+    """``g = dy + dr * (r > 0)`` (either term may be ``None``) and the per-channel sum of ``g`` (the bias gradient of
+    the op whose output ``g`` belongs to).  With ``dr is None`` no tensor is written: ``g`` is ``dy`` itself."""
+    ref = dy if dy is not None else dr
+    _require_cuda(ref)
+    for t, nm in ((dy, "dy"), (dr, "dr"), (r if dr is not None else None, "r")):
+        if t is not None:
+            _nhwc(t, "relu_bwd_add " + nm)
+            if t.shape != ref.shape:
+                raise RuntimeError("relu_bwd_add: shape mismatch %s vs %s" % (tuple(t.shape), tuple(ref.shape)))
+    N, C, H, W = ref.shape
+    n_ctas = _glue_ctas(N * H * W * C // 4)
+    partials = torch.empty((n_ctas, C), dtype=torch.float32, device=ref.device)
+    g = torch.empty_like(ref) if dr is not None else None
+    _cabi.call("b200rl_relu_bwd_add", _cabi.ptr(dy), _cabi.ptr(dr), _cabi.ptr(r if dr is not None else None),
+               _cabi.ptr(g), partials.data_ptr(), N * H * W, C, n_ctas, _stream())
+    return (g if g is not None else dy), partials.sum(0)

@@ -272,6 +272,34 @@ int32_t b200rl_ipc_export(const void *ptr, void *handle64, int64_t *offset);
 int32_t b200rl_ipc_import(const void *handle64, int64_t offset, void **out_ptr);
 int32_t b200rl_ipc_close(void *ptr, int64_t offset);
 
+/* K9 -- memory-bound glue of the IMPALA-CNN between its cuDNN convolutions (reference models/common.py:8-83:
+ * ResidualBlock :28-34, ImpalaCNNBlock :52-58, ImpalaCNNLarge :71-78; input scaling models/models.py:73).  All
+ * activations are fp32 NHWC (torch channels_last), C a multiple of 4, 16-byte aligned.
+ *  obs_u8_to_f32_nhwc: out[n,h,w,c] = (float)obs[n,c,h,w] * (1.0f / divisor) -- what torch's CUDA `x.float() / 255.`
+ *                      computes (scalar divisors become reciprocal multiplies)  (C == 3, H*W % 4 == 0).
+ *  maxpool3x3s2_fwd:   p = max_pool2d(u + bias[c], kernel 3, stride 2, padding 1) with torch's scan order and tie /
+ *                      NaN rule; u is [N,H,W,C], p (and r = relu(p) when r != NULL) are [N,OH,OW,C],
+ *                      OH = (H-1)/2+1; code holds one byte per output element: kh*3+kw of the selected tap.
+ *                      bias may be NULL.
+ *  maxpool3x3s2_bwd:   du[N,H,W,C] from g[N,OH,OW,C] and code; gather form, deterministic.
+ *  bias_act_fwd:       v = u + bias[c] (+ res when res != NULL); y = v when y != NULL; r = relu(v) when r != NULL.
+ *  relu_bwd_add:       v = (dy ? dy : 0) + (dr ? dr * (r > 0) : 0); g = v when g != NULL; partials[cta][C] =
+ *                      per-CTA channel sums of v (the caller adds the n_ctas rows in order: the bias gradient).
+ *  n_ctas = grid size of the two grid-stride kernels (<= 65535); C/4 must divide 256. */
+int32_t b200rl_obs_u8_to_f32_nhwc(
+    const uint8_t *obs, float *out, int64_t N, int64_t C, int64_t H, int64_t W, float divisor, void *stream);
+int32_t b200rl_maxpool3x3s2_fwd(
+    const float *u, const float *bias, float *p, float *r, uint8_t *code, int64_t N, int64_t H, int64_t W, int64_t C,
+    void *stream);
+int32_t b200rl_maxpool3x3s2_bwd(
+    const float *g, const uint8_t *code, float *du, int64_t N, int64_t H, int64_t W, int64_t C, void *stream);
+int32_t b200rl_bias_act_fwd(
+    const float *u, const float *bias, const float *res, float *y, float *r, int64_t n_pix, int64_t C, int64_t n_ctas,
+    void *stream);
+int32_t b200rl_relu_bwd_add(
+    const float *dy, const float *dr, const float *r, float *g, float *partials, int64_t n_pix, int64_t C,
+    int64_t n_ctas, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

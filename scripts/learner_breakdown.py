@@ -52,7 +52,10 @@ def run(channels_last, benchmark, tf32=False):
         ", ".join("%s %.3f" % (k, v / n) for k, v in tot.items())))
 
 
+if os.environ.get("TF32_ONLY") != "1":
+    for cl in (False, True):
+        for bm in (False, True):
+            run(cl, bm)
 for cl in (False, True):
     for bm in (False, True):
-        run(cl, bm)
-run(True, True, tf32=True)
+        run(cl, bm, tf32=True)

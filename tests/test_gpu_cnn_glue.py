@@ -1,0 +1,142 @@
+"""GPU: K9 (fused IMPALA-CNN glue, csrc/cnn_glue.cu) against the torch ops the reference's body is written in
+(``models/common.py:8-83``: ``nn.functional.relu`` / ``max_pool2d(kernel_size=3, stride=2, padding=1)`` / ``x + inputs``;
+``models/models.py:73``: ``obs.float() / 255``).  Forward results are bit-exact; gradients differ only by the order
+of <= 4 additions (pool) or of the bias-gradient reduction."""
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from gpu_util import assert_close
+from impala_b200 import cnn_glue, models, ops
+
+pytestmark = pytest.mark.gpu
+CL = torch.channels_last
+
+
+def _rand(shape, cuda, seed, levels=None):
+    g = torch.Generator(device=cuda).manual_seed(seed)
+    x = torch.randn(shape, device=cuda, generator=g)
+    if levels:                                   # few distinct values -> many ties inside every window
+        x = (x * levels).round() / levels
+    return x.contiguous(memory_format=CL)
+
+
+@pytest.mark.parametrize("shape", [(4, 3, 64, 64), (1, 3, 2, 2), (3, 3, 6, 10)])
+def test_obs_conversion_bit_exact(cuda, shape):
+    g = torch.Generator(device=cuda).manual_seed(1)
+    obs = torch.randint(0, 256, shape, device=cuda, dtype=torch.uint8, generator=g)
+    got = ops.obs_to_f32_nhwc(obs)
+    want = obs.float() / 255.
+    assert got.is_contiguous(memory_format=CL) and torch.equal(got, want)
+    with pytest.raises(RuntimeError):
+        ops.obs_to_f32_nhwc(obs[:, :2].contiguous())            # 2 planes: argument error from the C ABI
+
+
+@pytest.mark.parametrize("shape,levels", [((5, 16, 64, 64), None), ((3, 32, 7, 9), 2), ((2, 8, 1, 1), None),
+                                           ((2, 4, 2, 3), 1), ((7, 32, 16, 16), 3), ((1, 64, 5, 4), None)])
+@pytest.mark.parametrize("with_bias", [True, False])
+def test_maxpool_forward_and_backward_match_torch(cuda, shape, levels, with_bias):
+    u = _rand(shape, cuda, 7, levels).requires_grad_(True)
+    bias = torch.randn(shape[1], device=cuda) if with_bias else None
+    ub = u + bias.view(1, -1, 1, 1) if with_bias else u
+    want = F.max_pool2d(ub, kernel_size=3, stride=2, padding=1)
+    p, r, code = ops.maxpool3x3s2_fwd(u.detach(), bias, with_relu=True)
+    assert torch.equal(p, want) and torch.equal(r, F.relu(want))
+    assert p.is_contiguous(memory_format=CL) and int(code.max()) <= 8
+    gy = _rand(tuple(want.shape), cuda, 8)
+    want.backward(gy)
+    du = ops.maxpool3x3s2_bwd(gy, code, tuple(shape))
+    assert_close(du, u.grad, "pool grad", rtol=1e-6, atol=1e-7)
+    # every unit of gradient lands somewhere exactly once
+    assert_close(du.sum(), gy.sum(), "mass", rtol=1e-4, atol=1e-3)
+
+
+def test_maxpool_nan_rule(cuda):
+    u = _rand((1, 4, 6, 6), cuda, 3)
+    u[0, 1, 2, 2] = float("nan")
+    p, _, _ = ops.maxpool3x3s2_fwd(u)
+    want = F.max_pool2d(u, 3, 2, 1)
+    assert torch.equal(torch.isnan(p), torch.isnan(want)) and torch.equal(p.nan_to_num(7.), want.nan_to_num(7.))
+
+
+@pytest.mark.parametrize("shape", [(5, 16, 32, 32), (3, 32, 5, 7), (2, 4, 1, 1), (300, 32, 8, 8)])
+def test_bias_act_and_relu_bwd_add_match_torch(cuda, shape):
+    u, res = _rand(shape, cuda, 11, 2), _rand(shape, cuda, 12, 2)
+    bias = torch.randn(shape[1], device=cuda)
+    b4 = bias.view(1, -1, 1, 1)
+    y, r = ops.bias_act_fwd(u, bias, res, want_y=True, want_r=True)
+    assert torch.equal(y, (u + b4) + res) and torch.equal(r, F.relu((u + b4) + res))
+    y2, r2 = ops.bias_act_fwd(u, bias, None, want_y=False, want_r=True)
+    assert y2 is None and torch.equal(r2, F.relu(u + b4))
+    dy, dr = _rand(shape, cuda, 13), _rand(shape, cuda, 14)
+    g, db = ops.relu_bwd_add(dy, dr, r)
+    want_g = dy + dr * (r > 0)
+    assert torch.equal(g, want_g)
+    assert_close(db, want_g.sum((0, 2, 3)), "dbias", rtol=1e-5, atol=1e-4)
+    g2, db2 = ops.relu_bwd_add(None, dr, r)
+    assert torch.equal(g2, dr * (r > 0))
+    g3, db3 = ops.relu_bwd_add(dy, None, None)
+    assert g3 is dy
+    assert_close(db3, dy.sum((0, 2, 3)), "dbias colsum-only", rtol=1e-5, atol=1e-4)
+    g4, db4 = ops.relu_bwd_add(dy, dr, r)
+    assert torch.equal(db4, db)                                   # fixed-order sums: deterministic
+
+
+def test_autograd_pieces_match_torch_block(cuda):
+    """One ImpalaCNNBlock stage built from the fused pieces vs the same stage in eager torch (fp32 convs)."""
+    tf32 = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        torch.manual_seed(3)
+        stage = models._ImpalaStage(16, 32).to(cuda).to(memory_format=CL)
+        x = _rand((6, 16, 20, 20), cuda, 5)
+        xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+        want = stage(xa)
+        u = F.conv2d(xb, stage.conv.weight, None, padding=1)
+        p, r = cnn_glue.pool_bias(u, stage.conv.bias)
+        for k, blk in enumerate((stage.res_block0, stage.res_block1)):
+            r1 = cnn_glue.bias_relu(F.conv2d(r, blk.conv0.weight, None, padding=1), blk.conv0.bias)
+            u1 = F.conv2d(r1, blk.conv1.weight, None, padding=1)
+            if k == 0:
+                p, r = cnn_glue.bias_add(u1, blk.conv1.bias, p, True, True)
+            else:
+                got = cnn_glue.bias_add(u1, blk.conv1.bias, p, True, False)
+        assert_close(got, want, "stage output", rtol=1e-5, atol=1e-5)
+        gy = _rand(tuple(want.shape), cuda, 6)
+        grads_want = torch.autograd.grad(want, [xa] + list(stage.parameters()), gy)
+        grads_got = torch.autograd.grad(got, [xb] + list(stage.parameters()), gy)
+        for (n, _), a, b in zip([("x", None)] + list(stage.named_parameters()), grads_got, grads_want):
+            assert_close(a, b, n, rtol=1e-4, atol=1e-5 * max(1., b.abs().max().item()), rel_to_max=1e-4)   # sums of ~10^4 terms
+    finally:
+        torch.backends.cudnn.allow_tf32 = tf32
+
+
+def test_fused_model_matches_eager_model(cuda):
+    """ActorCritic(body='impala', fused_glue=True) == the eager channels_last model: same parameters, same outputs,
+    same gradients (fp32 convolutions so that the comparison is not limited by TF32)."""
+    tf32 = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = False
+    try:
+        torch.manual_seed(0)
+        eager = models.ActorCritic((3, 64, 64), 15, body="impala", channels_last=True).to(cuda).to(memory_format=CL)
+        fused = models.ActorCritic((3, 64, 64), 15, body="impala", channels_last=True, fused_glue=True).to(cuda).to(memory_format=CL)
+        fused.load_state_dict(copy.deepcopy(eager.state_dict()))
+        assert [n for n, _ in fused.named_parameters()] == [n for n, _ in eager.named_parameters()]
+        for p in eager.body.parameters():                           # biases are zero-initialised: make them matter
+            if p.dim() == 1:
+                torch.nn.init.normal_(p, std=0.1)
+        fused.load_state_dict(copy.deepcopy(eager.state_dict()))
+        obs = torch.randint(0, 256, (24, 3, 64, 64), device=cuda, dtype=torch.uint8)
+        outs = []
+        for m in (eager, fused):
+            pi, v = m(obs)
+            (pi.logsumexp(-1).mean() + (v - 1.).pow(2).mean() + 0.1 * pi.mean()).backward()
+            outs.append((pi.detach(), v.detach()))
+        assert_close(outs[1][0], outs[0][0], "logits", rtol=1e-4, atol=1e-5)
+        assert_close(outs[1][1], outs[0][1], "values", rtol=1e-4, atol=1e-5)
+        for (n, a), (_, b) in zip(fused.named_parameters(), eager.named_parameters()):
+            assert_close(a.grad, b.grad, n, rtol=1e-3, atol=1e-5 * max(1e-3, b.grad.abs().max().item()), rel_to_max=2e-4)
+    finally:
+        torch.backends.cudnn.allow_tf32 = tf32
