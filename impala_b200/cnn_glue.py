@@ -57,6 +57,35 @@ class BiasAct(torch.autograd.Function):
         return g, db, (g if has_res else None), None, None
 
 
+class Conv3x3(torch.autograd.Function):
+    """Bias-free ``conv2d(x, weight, padding=1)`` with a 3x3 kernel (``models/common.py:12-26,41-45``): forward and
+    input gradient in cuDNN, weight gradient in K10 (``csrc/conv3x3.cu``; cuDNN's wgrad kernels are ~9x off the HBM
+    roofline at these channel counts)."""
+
+    @staticmethod
+    def forward(ctx, x, weight):
+        ctx.save_for_backward(x, weight)
+        return torch.nn.functional.conv2d(x, weight, None, padding=1)
+
+    @staticmethod
+    def backward(ctx, gy):
+        x, weight = ctx.saved_tensors
+        gy = _cl(gy)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.ops.aten.convolution_backward(gy, x, weight, None, (1, 1), (1, 1), (1, 1), False, (0, 0), 1,
+                                                     (True, False, False))[0]
+        if ctx.needs_input_grad[1]:
+            dw = ops.conv3x3_wgrad(x, gy)
+        return dx, dw
+
+
+def conv3x3(x, weight):
+    if tuple(weight.shape[2:]) != (3, 3) or not ops.conv3x3_wgrad_supported(x.shape, weight.shape[0]):
+        return torch.nn.functional.conv2d(x, weight, None, padding=1)      # shapes outside K10: plain cuDNN autograd
+    return Conv3x3.apply(x, weight)
+
+
 def pool_bias(u, bias):
     return PoolBias.apply(u, bias)
 

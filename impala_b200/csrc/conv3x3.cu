@@ -1,0 +1,272 @@
+// K10: 3x3 / stride 1 / padding 1 convolution weight gradient for the IMPALA-CNN's small channel counts
+// (reference models/common.py:12-26,41-45: every convolution of ImpalaCNNLarge is 3x3, pad 1, with 3/16/32 input and
+// 16/32 output channels).  fp32 NHWC activations, TF32 tensor-core products with fp32 accumulation -- the arithmetic
+// torch's default (cudnn.allow_tf32 = True) already uses for these layers.
+//
+//   dW[co][kh][kw][ci] = sum over (n, h, w) of dy[n,h,w,co] * x[n, h+kh-1, w+kw-1, ci]
+//
+// is a GEMM with a tiny output (<= 32 x 288) and a reduction over millions of pixels: each pixel's Cin + Cout floats
+// feed Cout*9*Cin MACs, so the layer is HBM-bound once the products run on tensor cores (7.3 GB over the 15 layers
+// at B=256, T=20: ~1.1 ms; cuDNN's wgrad kernels take 10.1 ms).  Layout of the work:
+//   * one persistent CTA per SM walks tiles of 8 image rows (tile = blockIdx, += gridDim); the x rows with a one-pixel
+//     halo and the dy rows are staged in shared memory by cp.async in a 3-buffer ring: the copies of tiles k+1 and
+//     k+2 fly while tile k is multiplied, one __syncthreads per tile;
+//   * 24 (32 -> 32 channels: 12) warps = 3 kernel rows (kh) x 8 (4) pixel groups; a warp takes octets of 8 consecutive
+//     pixels of a row as the K dimension of mma.sync.m16n8k8 (A = dy^T: Cout x 8 pixels, B = shifted x: 8 pixels x
+//     Cin) for kw = 0..2, and keeps its 3 x (Cout/16) x (Cin/8) accumulator tiles in registers across ALL tiles of
+//     the CTA; the image width is a template parameter, so every fragment address is base + immediate (the first
+//     version spent 10 integer instructions per MMA on address arithmetic: ncu, 67 % issue-slot utilisation);
+//   * pixel strides in shared memory are = 8 (mod 32) floats, which makes every fragment load conflict-free;
+//   * at the end the pixel groups are added through shared memory in a fixed order and the CTA writes ONE partial
+//     dW; the caller adds the per-CTA partials in order (deterministic, no atomics).
+#include "common.cuh"
+
+namespace b200rl {
+
+constexpr int kWgTH = 8;            // image rows per tile
+// warps = 3 kernel rows x pixel groups; the 32 -> 32 layers keep 96 accumulator registers per thread, so 12 warps
+template <int CIN_P, int COUT>
+struct WgWarps { static constexpr int value = (CIN_P == 32 && COUT == 32) ? 12 : 24; };
+
+__device__ __forceinline__ void cp_async4(void *smem, const void *gmem, int src_bytes) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(smem_u32(smem)), "l"(gmem), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// TF32 operands are the fp32 bit patterns as they lie in memory: the tensor core reads the sign, the exponent and the
+// top 10 mantissa bits (truncation) -- what cuDNN's sm_100 TF32 kernels do as well (TMA -> shared memory -> MMA).
+__device__ __forceinline__ void mma_tf32_16x8x8(float (&d)[4], const float (&a)[4], float b0, float b1) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(__float_as_uint(a[0])), "r"(__float_as_uint(a[1])), "r"(__float_as_uint(a[2])), "r"(__float_as_uint(a[3])),
+          "r"(__float_as_uint(b0)), "r"(__float_as_uint(b1)));
+}
+
+template <int CIN_P>
+struct WgStride { static constexpr int value = CIN_P == 8 ? 8 : CIN_P + 8; };   // = 8 (mod 32)
+
+// Asynchronous staging of one tile: x rows h0-1 .. h0+TH (zero outside the image) and dy rows h0 .. h0+TH-1.
+// A thread owns one 16-byte (Cin = 3: 4-byte) column chunk of the row and walks the rows, so the per-copy cost is an
+// add and a bounds test; the chunk's offsets are computed once per kernel (RowPlan).  Rows whose chunk count does
+// not divide the CTA size take the generic (divide per copy) loop.
+struct RowPlan {
+    int soff, goff, r0, rstep;   // shared / global offset of the chunk inside a row (floats), first row, row step
+    bool fast, active;
+};
+
+template <int THREADS>
+__device__ __forceinline__ RowPlan make_plan(int per_row, int floats_per_chunk, int C, int smem_pixel_stride, int col0) {
+    RowPlan p;
+    p.fast = (THREADS % per_row) == 0;
+    const int c = threadIdx.x % per_row, e = c * floats_per_chunk, px = e / C;
+    p.soff = (px + col0) * smem_pixel_stride + (e - px * C);
+    p.goff = e;
+    p.r0 = threadIdx.x / per_row;
+    p.rstep = THREADS / per_row;
+    p.active = true;
+    return p;
+}
+
+template <int BYTES, int THREADS>
+__device__ __forceinline__ void stage_rows(float *s, int s_row_stride, const float *__restrict__ g, long long g_row_stride,
+                                           long long image_row0, int h_first, int rows, int H, const RowPlan &p,
+                                           int per_row, int C, int smem_pixel_stride, int col0) {
+    // image_row0 = n * H; row r of the tile is image row h_first + r
+    if (p.fast) {
+        for (int r = p.r0; r < rows; r += p.rstep) {
+            const int h = h_first + r;
+            const bool in = h >= 0 && h < H;
+            const float *src = g + (image_row0 + (in ? h : 0)) * g_row_stride + p.goff;
+            if (BYTES == 16) cp_async16(s + r * s_row_stride + p.soff, src, in ? 16 : 0);
+            else cp_async4(s + r * s_row_stride + p.soff, src, in ? 4 : 0);
+        }
+    } else {
+        constexpr int FPC = BYTES / 4;
+        for (int i = threadIdx.x; i < rows * per_row; i += THREADS) {
+            const int r = i / per_row, e = (i - r * per_row) * FPC, px = e / C, h = h_first + r;
+            const bool in = h >= 0 && h < H;
+            const float *src = g + (image_row0 + (in ? h : 0)) * g_row_stride + e;
+            float *dst = s + r * s_row_stride + (px + col0) * smem_pixel_stride + (e - px * C);
+            if (BYTES == 16) cp_async16(dst, src, in ? 16 : 0);
+            else cp_async4(dst, src, in ? 4 : 0);
+        }
+    }
+}
+
+constexpr int kWgStages = 3;
+
+template <int CIN_P, int COUT, int W>
+__global__ void __launch_bounds__(WgWarps<CIN_P, COUT>::value * 32, 1)
+conv3x3_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dy, float *__restrict__ partials, int N, int H,
+                     int Cin, int n_tiles) {
+    constexpr int XS = WgStride<CIN_P>::value, DS = COUT + 8;
+    constexpr int MT = COUT / 16, NT = CIN_P / 8, WARPS = WgWarps<CIN_P, COUT>::value, THREADS = WARPS * 32, PG = WARPS / 3;
+    constexpr int XBYTES = CIN_P == 8 ? 4 : 16;             // Cin = 3: 12-byte pixels, 4-byte copies
+    constexpr int XW = W + 2;                               // tile columns incl. the halo
+    constexpr int x_floats = (kWgTH + 2) * XW * XS, tile_floats = x_floats + kWgTH * W * DS;
+    constexpr int OCTS_PER_ROW = W / 8, N_OCTS = kWgTH * OCTS_PER_ROW;
+    static_assert(N_OCTS % PG == 0, "pixel groups must divide the octets of a tile");
+    extern __shared__ __align__(16) float smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, gid = lane >> 2, tig = lane & 3;
+    const int kh = warp % 3, pg = warp / 3;
+    const int tiles_per_image = (H + kWgTH - 1) / kWgTH;
+    const int x_per_row = W * Cin / (XBYTES / 4);
+    constexpr int dy_per_row = W * COUT / 4;
+    const RowPlan xplan = make_plan<THREADS>(x_per_row, XBYTES / 4, Cin, XS, 1);
+    const RowPlan dplan = make_plan<THREADS>(dy_per_row, 4, COUT, DS, 0);
+
+    float acc[3][MT][NT][4];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int b = 0; b < MT; ++b)
+#pragma unroll
+            for (int c = 0; c < NT; ++c)
+#pragma unroll
+                for (int d = 0; d < 4; ++d) acc[a][b][c][d] = 0.f;
+
+    // zero once, in every buffer, what the tile copies never touch: halo columns, padded input channels
+    for (int i = tid; i < kWgStages * tile_floats; i += THREADS) smem[i] = 0.f;
+    __syncthreads();
+
+    auto stage = [&](int t, int b) {
+        if (t < n_tiles) {
+            float *xs = smem + b * tile_floats;
+            const int n = t / tiles_per_image, h0 = (t - n * tiles_per_image) * kWgTH;
+            stage_rows<XBYTES, THREADS>(xs, XW * XS, x, (long long)W * Cin, (long long)n * H, h0 - 1, kWgTH + 2, H, xplan,
+                                        x_per_row, Cin, XS, 1);
+            stage_rows<16, THREADS>(xs + x_floats, W * DS, dy, (long long)W * COUT, (long long)n * H, h0, kWgTH, H, dplan,
+                                    dy_per_row, COUT, DS, 0);
+        }
+        cp_async_commit();                                  // one group per round, empty past the last tile
+    };
+
+    // per-warp fragment bases inside a tile (all remaining offsets are compile-time constants)
+    const int a_base = x_floats + tig * DS + gid;           // dy: pixel tig, channel gid
+    const int b_base = (kh * XW + tig) * XS + gid;          // x: tile row kh, column tig (= w - 1 + kw at kw = 0)
+
+    int tile = blockIdx.x, buf = 0;
+    stage(tile, 0);
+    stage(tile + gridDim.x, 1);
+    for (; tile < n_tiles; tile += gridDim.x, buf = (buf + 1 == kWgStages ? 0 : buf + 1)) {
+        cp_async_wait_group<kWgStages - 2>();               // everything but the newest group: this tile has landed
+        __syncthreads();                                    // ... for every thread; and the buffer consumed in the
+        stage(tile + 2 * gridDim.x, buf == 0 ? kWgStages - 1 : buf - 1);   // previous round is free to refill
+        const float *tb = smem + buf * tile_floats;
+        // ---- products: this warp's kernel row, its share of the pixel octets, all output channels ----
+#pragma unroll
+        for (int k = 0; k < N_OCTS / PG; ++k) {
+            const int oct = pg + k * PG, row = oct / OCTS_PER_ROW, w0 = (oct % OCTS_PER_ROW) * 8;
+            const float *dp = tb + a_base + (row * W + w0) * DS;
+            float a[MT][4];
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) {
+                a[mt][0] = dp[mt * 16];
+                a[mt][1] = dp[mt * 16 + 8];
+                a[mt][2] = dp[4 * DS + mt * 16];
+                a[mt][3] = dp[4 * DS + mt * 16 + 8];
+            }
+            const float *xp = tb + b_base + (row * XW + w0) * XS;
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    const float b0 = xp[kw * XS + nt * 8], b1 = xp[(kw + 4) * XS + nt * 8];
+#pragma unroll
+                    for (int mt = 0; mt < MT; ++mt) mma_tf32_16x8x8(acc[kw][mt][nt], a[mt], b0, b1);
+                }
+            }
+        }
+    }
+    cp_async_wait_group<0>();
+    __syncthreads();
+
+    // ---- add the pixel groups in order through shared memory: out[co][kh][kw][ci] (ci < CIN_P) ----
+    float *out = smem;
+    for (int g = 0; g < PG; ++g) {
+        if (pg == g) {
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw)
+#pragma unroll
+                for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                        for (int d = 0; d < 4; ++d) {
+                            const int co = mt * 16 + gid + ((d & 2) ? 8 : 0), ci = nt * 8 + 2 * tig + (d & 1);
+                            float *o = out + ((co * 3 + kh) * 3 + kw) * CIN_P + ci;
+                            *o = (g == 0 ? 0.f : *o) + acc[kw][mt][nt][d];
+                        }
+        }
+        __syncthreads();
+    }
+    float *dst = partials + (long long)blockIdx.x * COUT * 9 * Cin;
+    for (int i = tid; i < COUT * 9 * Cin; i += THREADS) {
+        const int ci = i % Cin, rest = i / Cin;
+        dst[i] = out[rest * CIN_P + ci];
+    }
+}
+
+template <int CIN_P, int COUT, int W>
+static int32_t launch_wgrad(const float *x, const float *dy, float *partials, int N, int H, int Cin, int n_ctas,
+                            cudaStream_t stream) {
+    constexpr int XS = WgStride<CIN_P>::value, DS = COUT + 8;
+    constexpr int tile_floats = (kWgTH + 2) * (W + 2) * XS + kWgTH * W * DS, out_floats = COUT * 9 * CIN_P;
+    constexpr int smem = 4 * (kWgStages * tile_floats > out_floats ? kWgStages * tile_floats : out_floats);
+    if (smem > 227 * 1024) {
+        set_error("conv3x3_wgrad: Cin=%d Cout=%d W=%d needs %d bytes of shared memory", Cin, COUT, W, smem);
+        return -2;
+    }
+    static int configured[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 64 && !configured[dev]) {
+        if (cudaFuncSetAttribute(conv3x3_wgrad_kernel<CIN_P, COUT, W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 smem <= 227 * 1024 ? smem : 0) != cudaSuccess)
+            return check_launch("conv3x3_wgrad: shared-memory opt-in");
+        configured[dev] = 1;
+    }
+    const int n_tiles = N * ((H + kWgTH - 1) / kWgTH);
+    conv3x3_wgrad_kernel<CIN_P, COUT, W><<<n_ctas, WgWarps<CIN_P, COUT>::value * 32, smem, stream>>>(x, dy, partials, N, H,
+                                                                                                  Cin, n_tiles);
+    return check_launch("conv3x3_wgrad_kernel");
+}
+
+template <int CIN_P, int COUT>
+static int32_t launch_wgrad_w(const float *x, const float *dy, float *partials, int N, int H, int W, int Cin, int n_ctas,
+                              cudaStream_t stream) {
+    switch (W) {
+        case 8: return launch_wgrad<CIN_P, COUT, 8>(x, dy, partials, N, H, Cin, n_ctas, stream);
+        case 16: return launch_wgrad<CIN_P, COUT, 16>(x, dy, partials, N, H, Cin, n_ctas, stream);
+        case 32: return launch_wgrad<CIN_P, COUT, 32>(x, dy, partials, N, H, Cin, n_ctas, stream);
+        case 64: return launch_wgrad<CIN_P, COUT, 64>(x, dy, partials, N, H, Cin, n_ctas, stream);
+    }
+    set_error("conv3x3_wgrad: W=%d (supported: 8, 16, 32, 64)", W);
+    return -2;
+}
+
+}  // namespace b200rl
+
+extern "C" int32_t b200rl_conv3x3_wgrad(const float *x, const float *dy, float *partials, int64_t N, int64_t H, int64_t W,
+                                         int64_t Cin, int64_t Cout, int64_t n_ctas, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(x && dy && partials, -1, "conv3x3_wgrad: null pointer argument");
+    B200RL_REQUIRE(N >= 1 && H >= 1 && N * H < (1ll << 30), -2, "conv3x3_wgrad: N=%lld H=%lld", (long long)N, (long long)H);
+    B200RL_REQUIRE(W == 8 || W == 16 || W == 32 || W == 64, -2, "conv3x3_wgrad: W=%lld (supported: 8, 16, 32, 64)", (long long)W);
+    B200RL_REQUIRE((Cin == 3 || Cin == 16 || Cin == 32) && (Cout == 16 || Cout == 32), -2,
+                   "conv3x3_wgrad: Cin=%lld Cout=%lld (supported: Cin 3/16/32, Cout 16/32)", (long long)Cin, (long long)Cout);
+    B200RL_REQUIRE(n_ctas >= 1 && n_ctas <= 65535, -2, "conv3x3_wgrad: n_ctas=%lld", (long long)n_ctas);
+    B200RL_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15u) == 0 && (reinterpret_cast<uintptr_t>(dy) & 15u) == 0, -3,
+                   "conv3x3_wgrad: tensors must be 16-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int n = (int)N, h = (int)H, w = (int)W, ci = (int)Cin, g = (int)n_ctas;
+    if (Cin == 3 && Cout == 16) return launch_wgrad_w<8, 16>(x, dy, partials, n, h, w, ci, g, s);
+    if (Cin == 3 && Cout == 32) return launch_wgrad_w<8, 32>(x, dy, partials, n, h, w, ci, g, s);
+    if (Cin == 16 && Cout == 16) return launch_wgrad_w<16, 16>(x, dy, partials, n, h, w, ci, g, s);
+    if (Cin == 16 && Cout == 32) return launch_wgrad_w<16, 32>(x, dy, partials, n, h, w, ci, g, s);
+    if (Cin == 32 && Cout == 16) return launch_wgrad_w<32, 16>(x, dy, partials, n, h, w, ci, g, s);
+    return launch_wgrad_w<32, 32>(x, dy, partials, n, h, w, ci, g, s);
+}

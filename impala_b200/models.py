@@ -75,11 +75,11 @@ class ImpalaCNN(nn.Module):
         from . import cnn_glue as G
         stages = [m for m in self.body if isinstance(m, _ImpalaStage)]
         for si, st in enumerate(stages):
-            u = F.conv2d(x, st.conv.weight, None, padding=1)
+            u = G.conv3x3(x, st.conv.weight)
             p, r = G.pool_bias(u, st.conv.bias)                            # max_pool(conv + b), relu of it
             for bi, blk in enumerate((st.res_block0, st.res_block1)):
-                r1 = G.bias_relu(F.conv2d(r, blk.conv0.weight, None, padding=1), blk.conv0.bias)
-                u1 = F.conv2d(r1, blk.conv1.weight, None, padding=1)
+                r1 = G.bias_relu(G.conv3x3(r, blk.conv0.weight), blk.conv0.bias)
+                u1 = G.conv3x3(r1, blk.conv1.weight)
                 if bi == 0:                                                # block output + the next block's opening ReLU
                     p, r = G.bias_add(u1, blk.conv1.bias, p, want_y=True, want_r=True)
                 elif si + 1 < len(stages):                                 # feeds the next stage's convolution

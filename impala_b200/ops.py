@@ -530,3 +530,29 @@ def relu_bwd_add(dy, dr, r):
     _cabi.call("b200rl_relu_bwd_add", _cabi.ptr(dy), _cabi.ptr(dr), _cabi.ptr(r if dr is not None else None),
                _cabi.ptr(g), partials.data_ptr(), N * H * W, C, n_ctas, _stream())
     return (g if g is not None else dy), partials.sum(0)
+
+
+# ---- K10: 3x3 convolution weight gradient (TF32 tensor cores, fp32 accumulation) -----------------------------------
+WGRAD_MAX_CTAS = 148              # one persistent CTA (24 warps, double-buffered tiles) per SM
+
+
+def conv3x3_wgrad_supported(x_shape, cout):
+    """Shapes ``b200rl_conv3x3_wgrad`` takes (the IMPALA-CNN's): 3x3/s1/p1, Cin 3/16/32, Cout 16/32, W in 8/16/32/64."""
+    return len(x_shape) == 4 and x_shape[1] in (3, 16, 32) and cout in (16, 32) and x_shape[3] in (8, 16, 32, 64)
+
+
+def conv3x3_wgrad(x, dy):
+    """``d loss / d weight`` of ``conv2d(x, weight, padding=1)`` with a 3x3 kernel: ``x [N,Cin,H,W]``, ``dy [N,Cout,H,W]``
+    (float32 channels_last) -> ``[Cout,Cin,3,3]`` in channels_last strides (physical ``[Cout,3,3,Cin]``)."""
+    _require_cuda(x, dy)
+    _nhwc(x, "conv3x3_wgrad x")
+    _nhwc(dy, "conv3x3_wgrad dy")
+    if not conv3x3_wgrad_supported(x.shape, dy.shape[1]) or x.shape[0] != dy.shape[0] or x.shape[2:] != dy.shape[2:]:
+        raise RuntimeError("conv3x3_wgrad: unsupported shapes x %s dy %s" % (tuple(x.shape), tuple(dy.shape)))
+    N, Cin, H, W = x.shape
+    Cout = dy.shape[1]
+    n_ctas = max(1, min(WGRAD_MAX_CTAS, N * ((H + 7) // 8)))
+    partials = torch.empty((n_ctas, Cout, 3, 3, Cin), dtype=torch.float32, device=x.device)
+    _cabi.call("b200rl_conv3x3_wgrad", x.data_ptr(), dy.data_ptr(), partials.data_ptr(), N, H, W, Cin, Cout, n_ctas,
+               _stream())
+    return partials.sum(0).permute(0, 3, 1, 2)

@@ -300,6 +300,15 @@ int32_t b200rl_relu_bwd_add(
     const float *dy, const float *dr, const float *r, float *g, float *partials, int64_t n_pix, int64_t C,
     int64_t n_ctas, void *stream);
 
+/* K10 -- weight gradient of a 3x3 / stride 1 / padding 1 convolution (every convolution of the reference's
+ * ImpalaCNNLarge, models/common.py:12-26,41-45) for fp32 NHWC activations: x [N,H,W,Cin], dy [N,H,W,Cout];
+ * TF32 tensor-core products, fp32 accumulation (torch's default arithmetic for these layers).  Each of the n_ctas
+ * CTAs writes its partial dW as partials[cta][Cout][3][3][Cin]; the caller adds the rows in order.
+ * Supported: Cin in {3,16,32}, Cout in {16,32}, W in {8,16,32,64} (the tile must fit 3x in 227 KB of shared memory). */
+int32_t b200rl_conv3x3_wgrad(
+    const float *x, const float *dy, float *partials, int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout,
+    int64_t n_ctas, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -9,7 +9,8 @@ from impala_b200 import models
 dev = torch.device("cuda", 0)
 cl = os.environ.get("CL", "1") == "1"
 torch.manual_seed(0)
-model = models.ActorCritic((3, 64, 64), 15, body="impala", channels_last=cl).to(dev)
+fused = cl and os.environ.get("FUSED", "1") == "1"
+model = models.ActorCritic((3, 64, 64), 15, body="impala", channels_last=cl, fused_glue=fused).to(dev)
 if cl:
     model = model.to(memory_format=torch.channels_last)
 obs = torch.randint(0, 256, (5120, 3, 64, 64), device=dev, dtype=torch.uint8)
