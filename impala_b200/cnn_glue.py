@@ -58,13 +58,15 @@ class BiasAct(torch.autograd.Function):
 
 
 class Conv3x3(torch.autograd.Function):
-    """Bias-free ``conv2d(x, weight, padding=1)`` with a 3x3 kernel (``models/common.py:12-26,41-45``): forward and
-    input gradient in cuDNN, weight gradient in K10 (``csrc/conv3x3.cu``; cuDNN's wgrad kernels are ~9x off the HBM
-    roofline at these channel counts)."""
+    """Bias-free ``conv2d(x, weight, padding=1)`` with a 3x3 kernel (``models/common.py:12-26,41-45``): forward and input
+    gradient in K11 (32 -> 32 channels: cuDNN, see ``_k11_wins``), weight gradient in K10 (``csrc/conv3x3.cu``) -- TF32 products with fp32 accumulation, torch's
+    default arithmetic for these layers.  cuDNN's kernels for 3/16/32 channels are 3-10x off the HBM roofline."""
 
     @staticmethod
     def forward(ctx, x, weight):
         ctx.save_for_backward(x, weight)
+        if _k11_wins(weight):
+            return ops.conv3x3_fwd(x, weight)
         return torch.nn.functional.conv2d(x, weight, None, padding=1)
 
     @staticmethod
@@ -73,16 +75,26 @@ class Conv3x3(torch.autograd.Function):
         gy = _cl(gy)
         dx = dw = None
         if ctx.needs_input_grad[0]:
-            dx = torch.ops.aten.convolution_backward(gy, x, weight, None, (1, 1), (1, 1), (1, 1), False, (0, 0), 1,
-                                                     (True, False, False))[0]
+            if _k11_wins(weight):
+                dx = ops.conv3x3_dgrad(gy, weight)
+            else:
+                dx = torch.ops.aten.convolution_backward(gy, x, weight, None, (1, 1), (1, 1), (1, 1), False, (0, 0), 1,
+                                                         (True, False, False))[0]
         if ctx.needs_input_grad[1]:
             dw = ops.conv3x3_wgrad(x, gy)
         return dx, dw
 
 
+def _k11_wins(weight):
+    """Measured at 5,120 frames (``scripts/bench_conv.py``): K11 beats cuDNN 1.8-4.9x wherever a channel count is below
+    32 (cuDNN falls back to sm80 kernels there); for 32 -> 32 cuDNN's tcgen05 kernels are 1.5x faster than K11's
+    mma.sync path, so those layers keep cuDNN for the forward and the input gradient."""
+    return not (weight.shape[0] == 32 and weight.shape[1] == 32)
+
+
 def conv3x3(x, weight):
     if tuple(weight.shape[2:]) != (3, 3) or not ops.conv3x3_wgrad_supported(x.shape, weight.shape[0]):
-        return torch.nn.functional.conv2d(x, weight, None, padding=1)      # shapes outside K10: plain cuDNN autograd
+        return torch.nn.functional.conv2d(x, weight, None, padding=1)      # shapes outside K10/K11: plain cuDNN autograd
     return Conv3x3.apply(x, weight)
 
 

@@ -96,7 +96,12 @@ __device__ __forceinline__ void stage_rows(float *s, int s_row_stride, const flo
     }
 }
 
-constexpr int kWgStages = 3;
+// ring depth: 3 buffers where they fit in 227 KB, else 2
+template <int CIN_P, int COUT, int W>
+struct WgStages {
+    static constexpr int tile_bytes = 4 * ((kWgTH + 2) * (W + 2) * WgStride<CIN_P>::value + kWgTH * W * (COUT + 8));
+    static constexpr int value = 3 * tile_bytes <= 227 * 1024 ? 3 : 2;
+};
 
 template <int CIN_P, int COUT, int W>
 __global__ void __launch_bounds__(WgWarps<CIN_P, COUT>::value * 32, 1)
@@ -107,7 +112,7 @@ conv3x3_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dy, 
     constexpr int XBYTES = CIN_P == 8 ? 4 : 16;             // Cin = 3: 12-byte pixels, 4-byte copies
     constexpr int XW = W + 2;                               // tile columns incl. the halo
     constexpr int x_floats = (kWgTH + 2) * XW * XS, tile_floats = x_floats + kWgTH * W * DS;
-    constexpr int OCTS_PER_ROW = W / 8, N_OCTS = kWgTH * OCTS_PER_ROW;
+    constexpr int OCTS_PER_ROW = W / 8, N_OCTS = kWgTH * OCTS_PER_ROW, kWgStages = WgStages<CIN_P, COUT, W>::value;
     static_assert(N_OCTS % PG == 0, "pixel groups must divide the octets of a tile");
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, gid = lane >> 2, tig = lane & 3;
@@ -149,12 +154,12 @@ conv3x3_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dy, 
     const int b_base = (kh * XW + tig) * XS + gid;          // x: tile row kh, column tig (= w - 1 + kw at kw = 0)
 
     int tile = blockIdx.x, buf = 0;
-    stage(tile, 0);
-    stage(tile + gridDim.x, 1);
+#pragma unroll
+    for (int k = 0; k < kWgStages - 1; ++k) stage(tile + k * gridDim.x, k);
     for (; tile < n_tiles; tile += gridDim.x, buf = (buf + 1 == kWgStages ? 0 : buf + 1)) {
-        cp_async_wait_group<kWgStages - 2>();               // everything but the newest group: this tile has landed
+        cp_async_wait_group<kWgStages - 2>();               // everything but the newest group(s): this tile has landed
         __syncthreads();                                    // ... for every thread; and the buffer consumed in the
-        stage(tile + 2 * gridDim.x, buf == 0 ? kWgStages - 1 : buf - 1);   // previous round is free to refill
+        stage(tile + (kWgStages - 1) * gridDim.x, buf == 0 ? kWgStages - 1 : buf - 1);   // previous round is free to refill
         const float *tb = smem + buf * tile_floats;
         // ---- products: this warp's kernel row, its share of the pixel octets, all output channels ----
 #pragma unroll
@@ -215,6 +220,7 @@ static int32_t launch_wgrad(const float *x, const float *dy, float *partials, in
                             cudaStream_t stream) {
     constexpr int XS = WgStride<CIN_P>::value, DS = COUT + 8;
     constexpr int tile_floats = (kWgTH + 2) * (W + 2) * XS + kWgTH * W * DS, out_floats = COUT * 9 * CIN_P;
+    constexpr int kWgStages = WgStages<CIN_P, COUT, W>::value;
     constexpr int smem = 4 * (kWgStages * tile_floats > out_floats ? kWgStages * tile_floats : out_floats);
     if (smem > 227 * 1024) {
         set_error("conv3x3_wgrad: Cin=%d Cout=%d W=%d needs %d bytes of shared memory", Cin, COUT, W, smem);
@@ -269,4 +275,202 @@ extern "C" int32_t b200rl_conv3x3_wgrad(const float *x, const float *dy, float *
     if (Cin == 16 && Cout == 32) return launch_wgrad_w<16, 32>(x, dy, partials, n, h, w, ci, g, s);
     if (Cin == 32 && Cout == 16) return launch_wgrad_w<32, 16>(x, dy, partials, n, h, w, ci, g, s);
     return launch_wgrad_w<32, 32>(x, dy, partials, n, h, w, ci, g, s);
+}
+
+// =====================================================================================================================
+// K11: the 3x3 / stride 1 / padding 1 convolution itself (forward, and -- with the weights read transposed and
+// flipped -- the input gradient), bias-free, fp32 NHWC, TF32 tensor-core products with fp32 accumulation:
+//
+//   y[n,h,w,o] = sum over (kh, kw, i) of x[n, h+kh-1, w+kw-1, i] * w[o][kh][kw][i]                      (forward)
+//   dx[n,h,w,i] = sum over (kh, kw, o) of dy[n, h-kh+1, w-kw+1, o] * w[o][kh][kw][i]                     (dgrad)
+//     = the forward form with in/out channels swapped and weight w'[i][kh'][kw'][o] = w[o][2-kh'][2-kw'][i].
+//
+// Implicit GEMM with M = pixels, N = output channels, K = 9 x input channels.  A CTA walks tiles of 8 image rows
+// (persistent; the x tile with its one-pixel halo arrives by cp.async, double-buffered); the whole weight tensor sits
+// in shared memory for the CTA's lifetime; a warp owns W/16 (W = 8: one) m-tiles of 16 pixels and all output
+// channels: per tap and 8 input channels it loads its A fragments (x, pixel stride = 4 mod 8 floats: conflict-free)
+// and the B fragments (weights, row stride = 8 mod 32) and issues MT x Cout/8 MMAs.  Results go straight from the
+// accumulator registers to global memory (8-byte stores, 32 contiguous bytes per pixel and n-tile).
+// cuDNN picks sm80 "indexed_wo_smem" kernels for the 16-channel layers (1.06 ms per layer at 5,120 frames, 22 TFLOP/s).
+namespace b200rl {
+
+constexpr int kFwTH = 8;
+template <int W> struct FwWarps { static constexpr int value = W >= 16 ? 8 : 4; };
+
+template <int CIN_P, int COUT, int W, bool DGRAD>
+__global__ void __launch_bounds__(FwWarps<W>::value * 32)
+conv3x3_fwd_kernel(const float *__restrict__ x, const float *__restrict__ wgt, float *__restrict__ y, int N, int H, int Cin,
+                   int n_tiles) {
+    constexpr int XS = CIN_P + 4;                          // pixel stride of the x tile: = 4 (mod 8)
+    constexpr int WS = COUT + 8;                           // row stride of the weights [tap][cin][cout]: = 8 (mod 32)
+    constexpr int WARPS = FwWarps<W>::value, THREADS = WARPS * 32;
+    constexpr int XW = W + 2, x_floats = (kFwTH + 2) * XW * XS, w_floats = 9 * CIN_P * WS;
+    constexpr int M_TILES = kFwTH * W / 16, MT = M_TILES / WARPS, NT = COUT / 8, KC = CIN_P / 8;
+    constexpr int XBYTES = CIN_P == 8 ? 4 : 16;
+    static_assert(M_TILES % WARPS == 0, "m-tiles must divide among the warps");
+    extern __shared__ __align__(16) float smem[];
+    float *ws = smem, *xbuf = smem + w_floats;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, gid = lane >> 2, tig = lane & 3;
+    const int tiles_per_image = (H + kFwTH - 1) / kFwTH;
+    const int x_per_row = W * Cin / (XBYTES / 4);
+    const RowPlan xplan = make_plan<THREADS>(x_per_row, XBYTES / 4, Cin, XS, 1);
+
+    // weights -> shared memory [tap][cin][cout] (zero rows for padded input channels); global layout [O][3][3][I]
+    for (int i = tid; i < w_floats; i += THREADS) {
+        const int o = i % WS, rest = i / WS, c = rest % CIN_P, tap = rest / CIN_P;
+        float v = 0.f;
+        if (o < COUT && c < Cin)
+            v = DGRAD ? __ldg(wgt + ((long long)c * 9 + (8 - tap)) * COUT + o)       // w[o'=c][2-kh][2-kw][i'=o]
+                      : __ldg(wgt + ((long long)o * 9 + tap) * Cin + c);
+        ws[i] = v;
+    }
+    for (int i = tid; i < 2 * x_floats; i += THREADS) xbuf[i] = 0.f;    // halo columns, padded channels: zero for good
+    __syncthreads();
+
+    auto stage = [&](int t, int b) {
+        if (t < n_tiles) {
+            const int n = t / tiles_per_image, h0 = (t - n * tiles_per_image) * kFwTH;
+            stage_rows<XBYTES, THREADS>(xbuf + b * x_floats, XW * XS, x, (long long)W * Cin, (long long)n * H, h0 - 1, kFwTH + 2,
+                                        H, xplan, x_per_row, Cin, XS, 1);
+        }
+        cp_async_commit();
+    };
+
+    // m-tile m of the tile: 16 consecutive pixels of a row (W >= 16) or 2 rows of 8 (W = 8); rows 0-7 of the fragment
+    // are pixels +0..7, rows 8-15 are `up8` floats further
+    constexpr int up8 = (W >= 16 ? 8 : XW) * XS;
+    int tile = blockIdx.x, buf = 0;
+    stage(tile, 0);
+    for (; tile < n_tiles; tile += gridDim.x, buf ^= 1) {
+        stage(tile + gridDim.x, buf ^ 1);
+        cp_async_wait_group<1>();
+        __syncthreads();
+        const float *xs = xbuf + buf * x_floats;
+        float acc[MT][NT][4];
+#pragma unroll
+        for (int a = 0; a < MT; ++a)
+#pragma unroll
+            for (int b = 0; b < NT; ++b)
+#pragma unroll
+                for (int d = 0; d < 4; ++d) acc[a][b][d] = 0.f;
+        int prow[MT], pcol[MT];
+#pragma unroll
+        for (int m = 0; m < MT; ++m) {
+            const int mt = warp * MT + m;
+            prow[m] = W >= 16 ? mt / (W / 16) : mt * 2;
+            pcol[m] = W >= 16 ? (mt % (W / 16)) * 16 : 0;
+        }
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+            const int kh = tap / 3, kw = tap % 3;
+#pragma unroll
+            for (int kc = 0; kc < KC; ++kc) {
+                float bf[NT][2];
+                const float *wp = ws + ((tap * CIN_P + kc * 8 + tig) * WS) + gid;
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    bf[nt][0] = wp[nt * 8];
+                    bf[nt][1] = wp[4 * WS + nt * 8];
+                }
+#pragma unroll
+                for (int m = 0; m < MT; ++m) {
+                    const float *ap = xs + ((prow[m] + kh) * XW + pcol[m] + kw + gid) * XS + kc * 8 + tig;
+                    float a[4];
+                    a[0] = ap[0];
+                    a[1] = ap[up8];
+                    a[2] = ap[4];
+                    a[3] = ap[up8 + 4];
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt) mma_tf32_16x8x8(acc[m][nt], a, bf[nt][0], bf[nt][1]);
+                }
+            }
+        }
+        // ---- accumulators -> y (rows of the image that exist) ----
+        const int n = tile / tiles_per_image, h0 = (tile - n * tiles_per_image) * kFwTH;
+#pragma unroll
+        for (int m = 0; m < MT; ++m) {
+#pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                const int r = prow[m] + (W >= 16 ? 0 : half), c = pcol[m] + gid + (W >= 16 ? 8 * half : 0), h = h0 + r;
+                if (h < H) {
+                    float *yp = y + (((long long)n * H + h) * W + c) * COUT + 2 * tig;
+#pragma unroll
+                    for (int nt = 0; nt < NT; ++nt)
+                        __stcs(reinterpret_cast<float2 *>(yp + nt * 8), make_float2(acc[m][nt][2 * half], acc[m][nt][2 * half + 1]));
+                }
+            }
+        }
+        __syncthreads();                                    // the buffer is refilled by the next round's copies
+    }
+    cp_async_wait_group<0>();
+}
+
+template <int CIN_P, int COUT, int W, bool DGRAD>
+static int32_t launch_fwd(const float *x, const float *wgt, float *y, int N, int H, int Cin, cudaStream_t stream) {
+    constexpr int XS = CIN_P + 4, WS = COUT + 8;
+    constexpr int smem = 4 * (9 * CIN_P * WS + 2 * (kFwTH + 2) * (W + 2) * XS);
+    if (smem > 227 * 1024) {
+        set_error("conv3x3_fwd: Cin=%d Cout=%d W=%d needs %d bytes of shared memory", Cin, COUT, W, smem);
+        return -2;
+    }
+    static int ctas_per_sm[64] = {};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 64) dev = 63;
+    auto kern = conv3x3_fwd_kernel<CIN_P, COUT, W, DGRAD>;
+    if (!ctas_per_sm[dev]) {
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem <= 227 * 1024 ? smem : 0) != cudaSuccess)
+            return check_launch("conv3x3_fwd: shared-memory opt-in");
+        int nb = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, FwWarps<W>::value * 32, smem) != cudaSuccess || nb < 1)
+            return check_launch("conv3x3_fwd: occupancy query");
+        ctas_per_sm[dev] = nb;
+    }
+    int sms = 148;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const int n_tiles = N * ((H + kFwTH - 1) / kFwTH);
+    int grid = sms * ctas_per_sm[dev];
+    if (grid > n_tiles) grid = n_tiles;
+    kern<<<grid, FwWarps<W>::value * 32, smem, stream>>>(x, wgt, y, N, H, Cin, n_tiles);
+    return check_launch("conv3x3_fwd_kernel");
+}
+
+template <int CIN_P, int COUT, bool DGRAD>
+static int32_t launch_fwd_w(const float *x, const float *wgt, float *y, int N, int H, int W, int Cin, cudaStream_t stream) {
+    switch (W) {
+        case 8: return launch_fwd<CIN_P, COUT, 8, DGRAD>(x, wgt, y, N, H, Cin, stream);
+        case 16: return launch_fwd<CIN_P, COUT, 16, DGRAD>(x, wgt, y, N, H, Cin, stream);
+        case 32: return launch_fwd<CIN_P, COUT, 32, DGRAD>(x, wgt, y, N, H, Cin, stream);
+        case 64: return launch_fwd<CIN_P, COUT, 64, DGRAD>(x, wgt, y, N, H, Cin, stream);
+    }
+    set_error("conv3x3_fwd: W=%d (supported: 8, 16, 32, 64)", W);
+    return -2;
+}
+
+template <bool DGRAD>
+static int32_t dispatch_fwd(const float *x, const float *wgt, float *y, int N, int H, int W, int Cin, int Cout, cudaStream_t s) {
+    if (Cin == 3 && Cout == 16) return launch_fwd_w<8, 16, DGRAD>(x, wgt, y, N, H, W, Cin, s);
+    if (Cin == 3 && Cout == 32) return launch_fwd_w<8, 32, DGRAD>(x, wgt, y, N, H, W, Cin, s);
+    if (Cin == 16 && Cout == 16) return launch_fwd_w<16, 16, DGRAD>(x, wgt, y, N, H, W, Cin, s);
+    if (Cin == 16 && Cout == 32) return launch_fwd_w<16, 32, DGRAD>(x, wgt, y, N, H, W, Cin, s);
+    if (Cin == 32 && Cout == 16) return launch_fwd_w<32, 16, DGRAD>(x, wgt, y, N, H, W, Cin, s);
+    return launch_fwd_w<32, 32, DGRAD>(x, wgt, y, N, H, W, Cin, s);
+}
+
+}  // namespace b200rl
+
+extern "C" int32_t b200rl_conv3x3_fwd(const float *x, const float *weight, float *y, int64_t N, int64_t H, int64_t W,
+                                       int64_t Cin, int64_t Cout, int32_t dgrad, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(x && weight && y, -1, "conv3x3_fwd: null pointer argument");
+    B200RL_REQUIRE(N >= 1 && H >= 1 && N * H < (1ll << 30), -2, "conv3x3_fwd: N=%lld H=%lld", (long long)N, (long long)H);
+    B200RL_REQUIRE(W == 8 || W == 16 || W == 32 || W == 64, -2, "conv3x3_fwd: W=%lld (supported: 8, 16, 32, 64)", (long long)W);
+    B200RL_REQUIRE((Cin == 3 || Cin == 16 || Cin == 32) && (Cout == 16 || Cout == 32), -2,
+                   "conv3x3_fwd: Cin=%lld Cout=%lld (supported: in 3/16/32, out 16/32)", (long long)Cin, (long long)Cout);
+    B200RL_REQUIRE(!(dgrad && Cin == 3), -2, "conv3x3_fwd: dgrad needs 16 or 32 input channels");
+    B200RL_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15u) == 0 && (reinterpret_cast<uintptr_t>(y) & 15u) == 0, -3,
+                   "conv3x3_fwd: tensors must be 16-byte aligned");
+    cudaStream_t s = (cudaStream_t)stream;
+    return dgrad ? dispatch_fwd<true>(x, weight, y, (int)N, (int)H, (int)W, (int)Cin, (int)Cout, s)
+                 : dispatch_fwd<false>(x, weight, y, (int)N, (int)H, (int)W, (int)Cin, (int)Cout, s);
 }

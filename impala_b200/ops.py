@@ -556,3 +556,38 @@ def conv3x3_wgrad(x, dy):
     _cabi.call("b200rl_conv3x3_wgrad", x.data_ptr(), dy.data_ptr(), partials.data_ptr(), N, H, W, Cin, Cout, n_ctas,
                _stream())
     return partials.sum(0).permute(0, 3, 1, 2)
+
+
+# ---- K11: the 3x3 convolution itself, forward and input gradient ----------------------------------------------------
+def _w_cl(weight):
+    if weight.dim() != 4 or tuple(weight.shape[2:]) != (3, 3) or weight.dtype != torch.float32:
+        raise RuntimeError("conv3x3: expected a float32 [O,I,3,3] weight, got %s %s" % (tuple(weight.shape), weight.dtype))
+    return weight.detach().contiguous(memory_format=torch.channels_last)        # physical [O][3][3][I]
+
+
+def conv3x3_fwd(x, weight):
+    """``conv2d(x, weight, None, padding=1)`` for a 3x3 kernel: float32 channels_last in and out."""
+    _require_cuda(x, weight)
+    _nhwc(x, "conv3x3_fwd x")
+    w = _w_cl(weight)
+    N, Cin, H, W = x.shape
+    Cout = w.shape[0]
+    if w.shape[1] != Cin or not conv3x3_wgrad_supported(x.shape, Cout):
+        raise RuntimeError("conv3x3_fwd: unsupported shapes x %s weight %s" % (tuple(x.shape), tuple(w.shape)))
+    y = _empty_nhwc(N, Cout, H, W, x.device)
+    _cabi.call("b200rl_conv3x3_fwd", x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cin, Cout, 0, _stream())
+    return y
+
+
+def conv3x3_dgrad(dy, weight):
+    """Gradient of ``conv2d(x, weight, None, padding=1)`` w.r.t. ``x`` from ``dy [N,O,H,W]`` (channels_last)."""
+    _require_cuda(dy, weight)
+    _nhwc(dy, "conv3x3_dgrad dy")
+    w = _w_cl(weight)
+    N, O, H, W = dy.shape
+    I = w.shape[1]
+    if w.shape[0] != O or O not in (16, 32) or I not in (16, 32) or W not in (8, 16, 32, 64):
+        raise RuntimeError("conv3x3_dgrad: unsupported shapes dy %s weight %s" % (tuple(dy.shape), tuple(w.shape)))
+    dx = _empty_nhwc(N, I, H, W, dy.device)
+    _cabi.call("b200rl_conv3x3_fwd", dy.data_ptr(), w.data_ptr(), dx.data_ptr(), N, H, W, O, I, 1, _stream())
+    return dx

@@ -309,6 +309,16 @@ int32_t b200rl_conv3x3_wgrad(
     const float *x, const float *dy, float *partials, int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout,
     int64_t n_ctas, void *stream);
 
+/* K11 -- the bias-free 3x3 / stride 1 / padding 1 convolution of the same layers (reference models/common.py:12-26,
+ * 41-45), forward (dgrad = 0: y[N,H,W,Cout] from x[N,H,W,Cin]) and input gradient (dgrad = 1: x is dy [N,H,W,Cin'],
+ * y is dx [N,H,W,Cout'] with Cin' = the layer's output and Cout' = its input channels).  `weight` is ALWAYS the
+ * layer's weight as torch holds it in channels_last: physical [O][3][3][I]; dgrad reads it transposed and flipped.
+ * fp32 NHWC, TF32 tensor-core products, fp32 accumulation.  Supported: in 3/16/32 (dgrad: 16/32), out 16/32,
+ * W in {8,16,32,64}. */
+int32_t b200rl_conv3x3_fwd(
+    const float *x, const float *weight, float *y, int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout,
+    int32_t dgrad, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -38,9 +38,7 @@ for name, cin, cout, hw in LAYERS:
     row["cudnn_fprop_ms"] = round(timeit(lambda: F.conv2d(x, w, None, padding=1)), 3)
     row["cudnn_dgrad_ms"] = round(timeit(lambda: torch.ops.aten.convolution_backward(
         dy, x, w, None, (1, 1), (1, 1), (1, 1), False, (0, 0), 1, (True, False, False))), 3)
-    if hasattr(ops, "conv3x3_fwd"):
-        row["k11_fprop_ms"] = round(timeit(lambda: ops.conv3x3_fwd(x, w)), 3)
-        wt = ops.conv3x3_dgrad_weight(w) if hasattr(ops, "conv3x3_dgrad_weight") else None
-        if wt is not None:
-            row["k11_dgrad_ms"] = round(timeit(lambda: ops.conv3x3_fwd(dy, wt)), 3)
+    row["k11_fprop_ms"] = round(timeit(lambda: ops.conv3x3_fwd(x, w)), 3)
+    if cin != 3:
+        row["k11_dgrad_ms"] = round(timeit(lambda: ops.conv3x3_dgrad(dy, w)), 3)
     print(row, flush=True)
