@@ -47,89 +47,108 @@ __device__ __forceinline__ void pool_take(float v, int pos, float &best, uint32_
     if (v > best || v != v) { best = v; arg = (uint32_t)pos; }
 }
 
-template <bool WITH_RELU>
-__global__ void __launch_bounds__(kGlueThreads) maxpool3x3s2_fwd_kernel(
-    const float4 *__restrict__ u, const float4 *__restrict__ bias, float4 *__restrict__ p, float4 *__restrict__ r,
-    uint32_t *__restrict__ code, long long total, int H, int W, int OH, int OW, int C4) {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= total) return;
-    const int c4 = (int)(i % C4);
-    long long t = i / C4;
-    const int ow = (int)(t % OW);
-    t /= OW;
-    const int oh = (int)(t % OH);
-    const long long n = t / OH;
-    const float4 *base = u + n * (long long)H * W * C4 + c4;
-    float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
-    uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-    // the 9 taps are independent loads; windows clipped at the border (padding = -inf, never selected first
-    // unless every tap is out of range, which cannot happen for pad 1)
-    bool first = true;
-    const float4 b = bias ? __ldg(bias + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll
-    for (int kh = 0; kh < 3; ++kh) {
-        const int h = 2 * oh - 1 + kh;
-        if (h < 0 || h >= H) continue;
-#pragma unroll
-        for (int kw = 0; kw < 3; ++kw) {
-            const int w = 2 * ow - 1 + kw;
-            if (w < 0 || w >= W) continue;
-            float4 v = __ldg(base + ((long long)h * W + w) * C4);
-            v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;  // per tap, so ties break exactly as max_pool2d(u + bias)
-            const int pos = kh * 3 + kw;
-            if (first) {  // torch initialises (best, arg) with the first in-range tap
-                best = v;
-                a0 = a1 = a2 = a3 = (uint32_t)pos;
-                first = false;
-            } else {
-                pool_take(v.x, pos, best.x, a0);
-                pool_take(v.y, pos, best.y, a1);
-                pool_take(v.z, pos, best.z, a2);
-                pool_take(v.w, pos, best.w, a3);
-            }
-        }
-    }
-    p[i] = best;
-    if (WITH_RELU) r[i] = make_float4(fmaxf(best.x, 0.f), fmaxf(best.y, 0.f), fmaxf(best.z, 0.f), fmaxf(best.w, 0.f));
-    code[i] = a0 | (a1 << 8) | (a2 << 16) | (a3 << 24);
+// Pool kernels: block = (columns of one image row: ow * C4 + c4) x (rows), grid = (column blocks, row blocks, images).
+// With C/4 a power of two (LOG_C4 >= 0) no thread divides by a run-time value; the first version flattened everything
+// into one 64-bit index and spent 60-80 % of its issue slots on the divisions (ncu: profiles/r01_ncu_cnn_kernels_*).
+template <int LOG_C4>
+__device__ __forceinline__ void split_col(unsigned col, int C4, int &px, int &c4) {
+    if constexpr (LOG_C4 >= 0) { px = (int)(col >> LOG_C4); c4 = (int)(col & ((1u << LOG_C4) - 1u)); }
+    else { px = (int)(col / (unsigned)C4); c4 = (int)(col - (unsigned)px * (unsigned)C4); }
 }
 
+template <bool WITH_RELU, int LOG_C4>
+__global__ void __launch_bounds__(kGlueThreads) maxpool3x3s2_fwd_kernel(
+    const float4 *__restrict__ u, const float4 *__restrict__ bias, float4 *__restrict__ p, float4 *__restrict__ r,
+    uint32_t *__restrict__ code, int N, int H, int W, int OH, int OW, int C4) {
+    const unsigned col = blockIdx.x * blockDim.x + threadIdx.x;
+    const int oh = blockIdx.y * blockDim.y + threadIdx.y;
+    if (col >= (unsigned)(OW * C4) || oh >= OH) return;
+    int ow, c4;
+    split_col<LOG_C4>(col, C4, ow, c4);
+    const float4 b = bias ? __ldg(bias + c4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int n = blockIdx.z; n < N; n += gridDim.z) {
+        const float4 *base = u + (long long)n * H * W * C4 + c4;
+        float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+        uint32_t a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+        // the 9 taps are independent loads; windows are clipped at the border (padding 1: at least 4 taps in range)
+        bool first = true;
+#pragma unroll
+        for (int kh = 0; kh < 3; ++kh) {
+            const int h = 2 * oh - 1 + kh;
+            if (h < 0 || h >= H) continue;
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw) {
+                const int w = 2 * ow - 1 + kw;
+                if (w < 0 || w >= W) continue;
+                float4 v = __ldg(base + (h * W + w) * C4);
+                v.x += b.x; v.y += b.y; v.z += b.z; v.w += b.w;  // per tap, so ties break exactly as max_pool2d(u + bias)
+                const int pos = kh * 3 + kw;
+                if (first) {  // torch initialises (best, arg) with the first in-range tap
+                    best = v;
+                    a0 = a1 = a2 = a3 = (uint32_t)pos;
+                    first = false;
+                } else {
+                    pool_take(v.x, pos, best.x, a0);
+                    pool_take(v.y, pos, best.y, a1);
+                    pool_take(v.z, pos, best.z, a2);
+                    pool_take(v.w, pos, best.w, a3);
+                }
+            }
+        }
+        const long long i = ((long long)n * OH + oh) * (OW * C4) + col;
+        p[i] = best;
+        if (WITH_RELU) r[i] = make_float4(fmaxf(best.x, 0.f), fmaxf(best.y, 0.f), fmaxf(best.z, 0.f), fmaxf(best.w, 0.f));
+        code[i] = a0 | (a1 << 8) | (a2 << 16) | (a3 << 24);
+    }
+}
+
+template <int LOG_C4>
 __global__ void __launch_bounds__(kGlueThreads) maxpool3x3s2_bwd_kernel(
-    const float4 *__restrict__ g, const uint32_t *__restrict__ code, float4 *__restrict__ du, long long total, int H,
-    int W, int OH, int OW, int C4) {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= total) return;
-    const int c4 = (int)(i % C4);
-    long long t = i / C4;
-    const int w = (int)(t % W);
-    t /= W;
-    const int h = (int)(t % H);
-    const long long n = t / H;
+    const float4 *__restrict__ g, const uint32_t *__restrict__ code, float4 *__restrict__ du, int N, int H, int W, int OH,
+    int OW, int C4) {
+    const unsigned col = blockIdx.x * blockDim.x + threadIdx.x;
+    const int h = blockIdx.y * blockDim.y + threadIdx.y;
+    if (col >= (unsigned)(W * C4) || h >= H) return;
+    int w, c4;
+    split_col<LOG_C4>(col, C4, w, c4);
     // windows containing row h: oh = h/2 (kh = 1 for even h, 2 for odd h) and, for odd h, oh = h/2 + 1 (kh = 0)
     const int oh0 = h >> 1, ow0 = w >> 1;
     const int nh = (h & 1) && (oh0 + 1 < OH) ? 2 : 1, nw = (w & 1) && (ow0 + 1 < OW) ? 2 : 1;
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    const long long obase = n * (long long)OH * OW * C4 + c4;
+    for (int n = blockIdx.z; n < N; n += gridDim.z) {
+        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+        const long long obase = (long long)n * OH * OW * C4 + c4;
 #pragma unroll
-    for (int a = 0; a < 2; ++a) {
-        if (a >= nh) break;
-        const int oh = oh0 + a, kh = h - (2 * oh - 1);
+        for (int a = 0; a < 2; ++a) {
+            if (a >= nh) break;
+            const int oh = oh0 + a, kh = h - (2 * oh - 1);
 #pragma unroll
-        for (int b = 0; b < 2; ++b) {
-            if (b >= nw) break;
-            const int ow = ow0 + b, kw = w - (2 * ow - 1);
-            const uint32_t pos = (uint32_t)(kh * 3 + kw);
-            const long long o = obase + ((long long)oh * OW + ow) * C4;
-            const uint32_t cw = __ldg(code + o);
-            const float4 gv = __ldg(g + o);
-            if ((cw & 0xffu) == pos) acc.x += gv.x;
-            if (((cw >> 8) & 0xffu) == pos) acc.y += gv.y;
-            if (((cw >> 16) & 0xffu) == pos) acc.z += gv.z;
-            if ((cw >> 24) == pos) acc.w += gv.w;
+            for (int b = 0; b < 2; ++b) {
+                if (b >= nw) break;
+                const int ow = ow0 + b, kw = w - (2 * ow - 1);
+                const uint32_t pos = (uint32_t)(kh * 3 + kw);
+                const long long o = obase + (oh * OW + ow) * C4;
+                const uint32_t cw = __ldg(code + o);
+                const float4 gv = __ldg(g + o);
+                if ((cw & 0xffu) == pos) acc.x += gv.x;
+                if (((cw >> 8) & 0xffu) == pos) acc.y += gv.y;
+                if (((cw >> 16) & 0xffu) == pos) acc.z += gv.z;
+                if ((cw >> 24) == pos) acc.w += gv.w;
+            }
         }
+        __stcs(du + ((long long)n * H + h) * (W * C4) + col, acc);
     }
-    __stcs(du + i, acc);
 }
+
+// block / grid shape of the pool kernels: as many whole rows per 256-thread block as fit
+static inline void pool_launch_shape(int cols, int rows, long long N, dim3 &block, dim3 &grid) {
+    int bx = cols >= kGlueThreads ? kGlueThreads : ((cols + 31) / 32) * 32;
+    int by = kGlueThreads / bx;
+    if (by > rows) by = rows;
+    block = dim3((unsigned)bx, (unsigned)by, 1);
+    grid = dim3((unsigned)((cols + bx - 1) / bx), (unsigned)((rows + by - 1) / by), (unsigned)(N > 65535 ? 65535 : N));
+}
+
+static inline int log2_c4(int C4) { return C4 == 1 ? 0 : C4 == 2 ? 1 : C4 == 4 ? 2 : C4 == 8 ? 3 : C4 == 16 ? 4 : -1; }
 
 template <bool HAS_RES, bool WRITE_Y, bool WRITE_R>
 __global__ void __launch_bounds__(kGlueThreads) bias_act_fwd_kernel(const float4 *__restrict__ u,
@@ -216,7 +235,7 @@ extern "C" int32_t b200rl_obs_u8_to_f32_nhwc(const uint8_t *obs, float *out, int
 extern "C" int32_t b200rl_maxpool3x3s2_fwd(const float *u, const float *bias, float *p, float *r, uint8_t *code,
                                             int64_t N, int64_t H, int64_t W, int64_t C, void *stream) {
     using namespace b200rl;
-    B200RL_REQUIRE(N >= 0 && H >= 1 && W >= 1 && H < (1 << 20) && W < (1 << 20), -2, "maxpool3x3s2_fwd: N=%lld H=%lld W=%lld",
+    B200RL_REQUIRE(N >= 0 && N < (1ll << 31) && H >= 1 && W >= 1 && H < (1 << 20) && W < (1 << 20), -2, "maxpool3x3s2_fwd: N=%lld H=%lld W=%lld",
                    (long long)N, (long long)H, (long long)W);
     B200RL_REQUIRE(C >= 4 && C % 4 == 0 && C <= 4096, -2, "maxpool3x3s2_fwd: C=%lld must be a multiple of 4", (long long)C);
     if (N == 0) return 0;
@@ -224,21 +243,24 @@ extern "C" int32_t b200rl_maxpool3x3s2_fwd(const float *u, const float *bias, fl
     B200RL_REQUIRE(aligned16(u) && aligned16(p) && aligned16(r) && aligned16(bias) && (reinterpret_cast<uintptr_t>(code) & 3u) == 0,
                    -3, "maxpool3x3s2_fwd: tensors must be 16-byte aligned");
     const int OH = (int)((H - 1) / 2 + 1), OW = (int)((W - 1) / 2 + 1), C4 = (int)(C / 4);
-    const long long total = N * OH * OW * C4;
-    const unsigned grid = (unsigned)((total + kGlueThreads - 1) / kGlueThreads);
-    if (r)
-        maxpool3x3s2_fwd_kernel<true><<<grid, kGlueThreads, 0, (cudaStream_t)stream>>>(
-            (const float4 *)u, (const float4 *)bias, (float4 *)p, (float4 *)r, (uint32_t *)code, total, (int)H, (int)W, OH, OW, C4);
-    else
-        maxpool3x3s2_fwd_kernel<false><<<grid, kGlueThreads, 0, (cudaStream_t)stream>>>(
-            (const float4 *)u, (const float4 *)bias, (float4 *)p, nullptr, (uint32_t *)code, total, (int)H, (int)W, OH, OW, C4);
+    B200RL_REQUIRE(H * W * C4 < (1ll << 31), -2, "maxpool3x3s2_fwd: image of %lld float4 is too large", (long long)(H * W * C4));
+    dim3 block, grid;
+    pool_launch_shape(OW * C4, OH, N, block, grid);
+    cudaStream_t s = (cudaStream_t)stream;
+#define B200RL_PF(R, L) maxpool3x3s2_fwd_kernel<R, L><<<grid, block, 0, s>>>( \
+        (const float4 *)u, (const float4 *)bias, (float4 *)p, (float4 *)r, (uint32_t *)code, (int)N, (int)H, (int)W, OH, OW, C4)
+#define B200RL_PFL(R) switch (log2_c4(C4)) { case 0: B200RL_PF(R, 0); break; case 1: B200RL_PF(R, 1); break; \
+        case 2: B200RL_PF(R, 2); break; case 3: B200RL_PF(R, 3); break; case 4: B200RL_PF(R, 4); break; default: B200RL_PF(R, -1); }
+    if (r) { B200RL_PFL(true) } else { B200RL_PFL(false) }
+#undef B200RL_PFL
+#undef B200RL_PF
     return check_launch("maxpool3x3s2_fwd_kernel");
 }
 
 extern "C" int32_t b200rl_maxpool3x3s2_bwd(const float *g, const uint8_t *code, float *du, int64_t N, int64_t H,
                                             int64_t W, int64_t C, void *stream) {
     using namespace b200rl;
-    B200RL_REQUIRE(N >= 0 && H >= 1 && W >= 1 && H < (1 << 20) && W < (1 << 20), -2, "maxpool3x3s2_bwd: N=%lld H=%lld W=%lld",
+    B200RL_REQUIRE(N >= 0 && N < (1ll << 31) && H >= 1 && W >= 1 && H < (1 << 20) && W < (1 << 20), -2, "maxpool3x3s2_bwd: N=%lld H=%lld W=%lld",
                    (long long)N, (long long)H, (long long)W);
     B200RL_REQUIRE(C >= 4 && C % 4 == 0 && C <= 4096, -2, "maxpool3x3s2_bwd: C=%lld must be a multiple of 4", (long long)C);
     if (N == 0) return 0;
@@ -246,10 +268,15 @@ extern "C" int32_t b200rl_maxpool3x3s2_bwd(const float *g, const uint8_t *code, 
     B200RL_REQUIRE(aligned16(g) && aligned16(du) && (reinterpret_cast<uintptr_t>(code) & 3u) == 0, -3,
                    "maxpool3x3s2_bwd: tensors must be 16-byte aligned");
     const int OH = (int)((H - 1) / 2 + 1), OW = (int)((W - 1) / 2 + 1), C4 = (int)(C / 4);
-    const long long total = N * H * W * C4;
-    maxpool3x3s2_bwd_kernel<<<(unsigned)((total + kGlueThreads - 1) / kGlueThreads), kGlueThreads, 0,
-                              (cudaStream_t)stream>>>((const float4 *)g, (const uint32_t *)code, (float4 *)du, total,
-                                                      (int)H, (int)W, OH, OW, C4);
+    B200RL_REQUIRE(H * W * C4 < (1ll << 31), -2, "maxpool3x3s2_bwd: image of %lld float4 is too large", (long long)(H * W * C4));
+    dim3 block, grid;
+    pool_launch_shape((int)W * C4, (int)H, N, block, grid);
+    cudaStream_t s = (cudaStream_t)stream;
+#define B200RL_PB(L) maxpool3x3s2_bwd_kernel<L><<<grid, block, 0, s>>>( \
+        (const float4 *)g, (const uint32_t *)code, (float4 *)du, (int)N, (int)H, (int)W, OH, OW, C4)
+    switch (log2_c4(C4)) { case 0: B200RL_PB(0); break; case 1: B200RL_PB(1); break; case 2: B200RL_PB(2); break;
+        case 3: B200RL_PB(3); break; case 4: B200RL_PB(4); break; default: B200RL_PB(-1); }
+#undef B200RL_PB
     return check_launch("maxpool3x3s2_bwd_kernel");
 }
 

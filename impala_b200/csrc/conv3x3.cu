@@ -70,18 +70,27 @@ __device__ __forceinline__ RowPlan make_plan(int per_row, int floats_per_chunk, 
     return p;
 }
 
+__device__ __forceinline__ void cp_async_u32(uint32_t saddr, const void *gmem, int bytes16, int src_bytes) {
+    if (bytes16)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(saddr), "l"(gmem), "r"(src_bytes) : "memory");
+    else
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(saddr), "l"(gmem), "r"(src_bytes) : "memory");
+}
+
 template <int BYTES, int THREADS>
 __device__ __forceinline__ void stage_rows(float *s, int s_row_stride, const float *__restrict__ g, long long g_row_stride,
                                            long long image_row0, int h_first, int rows, int H, const RowPlan &p,
                                            int per_row, int C, int smem_pixel_stride, int col0) {
     // image_row0 = n * H; row r of the tile is image row h_first + r
     if (p.fast) {
-        for (int r = p.r0; r < rows; r += p.rstep) {
-            const int h = h_first + r;
-            const bool in = h >= 0 && h < H;
-            const float *src = g + (image_row0 + (in ? h : 0)) * g_row_stride + p.goff;
-            if (BYTES == 16) cp_async16(s + r * s_row_stride + p.soff, src, in ? 16 : 0);
-            else cp_async4(s + r * s_row_stride + p.soff, src, in ? 4 : 0);
+        // one pointer / one shared address per thread, stepped by whole rows: ~6 instructions per copy
+        const float *src = g + (image_row0 + h_first + p.r0) * g_row_stride + p.goff;   // dereferenced only when in range
+        uint32_t dst = smem_u32(s) + 4u * (unsigned)(p.r0 * s_row_stride + p.soff);
+        const long long gstep = (long long)p.rstep * g_row_stride;
+        const uint32_t sstep = 4u * (unsigned)(p.rstep * s_row_stride);
+        for (int r = p.r0; r < rows; r += p.rstep, src += gstep, dst += sstep) {
+            const bool in = (unsigned)(h_first + r) < (unsigned)H;
+            cp_async_u32(dst, in ? src : g, BYTES == 16, in ? BYTES : 0);
         }
     } else {
         constexpr int FPC = BYTES / 4;
@@ -90,8 +99,7 @@ __device__ __forceinline__ void stage_rows(float *s, int s_row_stride, const flo
             const bool in = h >= 0 && h < H;
             const float *src = g + (image_row0 + (in ? h : 0)) * g_row_stride + e;
             float *dst = s + r * s_row_stride + (px + col0) * smem_pixel_stride + (e - px * C);
-            if (BYTES == 16) cp_async16(dst, src, in ? 16 : 0);
-            else cp_async4(dst, src, in ? 4 : 0);
+            cp_async_u32(smem_u32(dst), src, BYTES == 16, in ? BYTES : 0);
         }
     }
 }

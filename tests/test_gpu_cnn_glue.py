@@ -215,3 +215,34 @@ def test_conv3x3_forward_and_dgrad_match_cudnn_fp32(cuda, N, Cin, Cout, H, W):
             assert torch.equal(ops.conv3x3_dgrad(di, wi), xi64.grad.float())
     finally:
         torch.backends.cudnn.allow_tf32 = tf32
+
+
+def test_cnn_kernels_against_cpu_torch_ops(cuda):
+    """The same pieces against torch's CPU kernels (the reference's arithmetic on the host, fp32, no TF32 anywhere):
+    pool / bias / ReLU / residual exactly, the convolution pieces at TF32 tolerance."""
+    g = torch.Generator().manual_seed(5)
+    N, Cin, Cout, H, W = 3, 16, 32, 16, 16
+    x = torch.randn(N, Cin, H, W, generator=g)
+    w = torch.randn(Cout, Cin, 3, 3, generator=g) / 12.
+    b = torch.randn(Cout, generator=g)
+    dy = torch.randn(N, Cout, H, W, generator=g)
+    xc = x.clone().requires_grad_(True)
+    wc = w.clone().requires_grad_(True)
+    y_cpu = F.conv2d(xc, wc, None, padding=1)
+    y_cpu.backward(dy)
+    xg, wg, dyg = (t.to(cuda).contiguous(memory_format=CL) for t in (x, w, dy))
+    for got, want in ((ops.conv3x3_fwd(xg, wg), y_cpu.detach()), (ops.conv3x3_dgrad(dyg, wg), xc.grad),
+                      (ops.conv3x3_wgrad(xg, dyg), wc.grad)):
+        assert (got.cpu() - want).abs().max().item() <= 2e-3 * want.abs().max().item()
+    u = y_cpu.detach()
+    pool_cpu = F.max_pool2d(u + b.view(1, -1, 1, 1), 3, 2, 1)
+    p, r, code = ops.maxpool3x3s2_fwd(u.to(cuda).contiguous(memory_format=CL), b.to(cuda), with_relu=True)
+    assert torch.equal(p.cpu(), pool_cpu) and torch.equal(r.cpu(), F.relu(pool_cpu))
+    uc = u.clone().requires_grad_(True)
+    gp = torch.randn(pool_cpu.shape, generator=g)
+    F.max_pool2d(uc + b.view(1, -1, 1, 1), 3, 2, 1).backward(gp)
+    du = ops.maxpool3x3s2_bwd(gp.to(cuda).contiguous(memory_format=CL), code, tuple(u.shape))
+    assert_close(du, uc.grad, "pool grad vs CPU", rtol=1e-6, atol=1e-7)
+    obs = torch.randint(0, 256, (2, 3, 8, 8), dtype=torch.uint8, generator=g)
+    got = ops.obs_to_f32_nhwc(obs.to(cuda)).cpu()
+    assert (got - obs.float() / 255.).abs().max().item() <= 6e-8      # CPU divides, CUDA multiplies by 1/255: 1 ulp
