@@ -129,10 +129,11 @@ __global__ void __launch_bounds__(kGlueThreads) maxpool3x3s2_bwd_kernel(
                 const long long o = obase + (oh * OW + ow) * C4;
                 const uint32_t cw = __ldg(code + o);
                 const float4 gv = __ldg(g + o);
-                if ((cw & 0xffu) == pos) acc.x += gv.x;
-                if (((cw >> 8) & 0xffu) == pos) acc.y += gv.y;
-                if (((cw >> 16) & 0xffu) == pos) acc.z += gv.z;
-                if ((cw >> 24) == pos) acc.w += gv.w;
+                const uint32_t hit = __vcmpeq4(cw, pos * 0x01010101u);   // 0xff in every byte whose code is this tap
+                if (hit & 0x000000ffu) acc.x += gv.x;
+                if (hit & 0x0000ff00u) acc.y += gv.y;
+                if (hit & 0x00ff0000u) acc.z += gv.z;
+                if (hit & 0xff000000u) acc.w += gv.w;
             }
         }
         __stcs(du + ((long long)n * H + h) * (W * C4) + col, acc);

@@ -10,6 +10,7 @@ from typing import Iterable
 import torch
 
 from . import ops
+from .parallel import flat_view
 
 
 class FusedClipAdam(torch.optim.Optimizer):
@@ -33,7 +34,7 @@ class FusedClipAdam(torch.optim.Optimizer):
         self.flat = torch.empty(n, dtype=torch.float32, device=dev)
         off = 0
         for p in self.params:
-            v = self.flat[off:off + p.numel()].view_as(p)
+            v = flat_view(self.flat, off, p)          # keeps a channels_last weight channels_last
             v.copy_(p.data)
             p.data = v
             off += p.numel()

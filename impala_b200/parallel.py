@@ -27,6 +27,18 @@ def shard_columns(B_global: int, rank: int, world_size: int):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
+def flat_view(flat: torch.Tensor, off: int, p: torch.Tensor) -> torch.Tensor:
+    """View of ``flat[off : off + p.numel()]`` with ``p``'s shape AND memory format: a channels_last convolution weight
+    stays channels_last when its storage moves into a flat bucket (physical ``[O][3][3][I]``, what K10/K11 read and
+    write), so no layout copy is needed per step; everything else is a plain contiguous view.  Adam and the allreduce
+    are elementwise, so the order of elements inside the slice is free as long as parameter, gradient and moments
+    use the same one -- they do, all three are built by this function from the same strides."""
+    chunk = flat[off:off + p.numel()]
+    if p.dim() == 4 and not p.is_contiguous() and p.is_contiguous(memory_format=torch.channels_last):
+        return chunk.as_strided(p.shape, p.stride())
+    return chunk.view_as(p)
+
+
 class GradBucket:
     """All parameter gradients as views into one flat fp32 buffer + ``n_extra`` tail floats, so a step
     needs exactly one allreduce (630,352 params = 2.52 MB for the IMPALA-CNN: latency-bound, one bucket)."""
@@ -41,7 +53,7 @@ class GradBucket:
         self.n, self.n_extra = n, n_extra
         self.views, off = [], 0
         for p in self.params:
-            self.views.append(self.flat[off:off + p.numel()].view_as(p))
+            self.views.append(flat_view(self.flat, off, p))
             off += p.numel()
 
     @property

@@ -105,3 +105,20 @@ def test_make_bucket_routes_on_cpu(monkeypatch):
     assert type(parallel.make_bucket(ps, None, fused_optimizer=True)) is parallel.GradBucket
     with pytest.raises(RuntimeError):
         parallel.PeerGradBucket(ps)
+
+
+def test_flat_view_keeps_memory_format():
+    """Flat parameter / gradient buckets keep a channels_last convolution weight channels_last (K10/K11 read and
+    write the physical [O][3][3][I] layout), everything else contiguous."""
+    from impala_b200.parallel import flat_view
+    w = torch.randn(32, 16, 3, 3).contiguous(memory_format=torch.channels_last)
+    b = torch.randn(32)
+    flat = torch.zeros(5 + w.numel() + b.numel())
+    vw, vb = flat_view(flat, 5, w), flat_view(flat, 5 + w.numel(), b)
+    vw.copy_(w)
+    vb.copy_(b)
+    assert torch.equal(vw, w) and vw.stride() == w.stride() and vw.data_ptr() == flat[5:].data_ptr()
+    assert torch.equal(flat[5:5 + w.numel()].view(32, 3, 3, 16).permute(0, 3, 1, 2), w)
+    assert torch.equal(flat[5 + w.numel():], b) and flat[:5].abs().sum() == 0
+    wc = torch.randn(8, 4, 3, 3)                                # plain contiguous weight: plain view
+    assert flat_view(torch.zeros(wc.numel()), 0, wc).is_contiguous()
