@@ -102,41 +102,65 @@ __global__ void __launch_bounds__(kGlueThreads) maxpool3x3s2_fwd_kernel(
     }
 }
 
+// Backward: one thread owns the 2x2 input patch (2k..2k+1, 2l..2l+1) of one channel quad.  The patch is covered by
+// exactly the windows (k,l), (k,l+1), (k+1,l), (k+1,l+1), each fetched once (gradient + 4 tap codes); which tap of a
+// window a patch pixel is, is a compile-time constant:
+//   pixel (0,0): window (k,l) tap 4            pixel (0,1): (k,l) tap 5, (k,l+1) tap 3
+//   pixel (1,0): (k,l) tap 7, (k+1,l) tap 1    pixel (1,1): (k,l) tap 8, (k,l+1) tap 6, (k+1,l) tap 2, (k+1,l+1) tap 0
+// (the first version, one thread per input pixel, fetched 9 windows per patch and was issue-bound: ncu 75 %).
+__device__ __forceinline__ void pool_acc(float4 &acc, const float4 &gv, uint32_t cw, uint32_t tap) {
+    const uint32_t hit = __vcmpeq4(cw, tap * 0x01010101u);   // 0xff in every byte whose code is this tap
+    if (hit & 0x000000ffu) acc.x += gv.x;
+    if (hit & 0x0000ff00u) acc.y += gv.y;
+    if (hit & 0x00ff0000u) acc.z += gv.z;
+    if (hit & 0xff000000u) acc.w += gv.w;
+}
+
 template <int LOG_C4>
 __global__ void __launch_bounds__(kGlueThreads) maxpool3x3s2_bwd_kernel(
     const float4 *__restrict__ g, const uint32_t *__restrict__ code, float4 *__restrict__ du, int N, int H, int W, int OH,
     int OW, int C4) {
     const unsigned col = blockIdx.x * blockDim.x + threadIdx.x;
-    const int h = blockIdx.y * blockDim.y + threadIdx.y;
-    if (col >= (unsigned)(W * C4) || h >= H) return;
-    int w, c4;
-    split_col<LOG_C4>(col, C4, w, c4);
-    // windows containing row h: oh = h/2 (kh = 1 for even h, 2 for odd h) and, for odd h, oh = h/2 + 1 (kh = 0)
-    const int oh0 = h >> 1, ow0 = w >> 1;
-    const int nh = (h & 1) && (oh0 + 1 < OH) ? 2 : 1, nw = (w & 1) && (ow0 + 1 < OW) ? 2 : 1;
+    const int k = blockIdx.y * blockDim.y + threadIdx.y;
+    if (col >= (unsigned)(OW * C4) || k >= OH) return;
+    int l, c4;
+    split_col<LOG_C4>(col, C4, l, c4);
+    const bool down = k + 1 < OH, right = l + 1 < OW;          // windows (k+1, .), (., l+1) exist
+    const bool row1 = 2 * k + 1 < H, col1 = 2 * l + 1 < W;     // patch pixels (1, .), (., 1) exist
+    const float4 zero = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int n = blockIdx.z; n < N; n += gridDim.z) {
-        float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-        const long long obase = (long long)n * OH * OW * C4 + c4;
-#pragma unroll
-        for (int a = 0; a < 2; ++a) {
-            if (a >= nh) break;
-            const int oh = oh0 + a, kh = h - (2 * oh - 1);
-#pragma unroll
-            for (int b = 0; b < 2; ++b) {
-                if (b >= nw) break;
-                const int ow = ow0 + b, kw = w - (2 * ow - 1);
-                const uint32_t pos = (uint32_t)(kh * 3 + kw);
-                const long long o = obase + (oh * OW + ow) * C4;
-                const uint32_t cw = __ldg(code + o);
-                const float4 gv = __ldg(g + o);
-                const uint32_t hit = __vcmpeq4(cw, pos * 0x01010101u);   // 0xff in every byte whose code is this tap
-                if (hit & 0x000000ffu) acc.x += gv.x;
-                if (hit & 0x0000ff00u) acc.y += gv.y;
-                if (hit & 0x00ff0000u) acc.z += gv.z;
-                if (hit & 0xff000000u) acc.w += gv.w;
+        const long long o00 = ((long long)n * OH + k) * (OW * C4) + col;
+        const float4 g00 = __ldg(g + o00);
+        const uint32_t c00 = __ldg(code + o00);
+        float4 g01 = zero, g10 = zero, g11 = zero;
+        uint32_t c01 = 0xffffffffu, c10 = 0xffffffffu, c11 = 0xffffffffu;   // 0xff matches no tap
+        if (right) { g01 = __ldg(g + o00 + C4); c01 = __ldg(code + o00 + C4); }
+        if (down) { g10 = __ldg(g + o00 + OW * C4); c10 = __ldg(code + o00 + OW * C4); }
+        if (right && down) { g11 = __ldg(g + o00 + OW * C4 + C4); c11 = __ldg(code + o00 + OW * C4 + C4); }
+        float4 *out = du + (((long long)n * H + 2 * k) * W + 2 * l) * C4 + c4;
+        float4 acc = zero;
+        pool_acc(acc, g00, c00, 4);
+        __stcs(out, acc);
+        if (col1) {
+            acc = zero;
+            pool_acc(acc, g00, c00, 5);
+            pool_acc(acc, g01, c01, 3);
+            __stcs(out + C4, acc);
+        }
+        if (row1) {
+            acc = zero;
+            pool_acc(acc, g00, c00, 7);
+            pool_acc(acc, g10, c10, 1);
+            __stcs(out + W * C4, acc);
+            if (col1) {
+                acc = zero;
+                pool_acc(acc, g00, c00, 8);
+                pool_acc(acc, g01, c01, 6);
+                pool_acc(acc, g10, c10, 2);
+                pool_acc(acc, g11, c11, 0);
+                __stcs(out + W * C4 + C4, acc);
             }
         }
-        __stcs(du + ((long long)n * H + h) * (W * C4) + col, acc);
     }
 }
 
@@ -271,7 +295,7 @@ extern "C" int32_t b200rl_maxpool3x3s2_bwd(const float *g, const uint8_t *code, 
     const int OH = (int)((H - 1) / 2 + 1), OW = (int)((W - 1) / 2 + 1), C4 = (int)(C / 4);
     B200RL_REQUIRE(H * W * C4 < (1ll << 31), -2, "maxpool3x3s2_bwd: image of %lld float4 is too large", (long long)(H * W * C4));
     dim3 block, grid;
-    pool_launch_shape((int)W * C4, (int)H, N, block, grid);
+    pool_launch_shape(OW * C4, OH, N, block, grid);            // one thread per 2x2 input patch and channel quad
     cudaStream_t s = (cudaStream_t)stream;
 #define B200RL_PB(L) maxpool3x3s2_bwd_kernel<L><<<grid, block, 0, s>>>( \
         (const float4 *)g, (const uint32_t *)code, (float4 *)du, (int)N, (int)H, (int)W, OH, OW, C4)
