@@ -76,7 +76,10 @@ def _worker(rank, world_size, port, out):
 def test_sharded_sum_equals_global_gloo():
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
-    port = 29500 + os.getpid() % 2000
+    import socket
+    with socket.socket() as sk:                                  # a port that is free right now (not pid-derived)
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
     procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
     [p.start() for p in procs]
     (flat,) = q.get(timeout=120)
