@@ -57,6 +57,7 @@ SIGNATURES = {
     "b200rl_relu_bwd_add": (_i32, [_vp] * 5 + [_i64] * 3 + [_vp]),
     "b200rl_conv3x3_wgrad": (_i32, [_vp] * 3 + [_i64] * 6 + [_vp]),
     "b200rl_conv3x3_fwd": (_i32, [_vp] * 3 + [_i64] * 5 + [_i32, _vp]),
+    "b200rl_conv3x3_fwd_fused": (_i32, [_vp] * 6 + [_i64] * 5 + [_vp]),
 }
 
 

@@ -98,6 +98,59 @@ def conv3x3(x, weight):
     return Conv3x3.apply(x, weight)
 
 
+class ConvBiasAct(torch.autograd.Function):
+    """One convolution of a residual block with its elementwise tail (``models/common.py:30-34``):
+    ``v = conv3x3(x, weight) + bias (+ res)``, outputs ``v`` and/or ``relu(v)``.  Where K11 runs the convolution the
+    tail is its epilogue (the raw convolution output never reaches HBM); for 32 -> 32 channels cuDNN convolves and the
+    K9 ``bias_act`` kernel does the tail.  Backward: ``g = dv + d relu * (relu > 0)`` with the bias gradient in the same
+    pass (K9), then K11 / cuDNN input gradient and K10 weight gradient of ``g``; ``res`` receives ``g`` itself."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, res, want_y, want_r):
+        if _k11_wins(weight) and ops.conv3x3_wgrad_supported(x.shape, weight.shape[0]):
+            y, r = ops.conv3x3_fwd_fused(x, weight, bias, res, want_y, want_r)
+        else:
+            y, r = ops.bias_act_fwd(torch.nn.functional.conv2d(x, weight, None, padding=1), bias, res, want_y, want_r)
+        ctx.save_for_backward(*((x, weight, r) if want_r else (x, weight)))
+        ctx.flags = (res is not None, want_y, want_r)
+        return tuple(t for t in (y, r) if t is not None)
+
+    @staticmethod
+    def backward(ctx, *grads):
+        has_res, want_y, want_r = ctx.flags
+        x, weight = ctx.saved_tensors[:2]
+        r = ctx.saved_tensors[2] if want_r else None
+        grads = list(grads)
+        dy = _cl(grads.pop(0)) if want_y else None
+        dr = _cl(grads.pop(0)) if want_r else None
+        g, db = ops.relu_bwd_add(dy, dr, r if dr is not None else None)
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            if _k11_wins(weight) and ops.conv3x3_wgrad_supported(x.shape, weight.shape[0]):
+                dx = ops.conv3x3_dgrad(g, weight)
+            else:
+                dx = torch.ops.aten.convolution_backward(g, x, weight, None, (1, 1), (1, 1), (1, 1), False, (0, 0), 1,
+                                                         (True, False, False))[0]
+        if ctx.needs_input_grad[1]:
+            if ops.conv3x3_wgrad_supported(x.shape, weight.shape[0]):
+                dw = ops.conv3x3_wgrad(x, g)
+            else:
+                dw = torch.ops.aten.convolution_backward(g, x, weight, None, (1, 1), (1, 1), (1, 1), False, (0, 0), 1,
+                                                         (False, True, False))[1]
+        return dx, dw, db, (g if has_res else None), None, None
+
+
+def conv_bias_relu(x, weight, bias):
+    """``relu(conv3x3(x) + bias)`` (``models/common.py:31-32``)."""
+    return ConvBiasAct.apply(x, weight, bias, None, False, True)[0]
+
+
+def conv_bias_add(x, weight, bias, res, want_y=True, want_r=False):
+    """``res + (conv3x3(x) + bias)`` and/or its ReLU (``models/common.py:33-34`` + the next block's ``:30``)."""
+    out = ConvBiasAct.apply(x, weight, bias, res, want_y, want_r)
+    return out if len(out) > 1 else out[0]
+
+
 def pool_bias(u, bias):
     return PoolBias.apply(u, bias)
 

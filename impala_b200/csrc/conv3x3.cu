@@ -309,12 +309,17 @@ extern "C" int32_t b200rl_conv3x3_wgrad(const float *x, const float *dy, float *
 namespace b200rl {
 
 constexpr int kFwTH = 8;
+// optional epilogue of the forward form: v = acc + bias[o] (+ res); y = v (when y != NULL); relu_out = max(v, 0)
+struct FwEpilogue {
+    const float *bias, *res;
+    float *relu_out;
+};
 template <int W> struct FwWarps { static constexpr int value = W >= 16 ? 8 : 4; };
 
 template <int CIN_P, int COUT, int W, bool DGRAD>
 __global__ void __launch_bounds__(FwWarps<W>::value * 32)
-conv3x3_fwd_kernel(const float *__restrict__ x, const float *__restrict__ wgt, float *__restrict__ y, int N, int H, int Cin,
-                   int n_tiles) {
+conv3x3_fwd_kernel(const float *__restrict__ x, const float *__restrict__ wgt, float *__restrict__ y, FwEpilogue ep, int N,
+                   int H, int Cin, int n_tiles) {
     constexpr int XS = CIN_P + 4;                          // pixel stride of the x tile: = 4 (mod 8)
     constexpr int WS = COUT + 8;                           // row stride of the weights [tap][cin][cout]: = 8 (mod 32)
     constexpr int WARPS = FwWarps<W>::value, THREADS = WARPS * 32;
@@ -407,10 +412,22 @@ conv3x3_fwd_kernel(const float *__restrict__ x, const float *__restrict__ wgt, f
             for (int half = 0; half < 2; ++half) {
                 const int r = prow[m] + (W >= 16 ? 0 : half), c = pcol[m] + gid + (W >= 16 ? 8 * half : 0), h = h0 + r;
                 if (h < H) {
-                    float *yp = y + (((long long)n * H + h) * W + c) * COUT + 2 * tig;
+                    const long long off = (((long long)n * H + h) * W + c) * COUT + 2 * tig;
 #pragma unroll
-                    for (int nt = 0; nt < NT; ++nt)
-                        __stcs(reinterpret_cast<float2 *>(yp + nt * 8), make_float2(acc[m][nt][2 * half], acc[m][nt][2 * half + 1]));
+                    for (int nt = 0; nt < NT; ++nt) {
+                        float2 v = make_float2(acc[m][nt][2 * half], acc[m][nt][2 * half + 1]);
+                        if (ep.bias) {                      // torch order: (conv + bias), then inputs + that
+                            const float2 b = __ldg(reinterpret_cast<const float2 *>(ep.bias + nt * 8 + 2 * tig));
+                            v.x += b.x; v.y += b.y;
+                        }
+                        if (ep.res) {
+                            const float2 s2 = __ldcs(reinterpret_cast<const float2 *>(ep.res + off + nt * 8));
+                            v.x = s2.x + v.x; v.y = s2.y + v.y;
+                        }
+                        if (y) __stcs(reinterpret_cast<float2 *>(y + off + nt * 8), v);
+                        if (ep.relu_out)
+                            __stcs(reinterpret_cast<float2 *>(ep.relu_out + off + nt * 8), make_float2(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f)));
+                    }
                 }
             }
         }
@@ -420,7 +437,7 @@ conv3x3_fwd_kernel(const float *__restrict__ x, const float *__restrict__ wgt, f
 }
 
 template <int CIN_P, int COUT, int W, bool DGRAD>
-static int32_t launch_fwd(const float *x, const float *wgt, float *y, int N, int H, int Cin, cudaStream_t stream) {
+static int32_t launch_fwd(const float *x, const float *wgt, float *y, FwEpilogue ep, int N, int H, int Cin, cudaStream_t stream) {
     constexpr int XS = CIN_P + 4, WS = COUT + 8;
     constexpr int smem = 4 * (9 * CIN_P * WS + 2 * (kFwTH + 2) * (W + 2) * XS);
     if (smem > 227 * 1024) {
@@ -445,30 +462,32 @@ static int32_t launch_fwd(const float *x, const float *wgt, float *y, int N, int
     const int n_tiles = N * ((H + kFwTH - 1) / kFwTH);
     int grid = sms * ctas_per_sm[dev];
     if (grid > n_tiles) grid = n_tiles;
-    kern<<<grid, FwWarps<W>::value * 32, smem, stream>>>(x, wgt, y, N, H, Cin, n_tiles);
+    kern<<<grid, FwWarps<W>::value * 32, smem, stream>>>(x, wgt, y, ep, N, H, Cin, n_tiles);
     return check_launch("conv3x3_fwd_kernel");
 }
 
 template <int CIN_P, int COUT, bool DGRAD>
-static int32_t launch_fwd_w(const float *x, const float *wgt, float *y, int N, int H, int W, int Cin, cudaStream_t stream) {
+static int32_t launch_fwd_w(const float *x, const float *wgt, float *y, FwEpilogue ep, int N, int H, int W, int Cin,
+                            cudaStream_t stream) {
     switch (W) {
-        case 8: return launch_fwd<CIN_P, COUT, 8, DGRAD>(x, wgt, y, N, H, Cin, stream);
-        case 16: return launch_fwd<CIN_P, COUT, 16, DGRAD>(x, wgt, y, N, H, Cin, stream);
-        case 32: return launch_fwd<CIN_P, COUT, 32, DGRAD>(x, wgt, y, N, H, Cin, stream);
-        case 64: return launch_fwd<CIN_P, COUT, 64, DGRAD>(x, wgt, y, N, H, Cin, stream);
+        case 8: return launch_fwd<CIN_P, COUT, 8, DGRAD>(x, wgt, y, ep, N, H, Cin, stream);
+        case 16: return launch_fwd<CIN_P, COUT, 16, DGRAD>(x, wgt, y, ep, N, H, Cin, stream);
+        case 32: return launch_fwd<CIN_P, COUT, 32, DGRAD>(x, wgt, y, ep, N, H, Cin, stream);
+        case 64: return launch_fwd<CIN_P, COUT, 64, DGRAD>(x, wgt, y, ep, N, H, Cin, stream);
     }
     set_error("conv3x3_fwd: W=%d (supported: 8, 16, 32, 64)", W);
     return -2;
 }
 
 template <bool DGRAD>
-static int32_t dispatch_fwd(const float *x, const float *wgt, float *y, int N, int H, int W, int Cin, int Cout, cudaStream_t s) {
-    if (Cin == 3 && Cout == 16) return launch_fwd_w<8, 16, DGRAD>(x, wgt, y, N, H, W, Cin, s);
-    if (Cin == 3 && Cout == 32) return launch_fwd_w<8, 32, DGRAD>(x, wgt, y, N, H, W, Cin, s);
-    if (Cin == 16 && Cout == 16) return launch_fwd_w<16, 16, DGRAD>(x, wgt, y, N, H, W, Cin, s);
-    if (Cin == 16 && Cout == 32) return launch_fwd_w<16, 32, DGRAD>(x, wgt, y, N, H, W, Cin, s);
-    if (Cin == 32 && Cout == 16) return launch_fwd_w<32, 16, DGRAD>(x, wgt, y, N, H, W, Cin, s);
-    return launch_fwd_w<32, 32, DGRAD>(x, wgt, y, N, H, W, Cin, s);
+static int32_t dispatch_fwd(const float *x, const float *wgt, float *y, FwEpilogue ep, int N, int H, int W, int Cin, int Cout,
+                            cudaStream_t s) {
+    if (Cin == 3 && Cout == 16) return launch_fwd_w<8, 16, DGRAD>(x, wgt, y, ep, N, H, W, Cin, s);
+    if (Cin == 3 && Cout == 32) return launch_fwd_w<8, 32, DGRAD>(x, wgt, y, ep, N, H, W, Cin, s);
+    if (Cin == 16 && Cout == 16) return launch_fwd_w<16, 16, DGRAD>(x, wgt, y, ep, N, H, W, Cin, s);
+    if (Cin == 16 && Cout == 32) return launch_fwd_w<16, 32, DGRAD>(x, wgt, y, ep, N, H, W, Cin, s);
+    if (Cin == 32 && Cout == 16) return launch_fwd_w<32, 16, DGRAD>(x, wgt, y, ep, N, H, W, Cin, s);
+    return launch_fwd_w<32, 32, DGRAD>(x, wgt, y, ep, N, H, W, Cin, s);
 }
 
 }  // namespace b200rl
@@ -485,6 +504,24 @@ extern "C" int32_t b200rl_conv3x3_fwd(const float *x, const float *weight, float
     B200RL_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15u) == 0 && (reinterpret_cast<uintptr_t>(y) & 15u) == 0, -3,
                    "conv3x3_fwd: tensors must be 16-byte aligned");
     cudaStream_t s = (cudaStream_t)stream;
-    return dgrad ? dispatch_fwd<true>(x, weight, y, (int)N, (int)H, (int)W, (int)Cin, (int)Cout, s)
-                 : dispatch_fwd<false>(x, weight, y, (int)N, (int)H, (int)W, (int)Cin, (int)Cout, s);
+    const FwEpilogue none = {nullptr, nullptr, nullptr};
+    return dgrad ? dispatch_fwd<true>(x, weight, y, none, (int)N, (int)H, (int)W, (int)Cin, (int)Cout, s)
+                 : dispatch_fwd<false>(x, weight, y, none, (int)N, (int)H, (int)W, (int)Cin, (int)Cout, s);
+}
+
+extern "C" int32_t b200rl_conv3x3_fwd_fused(const float *x, const float *weight, const float *bias, const float *res, float *y,
+                                             float *relu_out, int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout,
+                                             void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(x && weight && bias && (y || relu_out), -1, "conv3x3_fwd_fused: null pointer argument");
+    B200RL_REQUIRE(N >= 1 && H >= 1 && N * H < (1ll << 30), -2, "conv3x3_fwd_fused: N=%lld H=%lld", (long long)N, (long long)H);
+    B200RL_REQUIRE(W == 8 || W == 16 || W == 32 || W == 64, -2, "conv3x3_fwd_fused: W=%lld (supported: 8, 16, 32, 64)", (long long)W);
+    B200RL_REQUIRE((Cin == 3 || Cin == 16 || Cin == 32) && (Cout == 16 || Cout == 32), -2,
+                   "conv3x3_fwd_fused: Cin=%lld Cout=%lld (supported: in 3/16/32, out 16/32)", (long long)Cin, (long long)Cout);
+    const uintptr_t all = reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(res) |
+                          reinterpret_cast<uintptr_t>(relu_out);
+    B200RL_REQUIRE((all & 15u) == 0 && (reinterpret_cast<uintptr_t>(bias) & 7u) == 0, -3,
+                   "conv3x3_fwd_fused: tensors must be 16-byte (bias: 8-byte) aligned");
+    const FwEpilogue ep = {bias, res, relu_out};
+    return dispatch_fwd<false>(x, weight, y, ep, (int)N, (int)H, (int)W, (int)Cin, (int)Cout, (cudaStream_t)stream);
 }

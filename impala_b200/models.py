@@ -78,14 +78,14 @@ class ImpalaCNN(nn.Module):
             u = G.conv3x3(x, st.conv.weight)
             p, r = G.pool_bias(u, st.conv.bias)                            # max_pool(conv + b), relu of it
             for bi, blk in enumerate((st.res_block0, st.res_block1)):
-                r1 = G.bias_relu(G.conv3x3(r, blk.conv0.weight), blk.conv0.bias)
-                u1 = G.conv3x3(r1, blk.conv1.weight)
+                r1 = G.conv_bias_relu(r, blk.conv0.weight, blk.conv0.bias)
+                w1, b1 = blk.conv1.weight, blk.conv1.bias
                 if bi == 0:                                                # block output + the next block's opening ReLU
-                    p, r = G.bias_add(u1, blk.conv1.bias, p, want_y=True, want_r=True)
+                    p, r = G.conv_bias_add(r1, w1, b1, p, want_y=True, want_r=True)
                 elif si + 1 < len(stages):                                 # feeds the next stage's convolution
-                    x = G.bias_add(u1, blk.conv1.bias, p, want_y=True, want_r=False)
+                    x = G.conv_bias_add(r1, w1, b1, p, want_y=True, want_r=False)
                 else:                                                      # the body's closing ReLU
-                    x = G.bias_add(u1, blk.conv1.bias, p, want_y=False, want_r=True)
+                    x = G.conv_bias_add(r1, w1, b1, p, want_y=False, want_r=True)
         return x.flatten(1)
 
 

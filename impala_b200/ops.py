@@ -591,3 +591,25 @@ def conv3x3_dgrad(dy, weight):
     dx = _empty_nhwc(N, I, H, W, dy.device)
     _cabi.call("b200rl_conv3x3_fwd", dy.data_ptr(), w.data_ptr(), dx.data_ptr(), N, H, W, O, I, 1, _stream())
     return dx
+
+
+def conv3x3_fwd_fused(x, weight, bias, res=None, want_y=True, want_r=False):
+    """K11 forward with the residual block's tail in the epilogue: ``v = conv2d(x, weight, bias, padding=1) (+ res)``;
+    returns ``(v or None, relu(v) or None)`` as requested (reference ``models/common.py:30-34``)."""
+    _require_cuda(x, weight, bias)
+    _nhwc(x, "conv3x3_fwd_fused x")
+    w = _w_cl(weight)
+    N, Cin, H, W = x.shape
+    Cout = w.shape[0]
+    if w.shape[1] != Cin or not conv3x3_wgrad_supported(x.shape, Cout) or not (want_y or want_r):
+        raise RuntimeError("conv3x3_fwd_fused: unsupported shapes x %s weight %s" % (tuple(x.shape), tuple(w.shape)))
+    if res is not None:
+        _nhwc(res, "conv3x3_fwd_fused res")
+        if tuple(res.shape) != (N, Cout, H, W):
+            raise RuntimeError("conv3x3_fwd_fused: res %s vs output %s" % (tuple(res.shape), (N, Cout, H, W)))
+    b = _f32c(bias.detach())
+    y = _empty_nhwc(N, Cout, H, W, x.device) if want_y else None
+    r = _empty_nhwc(N, Cout, H, W, x.device) if want_r else None
+    _cabi.call("b200rl_conv3x3_fwd_fused", x.data_ptr(), w.data_ptr(), b.data_ptr(), _cabi.ptr(res), _cabi.ptr(y),
+               _cabi.ptr(r), N, H, W, Cin, Cout, _stream())
+    return y, r

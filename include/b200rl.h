@@ -319,6 +319,14 @@ int32_t b200rl_conv3x3_fwd(
     const float *x, const float *weight, float *y, int64_t N, int64_t H, int64_t W, int64_t Cin, int64_t Cout,
     int32_t dgrad, void *stream);
 
+/* K11 forward with the residual block's elementwise tail in the epilogue (reference models/common.py:30-34):
+ * v = conv(x, weight) + bias[o] (+ res when res != NULL);  y = v when y != NULL;  relu_out = max(v, 0) when
+ * relu_out != NULL (at least one of the two).  `relu(conv0(.))` is (y, relu_out) = (NULL, r1); `conv1(.) + inputs`
+ * passes res = inputs and may also ask for the ReLU that opens the next block. */
+int32_t b200rl_conv3x3_fwd_fused(
+    const float *x, const float *weight, const float *bias, const float *res, float *y, float *relu_out, int64_t N,
+    int64_t H, int64_t W, int64_t Cin, int64_t Cout, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -246,3 +246,43 @@ def test_cnn_kernels_against_cpu_torch_ops(cuda):
     obs = torch.randint(0, 256, (2, 3, 8, 8), dtype=torch.uint8, generator=g)
     got = ops.obs_to_f32_nhwc(obs.to(cuda)).cpu()
     assert (got - obs.float() / 255.).abs().max().item() <= 6e-8      # CPU divides, CUDA multiplies by 1/255: 1 ulp
+
+
+@pytest.mark.parametrize("N,C,Cout,H,W", [(5, 16, 16, 32, 32), (3, 16, 32, 9, 16), (4, 32, 32, 8, 8), (2, 3, 16, 6, 64)])
+def test_conv3x3_fused_epilogue_exact_on_integers(cuda, N, C, Cout, H, W):
+    """K11 with bias / residual / ReLU in its epilogue == conv2d(x, w, bias) (+ res) and its ReLU; bit-identical on
+    TF32-exact integer data against an fp64 reference."""
+    x = (_rand((N, C, H, W), cuda, 41) * 4).round().clamp(-8, 8).contiguous(memory_format=CL)
+    w = (torch.randn(Cout, C, 3, 3, device=cuda) * 2).round().clamp(-4, 4).contiguous(memory_format=CL)
+    b = (torch.randn(Cout, device=cuda) * 4).round()
+    res = (_rand((N, Cout, H, W), cuda, 42) * 4).round().contiguous(memory_format=CL)
+    conv = F.conv2d(x.double(), w.double(), b.double(), padding=1)
+    y, r = ops.conv3x3_fwd_fused(x, w, b, res, want_y=True, want_r=True)
+    assert torch.equal(y, (conv + res.double()).float()) and torch.equal(r, F.relu(conv + res.double()).float())
+    y2, r2 = ops.conv3x3_fwd_fused(x, w, b, None, want_y=False, want_r=True)
+    assert y2 is None and torch.equal(r2, F.relu(conv).float())
+    y3, r3 = ops.conv3x3_fwd_fused(x, w, b, None, want_y=True, want_r=False)
+    assert r3 is None and torch.equal(y3, conv.float())
+
+
+@pytest.mark.parametrize("C", [16, 32])
+def test_conv_bias_act_autograd_matches_torch_residual_block(cuda, C):
+    """ResidualBlock (models/common.py:28-34) from the two fused pieces vs eager torch, forward and all gradients; the
+    convolutions multiply in TF32 on both sides (K11 / cuDNN), so TF32 tolerance."""
+    torch.manual_seed(7)
+    blk = models._Residual(C).to(cuda).to(memory_format=CL)
+    torch.nn.init.normal_(blk.conv0.bias, std=0.2)
+    torch.nn.init.normal_(blk.conv1.bias, std=0.2)
+    x = _rand((6, C, 16, 16), cuda, 43)
+    xa, xb = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    want = blk(xa)
+    r = F.relu(xb)
+    r1 = cnn_glue.conv_bias_relu(r, blk.conv0.weight, blk.conv0.bias)
+    got, got_r = cnn_glue.conv_bias_add(r1, blk.conv1.weight, blk.conv1.bias, xb, want_y=True, want_r=True)
+    assert (got - want).abs().max().item() <= 3e-3 * want.abs().max().item()
+    assert torch.equal(got_r, F.relu(got))
+    gy, gr = _rand(tuple(want.shape), cuda, 44), _rand(tuple(want.shape), cuda, 45)
+    grads_want = torch.autograd.grad((want * gy).sum() + (F.relu(want) * gr).sum(), [xa] + list(blk.parameters()))
+    grads_got = torch.autograd.grad((got * gy).sum() + (got_r * gr).sum(), [xb] + list(blk.parameters()))
+    for (n, _), a, b in zip([("x", None)] + list(blk.named_parameters()), grads_got, grads_want):
+        assert (a - b).abs().max().item() <= 5e-3 * b.abs().max().item(), n
