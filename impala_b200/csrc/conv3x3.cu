@@ -229,6 +229,149 @@ conv3x3_wgrad_kernel(const float *__restrict__ x, const float *__restrict__ dy, 
     }
 }
 
+// ---- K10, row-streaming variant for the wide, few-channel layers (W >= 32, at most 16 input channels) ----------------
+// In the kernel above a fragment of x feeds ONE MMA per output-channel tile, so at 16 channels the shared-memory pipe
+// (2.7 fragment words per MMA) binds before the tensor pipe does.  Here a warp owns a strip of 8 columns x 4 dy rows
+// and all three kernel rows of KWN column shifts: walking down the strip, the x fragment of tile row R meets the dy
+// rows R, R-1, R-2 as taps kh = 0, 1, 2 -- three MMAs per x fragment, with the dy fragments of the last three rows kept
+// in registers.  Two shapes, chosen by measurement (profiles/r01_conv_layers_bench.txt):
+//   W = 32: a warp owns all 3 shifts (0.9 fragment words per MMA, 72-144 accumulator registers, 8 warps):
+//           16 -> 16 channels 0.26 -> 0.21 ms, 16 -> 32 channels 0.47 -> 0.32 ms;
+//   W = 64: one shift per warp (1.3 words per MMA, 24 warps): 3 -> 16 channels 0.60 -> 0.54 ms.
+template <int CIN_P, int COUT, int W>
+struct Wg2 {
+    static constexpr int SPLIT = W == 64 ? 3 : 1;           // warps sharing a strip, each with 3 / SPLIT column shifts
+    static constexpr int RS = W == 32 ? 4 : 8;              // dy rows per warp
+    static constexpr bool use = W >= 32 && CIN_P <= 16 && (W == 64 || (COUT / 16) * (CIN_P / 8) <= 4);
+    static constexpr int warps = (W / 8) * (kWgTH / RS) * SPLIT;
+};
+
+template <int CIN_P, int COUT, int W>
+__global__ void __launch_bounds__(Wg2<CIN_P, COUT, W>::warps * 32, 1)
+conv3x3_wgrad_rows_kernel(const float *__restrict__ x, const float *__restrict__ dy, float *__restrict__ partials, int N, int H,
+                          int Cin, int n_tiles) {
+    constexpr int XS = WgStride<CIN_P>::value, DS = COUT + 8;
+    constexpr int MT = COUT / 16, NT = CIN_P / 8, WARPS = Wg2<CIN_P, COUT, W>::warps, THREADS = WARPS * 32;
+    constexpr int XBYTES = CIN_P == 8 ? 4 : 16;
+    constexpr int XW = W + 2;
+    constexpr int x_floats = (kWgTH + 2) * XW * XS, tile_floats = x_floats + kWgTH * W * DS;
+    constexpr int kWgStages = WgStages<CIN_P, COUT, W>::value, kWg2RS = Wg2<CIN_P, COUT, W>::RS;
+    constexpr int SPLIT = Wg2<CIN_P, COUT, W>::SPLIT, KWN = 3 / SPLIT;
+    extern __shared__ __align__(16) float smem[];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, gid = lane >> 2, tig = lane & 3;
+    const int kw0 = (warp % SPLIT) * KWN, strip = (warp / SPLIT) % (W / 8), seg = warp / (SPLIT * (W / 8));
+    const int tiles_per_image = (H + kWgTH - 1) / kWgTH;
+    const int x_per_row = W * Cin / (XBYTES / 4);
+    constexpr int dy_per_row = W * COUT / 4;
+    const RowPlan xplan = make_plan<THREADS>(x_per_row, XBYTES / 4, Cin, XS, 1);
+    const RowPlan dplan = make_plan<THREADS>(dy_per_row, 4, COUT, DS, 0);
+
+    float acc[3][KWN][MT][NT][4];
+#pragma unroll
+    for (int a = 0; a < 3; ++a)
+#pragma unroll
+        for (int b = 0; b < KWN; ++b)
+#pragma unroll
+            for (int c = 0; c < MT; ++c)
+#pragma unroll
+                for (int d = 0; d < NT; ++d)
+#pragma unroll
+                    for (int e = 0; e < 4; ++e) acc[a][b][c][d][e] = 0.f;
+
+    for (int i = tid; i < kWgStages * tile_floats; i += THREADS) smem[i] = 0.f;
+    __syncthreads();
+
+    auto stage = [&](int t, int b) {
+        if (t < n_tiles) {
+            float *xs = smem + b * tile_floats;
+            const int n = t / tiles_per_image, h0 = (t - n * tiles_per_image) * kWgTH;
+            stage_rows<XBYTES, THREADS>(xs, XW * XS, x, (long long)W * Cin, (long long)n * H, h0 - 1, kWgTH + 2, H, xplan,
+                                        x_per_row, Cin, XS, 1);
+            stage_rows<16, THREADS>(xs + x_floats, W * DS, dy, (long long)W * COUT, (long long)n * H, h0, kWgTH, H, dplan,
+                                    dy_per_row, COUT, DS, 0);
+        }
+        cp_async_commit();
+    };
+
+    // fragment bases of this warp inside a tile: dy row seg*RS, column strip*8 + tig; x tile row seg*RS, column strip*8 + tig
+    const int a_base = x_floats + ((seg * kWg2RS) * W + strip * 8 + tig) * DS + gid;
+    const int b_base = ((seg * kWg2RS) * XW + strip * 8 + tig + kw0) * XS + gid;
+
+    int tile = blockIdx.x, buf = 0;
+#pragma unroll
+    for (int k = 0; k < kWgStages - 1; ++k) stage(tile + k * gridDim.x, k);
+    for (; tile < n_tiles; tile += gridDim.x, buf = (buf + 1 == kWgStages ? 0 : buf + 1)) {
+        cp_async_wait_group<kWgStages - 2>();
+        __syncthreads();
+        stage(tile + (kWgStages - 1) * gridDim.x, buf == 0 ? kWgStages - 1 : buf - 1);
+        const float *tb = smem + buf * tile_floats;
+        float a[3][MT][4];                                   // dy fragments of the last three rows (slot = row % 3)
+#pragma unroll
+        for (int j = 0; j < kWg2RS + 2; ++j) {               // x tile row seg*RS + j  (image row h0 - 1 + seg*RS + j)
+            float b[KWN][NT][2];
+            const float *xp = tb + b_base + j * XW * XS;
+#pragma unroll
+            for (int k = 0; k < KWN; ++k)
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt) {
+                    b[k][nt][0] = tf32_rna(xp[k * XS + nt * 8]);
+                    b[k][nt][1] = tf32_rna(xp[(k + 4) * XS + nt * 8]);
+                }
+            if (j < kWg2RS) {
+                const float *dp = tb + a_base + j * W * DS;
+#pragma unroll
+                for (int mt = 0; mt < MT; ++mt) {
+                    a[j % 3][mt][0] = tf32_rna(dp[mt * 16]);
+                    a[j % 3][mt][1] = tf32_rna(dp[mt * 16 + 8]);
+                    a[j % 3][mt][2] = tf32_rna(dp[4 * DS + mt * 16]);
+                    a[j % 3][mt][3] = tf32_rna(dp[4 * DS + mt * 16 + 8]);
+                }
+            }
+#pragma unroll
+            for (int kh = 0; kh < 3; ++kh) {
+                const int jr = j - kh;                       // dy row (local) that sees x row j as kernel row kh
+                if (jr < 0 || jr >= kWg2RS) continue;
+#pragma unroll
+                for (int k = 0; k < KWN; ++k)
+#pragma unroll
+                    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+                        for (int nt = 0; nt < NT; ++nt)
+                            mma_tf32_16x8x8(acc[kh][k][mt][nt], a[jr % 3][mt], b[k][nt][0], b[k][nt][1]);
+            }
+        }
+    }
+    cp_async_wait_group<0>();
+    __syncthreads();
+
+    // ---- add the warps in order through shared memory: out[co][kh][kw][ci] (ci < CIN_P) ----
+    float *out = smem;
+    for (int g = 0; g < WARPS; ++g) {
+        if (warp == g) {
+#pragma unroll
+            for (int kh = 0; kh < 3; ++kh)
+#pragma unroll
+                for (int k = 0; k < KWN; ++k)
+#pragma unroll
+                    for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+                        for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                            for (int d = 0; d < 4; ++d) {
+                                const int co = mt * 16 + gid + ((d & 2) ? 8 : 0), ci = nt * 8 + 2 * tig + (d & 1);
+                                float *o = out + ((co * 3 + kh) * 3 + kw0 + k) * CIN_P + ci;
+                                *o = (g < SPLIT ? 0.f : *o) + acc[kh][k][mt][nt][d];   // the first SPLIT warps open their shifts
+                            }
+        }
+        __syncthreads();
+    }
+    float *dst = partials + (long long)blockIdx.x * COUT * 9 * Cin;
+    for (int i = tid; i < COUT * 9 * Cin; i += THREADS) {
+        const int ci = i % Cin, rest = i / Cin;
+        dst[i] = out[rest * CIN_P + ci];
+    }
+}
+
 template <int CIN_P, int COUT, int W>
 static int32_t launch_wgrad(const float *x, const float *dy, float *partials, int N, int H, int Cin, int n_ctas,
                             cudaStream_t stream) {
@@ -243,16 +386,28 @@ static int32_t launch_wgrad(const float *x, const float *dy, float *partials, in
     static int configured[64] = {};
     int dev = 0;
     cudaGetDevice(&dev);
-    if (dev < 64 && !configured[dev]) {
-        if (cudaFuncSetAttribute(conv3x3_wgrad_kernel<CIN_P, COUT, W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 smem <= 227 * 1024 ? smem : 0) != cudaSuccess)
-            return check_launch("conv3x3_wgrad: shared-memory opt-in");
-        configured[dev] = 1;
-    }
     const int n_tiles = N * ((H + kWgTH - 1) / kWgTH);
-    conv3x3_wgrad_kernel<CIN_P, COUT, W><<<n_ctas, WgWarps<CIN_P, COUT>::value * 32, smem, stream>>>(x, dy, partials, N, H,
-                                                                                                  Cin, n_tiles);
-    return check_launch("conv3x3_wgrad_kernel");
+    if constexpr (Wg2<CIN_P, COUT, W>::use) {
+        if (dev < 64 && !configured[dev]) {
+            if (cudaFuncSetAttribute(conv3x3_wgrad_rows_kernel<CIN_P, COUT, W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     smem <= 227 * 1024 ? smem : 0) != cudaSuccess)
+                return check_launch("conv3x3_wgrad: shared-memory opt-in");
+            configured[dev] = 1;
+        }
+        conv3x3_wgrad_rows_kernel<CIN_P, COUT, W><<<n_ctas, Wg2<CIN_P, COUT, W>::warps * 32, smem, stream>>>(
+            x, dy, partials, N, H, Cin, n_tiles);
+        return check_launch("conv3x3_wgrad_rows_kernel");
+    } else {
+        if (dev < 64 && !configured[dev]) {
+            if (cudaFuncSetAttribute(conv3x3_wgrad_kernel<CIN_P, COUT, W>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     smem <= 227 * 1024 ? smem : 0) != cudaSuccess)
+                return check_launch("conv3x3_wgrad: shared-memory opt-in");
+            configured[dev] = 1;
+        }
+        conv3x3_wgrad_kernel<CIN_P, COUT, W><<<n_ctas, WgWarps<CIN_P, COUT>::value * 32, smem, stream>>>(x, dy, partials, N,
+                                                                                                      H, Cin, n_tiles);
+        return check_launch("conv3x3_wgrad_kernel");
+    }
 }
 
 template <int CIN_P, int COUT>
