@@ -591,24 +591,148 @@ conv3x3_fwd_kernel(const float *__restrict__ x, const float *__restrict__ wgt, f
     cp_async_wait_group<0>();
 }
 
+// ---- K11, row-streaming variant for the 16-output-channel layers at W >= 32 ------------------------------------------
+// With 16 output channels an x fragment feeds only two MMAs above, and the weights are re-read from shared memory for
+// every m-tile: 3 fragment words per MMA.  Here the whole weight tensor lives in REGISTERS (9 taps x Cin/8 x 2 n-tiles
+// x 2 words = 72 at 16 -> 16 channels) and a warp walks down a strip of 16 columns: the x fragments of tile row j
+// (column shift kw, 8 input channels) feed the output rows j, j-1, j-2 as kernel rows kh = 0, 1, 2 -- six MMAs per
+// fragment, 0.67 words per MMA -- with three rolling accumulator rows; a row is stored as soon as its third x row is done.
+template <int CIN_P, int COUT, int W>
+struct Fw2 {
+    static constexpr bool use = COUT == 16 && CIN_P <= 16 && W >= 32;
+    static constexpr int RS = 4;                            // output rows per warp
+    static constexpr int warps = (W / 16) * (kFwTH / RS);
+};
+
 template <int CIN_P, int COUT, int W, bool DGRAD>
-static int32_t launch_fwd(const float *x, const float *wgt, float *y, FwEpilogue ep, int N, int H, int Cin, cudaStream_t stream) {
-    constexpr int XS = CIN_P + 4, WS = COUT + 8;
-    constexpr int smem = 4 * (9 * CIN_P * WS + 2 * (kFwTH + 2) * (W + 2) * XS);
-    if (smem > 227 * 1024) {
-        set_error("conv3x3_fwd: Cin=%d Cout=%d W=%d needs %d bytes of shared memory", Cin, COUT, W, smem);
-        return -2;
+__global__ void __launch_bounds__(Fw2<CIN_P, COUT, W>::warps * 32)
+conv3x3_fwd_rows_kernel(const float *__restrict__ x, const float *__restrict__ wgt, float *__restrict__ y, FwEpilogue ep, int N,
+                        int H, int Cin, int n_tiles) {
+    constexpr int XS = CIN_P + 4;
+    constexpr int WARPS = Fw2<CIN_P, COUT, W>::warps, THREADS = WARPS * 32, RS = Fw2<CIN_P, COUT, W>::RS;
+    constexpr int XW = W + 2, x_floats = (kFwTH + 2) * XW * XS;
+    constexpr int NT = COUT / 8, KC = CIN_P / 8;
+    constexpr int XBYTES = CIN_P == 8 ? 4 : 16;
+    extern __shared__ __align__(16) float smem[];
+    float *xbuf = smem;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, gid = lane >> 2, tig = lane & 3;
+    const int strip = warp % (W / 16), seg = warp / (W / 16);
+    const int tiles_per_image = (H + kFwTH - 1) / kFwTH;
+    const int x_per_row = W * Cin / (XBYTES / 4);
+    const RowPlan xplan = make_plan<THREADS>(x_per_row, XBYTES / 4, Cin, XS, 1);
+
+    // this lane's B fragments of every tap: b0 = w'[tap][i = kc*8 + tig][o = nt*8 + gid], b1 = same at i + 4
+    float bw[9][KC][NT][2];
+#pragma unroll
+    for (int tap = 0; tap < 9; ++tap)
+#pragma unroll
+        for (int kc = 0; kc < KC; ++kc)
+#pragma unroll
+            for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                for (int hf = 0; hf < 2; ++hf) {
+                    const int c = kc * 8 + tig + 4 * hf, o = nt * 8 + gid;
+                    float v = 0.f;
+                    if (c < Cin)
+                        v = DGRAD ? __ldg(wgt + ((long long)c * 9 + (8 - tap)) * COUT + o)
+                                  : __ldg(wgt + ((long long)o * 9 + tap) * Cin + c);
+                    bw[tap][kc][nt][hf] = tf32_rna(v);
+                }
+    for (int i = tid; i < 2 * x_floats; i += THREADS) xbuf[i] = 0.f;
+    __syncthreads();
+
+    auto stage = [&](int t, int b) {
+        if (t < n_tiles) {
+            const int n = t / tiles_per_image, h0 = (t - n * tiles_per_image) * kFwTH;
+            stage_rows<XBYTES, THREADS>(xbuf + b * x_floats, XW * XS, x, (long long)W * Cin, (long long)n * H, h0 - 1, kFwTH + 2,
+                                        H, xplan, x_per_row, Cin, XS, 1);
+        }
+        cp_async_commit();
+    };
+
+    const int a_base = ((seg * RS) * XW + strip * 16 + gid) * XS + tig;   // tile row seg*RS, column strip*16 + gid (kw = 0)
+    int tile = blockIdx.x, buf = 0;
+    stage(tile, 0);
+    for (; tile < n_tiles; tile += gridDim.x, buf ^= 1) {
+        stage(tile + gridDim.x, buf ^ 1);
+        cp_async_wait_group<1>();
+        __syncthreads();
+        const float *xs = xbuf + buf * x_floats + a_base;
+        const int n = tile / tiles_per_image, h0 = (tile - n * tiles_per_image) * kFwTH;
+        float acc[3][NT][4];
+#pragma unroll
+        for (int a = 0; a < 3; ++a)
+#pragma unroll
+            for (int b = 0; b < NT; ++b)
+#pragma unroll
+                for (int d = 0; d < 4; ++d) acc[a][b][d] = 0.f;
+#pragma unroll
+        for (int j = 0; j < RS + 2; ++j) {                  // x tile row seg*RS + j
+#pragma unroll
+            for (int kw = 0; kw < 3; ++kw)
+#pragma unroll
+                for (int kc = 0; kc < KC; ++kc) {
+                    const float *ap = xs + (j * XW + kw) * XS + kc * 8;
+                    float a[4];
+                    a[0] = tf32_rna(ap[0]);
+                    a[1] = tf32_rna(ap[8 * XS]);
+                    a[2] = tf32_rna(ap[4]);
+                    a[3] = tf32_rna(ap[8 * XS + 4]);
+#pragma unroll
+                    for (int kh = 0; kh < 3; ++kh) {
+                        const int i = j - kh;               // output row (local) that sees x row j as kernel row kh
+                        if (i < 0 || i >= RS) continue;
+#pragma unroll
+                        for (int nt = 0; nt < NT; ++nt)
+                            mma_tf32_16x8x8(acc[i % 3][nt], a, bw[kh * 3 + kw][kc][nt][0], bw[kh * 3 + kw][kc][nt][1]);
+                    }
+                }
+            if (j >= 2) {                                    // output row j - 2 has seen its three x rows: store, recycle
+                const int i = j - 2, h = h0 + seg * RS + i;
+#pragma unroll
+                for (int half = 0; half < 2; ++half) {
+                    if (h < H) {
+                        const long long off = (((long long)n * H + h) * W + strip * 16 + gid + 8 * half) * COUT + 2 * tig;
+#pragma unroll
+                        for (int nt = 0; nt < NT; ++nt) {
+                            float2 v = make_float2(acc[i % 3][nt][2 * half], acc[i % 3][nt][2 * half + 1]);
+                            if (ep.bias) {
+                                const float2 b = __ldg(reinterpret_cast<const float2 *>(ep.bias + nt * 8 + 2 * tig));
+                                v.x += b.x; v.y += b.y;
+                            }
+                            if (ep.res) {
+                                const float2 s2 = __ldcs(reinterpret_cast<const float2 *>(ep.res + off + nt * 8));
+                                v.x = s2.x + v.x; v.y = s2.y + v.y;
+                            }
+                            if (y) __stcs(reinterpret_cast<float2 *>(y + off + nt * 8), v);
+                            if (ep.relu_out)
+                                __stcs(reinterpret_cast<float2 *>(ep.relu_out + off + nt * 8),
+                                       make_float2(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f)));
+                        }
+                    }
+                }
+#pragma unroll
+                for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+                    for (int d = 0; d < 4; ++d) acc[i % 3][nt][d] = 0.f;
+            }
+        }
+        __syncthreads();
     }
-    static int ctas_per_sm[64] = {};
+    cp_async_wait_group<0>();
+}
+
+template <typename Kern>
+static int32_t launch_fwd_persistent(Kern kern, int threads, int smem, int *ctas_per_sm, const float *x, const float *wgt,
+                                     float *y, FwEpilogue ep, int N, int H, int Cin, cudaStream_t stream) {
     int dev = 0;
     cudaGetDevice(&dev);
     if (dev >= 64) dev = 63;
-    auto kern = conv3x3_fwd_kernel<CIN_P, COUT, W, DGRAD>;
     if (!ctas_per_sm[dev]) {
-        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem <= 227 * 1024 ? smem : 0) != cudaSuccess)
+        if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
             return check_launch("conv3x3_fwd: shared-memory opt-in");
         int nb = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, FwWarps<W>::value * 32, smem) != cudaSuccess || nb < 1)
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kern, threads, smem) != cudaSuccess || nb < 1)
             return check_launch("conv3x3_fwd: occupancy query");
         ctas_per_sm[dev] = nb;
     }
@@ -617,8 +741,27 @@ static int32_t launch_fwd(const float *x, const float *wgt, float *y, FwEpilogue
     const int n_tiles = N * ((H + kFwTH - 1) / kFwTH);
     int grid = sms * ctas_per_sm[dev];
     if (grid > n_tiles) grid = n_tiles;
-    kern<<<grid, FwWarps<W>::value * 32, smem, stream>>>(x, wgt, y, ep, N, H, Cin, n_tiles);
+    kern<<<grid, threads, smem, stream>>>(x, wgt, y, ep, N, H, Cin, n_tiles);
     return check_launch("conv3x3_fwd_kernel");
+}
+
+template <int CIN_P, int COUT, int W, bool DGRAD>
+static int32_t launch_fwd(const float *x, const float *wgt, float *y, FwEpilogue ep, int N, int H, int Cin, cudaStream_t stream) {
+    constexpr int XS = CIN_P + 4, WS = COUT + 8;
+    static int ctas_per_sm[64] = {};
+    if constexpr (Fw2<CIN_P, COUT, W>::use) {               // weights in registers: the tile buffers are all of it
+        constexpr int smem = 4 * 2 * (kFwTH + 2) * (W + 2) * XS;
+        return launch_fwd_persistent(conv3x3_fwd_rows_kernel<CIN_P, COUT, W, DGRAD>, Fw2<CIN_P, COUT, W>::warps * 32, smem,
+                                     ctas_per_sm, x, wgt, y, ep, N, H, Cin, stream);
+    } else {
+        constexpr int smem = 4 * (9 * CIN_P * WS + 2 * (kFwTH + 2) * (W + 2) * XS);
+        if (smem > 227 * 1024) {
+            set_error("conv3x3_fwd: Cin=%d Cout=%d W=%d needs %d bytes of shared memory", Cin, COUT, W, smem);
+            return -2;
+        }
+        return launch_fwd_persistent(conv3x3_fwd_kernel<CIN_P, COUT, W, DGRAD>, FwWarps<W>::value * 32, smem, ctas_per_sm, x,
+                                     wgt, y, ep, N, H, Cin, stream);
+    }
 }
 
 template <int CIN_P, int COUT, bool DGRAD>
