@@ -1,5 +1,6 @@
-// K9: the memory-bound glue of the IMPALA-CNN between its cuDNN convolutions (BASELINE config 5).
-// The convolutions stay in cuDNN; everything else of reference models/common.py:8-83 (ResidualBlock, ImpalaCNNBlock,
+// K9: the memory-bound glue of the IMPALA-CNN between its convolutions (BASELINE config 5).
+// The convolutions are K10/K11 (conv3x3.cu; cuDNN for 32 -> 32 channels); everything else of reference
+// models/common.py:8-83 (ResidualBlock, ImpalaCNNBlock,
 // ImpalaCNNLarge) -- bias adds, ReLUs, residual adds, 3x3/2 max-pools, their backward passes and the bias gradients --
 // is HBM-bound byte shuffling that eager PyTorch spreads over ~25 % of the learner step (max_pool_backward_nhwc alone
 // 8.7 ms of 41 ms at B=256, T=20).  All tensors are fp32 NHWC (torch channels_last), C % 4 == 0, one float4 = 4
@@ -9,7 +10,7 @@
 //                        times the fp32 reciprocal) + NCHW -> NHWC, one pass
 //   maxpool3x3s2_fwd     p = max_pool2d(u + bias[c], 3, 2, 1) (the bias of the preceding conv, added per tap so that ties
 //                        break as in torch), optional second output relu(p), 1-byte argmax code (kh*3+kw) per element
-//   maxpool3x3s2_bwd     gather form (each input pixel looks at the <= 4 windows that contain it): no atomics,
+//   maxpool3x3s2_bwd     gather form (a thread owns a 2x2 input patch and the 4 windows that cover it): no atomics,
 //                        deterministic
 //   bias_act_fwd         y = u + bias[c] (+ res);  optional outputs y and relu(y)
 //   relu_bwd_add         g = dy + dr * (r > 0)  (either term optional), per-CTA per-channel sums of g -> partials
