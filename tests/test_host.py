@@ -125,3 +125,26 @@ def test_flat_view_keeps_memory_format():
     assert torch.equal(flat[5 + w.numel():], b) and flat[:5].abs().sum() == 0
     wc = torch.randn(8, 4, 3, 3)                                # plain contiguous weight: plain view
     assert flat_view(torch.zeros(wc.numel()), 0, wc).is_contiguous()
+
+
+def test_fused_model_host_contract():
+    """K9-K11 host side, no kernel calls: the fused model has the eager model's parameters and state dict, refuses CPU
+    tensors (no fallback) and non-channels_last construction; the shape predicate matches the C ABI's supported set."""
+    from impala_b200 import cnn_glue, ops
+    eager = models.ActorCritic((3, 64, 64), 15, body="impala", channels_last=True)
+    fused = models.ActorCritic((3, 64, 64), 15, body="impala", channels_last=True, fused_glue=True)
+    assert [(n, tuple(p.shape)) for n, p in eager.named_parameters()] == [(n, tuple(p.shape)) for n, p in fused.named_parameters()]
+    fused.load_state_dict(eager.state_dict())
+    assert sum(p.numel() for p in fused.parameters()) == 630_352
+    with pytest.raises(RuntimeError):
+        fused(torch.zeros(2, 3, 64, 64, dtype=torch.uint8))                  # CPU tensor: raises, never falls back
+    with pytest.raises(RuntimeError):
+        models.ActorCritic((3, 64, 64), 15, body="impala", channels_last=False, fused_glue=True)
+    with pytest.raises(RuntimeError):
+        models.ActorCritic((3, 64, 64), 15, body="nature", channels_last=True, fused_glue=True)
+    for shape, cout, want in (((8, 3, 64, 64), 16, True), ((8, 16, 32, 32), 16, True), ((8, 16, 32, 32), 32, True),
+                              ((8, 32, 16, 16), 32, True), ((8, 32, 8, 8), 32, True), ((8, 16, 12, 24), 16, False),
+                              ((8, 8, 32, 32), 16, False), ((8, 16, 32, 32), 64, False), ((8, 16, 32, 128), 16, False)):
+        assert ops.conv3x3_wgrad_supported(shape, cout) is want, (shape, cout)
+    w3232, w1616 = torch.zeros(32, 32, 3, 3), torch.zeros(16, 16, 3, 3)
+    assert not cnn_glue._k11_wins(w3232) and cnn_glue._k11_wins(w1616)       # 32 -> 32 forward / dgrad stay on cuDNN
