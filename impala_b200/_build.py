@@ -14,6 +14,7 @@ LIB_PATH = os.path.join(OUT_DIR, "libb200rl.so")
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
     "--expt-extended-lambda", "-Xcompiler", "-fPIC", "-shared",
+    "--threads", "0",                    # the .cu files compile in parallel (conv3x3.cu alone is ~70 s of templates)
 ]
 
 
