@@ -26,7 +26,10 @@ def timeit(fn, reps=20):
     return e0.elapsed_time(e1) / reps
 
 
+ONLY = os.environ.get("LAYERS")
 for name, cin, cout, hw in LAYERS:
+    if ONLY and name not in ONLY.split(","):
+        continue
     x = torch.randn(N, cin, hw, hw, device=dev).contiguous(memory_format=CL)
     dy = torch.randn(N, cout, hw, hw, device=dev).contiguous(memory_format=CL)
     w = torch.randn(cout, cin, 3, 3, device=dev).contiguous(memory_format=CL)
