@@ -21,6 +21,8 @@ fixture                reference code that ran                                 t
 ``ref_impala_loss``    ``losses.impala_loss`` (``losses.py:92-128``)           same shim
 ``ref_make_replay``    ``ImpalaActor._make_replay``                            none (``moolib.Batcher`` shim only hands the
                        (``agents/impala/learning.py:77-80``)                   stacked tensors back)
+``ref_apex_replay``    ``ApexActor._async_make_replay``                        ``rlego.n_step_bootstrapped_returns`` (shim)
+                       (``agents/dqn/learning.py:56-65``)                      -> pins slicing, discount, priorities
 ``ref_models``         ``models.models.AtariActorCritic`` over ``AtariBody``   none -> parameter counts / output shapes
                        and ``ImpalaCNNLarge`` (``models/common.py:64-126``)
 =====================  =====================================================  ==========================================
@@ -82,7 +84,8 @@ def _collate_nested(fn, items):
 
 
 def _unbatch_nested(fn, nested, batch_size):
-    return [_map_nested(lambda x, i=i: fn(x[i]), nested) for i in range(batch_size)]
+    mapped = _map_nested(fn, nested)                           # fn sees the whole leaf (call sites unsqueeze dim 1), then dim 0 is unbound
+    return [_map_nested(lambda x, i=i: x[i], mapped) for i in range(batch_size)]
 
 
 class _Batcher:                                   # moolib.Batcher: only ever asked for what was stacked
@@ -119,6 +122,7 @@ def install_shims():
     _pkg("agents", os.path.join(REF, "agents"))
     _pkg("agents.impala", os.path.join(REF, "agents", "impala"))
     _pkg("agents.ppo", os.path.join(REF, "agents", "ppo"))
+    _pkg("agents.dqn", os.path.join(REF, "agents", "dqn"))
     sys.path.insert(0, REF)
     sys.modules["models.distributed_models"] = _mod("models.distributed_models")   # only get_muesli (dead) uses it
 
@@ -248,6 +252,27 @@ def ref_make_replay(learning):
     _save("ref_make_replay", done=done, discount=out[3], gamma=np.float64(0.99))
 
 
+def ref_apex_replay(dqn_learning):
+    """``ApexActor._async_make_replay`` (``agents/dqn/learning.py:56-65``): discount from done flags, 3-step bootstrapped
+    targets on ``(r[:-1], discount[:-1], q_star[1:])``, priorities ``|target - q_pi[:-1]|``."""
+    import asyncio
+    g = torch.Generator().manual_seed(4700)
+    T = 40
+    s = torch.zeros(T, 1)
+    a = torch.randint(0, 15, (T, 1), generator=g)
+    r = torch.randn(T, 1, generator=g)
+    done = torch.rand(T, 1, generator=g) < 0.1
+    q_pi = torch.randn(T, 1, generator=g)
+    q_star = q_pi + torch.rand(T, 1, generator=g)
+    actor = dqn_learning.ApexActor(None, None, n_step=3, rollout_length=T, gamma=0.99)
+    actor._trajectory.data = (s, a, r, done, q_pi, q_star)
+    replay, priorities = asyncio.run(actor._async_make_replay())
+    target = torch.cat([item[2] for item in replay])
+    assert len(replay) == T - 1 and target.shape == (T - 1,)
+    _save("ref_apex_replay", r=r.squeeze(1), done=done.squeeze(1), q_pi=q_pi.squeeze(1), q_star=q_star.squeeze(1),
+          target=target, priorities=priorities, n_step=np.int64(3), gamma=np.float64(0.99))
+
+
 def ref_models():
     mm = importlib.import_module("models.models")
     mc = importlib.import_module("models.common")
@@ -278,6 +303,7 @@ def main():
     ref_ppo_step(importlib.import_module("agents.ppo.learning"))
     ref_impala_loss(losses)
     ref_make_replay(learning)
+    ref_apex_replay(importlib.import_module("agents.dqn.learning"))
     ref_models()
 
 

@@ -110,3 +110,15 @@ def test_impala_loss_as_written_equals_reference_run(cuda):
         assert m[k].item() == pytest.approx(z["metrics"][i], rel=2e-5, abs=2e-6), k
     assert_close(model.logits.grad, torch.from_numpy(z["dlogits"]), "dlogits", rel_to_max=2e-5)
     assert_close(model.values.grad, torch.from_numpy(z["dvalues"]), "dvalues", rel_to_max=2e-5)
+
+
+def test_n_step_returns_equal_reference_apex_actor(cuda):
+    """N4 kernel on the exact tensors the reference's ApexActor hands to rlego (agents/dqn/learning.py:56-65): bit-exact."""
+    from impala_b200 import vtrace
+    from impala_b200.agents.impala import make_discount
+    z = np.load(os.path.join(GOLDEN, "ref_apex_replay.npz"))
+    r, done, q_pi, q_star = (torch.from_numpy(z[k]).to(cuda) for k in ("r", "done", "q_pi", "q_star"))
+    discount = make_discount(done, float(z["gamma"]))
+    target = vtrace.n_step_bootstrapped_returns(r[:-1], discount[:-1], q_star[1:], n=int(z["n_step"]))
+    assert torch.equal(target.cpu(), torch.from_numpy(z["target"]))
+    assert torch.equal((target - q_pi[:-1]).abs().cpu(), torch.from_numpy(z["priorities"]))

@@ -110,3 +110,15 @@ def test_make_discount_and_model_shapes_equal_reference_run():
     p, v = nature(x)
     assert list(p.shape) == list(zm["atari_ac_logits_shape"]) and list(v.shape) == list(zm["atari_ac_value_shape"])
     assert list(impala.body(x).shape) == list(zm["impala_cnn_out"])
+
+
+def test_oracle_n_step_targets_equal_reference_apex_actor():
+    """``ApexActor._async_make_replay`` (agents/dqn/learning.py:56-65) ran here with the rlego shim: pins the call-site
+    slicing ``(r[:-1], discount[:-1], q_star[1:])``, ``discount = logical_not(done) * gamma`` and the priorities."""
+    from oracle import rlego_ref
+    z = np.load(os.path.join(GOLDEN, "ref_apex_replay.npz"))
+    r, done, q_pi, q_star = (torch.from_numpy(z[k]) for k in ("r", "done", "q_pi", "q_star"))
+    discount = torch.logical_not(done) * float(z["gamma"])
+    target = rlego_ref.n_step_bootstrapped_returns(r[:-1], discount[:-1], q_star[1:], n=int(z["n_step"]))
+    assert np.array_equal(target.numpy(), z["target"])
+    assert np.array_equal((target - q_pi[:-1]).abs().numpy(), z["priorities"])
