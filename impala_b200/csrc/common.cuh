@@ -42,8 +42,8 @@ inline int32_t ensure_dynamic_smem(F func, size_t bytes, size_t (&cache)[kMaxDev
     } while (0)
 
 constexpr int kNumScalars = 8;
-// workspace layout: 256 B reserved, then the published partial sums, uint64 words [8][kMaxPartialCtas]
-// (tag << 32 | float bits), then the trace area.
+// workspace layout: 256 B header (uint32 launch generation, uint32 poisoned; see grid_collect), then the
+// published partial sums, uint64 words [8][kMaxPartialCtas] (launch tag << 32 | float bits), then the trace area.
 constexpr int kMaxPartialCtas = 16384;
 constexpr int64_t kTraceOffset = 256 + (int64_t)kMaxPartialCtas * kNumScalars * 8;
 // B200RL_TRACE: [kMaxTraceCtas][16] uint64 per CTA: 8 %globaltimer stamps then 8 clock64 stamps (profiling aid)
@@ -224,36 +224,59 @@ __device__ __forceinline__ void st_volatile_u64(unsigned long long *p, unsigned 
     asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
-// Deterministic grid-wide sum of NV per-thread values, without fences or atomics.
+__device__ __forceinline__ unsigned int ld_volatile_u32(const unsigned int *p) {
+    unsigned int v;
+    asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_volatile_u32(unsigned int *p, unsigned int v) {
+    asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Deterministic grid-wide sum of NV per-CTA partial sums, without fences or atomics.
 //
-// Every CTA reduces its values (cta_sum) and PUBLISHES each partial sum as one 64-bit word
-// (valid tag << 32 | float bits) with a single store: the flag travels with the data, so no
-// fence is needed and the CTA retires immediately.  The CTA with the highest blockIdx -- the
-// last one the hardware dispatches, so every CTA it waits for is already resident or done --
-// collects the words in a fixed order, clears them for the next launch, and hands the totals
-// to `finalize(sums)` (one thread).  workspace: zero-initialised once; left zeroed.
-// `red`: shared scratch of NV * blockDim.x floats.  All threads must call.
-// `before_publish()` runs in every thread right before the workspace is touched (PDL wait).
-// A collector that sees no progress for kSpinLimitCycles gives up and reports NaN sums
-// instead of hanging the GPU.
+// Workspace header (the first 256 bytes): uint32 generation, uint32 poisoned.  Every CTA PUBLISHES each
+// partial as one 64-bit word (launch tag << 32 | float bits) with a single store: the tag travels with
+// the data, so no fence is needed and the CTA retires immediately.  The tag is the workspace's launch
+// generation + 1 (never 0): words are never cleared, a word of an older launch can not be mistaken for
+// this launch's.  One collector CTA (the highest blockIdx: normally dispatched last, so it rarely waits)
+// polls the words until every one carries this launch's tag, sums them in a fixed order --
+// deterministic, bit-reproducible scalars -- hands the totals to `finalize(sums)` (one thread) and
+// bumps the generation.
+//
+// Forward progress does NOT depend on the dispatch order: the polling CTA holds one CTA slot of one SM;
+// every other CTA of the grid only needs some slot somewhere on the GPU and never waits for anything,
+// so all of them publish eventually whatever order the hardware picks.  Only the polling time depends
+// on the order.  A collector that still sees a missing word after kSpinLimitCycles (~1 s: the GPU is
+// wedged by something else) reports NaN sums and POISONS the workspace: every later launch on it
+// reports NaN too, until the owner zeroes the workspace again -- a stale word can therefore never be
+// summed silently.
+//
+// The generation is read after `before_publish()` (the PDL wait): the previous launch on this
+// workspace has completed by then, its collector included.
 constexpr long long kSpinLimitCycles = 1ll << 31;
 
-template <int NV, typename Finalize, typename BeforePublish>
-__device__ __forceinline__ void grid_reduce(float (&vals)[NV], float *red, void *workspace,
-                                            Finalize finalize, BeforePublish before_publish) {
+// tot[k]: this CTA's partial sums, valid in thread 0..NV-1 at least (cta_sum leaves them in all of warp 0).
+// `red`: shared scratch of NV * blockDim.x floats.  All threads of the CTA must call.
+__device__ __forceinline__ unsigned int grid_generation(const void *workspace) {
+    return ld_volatile_u32(reinterpret_cast<const unsigned int *>(workspace));
+}
+
+template <int NV, typename Finalize>
+__device__ __forceinline__ void grid_collect(const float (&tot)[NV], float *red, void *workspace,
+                                             unsigned int gen, Finalize finalize) {
     static_assert(NV <= kNumScalars, "partials rows");
+    unsigned int *hdr = reinterpret_cast<unsigned int *>(workspace);
     unsigned long long *words =
         reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(workspace) + 256);
-    float tot[NV];
-    cta_sum<NV>(vals, red, tot);
-    before_publish();
+    const unsigned int tag = (gen & 0x7fffffffu) + 1u;
     const unsigned int n_other = gridDim.x - 1;
     if (blockIdx.x != n_other) {
 #pragma unroll
         for (int k = 0; k < NV; ++k)
             if (threadIdx.x == k)
                 st_volatile_u64(&words[k * kMaxPartialCtas + blockIdx.x],
-                                (1ull << 32) | (unsigned long long)__float_as_uint(tot[k]));
+                                ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(tot[k]));
         return;
     }
     // collector
@@ -262,6 +285,7 @@ __device__ __forceinline__ void grid_reduce(float (&vals)[NV], float *red, void 
 #pragma unroll
     for (int k = 0; k < NV; ++k) acc[k] = 0.f;
     const long long t0 = clock64();
+    bool timed_out = false;
     for (unsigned int c0 = threadIdx.x; c0 < n_other; c0 += U * blockDim.x) {
         unsigned long long w[U][NV];
         bool all;
@@ -272,30 +296,104 @@ __device__ __forceinline__ void grid_reduce(float (&vals)[NV], float *red, void 
                 const unsigned int c = c0 + u * blockDim.x;
 #pragma unroll
                 for (int k = 0; k < NV; ++k) {
-                    w[u][k] = c < n_other ? ld_volatile_u64(&words[k * kMaxPartialCtas + c]) : (1ull << 32);
-                    all = all && (w[u][k] >> 32) != 0ull;
+                    w[u][k] = c < n_other ? ld_volatile_u64(&words[k * kMaxPartialCtas + c]) : ((unsigned long long)tag << 32);
+                    all = all && (unsigned int)(w[u][k] >> 32) == tag;
                 }
             }
         } while (!all && clock64() - t0 < kSpinLimitCycles);
+        timed_out = timed_out || !all;
 #pragma unroll
-        for (int u = 0; u < U; ++u) {
-            const unsigned int c = c0 + u * blockDim.x;
+        for (int u = 0; u < U; ++u)
 #pragma unroll
-            for (int k = 0; k < NV; ++k) {
-                acc[k] += all ? __uint_as_float((unsigned int)w[u][k]) : __int_as_float(0x7fc00000);
-                if (c < n_other) st_volatile_u64(&words[k * kMaxPartialCtas + c], 0ull);
-            }
-        }
+            for (int k = 0; k < NV; ++k) acc[k] += __uint_as_float((unsigned int)w[u][k]);
     }
+    if (timed_out) st_volatile_u32(hdr + 1, 1u);
     float own[NV];
 #pragma unroll
-    for (int k = 0; k < NV; ++k) own[k] = tot[k];  // valid in warp 0
-    __syncthreads();  // warp 0 is done reading `red` from the first cta_sum
-    cta_sum<NV>(acc, red, tot);
+    for (int k = 0; k < NV; ++k) own[k] = tot[k];
+    __syncthreads();  // `red` may still be read by warp 0 (the caller's cta_sum); the poison store is ordered too
+    float all_tot[NV];
+    cta_sum<NV>(acc, red, all_tot);
     if (threadIdx.x == 0) {
+        const bool poisoned = ld_volatile_u32(hdr + 1) != 0u;
 #pragma unroll
-        for (int k = 0; k < NV; ++k) tot[k] += own[k];
-        finalize(tot);
+        for (int k = 0; k < NV; ++k) all_tot[k] = poisoned ? __int_as_float(0x7fc00000) : all_tot[k] + own[k];
+        finalize(all_tot);
+        st_volatile_u32(hdr, gen + 1u);
+    }
+}
+
+// Grid-wide sum of NV per-thread values: CTA reduction (cta_sum) then grid_collect.
+// `before_publish()` runs in every thread right before the workspace is touched (PDL wait).
+template <int NV, typename Finalize, typename BeforePublish>
+__device__ __forceinline__ void grid_reduce(float (&vals)[NV], float *red, void *workspace,
+                                            Finalize finalize, BeforePublish before_publish) {
+    float tot[NV];
+    cta_sum<NV>(vals, red, tot);
+    before_publish();
+    grid_collect<NV>(tot, red, workspace, grid_generation(workspace), finalize);
+}
+
+// The same protocol for small persistent grids (gridDim.x <= a few hundred), run by ONE WARP of each CTA:
+// no block-wide barrier anywhere.  tot[k] must be valid in every lane of the calling warp.  The collector
+// warp's lanes take CTAs lane, lane + 32, ... and the partials are summed in a fixed order.
+template <int NV, typename Finalize>
+__device__ __forceinline__ void warp_collect(const float (&tot)[NV], void *workspace, unsigned int gen,
+                                             Finalize finalize) {
+    static_assert(NV <= kNumScalars, "partials rows");
+    unsigned int *hdr = reinterpret_cast<unsigned int *>(workspace);
+    unsigned long long *words =
+        reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(workspace) + 256);
+    const unsigned int tag = (gen & 0x7fffffffu) + 1u;
+    const unsigned int n_other = gridDim.x - 1, lane = threadIdx.x & 31;
+    if (blockIdx.x != n_other) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k)
+            if (lane == k)
+                st_volatile_u64(&words[k * kMaxPartialCtas + blockIdx.x],
+                                ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(tot[k]));
+        return;
+    }
+    float acc[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) acc[k] = 0.f;
+    const long long t0 = clock64();
+    bool timed_out = false;
+    constexpr int U = 5;  // CTAs per lane per batch: all U * NV loads are in flight together (160 CTAs = one batch)
+    for (unsigned int c0 = lane; c0 < n_other; c0 += 32 * U) {
+        unsigned long long w[U][NV];
+        bool all;
+        do {
+            all = true;
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const unsigned int c = c0 + 32 * u;
+#pragma unroll
+                for (int k = 0; k < NV; ++k) {
+                    w[u][k] = c < n_other ? ld_volatile_u64(&words[k * kMaxPartialCtas + c]) : ((unsigned long long)tag << 32);
+                    all = all && (unsigned int)(w[u][k] >> 32) == tag;
+                }
+            }
+        } while (!all && clock64() - t0 < kSpinLimitCycles);
+        timed_out = timed_out || !all;
+#pragma unroll
+        for (int u = 0; u < U; ++u)
+#pragma unroll
+            for (int k = 0; k < NV; ++k) acc[k] += __uint_as_float((unsigned int)w[u][k]);
+    }
+    timed_out = __any_sync(0xffffffffu, timed_out);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int k = 0; k < NV; ++k) acc[k] += __shfl_xor_sync(0xffffffffu, acc[k], o);
+    }
+    if (lane == 0) {
+        if (timed_out) st_volatile_u32(hdr + 1, 1u);
+        const bool poisoned = timed_out || ld_volatile_u32(hdr + 1) != 0u;
+#pragma unroll
+        for (int k = 0; k < NV; ++k) acc[k] = poisoned ? __int_as_float(0x7fc00000) : acc[k] + tot[k];
+        finalize(acc);
+        st_volatile_u32(hdr, gen + 1u);
     }
 }
 

@@ -1,290 +1,314 @@
-// K1: fused V-trace + IMPALA loss, forward and backward in ONE launch.
-// Replaces reference agents/impala/learning.py:146-160,167-168 (+ rlego V-trace).
+// K1: fused V-trace + IMPALA loss, forward and backward in ONE launch -- persistent, warp-group pipelined.
+// Replaces reference agents/impala/learning.py:146-160,167-168 (+ rlego V-trace, learning.py:15-26).
 //
-// Work split: a CTA owns a tile of `C` batch columns x all T steps; one thread per
-// (column, step) sample.  The tile's logits and behaviour logits are staged in
-// shared memory by TMA 1-D bulk copies (batch-major: one contiguous copy per tensor;
-// time-major: one copy per step), each thread keeps its A logits in registers, the
-// T-1 step V-trace recursion runs as a register chain in C threads (reference
-// operation order), and d loss/d logits is written back over the staged tile and
-// leaves by a bulk store.  Every input byte is read once, every gradient byte
-// written once: 204 B/sample at A=15.
+// One learner step issues ONE K1, so a single launch has to keep HBM busy by itself.  The first version
+// (impala_loss_tile.cu) gave every CTA one tile: all CTAs loaded, then all computed, then all stored, and
+// every CTA paid a block-wide reduction.  Here the grid is one CTA per SM; CTA k owns a CONTIGUOUS range of
+// batch columns, cut into UNITS of C whole columns (C*T <= 32*W samples, one thread per sample; T = 20:
+// W = 2 warps, C = 3) and into CHUNKS of GPC consecutive units.
+//
+//   * loads: per chunk TWO TMA bulk copies (cp.async.bulk, SASS UBLKCP) -- logits and behaviour logits --
+//     on the chunk's mbarrier, all chunks issued the moment the kernel starts.  Measured on B200
+//     (scripts/micro/tma_lat.cu, profiles/r02_tma_bulk_latency.txt): a bulk copy costs the SM's TMA unit
+//     ~150 cycles whatever its size and copies complete in issue order, so FEW LARGE copies per SM land
+//     one after the other over the load time; many small ones (a copy per tensor per unit, the first
+//     attempt: 55 per SM) are op-rate bound at a third of the bandwidth.  The 20 bytes per sample of
+//     actions / rewards / discounts / values are plain coalesced loads of the owning thread;
+//   * a GROUP of W warps takes the units g, g + G, ... of its CTA and runs as soon as the unit's chunk has
+//     landed, synchronising only with itself (named barrier / __syncwarp): softmax statistics per sample
+//     (registers), the (T-1)-step V-trace recursion as a register chain in C threads (reference operation
+//     order), closed-form gradients written over the staged logits.  Groups are in different phases at
+//     any time, so loads, arithmetic and stores of different chunks overlap inside the launch;
+//   * stores: the group that finishes a chunk last sends it out with ONE bulk store and, when the CTA has
+//     more chunks than stages, refills the stage;
+//   * the five loss sums stay in registers across a thread's units; the CTA's last-arriving warp adds the
+//     warps' sums (no block-wide barrier) and publishes them as generation-tagged words; one collector
+//     warp sums the CTAs in a fixed order (warp_collect, common.cuh).
+//
+// Every input byte is read once, every gradient byte written once: 204 B/sample at A=15.
+#include "impala_loss.cuh"
 #include "softmax.cuh"
 
 namespace b200rl {
 
-// Tensor maps of the time-major instantiation ([T rows][B*A] tensors, box = T x C*A); a separate kernel
-// parameter so that batch-major launches do not carry 384 bytes of unused maps.
-template <bool TM>
-struct TileMaps {};
-template <>
-struct TileMaps<true> {
-    CUtensorMap logits, pi_ref, dlogits;
-};
-
-struct ImpalaParams {
-    int use_tmap;
+struct K1Params {
     const float *logits, *pi_ref, *rewards, *discounts, *values;
     const long long *actions;
     float *dlogits, *dvalues, *scalars;
     void *workspace;
-    int B, T, A, C, time_major;
-    int bulk_full, bulk_last;  // tiles that can use TMA bulk copies (alignment), see the launcher
-    unsigned int inv_div;  // ceil(2^32 / T) batch-major, ceil(2^32 / C) time-major
+    int B, T, A;
+    int C, W, G, U;             // columns per unit, warps per group, groups per CTA, units
+    int GPC, NSTAGE;            // units per chunk, chunk stages in shared memory
+    int unit_words, ns4;        // C*T*A, C*T rounded up to 4 (4-byte words)
+    unsigned int inv_T;         // ceil(2^32 / T)
     float lambda_, one_minus_lambda, clip_rho, clip_pg_rho, entropy_coeff, inv_n_pg, inv_n_all;
     uint32_t flags;
+    int debug;                  // B200RL_K1_DEBUG (profiling): 1 = skip the arithmetic, 2 = skip the grid collector
 };
 
-// TM: time-major [T,B,...] layout.  A template parameter so that the batch-major kernel carries no stride
-// arithmetic and no per-row copy loop (it executes ~10% fewer instructions than a run-time switch).
-template <int AT, bool EXACT, bool TRACE, bool TM>
-__global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_kernel(const __grid_constant__ ImpalaParams p, const __grid_constant__ TileMaps<TM> maps) {
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int T = p.T, A = EXACT ? AT : p.A, C = p.C, NS = C * T;
-    float *sx = reinterpret_cast<float *>(smem_raw);    // [NS*A] logits -> dlogits
-    const int tile_elems = TM ? ((NS * A + 31) & ~31) : NS * A;  // tensor-map tiles start 128-byte aligned
-    float *sy = sx + tile_elems;                        // [NS*A] behaviour logits
-    float2 *s_tg = reinterpret_cast<float2 *>(sy + tile_elems);  // [NS] (clipped TD error, discount * c)
-    float *s_e = reinterpret_cast<float *>(s_tg + NS);  // [NS] V-trace errors e_t
-    float *s_nx = s_e + NS;                             // [NS] d loss/d v_{t+1} pushed by step t
-    float *red = s_nx + NS;                             // [5*blockDim]
-    uint64_t *bar = reinterpret_cast<uint64_t *>(red + 5 * blockDim.x);
+__device__ __forceinline__ void group_sync(int id, int nthreads) {
+    if (nthreads == 32) __syncwarp();
+    else asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
 
-    // B200RL_TRACE selects a separate instantiation: the production kernel carries no stamp code
-    const bool trace = TRACE && threadIdx.x == 0 && blockIdx.x < kMaxTraceCtas;
-    unsigned long long *tr = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(p.workspace) + kTraceOffset) + blockIdx.x * 16;
-#define K1_STAMP(i) do { if (TRACE && trace) { tr[i] = globaltimer_ns(); tr[8 + i] = (unsigned long long)clock64(); } } while (0)
-    K1_STAMP(0);
+// AT <= 16: up to 20 warps per CTA at <= 96 registers; wider action spaces: 10 warps
+template <int AT> constexpr int k1_max_threads() { return AT <= 16 ? 640 : 320; }
+
+template <int AT, bool EXACT, bool TRACE>
+__global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(const __grid_constant__ K1Params p) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int T = p.T, A = EXACT ? AT : p.A, C = p.C, G = p.G, GPC = p.GPC, NSTAGE = p.NSTAGE;
+    const int gthreads = p.W * 32;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+    const int grp = warp / p.W;
+    const int i = threadIdx.x - grp * gthreads;  // thread (= sample) index inside the group
+    const int bar_id = grp + 1;                  // named barrier of the group (0 is __syncthreads)
+    const int chunk_words = GPC * p.unit_words;
+    // shared memory: [NSTAGE][logits chunk | pi_ref chunk] | per-group scratch (td, g*c), e, nx | mbarriers | done | red | ctl
+    float *smem = reinterpret_cast<float *>(smem_raw);
+    float *scratch = smem + (size_t)NSTAGE * 2 * chunk_words + (size_t)grp * 4 * p.ns4;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)NSTAGE * 2 * chunk_words + (size_t)G * 4 * p.ns4);
+    int *done = reinterpret_cast<int *>(bars + NSTAGE);  // [NSTAGE] groups that finished the stage's chunk
+    float *red = reinterpret_cast<float *>(done + NSTAGE);  // [5][nwarps]
+    int *ctl = reinterpret_cast<int *>(red + 5 * nwarps);   // [0] warps arrived at the reduction
+
+    const bool trace = TRACE && i == 0 && (int)(blockIdx.x * G + grp) < kMaxTraceCtas;
+    unsigned long long *tr = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(p.workspace) + kTraceOffset) +
+                             (size_t)(blockIdx.x * G + grp) * 16;
+#define K1_STAMP(k) do { if (TRACE && trace) { tr[k] = globaltimer_ns(); tr[8 + (k)] = (unsigned long long)clock64(); } } while (0)
     if (trace) { unsigned int smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid)); tr[7] = smid; }
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < NSTAGE; ++s) { mbar_init(bars + s, 1); done[s] = 0; }
+        ctl[0] = 0;
+        fence_mbar_init();
+    }
     pdl_launch_dependents();
     const bool late_wait = p.flags & B200RL_INPUTS_STABLE;
-    if (!late_wait) pdl_wait();  // inputs may come from the preceding kernel
-
-    const int b0 = blockIdx.x * C;
-    const int cols = min(C, p.B - b0);
-    const int s = threadIdx.x;
-    int c, t;
-    // s / T (resp. s / C) by one IMAD.HI with the host-computed ceil(2^32 / divisor): exact for s * divisor < 2^32
-    if (TM) { t = C == 1 ? s : (int)__umulhi((unsigned)s, p.inv_div); c = s - t * C; }
-    else { c = (int)__umulhi((unsigned)s, p.inv_div); t = s - c * T; }
-    const bool valid = s < NS && c < cols;
-    const int st_local = TM ? C : 1;  // local index distance between t and t+1
-    const int n = TM ? t * p.B + b0 + c : (b0 + c) * T + t;
-    const int n_stride_t = TM ? p.B : 1;
-
-    // ---- phase 1: stage the tile ------------------------------------------------------
-    const int row_elems = (TM ? cols : cols * T) * A;  // contiguous run
-    const int nrows = TM ? T : 1;
-    const size_t g_row0 = (size_t)(TM ? b0 : b0 * T) * A;
-    const size_t g_row_stride = (size_t)p.B * A;  // time-major only
-    const int s_row_stride = C * A;               // time-major only
-    const uint32_t row_bytes = (uint32_t)row_elems * 4u;
-    // TMA bulk copies need 16-byte aligned addresses and sizes: decided on the host (full tiles / the ragged
-    // last tile), since every term depends on launch arguments only
-    // time-major with a tensor map: ONE 2-D tiled copy per tensor (T rows x C*A floats; the ragged last tile
-    // is zero-filled / clipped by the TMA unit) instead of T row copies
-    const bool tmap = TM && p.use_tmap;
-    const bool bulk_ok = tmap || ((cols == C) ? p.bulk_full : p.bulk_last);
-    // The copies are issued by lane 0 of every warp, rows dealt round-robin: a UBLKCP takes tens of
-    // cycles to issue, so one thread issuing 2*T of them (time-major) would delay the last row by
-    // microseconds.  Batch-major has one row per tensor: thread 0 alone, no extra barrier.
-    const int warp = threadIdx.x >> 5, nwarps = blockDim.x >> 5;
-    const bool issuer = (TM && !tmap) ? ((threadIdx.x & 31) == 0 && warp < nrows) : threadIdx.x == 0;
-    if (bulk_ok) {
-        if (threadIdx.x == 0) {
-            mbar_init(bar, 1);
-            fence_mbar_init();
-            mbar_expect_tx(bar, tmap ? 2u * (uint32_t)(NS * A) * 4u : 2u * row_bytes * nrows);
-        }
-        if constexpr (TM) {
-            if (tmap && threadIdx.x == 0) {
-                tma_load_2d(sx, &maps.logits, b0 * A, 0, bar);
-                tma_load_2d(sy, &maps.pi_ref, b0 * A, 0, bar);
-            }
-        }
-        if (tmap) {
-        } else if (TM) {
-            __syncthreads();  // barrier initialised before other warps' copies can complete on it
-            if (issuer) {
-                for (int r = warp; r < nrows; r += nwarps) {
-                    bulk_g2s(sx + r * s_row_stride, p.logits + g_row0 + r * g_row_stride, row_bytes, bar);
-                    bulk_g2s(sy + r * s_row_stride, p.pi_ref + g_row0 + r * g_row_stride, row_bytes, bar);
-                }
-            }
-        } else if (threadIdx.x == 0) {
-            bulk_g2s(sx, p.logits + g_row0, row_bytes, bar);
-            bulk_g2s(sy, p.pi_ref + g_row0, row_bytes, bar);
-        }
-    } else {
-        for (int r = 0; r < nrows; ++r)
-            for (int i = threadIdx.x; i < row_elems; i += blockDim.x) {
-                sx[r * s_row_stride + i] = ld_stream_f32(p.logits + g_row0 + r * g_row_stride + i);
-                sy[r * s_row_stride + i] = ld_stream_f32(p.pi_ref + g_row0 + r * g_row_stride + i);
-            }
+    unsigned int gen = 0;
+    if (!late_wait) {
+        pdl_wait();  // inputs may come from the preceding kernel
+        gen = grid_generation(p.workspace);  // consumed by the last warp at the very end: latency hidden
     }
+    __syncthreads();
+    K1_STAMP(0);
+
+    // this CTA's contiguous range of units, its chunks
+    const int ustart = (int)((long long)blockIdx.x * p.U / gridDim.x);
+    const int n_units = (int)((long long)(blockIdx.x + 1) * p.U / gridDim.x) - ustart;
+    const int n_chunks = (n_units + GPC - 1) / GPC;
+    auto chunk_units = [&](int c) { return min(GPC, n_units - c * GPC); };
+    auto chunk_col0 = [&](int c) { return (ustart + c * GPC) * C; };
+    auto chunk_cols = [&](int c) { return min((ustart + c * GPC + chunk_units(c)) * C, p.B) - chunk_col0(c); };
+    auto issue_chunk = [&](int c) {  // one thread
+        const int st = c % NSTAGE;
+        float *sx = smem + (size_t)st * 2 * chunk_words;
+        const size_t e0 = (size_t)chunk_col0(c) * T * A;
+        const uint32_t bytes = (uint32_t)(chunk_cols(c) * T * A * 4);
+        mbar_expect_tx(bars + st, 2u * bytes);
+        bulk_g2s(sx, p.logits + e0, bytes, bars + st);
+        bulk_g2s(sx + chunk_words, p.pi_ref + e0, bytes, bars + st);
+    };
+    if (lane == 0)  // copies complete in issue order: chunk 0 first.  Spread over warps: an issue costs ~55 cycles
+        for (int c = warp; c < min(NSTAGE, n_chunks); c += nwarps) issue_chunk(c);
+
+    const bool detach_adv = p.flags & B200RL_DETACH_ADV, detach_rho = p.flags & B200RL_DETACH_RHO;
+    const int col = (int)__umulhi((unsigned)i, p.inv_T), t = i - col * T;
+    float2 *s_tg = reinterpret_cast<float2 *>(scratch);
+    float *s_e = scratch + 2 * p.ns4, *s_nx = s_e + p.ns4;
+    float sums[5] = {0.f, 0.f, 0.f, 0.f, 0.f};  // pg, value, entropy, kl, ratio
+
+    // the 20 bytes per sample outside the logits: plain loads, fetched one unit ahead
     long long act = 0;
     float rew = 0.f, disc = 0.f, v = 0.f, v_next = 0.f;
-    const bool has_next = valid && t < T - 1;
-    if (valid) {
-        act = __ldg(p.actions + n);
-        rew = __ldg(p.rewards + n);
-        disc = __ldg(p.discounts + n);
-        v = __ldg(p.values + n);
-        if (has_next) v_next = __ldg(p.values + n + n_stride_t);
-    }
-    __syncthreads();  // mbarrier init visible / cooperative stores done
-    if (bulk_ok) mbar_wait(bar, 0);
-    K1_STAMP(1);
-
-    // ---- phase 2: per-sample softmax statistics, TD error, trace coefficient -----------
-    SampleStats<AT> st;
-    float c_pg = 0.f;
-    const bool detach_adv = p.flags & B200RL_DETACH_ADV, detach_rho = p.flags & B200RL_DETACH_RHO;
-    if (valid) {
-        sample_stats<AT, EXACT>(st, sx + s * A, sy + s * A, A, act);
-        c_pg = fminf(st.rho, p.clip_pg_rho);
-        if (has_next) {
-            s_tg[s] = make_float2(fminf(st.rho, p.clip_rho) * (rew + disc * v_next - v),
-                                  disc * (fminf(st.rho, 1.0f) * p.lambda_));
-            // adv_t depends on v_{t+1} through the q bootstrap: weight 1 at the last step,
-            // (1 - lambda) elsewhere (the lambda * vs_{t+1} part is a stop-gradient target)
-            const float w = (t == T - 2) ? 1.f : p.one_minus_lambda;
-            s_nx[s] = detach_adv ? 0.f : -st.lp * c_pg * disc * w * p.inv_n_pg;
+    auto fetch_small = [&](int j) {
+        if (j >= n_units) return;
+        const int b0 = (ustart + j) * C, nsu = min(C, p.B - b0) * T;
+        const size_t n = (size_t)b0 * T + i;
+        if (i < nsu) {
+            act = __ldg(p.actions + n);
+            rew = __ldg(p.rewards + n);
+            disc = __ldg(p.discounts + n);
+            v = __ldg(p.values + n);
+            if (t < T - 1) v_next = __ldg(p.values + n + 1);
         }
-    }
-    __syncthreads();
-    K1_STAMP(2);
+    };
+    fetch_small(grp);
 
-    // ---- phase 3: backward-in-time recursion e_k = td_k + (discount_k c_k) e_{k+1} ----------
-    // One register chain per column (the column's first thread), steps fetched 4 at a time, in the
-    // reference loop's operation order; results go to s_e.
-    float e_t = 0.f, e_t1 = 0.f;  // e_t, e_{t+1} of this thread's sample
-    if (s < cols) {
-        const int base = TM ? s : s * T;
-        const float2 *__restrict__ qp = s_tg + base + (T - 2) * st_local;  // step k
-        float *__restrict__ ep = s_e + base + (T - 2) * st_local;
-        const int st4 = 4 * st_local;
-        float e = 0.f;
-        int k = T - 2;
-        for (; k >= 3; k -= 4, qp -= st4, ep -= st4) {  // 4 independent loads, then 4 chained FMAs
-            const float2 q0 = qp[0], q1 = qp[-st_local], q2 = qp[-2 * st_local], q3 = qp[-3 * st_local];
-            e = q0.x + q0.y * e; ep[0] = e;
-            e = q1.x + q1.y * e; ep[-st_local] = e;
-            e = q2.x + q2.y * e; ep[-2 * st_local] = e;
-            e = q3.x + q3.y * e; ep[-3 * st_local] = e;
-        }
-        for (; k >= 0; --k, qp -= st_local, ep -= st_local) {
-            const float2 q = *qp;
-            e = q.x + q.y * e;
-            *ep = e;
-        }
-    }
-    __syncthreads();
-    if (has_next) {
-        e_t = s_e[s];
-        if (t < T - 2) e_t1 = s_e[s + st_local];
-    }
-    K1_STAMP(3);
+    bool first = true;
+    for (int j = grp; j < n_units; j += G) {
+        const int c = j / GPC, st_i = c % NSTAGE;
+        float *sx = smem + (size_t)st_i * 2 * chunk_words + (size_t)(j - c * GPC) * p.unit_words;
+        float *sy = sx + chunk_words;
+        const int b0 = (ustart + j) * C, ucols = min(C, p.B - b0), nsu = ucols * T;
+        const size_t n0 = (size_t)b0 * T;
 
-    // ---- phase 4: losses and gradients -------------------------------------------------
-    float sums[5] = {0.f, 0.f, 0.f, 0.f, 0.f};  // pg, value, entropy, kl, ratio
-    if (valid) {
-        float g_lp = 0.f, dv = 0.f;
-        if (has_next) {
-            const float e = e_t;
-            const float tgt = e + v;     // stop-gradient target vs_t
-            const float err = tgt - v;   // rlego "errors"
-            float qb = v_next;
-            if (t < T - 2) {
-                const float e1 = e_t1;
-                const float tgt1 = ((e1 + v_next) - v_next) + v_next;
-                qb = p.lambda_ * tgt1 + p.one_minus_lambda * v_next;
+        mbar_wait(bars + st_i, (uint32_t)(c / NSTAGE) & 1u);  // the unit's chunk has landed
+        if (first) K1_STAMP(1);
+
+        // ---- per-sample softmax statistics, TD error, trace coefficient ------------------------
+        const bool valid = i < nsu && !(p.debug & 1);
+        const bool has_next = valid && t < T - 1;
+        SampleStats<AT> st;
+        float c_pg = 0.f;
+        const float u_rew = rew, u_disc = disc, u_v = v, u_vn = v_next;
+        if (valid) {
+            sample_stats<AT, EXACT>(st, sx + i * A, sy + i * A, A, act);
+            c_pg = fminf(st.rho, p.clip_pg_rho);
+            if (has_next) {
+                s_tg[i] = make_float2(fminf(st.rho, p.clip_rho) * (u_rew + u_disc * u_vn - u_v),
+                                      u_disc * (fminf(st.rho, 1.0f) * p.lambda_));
+                // adv_t depends on v_{t+1} through the q bootstrap: weight 1 at the last step,
+                // (1 - lambda) elsewhere (the lambda * vs_{t+1} part is a stop-gradient target)
+                const float w = (t == T - 2) ? 1.f : p.one_minus_lambda;
+                s_nx[i] = detach_adv ? 0.f : -st.lp * c_pg * u_disc * w * p.inv_n_pg;
             }
-            const float q = rew + disc * qb;
-            const float qmv = q - v;
-            const float adv = c_pg * qmv;
-            sums[0] = st.lp * adv;
-            sums[1] = err * err;
-            float dpg_dlp = adv;  // d(lp*adv)/dlp, adv's own dependence on lp via rho below
-            if (!detach_adv && !detach_rho && st.rho <= p.clip_pg_rho) dpg_dlp += st.lp * st.rho * qmv;
-            g_lp = -dpg_dlp * p.inv_n_pg;
-            dv = -2.f * err * p.inv_n_pg;
-            if (!detach_adv) dv += st.lp * c_pg * p.inv_n_pg;
         }
-        if (t > 0) dv += s_nx[s - st_local];
-        p.dvalues[n] = dv;
-        sums[2] = st.H;
-        sums[3] = st.kl;
-        sums[4] = st.rho;
-        write_dlogits<AT, EXACT>(st, sx + s * A, A, g_lp, p.entropy_coeff * p.inv_n_all);
-    }
-    if (bulk_ok) fence_proxy_async_smem();
-    __syncthreads();
-    K1_STAMP(4);
-    if (bulk_ok) {
-        if (issuer) {
-            if (tmap) {
-                if constexpr (TM) tma_store_2d(&maps.dlogits, sx, b0 * A, 0);
-            } else if (TM) {
-                for (int r = warp; r < nrows; r += nwarps)
-                    bulk_s2g(p.dlogits + g_row0 + r * g_row_stride, sx + r * s_row_stride, row_bytes);
-            } else {
-                bulk_s2g(p.dlogits + g_row0, sx, row_bytes);
+        fetch_small(j + G);  // next unit's small fields: in flight during the rest of this unit
+        group_sync(bar_id, gthreads);
+        if (first) K1_STAMP(2);
+
+        // ---- backward-in-time recursion e_k = td_k + (discount_k c_k) e_{k+1} ------------------
+        // one register chain per column, steps fetched 4 at a time, in the reference loop's operation order
+        if (i < ucols) {
+            const float2 *__restrict__ qp = s_tg + i * T + (T - 2);
+            float *__restrict__ ep = s_e + i * T + (T - 2);
+            float e = 0.f;
+            int k = T - 2;
+            for (; k >= 3; k -= 4, qp -= 4, ep -= 4) {  // 4 independent loads, then 4 chained FMAs
+                const float2 q0 = qp[0], q1 = qp[-1], q2 = qp[-2], q3 = qp[-3];
+                e = q0.x + q0.y * e; ep[0] = e;
+                e = q1.x + q1.y * e; ep[-1] = e;
+                e = q2.x + q2.y * e; ep[-2] = e;
+                e = q3.x + q3.y * e; ep[-3] = e;
             }
-            bulk_commit();
+            for (; k >= 0; --k, --qp, --ep) {
+                const float2 q = *qp;
+                e = q.x + q.y * e;
+                *ep = e;
+            }
         }
-    } else {
-        for (int r = 0; r < nrows; ++r)
-            for (int i = threadIdx.x; i < row_elems; i += blockDim.x)
-                p.dlogits[g_row0 + r * g_row_stride + i] = sx[r * s_row_stride + i];
+        group_sync(bar_id, gthreads);
+        if (first) K1_STAMP(3);
+
+        // ---- losses and gradients ---------------------------------------------------------------
+        if (valid) {
+            float g_lp = 0.f, dv = 0.f;
+            if (has_next) {
+                const float e = s_e[i];
+                const float tgt = e + u_v;     // stop-gradient target vs_t
+                const float err = tgt - u_v;   // rlego "errors"
+                float qb = u_vn;
+                if (t < T - 2) {
+                    const float e1 = s_e[i + 1];
+                    const float tgt1 = ((e1 + u_vn) - u_vn) + u_vn;
+                    qb = p.lambda_ * tgt1 + p.one_minus_lambda * u_vn;
+                }
+                const float q = u_rew + u_disc * qb;
+                const float qmv = q - u_v;
+                const float adv = c_pg * qmv;
+                sums[0] += st.lp * adv;
+                sums[1] += err * err;
+                float dpg_dlp = adv;  // d(lp*adv)/dlp, adv's own dependence on lp via rho below
+                if (!detach_adv && !detach_rho && st.rho <= p.clip_pg_rho) dpg_dlp += st.lp * st.rho * qmv;
+                g_lp = -dpg_dlp * p.inv_n_pg;
+                dv = -2.f * err * p.inv_n_pg;
+                if (!detach_adv) dv += st.lp * c_pg * p.inv_n_pg;
+            }
+            if (t > 0) dv += s_nx[i - 1];
+            p.dvalues[n0 + i] = dv;
+            sums[2] += st.H;
+            sums[3] += st.kl;
+            sums[4] += st.rho;
+            write_dlogits<AT, EXACT>(st, sx + i * A, A, g_lp, p.entropy_coeff * p.inv_n_all);
+        }
+        fence_proxy_async_smem();  // gradient rows -> visible to the bulk store
+        group_sync(bar_id, gthreads);
+        if (i == 0) {
+            __threadfence_block();
+            if (atomicAdd(&done[st_i], 1) == chunk_units(c) - 1) {  // this group finished the chunk last: send it out
+                __threadfence_block();
+                done[st_i] = 0;
+                fence_proxy_async_smem();
+                bulk_s2g(p.dlogits + (size_t)chunk_col0(c) * T * A, smem + (size_t)st_i * 2 * chunk_words,
+                         (uint32_t)(chunk_cols(c) * T * A * 4));
+                bulk_commit();
+                if (c + NSTAGE < n_chunks) {  // refill the stage once the store has read it
+                    bulk_wait_read0();
+                    issue_chunk(c + NSTAGE);
+                }
+            }
+        }
+        if (first) K1_STAMP(4);
+        first = false;
     }
 
-    // ---- scalars: deterministic grid reduction -----------------------------------------
-    const float inv_n_pg = p.inv_n_pg, inv_n_all = p.inv_n_all, ec = p.entropy_coeff;
-    float *scalars = p.scalars;
-    grid_reduce<5>(
-        sums, red, p.workspace,
-        [=](const float(&tot)[5]) {
-            const float pg = tot[0] * inv_n_pg, td = tot[1] * inv_n_pg, ent = tot[2] * inv_n_all;
+    // ---- scalars: one reduction per CTA by its last-arriving warp, then the grid collector -------
+    // no block-wide barrier: a warp leaves its five sums in shared memory and retires; the warp that arrives
+    // last adds the warps' sums in index order (fixed order everywhere: bit-reproducible scalars)
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) sums[k] += __shfl_xor_sync(0xffffffffu, sums[k], o);
+    }
+    int arrived = 0;
+    if (lane == 0) {
+#pragma unroll
+        for (int k = 0; k < 5; ++k) red[k * nwarps + warp] = sums[k];
+        __threadfence_block();
+        arrived = atomicAdd(&ctl[0], 1);
+    }
+    arrived = __shfl_sync(0xffffffffu, arrived, 0);
+    if (arrived == nwarps - 1) {
+        __threadfence_block();
+        float tot[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int k = 0; k < 5; ++k)
+            for (int w = 0; w < nwarps; ++w) tot[k] += red[k * nwarps + w];
+        if (late_wait) {
+            pdl_wait();  // the workspace and scalars are shared with the previous launch
+            gen = grid_generation(p.workspace);
+        }
+        const float inv_n_pg = p.inv_n_pg, inv_n_all = p.inv_n_all, ec = p.entropy_coeff;
+        float *scalars = p.scalars;
+        if (!(p.debug & 2)) warp_collect<5>(tot, p.workspace, gen, [=](const float(&s)[5]) {
+            const float pg = s[0] * inv_n_pg, td = s[1] * inv_n_pg, ent = s[2] * inv_n_all;
             scalars[B200RL_S_LOSS] = -pg + td - ec * ent;
             scalars[B200RL_S_ENTROPY] = ent;
             scalars[B200RL_S_TD] = td;
             scalars[B200RL_S_PG] = pg;
-            scalars[B200RL_S_KL] = tot[3] * inv_n_all;
-            scalars[B200RL_S_RATIO] = tot[4] * inv_n_all;
+            scalars[B200RL_S_KL] = s[3] * inv_n_all;
+            scalars[B200RL_S_RATIO] = s[4] * inv_n_all;
             scalars[6] = 0.f;
             scalars[7] = 0.f;
-        },
-        [=]() { if (late_wait) pdl_wait(); });  // the workspace and scalars are shared with the previous launch
+        });
+    }
     K1_STAMP(5);
-    if (bulk_ok && issuer) bulk_wait_read0();  // smem must outlive the bulk store's reads
+    if (i == 0) bulk_wait_read0();  // shared memory must outlive the bulk stores' reads
     K1_STAMP(6);
 #undef K1_STAMP
 }
 
-}  // namespace b200rl
-
 // ------------------------------------------------------------------------ host side
-namespace b200rl {
-
-int env_int(const char *name, int dflt);
-
-template <int AT, bool EXACT, bool TRACE, bool TM>
-static int32_t launch_impala_t(ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
-    TileMaps<TM> maps;
-    if constexpr (TM) {
-        if (env_int("B200RL_K1_TMAP", 1)) {
-            const uint64_t inner = (uint64_t)p.B * p.A, pitch = inner * 4;
-            const uint32_t bi = (uint32_t)(p.C * p.A), br = (uint32_t)p.T;
-            p.use_tmap = encode_tmap_2d_f32(&maps.logits, p.logits, inner, br, pitch, bi, br) &&
-                         encode_tmap_2d_f32(&maps.pi_ref, p.pi_ref, inner, br, pitch, bi, br) &&
-                         encode_tmap_2d_f32(&maps.dlogits, p.dlogits, inner, br, pitch, bi, br);
-        }
+static int sm_count() {
+    static int cache[kMaxDevices];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    dev = (dev >= 0 && dev < kMaxDevices) ? dev : 0;
+    if (!cache[dev]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cache[dev] = n;
     }
+    return cache[dev];
+}
+
+template <int AT, bool EXACT, bool TRACE>
+static int32_t launch_k1_t(const K1Params &p, int grid, int threads, size_t smem, cudaStream_t stream) {
     static size_t smem_cache[kMaxDevices];
-    if (int32_t rc = ensure_dynamic_smem(impala_loss_kernel<AT, EXACT, TRACE, TM>, smem, smem_cache, "impala_loss")) return rc;
+    if (int32_t rc = ensure_dynamic_smem(impala_loss_kernel<AT, EXACT, TRACE>, smem, smem_cache, "impala_loss")) return rc;
     cudaLaunchConfig_t cfg = {};
-    cfg.gridDim = dim3((unsigned)((p.B + p.C - 1) / p.C));
+    cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3((unsigned)threads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
@@ -293,7 +317,7 @@ static int32_t launch_impala_t(ImpalaParams &p, int threads, size_t smem, cudaSt
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = env_int("B200RL_PDL", 1) ? 1 : 0;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, impala_loss_kernel<AT, EXACT, TRACE, TM>, p, maps);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, impala_loss_kernel<AT, EXACT, TRACE>, p);
     if (e != cudaSuccess) {
         set_error("impala_loss_kernel launch: %s", cudaGetErrorString(e));
         (void)cudaGetLastError();
@@ -303,13 +327,83 @@ static int32_t launch_impala_t(ImpalaParams &p, int threads, size_t smem, cudaSt
 }
 
 template <int AT, bool EXACT>
-static int32_t launch_impala(ImpalaParams &p, int threads, size_t smem, cudaStream_t stream) {
-    if (p.flags & B200RL_TRACE) {  // stamped instantiations (scripts/k1_trace.py)
-        if (p.time_major) return launch_impala_t<AT, EXACT, true, true>(p, threads, smem, stream);
-        return launch_impala_t<AT, EXACT, true, false>(p, threads, smem, stream);
+static int32_t launch_k1(const ImpalaArgs &a, cudaStream_t stream) {
+    const int T = a.T, A = a.A, B = a.B;
+    const int max_threads = k1_max_threads<AT>();
+    const int max_w = max_threads / 32;
+    if (T > 32 * max_w) return 1;
+    // TMA bulk copies: 16-byte aligned addresses and sizes for every chunk (a whole number of units, or the
+    // tail of the batch)
+    if (((reinterpret_cast<uintptr_t>(a.logits) | reinterpret_cast<uintptr_t>(a.pi_ref) |
+          reinterpret_cast<uintptr_t>(a.dlogits)) % 16) != 0 || ((long long)B * T) % 4 != 0)
+        return 1;
+    // group shape: the fewest warps whose lanes are >= 90 % samples, else the best fill
+    int W = 0, C = 0;
+    const int force_w = env_int("B200RL_K1_W", 0);
+    double best = 0.0;
+    for (int w = 1; w <= max_w; ++w) {
+        int c = (32 * w) / T;
+        if (c < 1) continue;
+        if (c > B) c = B;
+        while (c > 1 && (c * T) % 4 != 0) --c;  // units start 16-byte aligned
+        if ((c * T) % 4 != 0) continue;
+        const double eff = (double)c * T / (32.0 * w);
+        if (force_w ? (w == force_w) : (eff > best + 1e-9)) { best = eff; W = w; C = c; }
+        if (force_w ? (w == force_w) : (eff >= 0.9)) break;
     }
-    if (p.time_major) return launch_impala_t<AT, EXACT, false, true>(p, threads, smem, stream);
-    return launch_impala_t<AT, EXACT, false, false>(p, threads, smem, stream);
+    if (!W) return 1;
+    K1Params p;
+    p.logits = a.logits; p.pi_ref = a.pi_ref; p.rewards = a.rewards; p.discounts = a.discounts; p.values = a.values;
+    p.actions = a.actions; p.dlogits = a.dlogits; p.dvalues = a.dvalues; p.scalars = a.scalars; p.workspace = a.workspace;
+    p.B = B; p.T = T; p.A = A;
+    p.lambda_ = a.lambda_; p.one_minus_lambda = a.one_minus_lambda; p.clip_rho = a.clip_rho; p.clip_pg_rho = a.clip_pg_rho;
+    p.entropy_coeff = a.entropy_coeff; p.inv_n_pg = a.inv_n_pg; p.inv_n_all = a.inv_n_all; p.flags = a.flags;
+    p.C = C; p.W = W;
+    p.U = (B + C - 1) / C;
+    p.inv_T = (unsigned int)(((1ull << 32) + (unsigned)T - 1) / (unsigned)T);
+    p.ns4 = (C * T + 3) & ~3;
+    p.unit_words = C * T * A;
+    // one CTA per SM (small problems: one unit per CTA first); groups per CTA: fill the CTA, at most 15 named barriers
+    const int grid = min(sm_count(), p.U);
+    if (grid > kMaxPartialCtas) return 1;
+    const int units_per_cta = (p.U + grid - 1) / grid;
+    int G = max_threads / (32 * W);
+    if (W > 1 && G > 15) G = 15;
+    G = max(1, min(G, env_int("B200RL_K1_G", G)));
+    G = min(G, units_per_cta);
+    // chunks: GPC consecutive units per pair of bulk copies; every chunk of the CTA resident when shared memory allows
+    const size_t unit_bytes = (size_t)p.unit_words * 4, budget = 200 * 1024;
+    int GPC = max(1, min(env_int("B200RL_K1_GPC", 2), units_per_cta));
+    while (GPC > 1 && 2 * unit_bytes * GPC * 2 > budget) --GPC;
+    if (2 * unit_bytes * GPC > budget) return 1;
+    const int chunks_per_cta = (units_per_cta + GPC - 1) / GPC;
+    int NSTAGE = (int)min((size_t)chunks_per_cta, budget / (2 * unit_bytes * GPC));
+    const int min_stages = (G + GPC - 1) / GPC + 1;  // a round of groups plus one chunk in flight
+    NSTAGE = max(1, min(NSTAGE, env_int("B200RL_K1_STAGES", NSTAGE)));
+    if (NSTAGE < chunks_per_cta && NSTAGE < min_stages) {  // long rollouts: fewer groups so that the ring still pipelines
+        G = max(1, min(G, (NSTAGE - 1) * GPC));
+    }
+    p.G = G; p.GPC = GPC; p.NSTAGE = NSTAGE;
+    p.debug = env_int("B200RL_K1_DEBUG", 0);
+    const int threads = G * W * 32;
+    const size_t smem = (size_t)NSTAGE * 2 * GPC * unit_bytes + (size_t)G * 4 * p.ns4 * 4 + (size_t)NSTAGE * 12 +
+                        5 * (size_t)(threads / 32) * 4 + 16 + 128;
+    if (a.flags & B200RL_TRACE) return launch_k1_t<AT, EXACT, true>(p, grid, threads, smem, stream);
+    return launch_k1_t<AT, EXACT, false>(p, grid, threads, smem, stream);
+}
+
+int32_t launch_impala_persistent(const ImpalaArgs &a, cudaStream_t stream) {
+    if (a.time_major) return 1;
+    switch (a.A) {  // exact-A instantiations (no padding predicates) for the common action spaces
+        case 4: return launch_k1<4, true>(a, stream);
+        case 6: return launch_k1<6, true>(a, stream);
+        case 15: return launch_k1<15, true>(a, stream);
+        case 18: return launch_k1<18, true>(a, stream);
+        default: break;
+    }
+    if (a.A <= 8) return launch_k1<8, false>(a, stream);
+    if (a.A <= 16) return launch_k1<16, false>(a, stream);
+    return launch_k1<32, false>(a, stream);
 }
 
 }  // namespace b200rl
@@ -326,9 +420,6 @@ extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
     B200RL_REQUIRE(B >= 1 && T >= 2 && A >= 1, -2, "impala_loss: need B>=1, T>=2, A>=1 (got B=%lld T=%lld A=%lld)",
                    (long long)B, (long long)T, (long long)A);
     B200RL_REQUIRE(A <= 32, -3, "impala_loss: A=%lld > 32 actions not supported", (long long)A);
-    const int max_threads = A <= 16 ? 640 : 256;  // == __launch_bounds__ of the instantiation
-    B200RL_REQUIRE(T <= max_threads, -3, "impala_loss: T=%lld > %d steps not supported at A=%lld",
-                   (long long)T, max_threads, (long long)A);
     B200RL_REQUIRE(B * T < (1ll << 31), -3, "impala_loss: B*T too large");
     const bool batch_major = (stride_t == 1 && stride_b == T);
     const bool time_major = (stride_b == 1 && stride_t == B);
@@ -337,57 +428,21 @@ extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
                    (long long)stride_b, (long long)stride_t);
     B200RL_REQUIRE(n_global_b >= B, -2, "impala_loss: n_global_b < B");
 
-    ImpalaParams p;
-    p.logits = logits; p.pi_ref = pi_ref; p.rewards = rewards; p.discounts = discounts; p.values = values;
-    p.actions = reinterpret_cast<const long long *>(actions);
-    p.dlogits = dlogits; p.dvalues = dvalues; p.scalars = scalars; p.workspace = workspace;
-    p.B = (int)B; p.T = (int)T; p.A = (int)A;
-    p.time_major = (time_major && !batch_major) ? 1 : 0;
-    p.lambda_ = (float)lambda_; p.one_minus_lambda = (float)(1.0 - lambda_); p.clip_rho = clip_rho; p.clip_pg_rho = clip_pg_rho; p.entropy_coeff = entropy_coeff;
-    p.inv_n_pg = (float)(1.0 / ((double)n_global_b * (double)(T - 1)));
-    p.inv_n_all = (float)(1.0 / ((double)n_global_b * (double)T));
-    p.flags = flags;
-
-    // columns per CTA: a multiple of 4 so time-major rows stay 16-byte aligned
-    int target = env_int("B200RL_K1_SAMPLES", 160);
-    int C = (int)(target / T);
-    if (C >= 4 && time_major && !batch_major) C &= ~3;
-    if (C < 1) C = 1;
-    if (C > B) C = (int)B;
-    while (C > 1 && C * T > max_threads) C = (C > 4) ? ((C - 1) & ~3) : C - 1;
-    auto threads_for = [&](int c) { return ((c * (int)T + 31) / 32) * 32; };
-    auto smem_for = [&](int c) { return (size_t)c * T * (2 * A + 4) * 4 + 5 * (size_t)threads_for(c) * 4 + 16 + 256; };
-    while (C > 1 && smem_for(C) > 200 * 1024) C = (C > 4) ? ((C / 2) & ~3) : C - 1;
-    B200RL_REQUIRE(smem_for(C) <= 226 * 1024, -3, "impala_loss: T*A too large for one CTA tile");
-    B200RL_REQUIRE((B + C - 1) / C <= kMaxPartialCtas, -3, "impala_loss: B too large for the partials workspace");
-    p.C = C;
-    {   // alignment of the bulk copies: row start, row size, row strides (time-major), base pointers
-        const bool tm = p.time_major != 0;
-        const bool ptrs = ((reinterpret_cast<uintptr_t>(logits) | reinterpret_cast<uintptr_t>(pi_ref) |
-                            reinterpret_cast<uintptr_t>(dlogits)) % 16) == 0;
-        auto ok = [&](long long cols) {
-            const long long row_bytes = (tm ? cols : cols * T) * A * 4;
-            const long long tile_step = (tm ? (long long)C : (long long)C * T) * A * 4;  // distance between tiles' first rows
-            bool a = ptrs && row_bytes % 16 == 0 && tile_step % 16 == 0;
-            if (tm) a = a && ((long long)B * A * 4) % 16 == 0 && ((long long)C * A * 4) % 16 == 0;
-            return a ? 1 : 0;
-        };
-        p.bulk_full = ok(C);
-        p.bulk_last = (B % C) ? ok(B % C) : p.bulk_full;
-    }
-    p.use_tmap = 0;  // set by the time-major launcher
-    p.inv_div = (unsigned int)(((1ull << 32) + (unsigned)(p.time_major ? C : (int)T) - 1) / (unsigned)(p.time_major ? C : (int)T));
-    const int threads = threads_for(C);
-    const size_t smem = smem_for(C);
+    ImpalaArgs a;
+    a.logits = logits; a.pi_ref = pi_ref; a.rewards = rewards; a.discounts = discounts; a.values = values;
+    a.actions = reinterpret_cast<const long long *>(actions);
+    a.dlogits = dlogits; a.dvalues = dvalues; a.scalars = scalars; a.workspace = workspace;
+    a.B = (int)B; a.T = (int)T; a.A = (int)A;
+    a.time_major = (time_major && !batch_major) ? 1 : 0;
+    a.lambda_ = (float)lambda_; a.one_minus_lambda = (float)(1.0 - lambda_);
+    a.clip_rho = clip_rho; a.clip_pg_rho = clip_pg_rho; a.entropy_coeff = entropy_coeff;
+    a.inv_n_pg = (float)(1.0 / ((double)n_global_b * (double)(T - 1)));
+    a.inv_n_all = (float)(1.0 / ((double)n_global_b * (double)T));
+    a.flags = flags;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    switch (A) {  // exact-A instantiations (no padding predicates) for the common action spaces
-        case 4: return launch_impala<4, true>(p, threads, smem, s);
-        case 6: return launch_impala<6, true>(p, threads, smem, s);
-        case 15: return launch_impala<15, true>(p, threads, smem, s);
-        case 18: return launch_impala<18, true>(p, threads, smem, s);
-        default: break;
+    if (!a.time_major && env_int("B200RL_K1_TILE", 0) == 0) {
+        const int32_t rc = launch_impala_persistent(a, s);
+        if (rc != 1) return rc;
     }
-    if (A <= 8) return launch_impala<8, false>(p, threads, smem, s);
-    if (A <= 16) return launch_impala<16, false>(p, threads, smem, s);
-    return launch_impala<32, false>(p, threads, smem, s);
+    return launch_impala_tile(a, s);
 }

@@ -17,8 +17,10 @@ for i in range(24):
     sets.append((g, (torch.empty(8, device=dev), torch.empty_like(g["logits"]), torch.empty_like(g["values"]))))
 off = _cabi.load().b200rl_trace_offset_bytes()
 flags_list = {"serial": ops.TRACE, "independent": ops.TRACE | ops.INPUTS_STABLE}
-names = ["start", "landed", "stats", "scan", "grads", "reduce", "drained"]
+names = ["start", "landed", "stats", "scan", "stored", "reduced", "drained"]   # first unit of every warp group (persistent kernel)
 for mode, flags in flags_list.items():
+    if len(sys.argv) > 1 and sys.argv[1] == 'serial' and mode != 'serial':
+        continue
     def launch(i):
         g, out = sets[i % len(sets)]
         ops.impala_loss_fwdbwd(g["logits"], g["values"], g["a"], g["r"], g["discount"], g["pi_ref"], flags=flags, time_major=TM, out=out)
@@ -40,15 +42,17 @@ for mode, flags in flags_list.items():
     gr.replay(); torch.cuda.synchronize()
     ws = [w for w in ops._workspaces.values() if int(w[off:off + 8].view(torch.int64).item()) > 0][0]
     tr = ws[off:off + 4096 * 128].view(torch.int64).cpu().numpy().reshape(-1, 16)
-    ncta = int((tr[:, 0] > 0).sum())
-    tr = tr[:ncta]
+    tr = tr[tr[:, 1] > 0]          # warp groups that processed at least one unit
+    ncta = len(tr)
     gt, ck, sm = tr[:, :7].astype(np.float64), tr[:, 8:15].astype(np.float64), tr[:, 7]
     t0 = gt[:, 0].min()
-    print("== %s: last launch of a 20-launch graph, %d CTAs on %d SMs" % (mode, ncta, len(set(sm.tolist()))))
+    print("== %s: last launch of a 20-launch graph, %d warp groups on %d SMs" % (mode, ncta, len(set(sm.tolist()))))
     print("globaltimer (ns since first CTA start): phase  min  median  max")
     for i, n in enumerate(names):
         x = gt[:, i] - t0
         print("  %-8s %8.0f %8.0f %8.0f" % (n, x.min(), np.median(x), x.max()))
+    last = tr[tr[:, 6].argmax()]
+    print("  latest group: " + " ".join("%s=%d" % (n, last[i] - t0) for i, n in enumerate(names)) + " smid=%d" % last[7])
     print("clock64 deltas per CTA (cycles): phase  min  median  max")
     for i in range(1, 7):
         x = ck[:, i] - ck[:, i - 1]
