@@ -59,6 +59,9 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--repeats", type=int, default=50, help="timed K-step regions; the median is reported")
+    ap.add_argument("--others", default="ppo,replay,learner",
+                    help="secondary workloads timed after the headline and reported under config.other_workloads ('' = none)")
     ap.add_argument("--streams", type=int, default=6,
                     help="issue consecutive (independent) steps round-robin on this many CUDA streams")
     ap.add_argument("--pipeline", default="independent", choices=["independent", "serial"],
@@ -297,7 +300,6 @@ def make_learner(args, device, seed):
 
     def breakdown():
         """Per-phase device time of the learner step (mean of 5 profiled steps after the timed region)."""
-        desc["grad_exchange"] = grad_exchange()
         learner.profile = True
         tot, names = {}, []
         for _ in range(5):
@@ -314,8 +316,17 @@ def make_learner(args, device, seed):
         learner.profile = False
         return {k: round(v, 4) for k, v in tot.items()}
 
-    return dict(launch=launch, units=B * T, kernels=5, host=None, e2e_step=None, desc=desc, graph=False,
-                check=lambda: last["m"]["train/loss"], breakdown=breakdown)
+    def launches_per_step():
+        """Kernel launches of one learner step, counted by the profiler (one profiled step after the timed region)."""
+        from torch.profiler import profile, ProfilerActivity
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            launch(0)
+            torch.cuda.synchronize()
+        return int(sum(e.count for e in prof.key_averages() if e.device_type == torch.autograd.DeviceType.CUDA))
+
+    return dict(launch=launch, units=B * T, kernels=0, host=None, e2e_step=None, desc=desc, graph=False,
+                check=lambda: last["m"]["train/loss"], breakdown=breakdown, learner=learner, grad_exchange=grad_exchange,
+                launches_per_step=launches_per_step)
 
 
 MAKERS = {"impala_loss": make_impala_loss, "ppo": make_ppo, "replay": make_replay, "learner": make_learner}
@@ -357,31 +368,52 @@ def build_graphs(launch, steps, stream, n_streams=1):
     return plan
 
 
-def time_eager(launch, steps, warmup, device, world_size):
-    """Eager (no graph) variant for the full learner step: Python drives optimizer / NCCL, timed with CUDA events."""
+def _rank_stats(samples_ms, device, world_size):
+    """Median over this rank's repeats, MAX over ranks (the contract), plus what is needed to attribute a scaling
+    loss: every rank's median and the min / median / max of the slowest rank's repeats."""
+    srt = sorted(samples_ms)
+    med = srt[len(srt) // 2]
+    mine = torch.tensor([med, srt[0], srt[-1]], dtype=torch.float64, device=device)
+    if world_size > 1:
+        allr = [torch.empty_like(mine) for _ in range(world_size)]
+        dist.all_gather(allr, mine)
+    else:
+        allr = [mine]
+    per_rank = [float(x[0]) for x in allr]
+    slow = max(range(len(per_rank)), key=lambda r: per_rank[r])
+    return max(per_rank), {"repeats": len(srt), "per_rank_ms": [round(x, 6) for x in per_rank],
+                           "slowest_rank": slow, "min_ms": float(allr[slow][1]), "median_ms": float(allr[slow][0]),
+                           "max_ms": float(allr[slow][2])}
+
+
+def time_eager(launch, steps, warmup, device, world_size, repeats=3):
+    """Eager (no graph) variant for the full learner step: Python drives the model / NCCL.  K steps bracketed by a
+    barrier + synchronize, CUDA events, repeated `repeats` times: median repeat, max over ranks."""
     for i in range(max(warmup, 3)):
         launch(i)
-    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if world_size > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
+    samples = []
     with ClockSampler(device.index) as clk:
-        start.record()
-        for i in range(steps):
-            launch(i)
-        stop.record()
-        stop.synchronize()
-    torch.cuda.synchronize()
-    ms = torch.tensor([start.elapsed_time(stop)], dtype=torch.float64, device=device)
-    if world_size > 1:
-        dist.barrier()
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    return float(ms.item()), clk.summary()
+        for _ in range(repeats):
+            start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if world_size > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            start.record()
+            for i in range(steps):
+                launch(i)
+            stop.record()
+            stop.synchronize()
+            torch.cuda.synchronize()
+            samples.append(start.elapsed_time(stop))
+    ms, stats = _rank_stats(samples, device, world_size)
+    return ms, clk.summary(), stats
 
 
-def time_device(launch, steps, warmup, device, world_size, n_streams=1):
-    """K steps on the device, CUDA events on the launching stream, barrier + synchronize on both sides,
-    max over ranks.  Returns (elapsed ms, clocks summary)."""
+def time_device(launch, steps, warmup, device, world_size, n_streams=1, repeats=50):
+    """K steps on the device as ONE CUDA graph, CUDA events on the launching stream, barrier + synchronize on both
+    sides -- replayed `repeats` times.  A K-step region of a few-microsecond kernel is tens of microseconds, where one
+    sample measures the harness (graph launch ramp, NCCL barrier wake-up); the reported time is the MEDIAN replay,
+    max over ranks, and `timing` carries min / median / max and every rank's median."""
     stream = torch.cuda.Stream(device)
     with torch.cuda.stream(stream):
         for i in range(max(warmup, 3)):            # untimed warm-up (also creates workspaces / modules)
@@ -389,31 +421,33 @@ def time_device(launch, steps, warmup, device, world_size, n_streams=1):
     stream.synchronize()
     plan = build_graphs(launch, steps, stream, n_streams)
     with torch.cuda.stream(stream):
-        plan[-1].replay()                          # graph upload
+        for g in plan:
+            g.replay()                             # graph upload
     stream.synchronize()
-    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if world_size > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
+    samples = []
     with ClockSampler(device.index) as clk:
-        with torch.cuda.stream(stream):
-            start.record(stream)
-            for g in plan:
-                g.replay()
-            stop.record(stream)
-        stop.synchronize()
-    torch.cuda.synchronize()
-    ms = torch.tensor([start.elapsed_time(stop)], dtype=torch.float64, device=device)
-    if world_size > 1:
-        dist.barrier()
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    return float(ms.item()), clk.summary()
+        for _ in range(repeats):
+            start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            if world_size > 1:
+                dist.barrier()
+            torch.cuda.synchronize()
+            with torch.cuda.stream(stream):
+                start.record(stream)
+                for g in plan:
+                    g.replay()
+                stop.record(stream)
+            stop.synchronize()
+            torch.cuda.synchronize()
+            samples.append(start.elapsed_time(stop))
+    ms, stats = _rank_stats(samples, device, world_size)
+    return ms, clk.summary(), stats
 
 
-def time_e2e(w, steps, warmup, device, world_size):
+def time_e2e(w, steps, warmup, device, world_size, repeats=5):
     """Same metric end to end through the public API with HOST inputs: every step copies that step's inputs
     from pinned host memory (H2D), runs the fused kernel(s) and reads the loss/metric scalars back (D2H).
-    Copies of step i+1 overlap the kernel of step i on a second stream.  Wall clock, synchronised both sides."""
+    Copies of step i+1 overlap the kernel of step i on a second stream.  Wall clock, synchronised both sides;
+    median of `repeats` K-step regions, max over ranks."""
     host = w["host"]
     h2d = sum(v.numel() * v.element_size() for v in host.values())
     copy_s, comp_s = torch.cuda.Stream(device), torch.cuda.Stream(device)
@@ -450,14 +484,16 @@ def time_e2e(w, steps, warmup, device, world_size):
         torch.cuda.synchronize()
 
     run(max(warmup, 3))
-    if world_size > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    run(steps)
-    dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=device)
-    if world_size > 1:
-        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-    return float(dt.item()), h2d, 32
+    samples = []
+    for _ in range(repeats):
+        if world_size > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        run(steps)
+        samples.append((time.perf_counter() - t0) * 1e3)
+    ms, stats = _rank_stats(samples, device, world_size)
+    return ms * 1e-3, h2d, 32, stats
 
 
 # --------------------------------------------------------------------------------------------
@@ -521,18 +557,37 @@ def cpu_step_fn(args, B):
     return step, B
 
 
-def time_cpu(args, seconds, steps=None, warmup=2):
-    torch.set_num_threads(os.cpu_count() or 1)
-    full_B = {"impala_loss": args.B or 4096, "ppo": args.B or 8192, "replay": 4096, "learner": args.B or 256}[args.workload]
+def cpu_model():
+    """The host CPU's model string (what `lscpu` prints as "Model name"), read from /proc/cpuinfo."""
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.lower().startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    import platform
+    return platform.processor() or platform.machine()
+
+
+def time_cpu(args, seconds, steps=None, warmup=2, threads=None, full_B=None, allow_shrink=True):
+    """The oracle port of the reference's CPU path.  `threads` = torch intra-op threads (default: every host core).
+    The per-step column count is the workload's full batch; it is shrunk -- only when `allow_shrink`, and decided
+    AFTER the warm-up calls (the first call pays vmap / thread-pool start-up) -- if `steps` full steps would not fit
+    the `seconds` budget."""
+    n_thr = threads or (os.cpu_count() or 1)
+    torch.set_num_threads(n_thr)
+    if full_B is None:
+        full_B = {"impala_loss": args.B or 4096, "ppo": args.B or 8192, "replay": 4096, "learner": args.B or 256}[args.workload]
     step, units = cpu_step_fn(args, full_B)
+    for _ in range(max(warmup, 1)):
+        step()
     t0 = time.perf_counter()
     step()
     t_full = time.perf_counter() - t0
     B = full_B
-    if steps is not None and t_full * (steps + warmup) > seconds:   # shrink the per-step sample to fit the budget
-        B = max(8, int(full_B * seconds / (t_full * (steps + warmup))))
+    if allow_shrink and steps is not None and t_full * steps > seconds:   # shrink the per-step sample to fit the budget
+        B = max(8, int(full_B * seconds / (t_full * steps)))
         step, units = cpu_step_fn(args, B)
-    for _ in range(warmup):
         step()
     n, t0 = 0, time.perf_counter()
     while True:
@@ -541,35 +596,130 @@ def time_cpu(args, seconds, steps=None, warmup=2):
         el = time.perf_counter() - t0
         if (steps is not None and n >= steps) or (steps is None and (el > seconds and n >= 3)) or el > 4 * seconds + 60:
             break
-    return dict(value=units * n / el, seconds=el, steps=n, cores=torch.get_num_threads(),
-                sample="%d step(s) of %d of %d columns per step, fwd+bwd, torch %d threads" % (n, B, full_B, torch.get_num_threads()))
+    torch.set_num_threads(os.cpu_count() or 1)
+    return dict(value=units * n / el, seconds=el, steps=n, cores=n_thr,
+                sample="%d step(s) of %d of %d columns per step, fwd+bwd, torch %d thread(s)" % (n, B, full_B, n_thr))
+
+
+def cpu_baseline_legs(args, unit, seconds):
+    """SURVEY sec 8d "CPU baseline beside it": every host core, one thread, and (impala_loss) BASELINE config 1
+    (T=20, B=32 -- the reference's own CPU-runnable case), with the CPU model string beside the numbers."""
+    r = time_cpu(args, seconds=seconds)
+    out = {"value": r["value"], "unit": unit, "cores": r["cores"], "kind": "port", "sample": r["sample"],
+           "cpu_count": os.cpu_count(), "cpu_model": cpu_model()}
+    one = time_cpu(args, seconds=seconds / 2, threads=1)
+    out["one_thread"] = {"value": one["value"], "unit": unit, "cores": 1, "sample": one["sample"]}
+    if args.workload == "impala_loss":
+        c1 = time_cpu(args, seconds=3.0, full_B=32)
+        out["config1_T20_B32"] = {"value": c1["value"], "unit": unit, "cores": c1["cores"], "sample": c1["sample"],
+                                  "ms_per_step": 1e3 * c1["seconds"] / c1["steps"]}
+    return out
+
+
+def shared_config(args):
+    """The keys that name the workload -- identical in both arms' `config`."""
+    return {"workload": WORKLOAD_NAMES[args.workload], "T": args.T or DEFAULT_T[args.workload],
+            "B_per_gpu": args.B or (max(8192 // max(args.gpus, 1), 1) if args.workload == "ppo" else DEFAULT_B[args.workload]),
+            "A": args.A, "layout": args.layout}
 
 
 # --------------------------------------------------------------------------------------------
 def run_reference(args, rank, world_size):
     """`--impl reference`: the reference's own CPU path for this metric.  The reference cannot be imported
     (rlego / rlmeta / moolib are neither installed nor vendored), so this times the oracle port of
-    its torch code on all host cores.  Rank 0 only; other ranks exit 0."""
+    its torch code on all host cores, on the SAME per-GPU configuration as the b200 arm (the full batch every step for
+    the headline workload: never shrunk).  Rank 0 only; other ranks exit 0."""
     if rank != 0:
         return
     metric, unit, _ = WORKLOADS[args.workload]
     steps = args.steps if args.steps is not None else 20
-    warmup = args.warmup if args.warmup is not None else 3
-    r = time_cpu(args, seconds=90.0, steps=steps, warmup=min(warmup, 5))
+    warmup = min(args.warmup if args.warmup is not None else 3, 5)
+    full_B = shared_config(args)["B_per_gpu"] if args.workload != "replay" else 4096
+    r = time_cpu(args, seconds=90.0, steps=steps, warmup=max(warmup, 2), full_B=full_B,
+                 allow_shrink=args.workload in ("ppo", "learner"))
+    cfg = shared_config(args)
+    cfg.update({"sample": r["sample"], "cpu_model": cpu_model(),
+                "note": "reference CPU path = oracle port of the reference's torch code (the reference itself is "
+                        "not importable: rlego/rlmeta/moolib absent and unpinned, DESIGN.md sec 2)"})
     line = {
         "impl": "reference", "metric": metric, "value": r["value"], "unit": unit, "n_gpus": args.gpus,
-        "steps": r["steps"], "warmup": min(warmup, 5), "ms_per_step": 1e3 * r["seconds"] / r["steps"],
+        "steps": r["steps"], "warmup": max(warmup, 2), "ms_per_step": 1e3 * r["seconds"] / r["steps"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u8" if args.workload == "replay" else "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD_NAMES[args.workload], "T": args.T or DEFAULT_T[args.workload], "A": args.A,
-                   "B_per_gpu": args.B or DEFAULT_B[args.workload], "sample": r["sample"],
-                   "note": "reference CPU path = oracle port of the reference's torch code (the reference itself is "
-                           "not importable: rlego/rlmeta/moolib absent and unpinned, DESIGN.md sec 2)"},
-        "cpu_baseline": {"value": r["value"], "unit": unit, "cores": r["cores"], "kind": "port", "sample": r["sample"]},
+        "config": cfg,
+        "cpu_baseline": {"value": r["value"], "unit": unit, "cores": r["cores"], "kind": "port", "sample": r["sample"],
+                         "cpu_model": cpu_model()},
         "e2e": {"value": r["value"], "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+DEFAULT_STEPS = {"impala_loss": 2000, "ppo": 200, "replay": 400, "learner": 20}
+OTHER_STEPS = {"ppo": 20, "replay": 20, "learner": 10}      # the secondary workloads of the default run
+
+
+def measure(name, args, device, rank, world_size, steps, warmup, repeats, seed):
+    """Build workload `name`, time `steps` steps (median of `repeats` timed regions, max over ranks) and return
+    (workload, result dict)."""
+    import copy
+    a = copy.copy(args)
+    a.workload = name
+    _, unit, bytes_per_unit = WORKLOADS[name]
+    w = MAKERS[name](a, device, seed=seed)
+    if w.get("graph", True):
+        ms, clocks, stats = time_device(w["launch"], steps, warmup, device, world_size, a.streams if name == "impala_loss" else 1, repeats)
+    else:
+        ms, clocks, stats = time_eager(w["launch"], steps, warmup, device, world_size, max(1, min(repeats, 3)))
+    peak, peak_src = measured_peak()
+    res = {"value": w["units"] * steps * world_size / (ms * 1e-3), "unit": unit, "ms_per_step": ms / steps, "steps": steps,
+           "timing": stats, "clocks": clocks, "launches": steps * w["kernels"] * stats["repeats"]}
+    if bytes_per_unit is not None:
+        achieved = bytes_per_unit * w["units"] * steps / (ms * 1e-3) / 1e9     # per GPU, GB/s
+        res["roofline"] = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                           "traffic": recorded_traffic(name), "peak_source": peak_src,
+                           "algorithmic_bytes_per_step": bytes_per_unit * w["units"],
+                           "note": "per GPU; duration = median timed region / steps (launch gaps included); the measured peak is "
+                                   "a copy (half reads, half writes) -- a read-heavy kernel can exceed it"}
+    return w, res
+
+
+def k8_check(args, device, rank, world_size):
+    """N > 1: the gradient exchange of the learner step, checked in the driver-run process.  Two learners from the same
+    seed (same weights, same replay content, same sampler stream) run 3 steps: one through K8 (allreduce fused into
+    clip + Adam over NVLink peer memory), one through ONE NCCL allreduce + K6.  Reports whether the K8 parameters are
+    bit-identical on every rank and how far the two routes are apart."""
+    import copy
+    from impala_b200 import parallel
+    out = {}
+    flats = {}
+    for route, env in (("k8_peer", "auto"), ("nccl", "0")):
+        os.environ["B200RL_PEER_ALLREDUCE"] = env
+        a = copy.copy(args)
+        a.workload, a.B, a.T = "learner", 64, 20
+        w = make_learner(a, device, seed=4242)          # same seed on every rank: same model; replay stream differs by design
+        for i in range(3):
+            w["launch"](i)
+        torch.cuda.synchronize()
+        learner = w["learner"]
+        flat = torch.cat([p.detach().reshape(-1) for p in learner._model.parameters()])
+        flats[route] = flat
+        if route == "k8_peer":
+            out["route"] = w["grad_exchange"]()
+            out["peer_bucket"] = isinstance(learner._bucket, parallel.PeerGradBucket)
+        everyone = [torch.empty_like(flat) for _ in range(world_size)]
+        dist.all_gather(everyone, flat)
+        out["params_bit_identical_across_ranks" + ("" if route == "k8_peer" else "_nccl")] = all(torch.equal(everyone[0], e) for e in everyone)
+        if hasattr(learner._bucket, "close"):
+            learner._bucket.close()
+        del w, learner
+        torch.cuda.empty_cache()
+    os.environ.pop("B200RL_PEER_ALLREDUCE", None)
+    d = (flats["k8_peer"] - flats["nccl"]).abs().max().item()
+    out["max_abs_diff_vs_nccl_route"] = d
+    out["max_rel_diff_vs_nccl_route"] = d / max(flats["nccl"].abs().max().item(), 1e-30)
+    out["steps"] = 3
+    return out
 
 
 def main():
@@ -577,6 +727,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    args.gpus = world_size if world_size > 1 else args.gpus
     if args.impl == "reference":
         return run_reference(args, rank, world_size)
     if not torch.cuda.is_available():
@@ -587,67 +738,104 @@ def main():
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=device)
     metric, unit, bytes_per_unit = WORKLOADS[args.workload]
-    steps = args.steps if args.steps is not None else {"impala_loss": 20000, "ppo": 2000, "replay": 4000, "learner": 50}[args.workload]
-    warmup = args.warmup if args.warmup is not None else 50
-    args.gpus = world_size if world_size > 1 else args.gpus
+    steps = args.steps if args.steps is not None else DEFAULT_STEPS[args.workload]
+    warmup = args.warmup if args.warmup is not None else 20
+    repeats = args.repeats
 
-    w = MAKERS[args.workload](args, device, seed=2000 + 1000 * rank)
-    if w.get("graph", True):
-        ms, clocks = time_device(w["launch"], steps, warmup, device, world_size, args.streams)
-    else:
-        ms, clocks = time_eager(w["launch"], steps, warmup, device, world_size)
-    units_total = w["units"] * steps * world_size
-    value = units_total / (ms * 1e-3)
-    peak, peak_src = measured_peak()
-    achieved = (bytes_per_unit or 0) * w["units"] * steps / (ms * 1e-3) / 1e9     # per GPU, GB/s
+    w, res = measure(args.workload, args, device, rank, world_size, steps, warmup, repeats, seed=2000 + 1000 * rank)
+    launches = res["launches"]
+    cfg = shared_config(args)
+    cfg.update(w["desc"])
+    cfg.update(parallelism="dp%d (rank-local batches sharded along B, no data-path collective)" % world_size,
+               streams=args.streams if args.workload == "impala_loss" else 1,
+               timing=dict(res["timing"], method="ONE CUDA graph of the K steps, CUDA events on the launching stream, barrier + "
+                           "synchronize on both sides; replayed `repeats` times; ms_per_step = median replay / K, max over ranks"))
     line = {
-        "metric": metric, "value": value, "unit": unit, "n_gpus": world_size, "steps": steps, "warmup": max(warmup, 3),
-        "ms_per_step": ms / steps, "higher_is_better": True,
+        "metric": metric, "value": res["value"], "unit": unit, "n_gpus": world_size, "steps": steps, "warmup": max(warmup, 3),
+        "ms_per_step": res["ms_per_step"], "higher_is_better": True,
         "scaling": "strong" if (args.workload == "ppo" and args.B is None) else "weak",
         "vs_baseline": None, "dtype": "u8" if args.workload == "replay" else "f32", "data": "synthetic",
-        "config": dict(w["desc"], parallelism="dp%d (rank-local batches sharded along B, no data-path collective)" % world_size,
-                       streams=args.streams, timing="CUDA graph of back-to-back steps, CUDA events on the launching stream, max over ranks"),
-        "roofline": None if bytes_per_unit is None else {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": recorded_traffic(args.workload), "peak_source": peak_src,
-                     "algorithmic_bytes_per_step": bytes_per_unit * w["units"],
-                     "note": "per GPU; duration = timed region / steps (launch gaps included); the measured peak is a copy (half reads, half writes) -- a read-heavy kernel can exceed it"},
-        "clocks": clocks,
-        "gpu_launches": steps * w["kernels"],
+        "config": cfg, "roofline": res.get("roofline"), "clocks": res["clocks"],
     }
-    if args.workload == "impala_loss" and (args.streams > 1 or args.pipeline == "independent"):
-        # transparency: the same kernel as a plain dependent chain on ONE stream without the PDL input promise
+    peak, _ = measured_peak()
+    if args.workload == "impala_loss":
+        # the other launch pattern of the same kernel, for transparency: headline = what ONE learner step sees (a
+        # dependent chain on one stream); overlapped = independent rollout batches on 6 streams with the PDL input promise
         import copy
-        a2 = copy.copy(args)
-        a2.pipeline, a2.streams = "serial", 1
-        w2 = MAKERS[args.workload](a2, device, seed=7000 + 1000 * rank)
-        ms2, _ = time_device(w2["launch"], min(steps, 4000), warmup, device, world_size, 1)
-        per = ms2 / min(steps, 4000)
-        line["config"]["serial_single_stream"] = {
-            "ms_per_step": per, "frac": bytes_per_unit * w2["units"] / (per * 1e-3) / 1e9 / peak,
-            "note": "same launches as a dependent chain on one stream, every launch waits for its predecessor before "
-                    "reading (what a lone learner step sees); the headline overlaps independent batches"}
-        del w2
+        for key, (pl, st) in (("serial_single_stream", ("serial", 1)), ("overlapped_6_streams", ("independent", 6))):
+            if (args.pipeline, args.streams) == (pl, st):
+                line["config"][key] = {"ms_per_step": res["ms_per_step"], "frac": res["roofline"]["frac"], "note": "this is the headline"}
+                continue
+            a2 = copy.copy(args)
+            a2.pipeline, a2.streams = pl, st
+            w2, r2 = measure("impala_loss", a2, device, rank, world_size, steps, warmup, max(5, repeats // 2), seed=7000 + 1000 * rank)
+            launches += r2["launches"]
+            line["config"][key] = {"ms_per_step": r2["ms_per_step"], "frac": r2["roofline"]["frac"], "timing": r2["timing"],
+                                   "note": "same kernel, pipeline=%s on %d stream(s)" % (pl, st)}
+            del w2
     if w.get("breakdown"):
         line["config"]["breakdown_ms"] = w["breakdown"]()
-        if "grad_exchange" in w["desc"]:
-            line["config"]["grad_exchange"] = w["desc"]["grad_exchange"]
+        line["config"]["grad_exchange"] = w["grad_exchange"]()
+        line["config"]["launches_per_step"] = w["launches_per_step"]()
+        launches += line["config"]["launches_per_step"] * steps * res["timing"]["repeats"]
     if not args.no_e2e and w["e2e_step"] is not None:
-        e_steps = min(steps, 2000)
-        dt, h2d, d2h = time_e2e(w, e_steps, min(warmup, 20), device, world_size)
+        e_steps = min(steps, 500)
+        dt, h2d, d2h, est = time_e2e(w, e_steps, min(warmup, 20), device, world_size)
+        launches += e_steps * w["kernels"] * est["repeats"]
         line["e2e"] = {"value": w["units"] * e_steps * world_size / dt, "unit": unit, "h2d_bytes_per_step": h2d,
-                       "d2h_bytes_per_step": d2h, "steps": e_steps,
-                       "note": "pinned host arena -> ONE H2D copy -> fused kernel -> D2H of the 8 loss/metric scalars, every step"}
+                       "d2h_bytes_per_step": d2h, "steps": e_steps, "timing": est,
+                       "note": "pinned host arena -> ONE H2D copy -> fused kernel -> D2H of the 8 loss/metric scalars, every step; "
+                               "wall clock, median of the repeats, max over ranks"}
     elif not args.no_e2e:
         line["e2e"] = None
+    del w
+    torch.cuda.empty_cache()
+
+    # BASELINE configs 3 / 4 / 5 in the same driver-run record (same process, same ranks), each to the same timing rules
+    others = [n for n in (args.others.split(",") if args.others else []) if n and n != args.workload]
+    if others:
+        line["config"]["other_workloads"] = {}
+    for name in others:
+        try:
+            import copy
+            a3 = copy.copy(args)
+            a3.B = a3.T = None
+            a3.layout = "batch_major"
+            w3, r3 = measure(name, a3, device, rank, world_size, OTHER_STEPS[name], 3, 10, seed=9000 + 1000 * rank)
+            launches += r3["launches"]
+            entry = {"metric": WORKLOADS[name][0], "value": r3["value"], "unit": r3["unit"], "ms_per_step": r3["ms_per_step"],
+                     "steps": r3["steps"], "timing": r3["timing"], "config": dict(shared_config(a3_named(a3, name)), **w3["desc"])}
+            if "roofline" in r3:
+                entry["roofline"] = {k: r3["roofline"][k] for k in ("achieved", "peak", "frac", "algorithmic_bytes_per_step")}
+            if w3.get("breakdown"):
+                entry["breakdown_ms"] = w3["breakdown"]()
+                entry["grad_exchange"] = w3["grad_exchange"]()
+                entry["launches_per_step"] = w3["launches_per_step"]()
+                launches += entry["launches_per_step"] * r3["steps"] * r3["timing"]["repeats"]
+            line["config"]["other_workloads"][name] = entry
+            if hasattr(w3.get("learner", None), "_bucket") and hasattr(w3["learner"]._bucket, "close"):
+                w3["learner"]._bucket.close()
+            del w3
+            torch.cuda.empty_cache()
+            if name == "learner" and world_size > 1:
+                line["config"]["other_workloads"]["learner"]["k8_check"] = k8_check(args, device, rank, world_size)
+        except Exception as e:  # a secondary workload must not take the headline line down with it
+            line["config"]["other_workloads"][name] = {"error": "%s: %s" % (type(e).__name__, e)}
+            if world_size > 1:
+                raise
+    line["gpu_launches"] = launches
     if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
-        r = time_cpu(args, seconds=args.cpu_seconds)
-        line["cpu_baseline"] = {"value": r["value"], "unit": unit, "cores": r["cores"], "kind": "port",
-                                "sample": r["sample"], "cpu_count": os.cpu_count()}
+        line["cpu_baseline"] = cpu_baseline_legs(args, unit, args.cpu_seconds)
     if rank == 0:
         print(json.dumps(line), flush=True)
     if world_size > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def a3_named(a, name):
+    a.workload = name
+    return a
 
 
 if __name__ == "__main__":

@@ -96,6 +96,10 @@ __device__ __forceinline__ void bulk_s2g(void *dst, const void *src_smem, uint32
                  "r"(smem_u32(src_smem)), "r"(bytes)
                  : "memory");
 }
+// L2 prefetch of a contiguous global range (a hint: no data reaches the SM).  16-byte aligned address and size.
+__device__ __forceinline__ void bulk_prefetch_l2(const void *src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(src), "r"(bytes) : "memory");
+}
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() {
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
@@ -337,6 +341,20 @@ __device__ __forceinline__ void grid_reduce(float (&vals)[NV], float *red, void 
 // The same protocol for small persistent grids (gridDim.x <= a few hundred), run by ONE WARP of each CTA:
 // no block-wide barrier anywhere.  tot[k] must be valid in every lane of the calling warp.  The collector
 // warp's lanes take CTAs lane, lane + 32, ... and the partials are summed in a fixed order.
+// warp_publish: a non-collector CTA's partials (any CTA but the last); warp_collect: the last CTA's duty.
+template <int NV>
+__device__ __forceinline__ void warp_publish(const float (&tot)[NV], void *workspace, unsigned int gen) {
+    static_assert(NV <= kNumScalars, "partials rows");
+    unsigned long long *words =
+        reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(workspace) + 256);
+    const unsigned int tag = (gen & 0x7fffffffu) + 1u, lane = threadIdx.x & 31;
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+        if (lane == k)
+            st_volatile_u64(&words[k * kMaxPartialCtas + blockIdx.x],
+                            ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(tot[k]));
+}
+
 template <int NV, typename Finalize>
 __device__ __forceinline__ void warp_collect(const float (&tot)[NV], void *workspace, unsigned int gen,
                                              Finalize finalize) {
@@ -346,14 +364,6 @@ __device__ __forceinline__ void warp_collect(const float (&tot)[NV], void *works
         reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(workspace) + 256);
     const unsigned int tag = (gen & 0x7fffffffu) + 1u;
     const unsigned int n_other = gridDim.x - 1, lane = threadIdx.x & 31;
-    if (blockIdx.x != n_other) {
-#pragma unroll
-        for (int k = 0; k < NV; ++k)
-            if (lane == k)
-                st_volatile_u64(&words[k * kMaxPartialCtas + blockIdx.x],
-                                ((unsigned long long)tag << 32) | (unsigned long long)__float_as_uint(tot[k]));
-        return;
-    }
     float acc[NV];
 #pragma unroll
     for (int k = 0; k < NV; ++k) acc[k] = 0.f;

@@ -39,12 +39,23 @@ struct K1Params {
     int B, T, A;
     int C, W, G, U;             // columns per unit, warps per group, groups per CTA, units
     int GPC, NSTAGE;            // units per chunk, chunk stages in shared memory
+    int window;                 // chunks issued at kernel start; chunk c + window is issued when chunk c lands
     int unit_words, ns4;        // C*T*A, C*T rounded up to 4 (4-byte words)
     unsigned int inv_T;         // ceil(2^32 / T)
+    // no integer division on the device (a 64-bit one is ~100 instructions in every warp): the units-per-CTA split and
+    // the magic reciprocals ceil(2^32 / d) of W, GPC, NSTAGE come from the host (exact for operands < 2^16)
+    int units_lo, units_rem;    // CTA b owns units_lo + (b < units_rem) units starting at b * units_lo + min(b, units_rem)
+    unsigned int inv_W, inv_GPC, inv_NSTAGE;
     float lambda_, one_minus_lambda, clip_rho, clip_pg_rho, entropy_coeff, inv_n_pg, inv_n_all;
     uint32_t flags;
-    int debug;                  // B200RL_K1_DEBUG (profiling): 1 = skip the arithmetic, 2 = skip the grid collector
+    int prefetch;               // L2 prefetch hint of the CTA's inputs before the PDL dependency wait
+    int debug;                  // B200RL_K1_DEBUG (profiling): 1 = skip the arithmetic, 2 = skip the grid collector, 4 = skip the small-field loads
 };
+
+// x / d for small non-negative x with the host's magic m = ceil(2^32 / d) (d = 1 has no 32-bit magic)
+__device__ __forceinline__ int fast_div(int x, int d, unsigned int m) {
+    return d == 1 ? x : (int)__umulhi((unsigned)x, m);
+}
 
 __device__ __forceinline__ void group_sync(int id, int nthreads) {
     if (nthreads == 32) __syncwarp();
@@ -60,7 +71,7 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
     const int T = p.T, A = EXACT ? AT : p.A, C = p.C, G = p.G, GPC = p.GPC, NSTAGE = p.NSTAGE;
     const int gthreads = p.W * 32;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-    const int grp = warp / p.W;
+    const int grp = fast_div(warp, p.W, p.inv_W);
     const int i = threadIdx.x - grp * gthreads;  // thread (= sample) index inside the group
     const int bar_id = grp + 1;                  // named barrier of the group (0 is __syncthreads)
     const int chunk_words = GPC * p.unit_words;
@@ -87,6 +98,28 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
     const bool late_wait = p.flags & B200RL_INPUTS_STABLE;
     unsigned int gen = 0;
     if (!late_wait) {
+        if (p.prefetch) {
+            // A HINT, not a read: while the preceding kernel is still running, ask L2 for this CTA's share of the
+            // inputs (cp.async.bulk.prefetch.L2).  Address translation and the HBM reads then overlap the
+            // predecessor's tail; L2 is the coherence point, so lines the predecessor still writes are simply
+            // updated there, and every value is read only after the dependency wait below.
+            if (lane == 0 && warp < 4) {
+                const int b = (int)blockIdx.x, us = b * p.units_lo + min(b, p.units_rem), ue = us + p.units_lo + (b < p.units_rem ? 1 : 0);
+                const size_t e0 = (size_t)us * C * T, e1 = (size_t)min(ue * C, p.B) * T;   // samples [e0, e1)
+                const uint32_t ns = (uint32_t)(e1 - e0), nb = ns * (uint32_t)A * 4u;
+                const int w = nwarps >= 4 ? warp : -1;   // four issuing warps when the CTA has them, else warp 0 does all
+                if (ns && (w == 0 || (w < 0 && warp == 0))) bulk_prefetch_l2(p.logits + e0 * A, nb);
+                if (ns && (w == 1 || (w < 0 && warp == 0))) bulk_prefetch_l2(p.pi_ref + e0 * A, nb);
+                if (ns && (w == 2 || (w < 0 && warp == 0))) {
+                    bulk_prefetch_l2(p.actions + e0, ns * 8u);
+                    bulk_prefetch_l2(p.rewards + e0, ns * 4u);
+                }
+                if (ns && (w == 3 || (w < 0 && warp == 0))) {
+                    bulk_prefetch_l2(p.discounts + e0, ns * 4u);
+                    bulk_prefetch_l2(p.values + e0, ns * 4u);
+                }
+            }
+        }
         pdl_wait();  // inputs may come from the preceding kernel
         gen = grid_generation(p.workspace);  // consumed by the last warp at the very end: latency hidden
     }
@@ -94,14 +127,16 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
     K1_STAMP(0);
 
     // this CTA's contiguous range of units, its chunks
-    const int ustart = (int)((long long)blockIdx.x * p.U / gridDim.x);
-    const int n_units = (int)((long long)(blockIdx.x + 1) * p.U / gridDim.x) - ustart;
-    const int n_chunks = (n_units + GPC - 1) / GPC;
+    const int ustart = (int)blockIdx.x * p.units_lo + min((int)blockIdx.x, p.units_rem);
+    const int n_units = p.units_lo + ((int)blockIdx.x < p.units_rem ? 1 : 0);
+    const int n_chunks = fast_div(n_units + GPC - 1, GPC, p.inv_GPC);
+    auto stage_of = [&](int c, int &round) { round = fast_div(c, NSTAGE, p.inv_NSTAGE); return c - round * NSTAGE; };
     auto chunk_units = [&](int c) { return min(GPC, n_units - c * GPC); };
     auto chunk_col0 = [&](int c) { return (ustart + c * GPC) * C; };
     auto chunk_cols = [&](int c) { return min((ustart + c * GPC + chunk_units(c)) * C, p.B) - chunk_col0(c); };
     auto issue_chunk = [&](int c) {  // one thread
-        const int st = c % NSTAGE;
+        int round;
+        const int st = stage_of(c, round);
         float *sx = smem + (size_t)st * 2 * chunk_words;
         const size_t e0 = (size_t)chunk_col0(c) * T * A;
         const uint32_t bytes = (uint32_t)(chunk_cols(c) * T * A * 4);
@@ -110,7 +145,7 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
         bulk_g2s(sx + chunk_words, p.pi_ref + e0, bytes, bars + st);
     };
     if (lane == 0)  // copies complete in issue order: chunk 0 first.  Spread over warps: an issue costs ~55 cycles
-        for (int c = warp; c < min(NSTAGE, n_chunks); c += nwarps) issue_chunk(c);
+        for (int c = warp; c < min(min(NSTAGE, n_chunks), p.window); c += nwarps) issue_chunk(c);
 
     const bool detach_adv = p.flags & B200RL_DETACH_ADV, detach_rho = p.flags & B200RL_DETACH_RHO;
     const int col = (int)__umulhi((unsigned)i, p.inv_T), t = i - col * T;
@@ -122,7 +157,7 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
     long long act = 0;
     float rew = 0.f, disc = 0.f, v = 0.f, v_next = 0.f;
     auto fetch_small = [&](int j) {
-        if (j >= n_units) return;
+        if (j >= n_units || (p.debug & 4)) return;
         const int b0 = (ustart + j) * C, nsu = min(C, p.B - b0) * T;
         const size_t n = (size_t)b0 * T + i;
         if (i < nsu) {
@@ -135,15 +170,65 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
     };
     fetch_small(grp);
 
+    // One reduction per CTA by its last-arriving warp, no block-wide barrier: a warp leaves its five sums in shared
+    // memory; the warp that arrives last adds the warps' sums (fixed order everywhere: bit-reproducible scalars) and
+    // publishes the CTA's partials (warp_publish).  In the collector CTA that warp only notes its duty: it polls for the
+    // other CTAs' words at the very end, when they have long landed.
+    bool reduced = false, is_collector = false;
+    auto cta_reduce_publish = [&]() {  // consumes `sums`
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int k = 0; k < 5; ++k) sums[k] += __shfl_xor_sync(0xffffffffu, sums[k], o);
+        }
+        int arrived = 0;
+        if (lane == 0) {
+#pragma unroll
+            for (int k = 0; k < 5; ++k) red[k * nwarps + warp] = sums[k];
+            __threadfence_block();
+            arrived = atomicAdd(&ctl[0], 1);
+        }
+        arrived = __shfl_sync(0xffffffffu, arrived, 0);
+        if (arrived != nwarps - 1) return;
+        unsigned long long *ctr = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(p.workspace) + kTraceOffset) +
+                                  (size_t)(2048 + blockIdx.x) * 16;  // CTA-level stamps (trace instantiation only)
+        if (TRACE && lane == 0 && blockIdx.x < 2048) ctr[0] = globaltimer_ns();
+        __threadfence_block();
+        // lane w takes warp w's sums; xor-shuffle tree in a fixed order (nwarps <= 32)
+        float cta_tot[5];
+#pragma unroll
+        for (int k = 0; k < 5; ++k) cta_tot[k] = lane < nwarps ? red[k * nwarps + lane] : 0.f;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+            for (int k = 0; k < 5; ++k) cta_tot[k] += __shfl_xor_sync(0xffffffffu, cta_tot[k], o);
+        }
+        if (late_wait) {
+            pdl_wait();  // the workspace and scalars are shared with the previous launch
+            gen = grid_generation(p.workspace);
+        }
+        if (blockIdx.x == gridDim.x - 1) {  // the collector parks its own totals in shared memory until the end
+            is_collector = true;
+            __syncwarp();
+#pragma unroll
+            for (int k = 0; k < 5; ++k)
+                if (lane == k) red[k] = cta_tot[k];
+        } else if (!(p.debug & 2)) warp_publish<5>(cta_tot, p.workspace, gen);
+        if (TRACE && lane == 0 && blockIdx.x < 2048) ctr[1] = globaltimer_ns();
+    };
+
     bool first = true;
     for (int j = grp; j < n_units; j += G) {
-        const int c = j / GPC, st_i = c % NSTAGE;
+        const int c = fast_div(j, GPC, p.inv_GPC);
+        int round;
+        const int st_i = stage_of(c, round);
         float *sx = smem + (size_t)st_i * 2 * chunk_words + (size_t)(j - c * GPC) * p.unit_words;
         float *sy = sx + chunk_words;
         const int b0 = (ustart + j) * C, ucols = min(C, p.B - b0), nsu = ucols * T;
         const size_t n0 = (size_t)b0 * T;
 
-        mbar_wait(bars + st_i, (uint32_t)(c / NSTAGE) & 1u);  // the unit's chunk has landed
+        mbar_wait(bars + st_i, (uint32_t)round & 1u);  // the unit's chunk has landed
+        if (i == 0 && j == c * GPC && c + p.window < min(NSTAGE, n_chunks)) issue_chunk(c + p.window);  // first round only
         if (first) K1_STAMP(1);
 
         // ---- per-sample softmax statistics, TD error, trace coefficient ------------------------
@@ -169,31 +254,27 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
         if (first) K1_STAMP(2);
 
         // ---- backward-in-time recursion e_k = td_k + (discount_k c_k) e_{k+1} ------------------
-        // one register chain per column, steps fetched 4 at a time, in the reference loop's operation order
+        // one register chain per column, steps fetched 6 at a time, in the reference loop's operation order
         if (i < ucols) {
             const float2 *__restrict__ qp = s_tg + i * T + (T - 2);
             float *__restrict__ ep = s_e + i * T + (T - 2);
             float e = 0.f;
             int k = T - 2;
-            for (; k >= 3; k -= 4, qp -= 4, ep -= 4) {  // 4 independent loads, then 4 chained FMAs
-                const float2 q0 = qp[0], q1 = qp[-1], q2 = qp[-2], q3 = qp[-3];
-                e = q0.x + q0.y * e; ep[0] = e;
-                e = q1.x + q1.y * e; ep[-1] = e;
-                e = q2.x + q2.y * e; ep[-2] = e;
-                e = q3.x + q3.y * e; ep[-3] = e;
-            }
-            for (; k >= 0; --k, --qp, --ep) {
-                const float2 q = *qp;
-                e = q.x + q.y * e;
-                *ep = e;
+            for (; k >= 0; k -= 6, qp -= 6, ep -= 6) {  // 6 independent loads, then 6 chained FMAs
+                float2 q[6];
+#pragma unroll
+                for (int u = 0; u < 6; ++u) q[u] = (k - u >= 0) ? qp[-u] : make_float2(0.f, 0.f);
+#pragma unroll
+                for (int u = 0; u < 6; ++u)
+                    if (k - u >= 0) { e = q[u].x + q[u].y * e; ep[-u] = e; }
             }
         }
         group_sync(bar_id, gthreads);
         if (first) K1_STAMP(3);
 
-        // ---- losses and gradients ---------------------------------------------------------------
+        // ---- loss terms (they need only the statistics and the recursion), per-sample gradients of lp and v ----
+        float g_lp = 0.f, dv = 0.f;
         if (valid) {
-            float g_lp = 0.f, dv = 0.f;
             if (has_next) {
                 const float e = s_e[i];
                 const float tgt = e + u_v;     // stop-gradient target vs_t
@@ -216,10 +297,17 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
                 if (!detach_adv) dv += st.lp * c_pg * p.inv_n_pg;
             }
             if (t > 0) dv += s_nx[i - 1];
-            p.dvalues[n0 + i] = dv;
             sums[2] += st.H;
             sums[3] += st.kl;
             sums[4] += st.rho;
+        }
+        // The scalars are complete for this thread once its LAST unit is past the recursion: the CTA's reduction and
+        // the publication to the collector start here and travel while the gradients below are still being written.
+        if (!late_wait && j + G >= n_units) { cta_reduce_publish(); reduced = true; }
+
+        // ---- gradients ---------------------------------------------------------------------------
+        if (valid) {
+            p.dvalues[n0 + i] = dv;
             write_dlogits<AT, EXACT>(st, sx + i * A, A, g_lp, p.entropy_coeff * p.inv_n_all);
         }
         fence_proxy_async_smem();  // gradient rows -> visible to the bulk store
@@ -243,35 +331,17 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
         first = false;
     }
 
-    // ---- scalars: one reduction per CTA by its last-arriving warp, then the grid collector -------
-    // no block-wide barrier: a warp leaves its five sums in shared memory and retires; the warp that arrives
-    // last adds the warps' sums in index order (fixed order everywhere: bit-reproducible scalars)
+    // ---- scalars: warps that had no unit (or INPUTS_STABLE: the workspace is the previous launch's until it is
+    // complete) reduce here; then the collector warp, which parked its duty until its own gradients were out
+    if (!reduced) cta_reduce_publish();
+    if (is_collector) {
+        __syncwarp();
+        float cta_tot[5];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-        for (int k = 0; k < 5; ++k) sums[k] += __shfl_xor_sync(0xffffffffu, sums[k], o);
-    }
-    int arrived = 0;
-    if (lane == 0) {
-#pragma unroll
-        for (int k = 0; k < 5; ++k) red[k * nwarps + warp] = sums[k];
-        __threadfence_block();
-        arrived = atomicAdd(&ctl[0], 1);
-    }
-    arrived = __shfl_sync(0xffffffffu, arrived, 0);
-    if (arrived == nwarps - 1) {
-        __threadfence_block();
-        float tot[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-        for (int k = 0; k < 5; ++k)
-            for (int w = 0; w < nwarps; ++w) tot[k] += red[k * nwarps + w];
-        if (late_wait) {
-            pdl_wait();  // the workspace and scalars are shared with the previous launch
-            gen = grid_generation(p.workspace);
-        }
+        for (int k = 0; k < 5; ++k) cta_tot[k] = red[k];
         const float inv_n_pg = p.inv_n_pg, inv_n_all = p.inv_n_all, ec = p.entropy_coeff;
         float *scalars = p.scalars;
-        if (!(p.debug & 2)) warp_collect<5>(tot, p.workspace, gen, [=](const float(&s)[5]) {
+        if (!(p.debug & 2)) warp_collect<5>(cta_tot, p.workspace, gen, [=](const float(&s)[5]) {
             const float pg = s[0] * inv_n_pg, td = s[1] * inv_n_pg, ent = s[2] * inv_n_all;
             scalars[B200RL_S_LOSS] = -pg + td - ec * ent;
             scalars[B200RL_S_ENTROPY] = ent;
@@ -384,7 +454,12 @@ static int32_t launch_k1(const ImpalaArgs &a, cudaStream_t stream) {
         G = max(1, min(G, (NSTAGE - 1) * GPC));
     }
     p.G = G; p.GPC = GPC; p.NSTAGE = NSTAGE;
+    auto magic = [](int d) { return (unsigned int)(((1ull << 32) + (unsigned)d - 1) / (unsigned)d); };
+    p.inv_W = magic(W); p.inv_GPC = magic(GPC); p.inv_NSTAGE = magic(NSTAGE);
+    p.units_lo = p.U / grid; p.units_rem = p.U % grid;
     p.debug = env_int("B200RL_K1_DEBUG", 0);
+    p.window = max(1, env_int("B200RL_K1_WINDOW", 1 << 20));
+    p.prefetch = env_int("B200RL_K1_PREFETCH", 1);
     const int threads = G * W * 32;
     const size_t smem = (size_t)NSTAGE * 2 * GPC * unit_bytes + (size_t)G * 4 * p.ns4 * 4 + (size_t)NSTAGE * 12 +
                         5 * (size_t)(threads / 32) * 4 + 16 + 128;

@@ -254,7 +254,11 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams
         st_release_sys_u32(pp.flags[threadIdx.x] + kMaxPeers + pp.rank, pp.gen);
     const float norm = (PEER && !s_peer_ok) ? __int_as_float(0x7fc00000) : sqrtf(s_total);  // a peer never arrived: NaN
     float coef = 1.f;
-    if (a.max_norm > 0.f) coef = fminf(a.max_norm / (norm + 1e-6f), 1.f);  // torch clip_grad_norm_
+    // torch clip_grad_norm_: clamp(max_norm / (norm + 1e-6), max=1).  torch.clamp PROPAGATES NaN, CUDA fminf returns the
+    // non-NaN operand: a non-finite norm (NaN gradient, or the peer-timeout sentinel above) must poison the update
+    // like the reference's does, not turn into coef = 1 with partial gradients
+    if (a.max_norm > 0.f) coef = (norm == norm) ? fminf(a.max_norm / (norm + 1e-6f), 1.f) : norm;
+    else if (PEER && !s_peer_ok) coef = norm;
     if (blockIdx.x == 0 && threadIdx.x == 0) {
         *a.total_norm = norm;
         *reinterpret_cast<volatile unsigned int *>(a.gen) = tag;  // every CTA has read the old value (barrier above)

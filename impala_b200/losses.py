@@ -15,6 +15,25 @@ METRIC_SLOTS = (("train/loss", ops.S_LOSS), ("train/entropy", ops.S_ENTROPY), ("
                 ("train/pg", ops.S_PG), ("train/kl", ops.S_KL), ("train/ratio", ops.S_RATIO))
 
 
+_warned = set()
+
+
+def _as_input(x, name, dtype=torch.float32):
+    """The drop-in functions accept whatever the reference's torch code accepts (a sliced head output, a float64
+    reward, an int32 action ...); the kernels take contiguous float32 / int64 and ``ops`` raises on anything else.  The
+    conversion happens HERE, explicitly, and is announced once per (argument, reason): it is a copy the caller can
+    remove by producing the right layout."""
+    if x.dtype == dtype and x.is_contiguous():
+        return x
+    key = (name, str(x.dtype), x.is_contiguous())
+    if key not in _warned:
+        _warned.add(key)
+        import warnings
+        warnings.warn("impala_b200.losses: %s arrives as %s%s and is copied to contiguous %s before the fused kernel"
+                      % (name, x.dtype, "" if x.is_contiguous() else " (non-contiguous)", dtype))
+    return x.to(dtype).contiguous()
+
+
 class _FusedLoss(torch.autograd.Function):
     """loss = f(outputs...) whose gradients were already produced by the fused kernel."""
 
@@ -44,7 +63,8 @@ def impala_loss_from_outputs(logits, values, a, r, discount_t, pi_ref, entropy_c
     on model outputs ``logits [B,T,A]``, ``values [B,T]``.  Returns ``(loss, metrics)``."""
     flags = (ops.DETACH_ADV if detach_adv else 0) | (ops.DETACH_RHO if detach_rho else 0)
     scalars, dlogits, dvalues = ops.impala_loss_fwdbwd(
-        logits, values, a, r, discount_t, pi_ref, entropy_coeff, lambda_, clip_rho_threshold,
+        _as_input(logits, "logits"), _as_input(values, "values"), _as_input(a, "a", torch.int64), _as_input(r, "r"),
+        _as_input(discount_t, "discount_t"), _as_input(pi_ref, "pi_ref"), entropy_coeff, lambda_, clip_rho_threshold,
         clip_pg_rho_threshold, flags, n_global_b, time_major)
     loss = _attach(scalars[ops.S_LOSS], (logits, values), (dlogits, dvalues))
     metrics = {k: scalars[i] for k, i in METRIC_SLOTS}
@@ -53,7 +73,9 @@ def impala_loss_from_outputs(logits, values, a, r, discount_t, pi_ref, entropy_c
 
 def ppo_loss_from_outputs(logits, v, a, v_target, pi_ref, entropy_cost=0.01, clip_coeff=0.1, n_global=None):
     """Reference ``losses.py:134-155`` on model outputs ``logits [N,A]``, ``v [N,1]``."""
-    scalars, dlogits, dv = ops.ppo_loss_fwdbwd(logits, v, a, v_target, pi_ref, entropy_cost, clip_coeff, n_global)
+    scalars, dlogits, dv = ops.ppo_loss_fwdbwd(_as_input(logits, "logits"), _as_input(v, "v"), _as_input(a, "a", torch.int64),
+                                               _as_input(v_target, "v_target"), _as_input(pi_ref, "pi_ref"),
+                                               entropy_cost, clip_coeff, n_global)
     loss = _attach(scalars[ops.S_LOSS], (logits, v), (dlogits, dv))
     metrics = {k: scalars[i] for k, i in METRIC_SLOTS}
     metrics["train/target"] = scalars[ops.S_TARGET]
@@ -73,8 +95,9 @@ def ppo_is_loss_from_outputs(logits, v_tm1, v_boot, a, r, d, pi_ref, entropy_cos
                              lambda_=0.95, gamma=0.99, n_global_b=None):
     """Reference ``losses.py:64-89`` on model outputs ``logits [B,T,A]``, ``v_tm1 [B,T]`` and the bootstrap
     value ``v_boot [B]`` of ``s1[:, -1]``."""
-    scalars, dlogits, dv = ops.ppo_is_loss_fwdbwd(logits, v_tm1, v_boot, a, r, d, pi_ref, entropy_cost, clip_coeff,
-                                                  lambda_, gamma, n_global_b=n_global_b)
+    scalars, dlogits, dv = ops.ppo_is_loss_fwdbwd(_as_input(logits, "logits"), _as_input(v_tm1, "v_tm1"), _as_input(v_boot, "v_boot"),
+                                                  _as_input(a, "a", torch.int64), _as_input(r, "r"), d, _as_input(pi_ref, "pi_ref"),
+                                                  entropy_cost, clip_coeff, lambda_, gamma, n_global_b=n_global_b)
     loss = _attach(scalars[ops.S_LOSS], (logits, v_tm1), (dlogits, dv))
     metrics = {k: scalars[i] for k, i in METRIC_SLOTS}
     metrics["train/kl"] = scalars[ops.S_KL].clamp_min(0.)  # losses.py:79

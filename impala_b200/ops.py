@@ -36,8 +36,20 @@ def workspace(device):
     return ws
 
 
-def _f32c(x):
-    return x if (x.dtype == torch.float32 and x.is_contiguous()) else x.float().contiguous()
+def _f32c(x, name="tensor"):
+    """Kernel inputs are contiguous float32.  The library makes NO hidden copies (a silent ``.float().contiguous()``
+    is HBM traffic the size of the kernel's own): anything else raises, like every other contract violation here."""
+    if x.dtype == torch.float32 and x.is_contiguous():
+        return x
+    raise RuntimeError("impala_b200: %s must be a contiguous float32 tensor (got dtype %s, shape %s, strides %s); convert it "
+                       "explicitly -- the ops never copy behind the caller's back" % (name, x.dtype, tuple(x.shape), tuple(x.stride())))
+
+
+def _i64c(x, name="tensor"):
+    if x.dtype == torch.int64 and x.is_contiguous():
+        return x
+    raise RuntimeError("impala_b200: %s must be a contiguous int64 tensor (got dtype %s, shape %s, strides %s); convert it "
+                       "explicitly -- the ops never copy behind the caller's back" % (name, x.dtype, tuple(x.shape), tuple(x.stride())))
 
 
 def impala_loss_fwdbwd(logits, values, actions, rewards, discounts, pi_ref, entropy_coeff=0.01,
@@ -46,9 +58,9 @@ def impala_loss_fwdbwd(logits, values, actions, rewards, discounts, pi_ref, entr
     """K1.  Batch-major ``[B,T,A]`` / ``[B,T]`` tensors (or ``[T,B,A]`` / ``[T,B]`` with
     ``time_major=True``).  Returns ``(scalars[8], dlogits, dvalues)``; nothing is synchronised."""
     _require_cuda(logits, values, actions, rewards, discounts, pi_ref)
-    logits, pi_ref = _f32c(logits.detach()), _f32c(pi_ref.detach())
-    values, rewards, discounts = _f32c(values.detach()), _f32c(rewards), _f32c(discounts)
-    actions = actions if (actions.dtype == torch.int64 and actions.is_contiguous()) else actions.long().contiguous()
+    logits, pi_ref = _f32c(logits.detach(), "logits"), _f32c(pi_ref.detach(), "pi_ref")
+    values, rewards, discounts = _f32c(values.detach(), "values"), _f32c(rewards, "rewards"), _f32c(discounts, "discounts")
+    actions = _i64c(actions, "actions")
     if time_major:
         T, B, A = logits.shape
         sb, st = 1, B
@@ -171,10 +183,9 @@ def ppo_loss_fwdbwd(logits, v, actions, v_target, pi_ref, entropy_cost=0.01, cli
                     n_global=None, out=None):
     """K3.  ``logits, pi_ref [N,A]``; ``v, actions, v_target [N]``.  Returns ``(scalars[8], dlogits, dv)``."""
     _require_cuda(logits, v, actions, v_target, pi_ref)
-    logits, pi_ref = _f32c(logits.detach()), _f32c(pi_ref.detach())
-    v, v_target = _f32c(v.detach().reshape(-1)), _f32c(v_target.reshape(-1))
-    actions = actions.reshape(-1)
-    actions = actions if (actions.dtype == torch.int64 and actions.is_contiguous()) else actions.long().contiguous()
+    logits, pi_ref = _f32c(logits.detach(), "logits"), _f32c(pi_ref.detach(), "pi_ref")
+    v, v_target = _f32c(v.detach(), "v").reshape(-1), _f32c(v_target, "v_target").reshape(-1)
+    actions = _i64c(actions, "actions").reshape(-1)
     N, A = logits.shape
     if pi_ref.shape != logits.shape or v.numel() != N or v_target.numel() != N or actions.numel() != N:
         raise RuntimeError("ppo_loss: inconsistent shapes")
@@ -197,12 +208,12 @@ def ppo_is_loss_fwdbwd(logits, values, v_boot, actions, rewards, done, pi_ref, e
     """K7 (reference ``losses.py:62-89`` intent).  ``logits, pi_ref [B,T,A]``; ``values, actions, rewards, done
     [B,T]``; ``v_boot [B]``.  Returns ``(scalars[8], dlogits, dvalues)``."""
     _require_cuda(logits, values, v_boot, actions, rewards, done, pi_ref)
-    logits, pi_ref = _f32c(logits.detach()), _f32c(pi_ref.detach())
-    values, rewards, v_boot = _f32c(values.detach()), _f32c(rewards), _f32c(v_boot.detach().reshape(-1))
+    logits, pi_ref = _f32c(logits.detach(), "logits"), _f32c(pi_ref.detach(), "pi_ref")
+    values, rewards, v_boot = _f32c(values.detach(), "values"), _f32c(rewards, "rewards"), _f32c(v_boot.detach(), "v_boot").reshape(-1)
     if logits.dim() != 3:
         raise RuntimeError("ppo_is_loss: logits must be [B,T,A]")
     B, T, A = logits.shape
-    actions = actions if (actions.dtype == torch.int64 and actions.is_contiguous()) else actions.long().contiguous()
+    actions = _i64c(actions, "actions")
     if done.dtype == torch.bool and done.is_contiguous():
         done = done.view(torch.uint8)
     elif done.dtype != torch.uint8 or not done.is_contiguous():
@@ -239,7 +250,7 @@ def gather_rows(src, idx, out=None):
     _require_cuda(src, idx)
     if not src.is_contiguous():
         raise RuntimeError("gather_rows: storage must be contiguous")
-    idx = idx if (idx.dtype == torch.int64 and idx.is_contiguous()) else idx.long().contiguous()
+    idx = _i64c(idx, "idx")
     n, nrows = idx.numel(), src.shape[0]
     row_bytes = src[0].numel() * src.element_size() if nrows else 0
     if out is None:

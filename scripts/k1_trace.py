@@ -42,6 +42,9 @@ for mode, flags in flags_list.items():
     gr.replay(); torch.cuda.synchronize()
     ws = [w for w in ops._workspaces.values() if int(w[off:off + 8].view(torch.int64).item()) > 0][0]
     tr = ws[off:off + 4096 * 128].view(torch.int64).cpu().numpy().reshape(-1, 16)
+    cta = tr[2048:2048 + 1024]
+    cta = cta[cta[:, 0] > 0]
+    tr = tr[:2048]
     tr = tr[tr[:, 1] > 0]          # warp groups that processed at least one unit
     ncta = len(tr)
     gt, ck, sm = tr[:, :7].astype(np.float64), tr[:, 8:15].astype(np.float64), tr[:, 7]
@@ -53,6 +56,10 @@ for mode, flags in flags_list.items():
         print("  %-8s %8.0f %8.0f %8.0f" % (n, x.min(), np.median(x), x.max()))
     last = tr[tr[:, 6].argmax()]
     print("  latest group: " + " ".join("%s=%d" % (n, last[i] - t0) for i, n in enumerate(names)) + " smid=%d" % last[7])
+    if len(cta):
+        a, b = cta[:, 0].astype(np.float64) - t0, cta[:, 1].astype(np.float64) - t0
+        print("  per CTA, last warp arrives at the reduction: min %.0f median %.0f p90 %.0f max %.0f; published/collected: median %.0f max %.0f (collector CTA %d: arrives %.0f, done %.0f)"
+              % (a.min(), np.median(a), np.percentile(a, 90), a.max(), np.median(b), b.max(), len(cta) - 1, a[-1], b[-1]))
     print("clock64 deltas per CTA (cycles): phase  min  median  max")
     for i in range(1, 7):
         x = ck[:, i] - ck[:, i - 1]

@@ -36,7 +36,10 @@ __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)_
 
 // The same traffic through the TMA unit: every CTA bulk-loads its share in `nch` chunks (one mbarrier each, all issued
 // at once by `nissue` different warps) and bulk-stores the leading Wb/R part of every chunk as soon as it has landed.
-__global__ void __launch_bounds__(256) tma_stream_kernel(const char *__restrict__ in, char *__restrict__ out, int r_cta, int w_cta, int nch, int pdl) {
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+
+__global__ void __launch_bounds__(256) tma_stream_kernel(const char *__restrict__ in, char *__restrict__ out, int r_cta, int w_cta, int nch, int pdl,
+                                                          unsigned long long *stamps) {
     extern __shared__ __align__(128) unsigned char sm[];
     __shared__ unsigned long long bars[64];
     if (threadIdx.x == 0) {
@@ -48,6 +51,7 @@ __global__ void __launch_bounds__(256) tma_stream_kernel(const char *__restrict_
         asm volatile("griddepcontrol.wait;" ::: "memory");
     }
     __syncthreads();
+    if (stamps && threadIdx.x == 0) stamps[blockIdx.x * 4 + 0] = gtime();
     const int rc = r_cta / nch, wc = w_cta / nch;   // multiples of 16 by construction
     const char *src = in + (size_t)blockIdx.x * r_cta;
     char *dst = out + (size_t)blockIdx.x * w_cta;
@@ -64,10 +68,14 @@ __global__ void __launch_bounds__(256) tma_stream_kernel(const char *__restrict_
             while (!done)
                 asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
                              : "=r"(done) : "r"(smem_u32(&bars[k])) : "memory");
+            if (stamps && k == 0) stamps[blockIdx.x * 4 + 1] = gtime();
+            if (stamps && k == nch - 1) stamps[blockIdx.x * 4 + 2] = gtime();
             asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst + (size_t)k * wc), "r"(smem_u32(sm + (size_t)k * rc)), "r"(wc) : "memory");
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
         }
     if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+    __syncthreads();
+    if (stamps && threadIdx.x == 0) stamps[blockIdx.x * 4 + 3] = gtime();
 }
 
 int main() {
@@ -125,6 +133,8 @@ int main() {
                     printf("%6d %6d %4d %4d | %9.3f %9.0f\n", grid, thr, unr, pdl, us, (R + Wb) / us / 1e3);
                     cudaGraphExecDestroy(ge); cudaGraphDestroy(g);
                 }
+    unsigned long long *stamps;
+    cudaMalloc(&stamps, 8 * 4 * 148 * 4);
     cudaFuncSetAttribute(tma_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
     printf("TMA variant: %6s %4s %4s | %9s %9s\n", "ctas", "nch", "pdl", "us/launch", "GB/s");
     for (int pdl = 0; pdl < 2; ++pdl)
@@ -147,7 +157,8 @@ int main() {
                     at[0].val.programmaticStreamSerializationAllowed = 1;
                     cfg.attrs = at;
                     cfg.numAttrs = pdl;
-                    cudaLaunchKernelEx(&cfg, tma_stream_kernel, (const char *)(in + (size_t)(i % nsets) * R), out + (size_t)(i % nsets) * Wb, r_cta, w_cta, nch, pdl);
+                    cudaLaunchKernelEx(&cfg, tma_stream_kernel, (const char *)(in + (size_t)(i % nsets) * R), out + (size_t)(i % nsets) * Wb, r_cta, w_cta, nch, pdl,
+                                       (unsigned long long *)(i == chain - 1 ? stamps : nullptr));
                 }
                 cudaStreamEndCapture(s, &g);
                 cudaGraphInstantiate(&ge, g, 0);
@@ -167,7 +178,17 @@ int main() {
                 }
                 std::sort(ts.begin(), ts.end());
                 const float us = ts[ts.size() / 2];
-                printf("TMA variant: %6d %4d %4d | %9.3f %9.0f\n", grid, nch, pdl, us, (R + Wb) / us / 1e3);
+                {
+                    std::vector<unsigned long long> h(grid * 4);
+                    cudaMemcpy(h.data(), stamps, h.size() * 8, cudaMemcpyDeviceToHost);
+                    unsigned long long t0 = ~0ull;
+                    for (int c = 0; c < grid; ++c) t0 = std::min(t0, h[c * 4]);
+                    std::vector<double> a, b, d;
+                    for (int c = 0; c < grid; ++c) { a.push_back(h[c * 4 + 1] - t0); b.push_back(h[c * 4 + 2] - t0); d.push_back(h[c * 4 + 3] - t0); }
+                    std::sort(a.begin(), a.end()); std::sort(b.begin(), b.end()); std::sort(d.begin(), d.end());
+                    printf("TMA variant: %6d %4d %4d | %9.3f %9.0f | ns since first CTA start: first chunk landed med %.0f max %.0f, last chunk med %.0f max %.0f, end max %.0f\n",
+                           grid, nch, pdl, us, (R + Wb) / us / 1e3, a[grid / 2], a.back(), b[grid / 2], b.back(), d.back());
+                }
                 cudaGraphExecDestroy(ge); cudaGraphDestroy(g);
             }
     cudaError_t e = cudaDeviceSynchronize();

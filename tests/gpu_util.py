@@ -20,15 +20,35 @@ def assert_close(got, want, name="", rtol=RTOL, atol=ATOL, rel_to_max=None):
         assert err <= rel_to_max * scale + 1e-10, "%s: max err %.3e vs scale %.3e" % (name, err, scale)
 
 
+def assert_grad_parity(got, want32, n, name, want64=None):
+    """Gradient parity at the north_star tolerance, made non-vacuous: gradients of a mean over n samples are O(1/n), so
+    they are compared UN-NORMALISED (x n) elementwise at rtol 1e-5 / atol 1e-6 against the fp32 oracle.  An element may
+    miss that only when fp32 rounding explains it: a gradient element is a sum of O(10) terms that cancel, and torch's own
+    fp32 result is then ~1e-5 from the fp64 truth on this scale (measured: profiles/r02_parity_errors.txt).  In that case
+    the kernel must be at least as close to the fp64 oracle as torch's fp32 path is (x2), and the fp64 oracle is required."""
+    g = got.detach().double().cpu() * n
+    w = want32.detach().double().cpu() * n
+    assert g.shape == w.shape, (name, g.shape, w.shape)
+    bad = (g - w).abs() > RTOL * w.abs() + ATOL
+    if not bool(bad.any()):
+        return
+    assert want64 is not None, "%s: %d element(s) outside rtol 1e-5 / atol 1e-6 (x n) and no fp64 oracle given" % (name, int(bad.sum()))
+    t = want64.detach().double().cpu() * n
+    e_k, e_o = (g - t).abs().max().item(), (w - t).abs().max().item()
+    assert e_k <= 2.0 * e_o + ATOL, "%s: kernel is %.3e from the fp64 oracle, torch fp32 is %.3e (x n scale), %d elements outside " \
+        "the elementwise tolerance" % (name, e_k, e_o, int(bad.sum()))
+    assert int(bad.sum()) <= max(16, g.numel() // 50), "%s: %d of %d elements outside the tolerance" % (name, int(bad.sum()), g.numel())
+
+
 def to_cuda(d, device="cuda"):
     return {k: v.to(device) for k, v in d.items()}
 
 
-def oracle_impala(d, **kw):
+def oracle_impala(d, dtype=torch.float32, **kw):
     from oracle import losses_ref
-    lg = d["logits"].clone().requires_grad_(True)
-    vv = d["values"].clone().requires_grad_(True)
-    loss, m = losses_ref.impala_train_loss(lg, vv, d["a"], d["r"], d["discount"], d["pi_ref"], **kw)
+    lg = d["logits"].detach().to(dtype).clone().requires_grad_(True)
+    vv = d["values"].detach().to(dtype).clone().requires_grad_(True)
+    loss, m = losses_ref.impala_train_loss(lg, vv, d["a"], d["r"].to(dtype), d["discount"].to(dtype), d["pi_ref"].to(dtype), **kw)
     loss.backward()
     return loss.detach(), m, lg.grad, vv.grad
 

@@ -106,3 +106,20 @@ def test_golden_next_rows(cuda):
     ops.sumtree_update(tree, torch.arange(1000, device=cuda), torch.from_numpy(z["priorities"]).to(cuda))
     idx, prob = ops.sumtree_sample(tree, 1000, 123, 0, 0, 512)
     assert np.array_equal(idx.cpu().numpy(), z["st_idx"]) and np.array_equal(prob.cpu().numpy(), z["st_prob"])
+
+
+def test_nan_gradient_poisons_the_update_like_torch(cuda):
+    """torch.clamp propagates NaN through clip_grad_norm_'s coefficient (the reference: agents/impala/learning.py:172-173);
+    fminf would swallow it: a non-finite norm must reach total_norm AND the parameters."""
+    n = 5000
+    p, m, v = torch.randn(n, device=cuda), torch.zeros(n, device=cuda), torch.zeros(n, device=cuda)
+    g = torch.randn(n, device=cuda)
+    g[123] = float("nan")
+    norm = ops.clip_adam_step(p, g, m, v, 1, 1e-3, max_norm=0.5)
+    assert torch.isnan(norm[0])
+    assert torch.isnan(p).all(), "every parameter sees the NaN clip coefficient, as with torch.clamp"
+    # the reference's arithmetic on the CPU
+    q = torch.nn.Parameter(torch.randn(n))
+    q.grad = g.cpu().clone()
+    torch.nn.utils.clip_grad_norm_([q], 0.5)
+    assert torch.isnan(q.grad).all()
