@@ -39,7 +39,6 @@ struct K1Params {
     int B, T, A;
     int C, W, G, U;             // columns per unit, warps per group, groups per CTA, units
     int GPC, NSTAGE;            // units per chunk, chunk stages in shared memory
-    int window;                 // chunks issued at kernel start; chunk c + window is issued when chunk c lands
     int unit_words, ns4;        // C*T*A, C*T rounded up to 4 (4-byte words)
     unsigned int inv_T;         // ceil(2^32 / T)
     // no integer division on the device (a 64-bit one is ~100 instructions in every warp): the units-per-CTA split and
@@ -49,7 +48,7 @@ struct K1Params {
     float lambda_, one_minus_lambda, clip_rho, clip_pg_rho, entropy_coeff, inv_n_pg, inv_n_all;
     uint32_t flags;
     int prefetch;               // L2 prefetch hint of the CTA's inputs before the PDL dependency wait
-    int debug;                  // B200RL_K1_DEBUG (profiling): 1 = skip the arithmetic, 2 = skip the grid collector, 4 = skip the small-field loads
+    int debug;                  // B200RL_K1_DEBUG (profiling): 1 = skip the arithmetic, 2 = skip the grid collector, 4 = skip the small-field loads, 8 = reduce after the gradients
 };
 
 // x / d for small non-negative x with the host's magic m = ceil(2^32 / d) (d = 1 has no 32-bit magic)
@@ -65,20 +64,27 @@ __device__ __forceinline__ void group_sync(int id, int nthreads) {
 // AT <= 16: up to 20 warps per CTA at <= 96 registers; wider action spaces: 10 warps
 template <int AT> constexpr int k1_max_threads() { return AT <= 16 ? 640 : 320; }
 
-template <int AT, bool EXACT, bool TRACE>
+// TT, CW, CC, CG: compile-time rollout length T, warps per group W, columns per unit C and units per chunk GPC (0 = the
+// run-time values of the parameter block).  The kernel is issue-bound once its data is in flight (ncu: ~940 warp
+// instructions per warp in the all-run-time version, ~260 of them softmax arithmetic): with the reference's rollout
+// length as a constant the index arithmetic folds away and the recursion unrolls, as the exact-A instantiations do for
+// the logit loops.  Other shapes take the run-time instantiation.
+template <int AT, bool EXACT, bool TRACE, int TT, int CW, int CC, int CG>
 __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(const __grid_constant__ K1Params p) {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int T = p.T, A = EXACT ? AT : p.A, C = p.C, G = p.G, GPC = p.GPC, NSTAGE = p.NSTAGE;
-    const int gthreads = p.W * 32;
+    const int T = TT ? TT : p.T, A = EXACT ? AT : p.A, C = CC ? CC : p.C, G = p.G, GPC = CG ? CG : p.GPC, NSTAGE = p.NSTAGE;
+    const int W = CW ? CW : p.W;
+    const int unit_words = (TT && EXACT) ? CC * TT * AT : p.unit_words, ns4 = TT ? ((CC * TT + 3) & ~3) : p.ns4;
+    const int gthreads = W * 32;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-    const int grp = fast_div(warp, p.W, p.inv_W);
+    const int grp = CW ? warp / CW : fast_div(warp, p.W, p.inv_W);
     const int i = threadIdx.x - grp * gthreads;  // thread (= sample) index inside the group
     const int bar_id = grp + 1;                  // named barrier of the group (0 is __syncthreads)
-    const int chunk_words = GPC * p.unit_words;
+    const int chunk_words = GPC * unit_words;
     // shared memory: [NSTAGE][logits chunk | pi_ref chunk] | per-group scratch (td, g*c), e, nx | mbarriers | done | red | ctl
     float *smem = reinterpret_cast<float *>(smem_raw);
-    float *scratch = smem + (size_t)NSTAGE * 2 * chunk_words + (size_t)grp * 4 * p.ns4;
-    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)NSTAGE * 2 * chunk_words + (size_t)G * 4 * p.ns4);
+    float *scratch = smem + (size_t)NSTAGE * 2 * chunk_words + (size_t)grp * 4 * ns4;
+    uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)NSTAGE * 2 * chunk_words + (size_t)G * 4 * ns4);
     int *done = reinterpret_cast<int *>(bars + NSTAGE);  // [NSTAGE] groups that finished the stage's chunk
     float *red = reinterpret_cast<float *>(done + NSTAGE);  // [5][nwarps]
     int *ctl = reinterpret_cast<int *>(red + 5 * nwarps);   // [0] warps arrived at the reduction
@@ -94,6 +100,7 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
         ctl[0] = 0;
         fence_mbar_init();
     }
+    const unsigned long long t_entry = (TRACE && threadIdx.x == 0) ? globaltimer_ns() : 0ull;
     pdl_launch_dependents();
     const bool late_wait = p.flags & B200RL_INPUTS_STABLE;
     unsigned int gen = 0;
@@ -123,13 +130,18 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
         pdl_wait();  // inputs may come from the preceding kernel
         gen = grid_generation(p.workspace);  // consumed by the last warp at the very end: latency hidden
     }
+    // CTA-level stamps of the trace instantiation: rows 2048 + 1024 * (generation & 1) + blockIdx (two consecutive launches
+    // stay apart): 0 last warp at the reduction, 1 published, 2 kernel entry, 3 past the dependency wait, 4 last instruction
+    unsigned long long *ctr = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(p.workspace) + kTraceOffset) +
+                              (size_t)(2048 + 1024 * (gen & 1u) + (blockIdx.x & 1023u)) * 16;
+    if (TRACE && threadIdx.x == 0) { ctr[2] = t_entry; ctr[3] = globaltimer_ns(); }
     __syncthreads();
     K1_STAMP(0);
 
     // this CTA's contiguous range of units, its chunks
     const int ustart = (int)blockIdx.x * p.units_lo + min((int)blockIdx.x, p.units_rem);
     const int n_units = p.units_lo + ((int)blockIdx.x < p.units_rem ? 1 : 0);
-    const int n_chunks = fast_div(n_units + GPC - 1, GPC, p.inv_GPC);
+    const int n_chunks = CG ? (n_units + CG - 1) / CG : fast_div(n_units + GPC - 1, GPC, p.inv_GPC);
     auto stage_of = [&](int c, int &round) { round = fast_div(c, NSTAGE, p.inv_NSTAGE); return c - round * NSTAGE; };
     auto chunk_units = [&](int c) { return min(GPC, n_units - c * GPC); };
     auto chunk_col0 = [&](int c) { return (ustart + c * GPC) * C; };
@@ -145,12 +157,12 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
         bulk_g2s(sx + chunk_words, p.pi_ref + e0, bytes, bars + st);
     };
     if (lane == 0)  // copies complete in issue order: chunk 0 first.  Spread over warps: an issue costs ~55 cycles
-        for (int c = warp; c < min(min(NSTAGE, n_chunks), p.window); c += nwarps) issue_chunk(c);
+        for (int c = warp; c < min(NSTAGE, n_chunks); c += nwarps) issue_chunk(c);
 
     const bool detach_adv = p.flags & B200RL_DETACH_ADV, detach_rho = p.flags & B200RL_DETACH_RHO;
-    const int col = (int)__umulhi((unsigned)i, p.inv_T), t = i - col * T;
+    const int col = TT ? i / TT : (int)__umulhi((unsigned)i, p.inv_T), t = i - col * T;
     float2 *s_tg = reinterpret_cast<float2 *>(scratch);
-    float *s_e = scratch + 2 * p.ns4, *s_nx = s_e + p.ns4;
+    float *s_e = scratch + 2 * ns4, *s_nx = s_e + ns4;
     float sums[5] = {0.f, 0.f, 0.f, 0.f, 0.f};  // pg, value, entropy, kl, ratio
 
     // the 20 bytes per sample outside the logits: plain loads, fetched one unit ahead
@@ -190,9 +202,7 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
         }
         arrived = __shfl_sync(0xffffffffu, arrived, 0);
         if (arrived != nwarps - 1) return;
-        unsigned long long *ctr = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(p.workspace) + kTraceOffset) +
-                                  (size_t)(2048 + blockIdx.x) * 16;  // CTA-level stamps (trace instantiation only)
-        if (TRACE && lane == 0 && blockIdx.x < 2048) ctr[0] = globaltimer_ns();
+        if (TRACE && lane == 0) ctr[0] = globaltimer_ns();
         __threadfence_block();
         // lane w takes warp w's sums; xor-shuffle tree in a fixed order (nwarps <= 32)
         float cta_tot[5];
@@ -214,21 +224,20 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
             for (int k = 0; k < 5; ++k)
                 if (lane == k) red[k] = cta_tot[k];
         } else if (!(p.debug & 2)) warp_publish<5>(cta_tot, p.workspace, gen);
-        if (TRACE && lane == 0 && blockIdx.x < 2048) ctr[1] = globaltimer_ns();
+        if (TRACE && lane == 0) ctr[1] = globaltimer_ns();
     };
 
     bool first = true;
     for (int j = grp; j < n_units; j += G) {
-        const int c = fast_div(j, GPC, p.inv_GPC);
+        const int c = CG ? j / CG : fast_div(j, GPC, p.inv_GPC);
         int round;
         const int st_i = stage_of(c, round);
-        float *sx = smem + (size_t)st_i * 2 * chunk_words + (size_t)(j - c * GPC) * p.unit_words;
+        float *sx = smem + (size_t)st_i * 2 * chunk_words + (size_t)(j - c * GPC) * unit_words;
         float *sy = sx + chunk_words;
         const int b0 = (ustart + j) * C, ucols = min(C, p.B - b0), nsu = ucols * T;
         const size_t n0 = (size_t)b0 * T;
 
         mbar_wait(bars + st_i, (uint32_t)round & 1u);  // the unit's chunk has landed
-        if (i == 0 && j == c * GPC && c + p.window < min(NSTAGE, n_chunks)) issue_chunk(c + p.window);  // first round only
         if (first) K1_STAMP(1);
 
         // ---- per-sample softmax statistics, TD error, trace coefficient ------------------------
@@ -303,7 +312,7 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
         }
         // The scalars are complete for this thread once its LAST unit is past the recursion: the CTA's reduction and
         // the publication to the collector start here and travel while the gradients below are still being written.
-        if (!late_wait && j + G >= n_units) { cta_reduce_publish(); reduced = true; }
+        if (!late_wait && !(p.debug & 8) && j + G >= n_units) { cta_reduce_publish(); reduced = true; }
 
         // ---- gradients ---------------------------------------------------------------------------
         if (valid) {
@@ -356,6 +365,7 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
     K1_STAMP(5);
     if (i == 0) bulk_wait_read0();  // shared memory must outlive the bulk stores' reads
     K1_STAMP(6);
+    if (TRACE && threadIdx.x == 0) ctr[4] = globaltimer_ns();
 #undef K1_STAMP
 }
 
@@ -373,10 +383,10 @@ static int sm_count() {
     return cache[dev];
 }
 
-template <int AT, bool EXACT, bool TRACE>
+template <int AT, bool EXACT, bool TRACE, int TT, int CW, int CC, int CG>
 static int32_t launch_k1_t(const K1Params &p, int grid, int threads, size_t smem, cudaStream_t stream) {
     static size_t smem_cache[kMaxDevices];
-    if (int32_t rc = ensure_dynamic_smem(impala_loss_kernel<AT, EXACT, TRACE>, smem, smem_cache, "impala_loss")) return rc;
+    if (int32_t rc = ensure_dynamic_smem(impala_loss_kernel<AT, EXACT, TRACE, TT, CW, CC, CG>, smem, smem_cache, "impala_loss")) return rc;
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)grid);
     cfg.blockDim = dim3((unsigned)threads);
@@ -387,7 +397,7 @@ static int32_t launch_k1_t(const K1Params &p, int grid, int threads, size_t smem
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = env_int("B200RL_PDL", 1) ? 1 : 0;
-    cudaError_t e = cudaLaunchKernelEx(&cfg, impala_loss_kernel<AT, EXACT, TRACE>, p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, impala_loss_kernel<AT, EXACT, TRACE, TT, CW, CC, CG>, p);
     if (e != cudaSuccess) {
         set_error("impala_loss_kernel launch: %s", cudaGetErrorString(e));
         (void)cudaGetLastError();
@@ -434,15 +444,16 @@ static int32_t launch_k1(const ImpalaArgs &a, cudaStream_t stream) {
     p.ns4 = (C * T + 3) & ~3;
     p.unit_words = C * T * A;
     // one CTA per SM (small problems: one unit per CTA first); groups per CTA: fill the CTA, at most 15 named barriers
-    const int grid = min(sm_count(), p.U);
+    const int cps = max(1, min(4, env_int("B200RL_K1_CTAS_PER_SM", 1)));   // CTAs per SM the grid is sized for
+    const int grid = min(sm_count() * cps, p.U);
     if (grid > kMaxPartialCtas) return 1;
     const int units_per_cta = (p.U + grid - 1) / grid;
-    int G = max_threads / (32 * W);
+    int G = max_threads / cps / (32 * W);
     if (W > 1 && G > 15) G = 15;
     G = max(1, min(G, env_int("B200RL_K1_G", G)));
     G = min(G, units_per_cta);
     // chunks: GPC consecutive units per pair of bulk copies; every chunk of the CTA resident when shared memory allows
-    const size_t unit_bytes = (size_t)p.unit_words * 4, budget = 200 * 1024;
+    const size_t unit_bytes = (size_t)p.unit_words * 4, budget = (size_t)(200 * 1024) / cps;
     int GPC = max(1, min(env_int("B200RL_K1_GPC", 2), units_per_cta));
     while (GPC > 1 && 2 * unit_bytes * GPC * 2 > budget) --GPC;
     if (2 * unit_bytes * GPC > budget) return 1;
@@ -458,13 +469,19 @@ static int32_t launch_k1(const ImpalaArgs &a, cudaStream_t stream) {
     p.inv_W = magic(W); p.inv_GPC = magic(GPC); p.inv_NSTAGE = magic(NSTAGE);
     p.units_lo = p.U / grid; p.units_rem = p.U % grid;
     p.debug = env_int("B200RL_K1_DEBUG", 0);
-    p.window = max(1, env_int("B200RL_K1_WINDOW", 1 << 20));
     p.prefetch = env_int("B200RL_K1_PREFETCH", 1);
     const int threads = G * W * 32;
     const size_t smem = (size_t)NSTAGE * 2 * GPC * unit_bytes + (size_t)G * 4 * p.ns4 * 4 + (size_t)NSTAGE * 12 +
                         5 * (size_t)(threads / 32) * 4 + 16 + 128;
-    if (a.flags & B200RL_TRACE) return launch_k1_t<AT, EXACT, true>(p, grid, threads, smem, stream);
-    return launch_k1_t<AT, EXACT, false>(p, grid, threads, smem, stream);
+    // the reference's shape class (T = 20 rollouts, procgen's 15 actions): compile-time T / W / C / GPC
+    if constexpr (AT == 15 && EXACT) {
+        if (T == 20 && W == 2 && C == 3 && GPC == 2 && env_int("B200RL_K1_GENERIC", 0) == 0) {
+            if (a.flags & B200RL_TRACE) return launch_k1_t<AT, EXACT, true, 20, 2, 3, 2>(p, grid, threads, smem, stream);
+            return launch_k1_t<AT, EXACT, false, 20, 2, 3, 2>(p, grid, threads, smem, stream);
+        }
+    }
+    if (a.flags & B200RL_TRACE) return launch_k1_t<AT, EXACT, true, 0, 0, 0, 0>(p, grid, threads, smem, stream);
+    return launch_k1_t<AT, EXACT, false, 0, 0, 0, 0>(p, grid, threads, smem, stream);
 }
 
 int32_t launch_impala_persistent(const ImpalaArgs &a, cudaStream_t stream) {
@@ -515,7 +532,15 @@ extern "C" int32_t b200rl_vtrace_impala_loss_fwdbwd(
     a.inv_n_all = (float)(1.0 / ((double)n_global_b * (double)T));
     a.flags = flags;
     cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-    if (!a.time_major && env_int("B200RL_K1_TILE", 0) == 0) {
+    // Two implementations, chosen by what the caller told us about the launch (B200RL_K1_TILE: 0 = this rule,
+    // 1 = always the tile kernel, 2 = always the persistent kernel):
+    //  * a dependent launch (the default: one learner step = one K1 between the head GEMM and its backward) has the GPU
+    //    to itself, so latency is everything: the persistent, warp-group pipelined kernel (6.0-6.8 us against 8.0 us);
+    //  * B200RL_INPUTS_STABLE says launches on independent rollout batches are in flight together: throughput is
+    //    everything and many small CTAs of different launches interleave best: the tile kernel (2.7 us/step on 3+ streams).
+    const int impl = env_int("B200RL_K1_TILE", 0);
+    const bool want_persistent = impl == 2 || (impl == 0 && !(flags & B200RL_INPUTS_STABLE));
+    if (!a.time_major && want_persistent) {
         const int32_t rc = launch_impala_persistent(a, s);
         if (rc != 1) return rc;
     }

@@ -13,7 +13,7 @@ from impala_b200 import ops, synth  # noqa: E402
 B, T, A = int(os.environ.get("B", 4096)), int(os.environ.get("T", 20)), int(os.environ.get("A", 15))
 N_LAUNCH, REPLAYS = 100, 30
 dev = torch.device("cuda", 0)
-nsets = max(4, int(2.5 * 126 * 2**20 // (204 * B * T)) + 1)
+nsets = int(os.environ.get("NSETS", max(4, int(2.5 * 126 * 2**20 // (204 * B * T)) + 1)))   # NSETS=1: L2-warm inputs (diagnostic only)
 sets = []
 for i in range(nsets):
     d = synth.impala_rollout(B, T, A, seed=100 + i)

@@ -38,7 +38,7 @@ __device__ __forceinline__ unsigned smem_u32(const void *p) { return (unsigned)_
 // at once by `nissue` different warps) and bulk-stores the leading Wb/R part of every chunk as soon as it has landed.
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 
-__global__ void __launch_bounds__(256) tma_stream_kernel(const char *__restrict__ in, char *__restrict__ out, int r_cta, int w_cta, int nch, int pdl,
+__global__ void __launch_bounds__(640) tma_stream_kernel(const char *__restrict__ in, char *__restrict__ out, int r_cta, int w_cta, int nch, int pdl,
                                                           unsigned long long *stamps) {
     extern __shared__ __align__(128) unsigned char sm[];
     __shared__ unsigned long long bars[64];
@@ -55,15 +55,15 @@ __global__ void __launch_bounds__(256) tma_stream_kernel(const char *__restrict_
     const int rc = r_cta / nch, wc = w_cta / nch;   // multiples of 16 by construction
     const char *src = in + (size_t)blockIdx.x * r_cta;
     char *dst = out + (size_t)blockIdx.x * w_cta;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
     if (lane == 0)
-        for (int k = warp; k < nch; k += 8) {
+        for (int k = warp; k < nch; k += nw) {
             asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&bars[k])), "r"(rc) : "memory");
             asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
                              "r"(smem_u32(sm + (size_t)k * rc)), "l"(src + (size_t)k * rc), "r"(rc), "r"(smem_u32(&bars[k])) : "memory");
         }
     if (lane == 0)
-        for (int k = warp; k < nch; k += 8) {
+        for (int k = warp; k < nch; k += nw) {
             unsigned done = 0;
             while (!done)
                 asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n\tselp.u32 %0, 1, 0, p;\n\t}"
@@ -191,6 +191,49 @@ int main() {
                 }
                 cudaGraphExecDestroy(ge); cudaGraphDestroy(g);
             }
+    printf("CTA footprint (148 CTAs, nch 8, pdl 1): %6s %8s | %9s\n", "thr", "smemKB", "us/launch");
+    for (int thr : {256, 640})
+        for (int extra : {0, 100 * 1024}) {
+            const int grid = 148, nch = 8, pdl = 1;
+            const int r_cta = (int)(R / grid) / (16 * nch) * (16 * nch), w_cta = (int)(Wb / grid) / (16 * nch) * (16 * nch);
+            cudaFuncSetAttribute(tma_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+            cudaGraph_t g;
+            cudaGraphExec_t ge;
+            cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal);
+            for (int i = 0; i < chain; ++i) {
+                cudaLaunchConfig_t cfg = {};
+                cfg.gridDim = dim3(grid);
+                cfg.blockDim = dim3(thr);
+                cfg.dynamicSmemBytes = r_cta + 128 + extra;
+                cfg.stream = s;
+                cudaLaunchAttribute at[1];
+                at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+                at[0].val.programmaticStreamSerializationAllowed = 1;
+                cfg.attrs = at;
+                cfg.numAttrs = pdl;
+                cudaLaunchKernelEx(&cfg, tma_stream_kernel, (const char *)(in + (size_t)(i % nsets) * R), out + (size_t)(i % nsets) * Wb, r_cta, w_cta, nch, pdl,
+                                   (unsigned long long *)nullptr);
+            }
+            cudaStreamEndCapture(s, &g);
+            cudaGraphInstantiate(&ge, g, 0);
+            cudaGraphLaunch(ge, s);
+            cudaStreamSynchronize(s);
+            std::vector<float> ts;
+            for (int r = 0; r < reps; ++r) {
+                cudaEvent_t e0, e1;
+                cudaEventCreate(&e0); cudaEventCreate(&e1);
+                cudaEventRecord(e0, s);
+                cudaGraphLaunch(ge, s);
+                cudaEventRecord(e1, s);
+                cudaEventSynchronize(e1);
+                float ms; cudaEventElapsedTime(&ms, e0, e1);
+                ts.push_back(ms * 1e3f / chain);
+                cudaEventDestroy(e0); cudaEventDestroy(e1);
+            }
+            std::sort(ts.begin(), ts.end());
+            printf("CTA footprint: %6d %8d | %9.3f\n", thr, (r_cta + extra) / 1024, ts[ts.size() / 2]);
+            cudaGraphExecDestroy(ge); cudaGraphDestroy(g);
+        }
     cudaError_t e = cudaDeviceSynchronize();
     printf("status: %s\n", cudaGetErrorString(e));
     return e != cudaSuccess;
