@@ -6,22 +6,12 @@
 // logits in shared memory with one TMA bulk copy per tensor, one thread per sample
 // computes everything in registers, d loss/d logits is written over the staged tile
 // and leaves by one bulk store.  200 B/sample at A=15.
+#include "ppo_loss.cuh"
 #include "softmax.cuh"
 
 namespace b200rl {
 
 constexpr int kPpoTile = 256;
-
-struct PpoParams {
-    const float *logits, *pi_ref, *v_target, *v;
-    const long long *actions;
-    float *dlogits, *dv, *scalars;
-    void *workspace;
-    long long N;
-    int A;
-    float clip_coeff, entropy_cost, inv_n;
-    uint32_t flags;
-};
 
 template <int AT, bool EXACT>
 __global__ void __launch_bounds__(kPpoTile) ppo_loss_kernel(const PpoParams p) {
@@ -119,8 +109,6 @@ __global__ void __launch_bounds__(kPpoTile) ppo_loss_kernel(const PpoParams p) {
     if (bulk_ok && threadIdx.x == 0) bulk_wait_read0();
 }
 
-int env_int(const char *name, int dflt);
-
 template <int AT, bool EXACT>
 static int32_t launch_ppo(const PpoParams &p, size_t smem, cudaStream_t stream) {
     static size_t smem_cache[kMaxDevices];
@@ -169,6 +157,14 @@ extern "C" int32_t b200rl_ppo_loss_fwdbwd(const float *logits, const float *pi_r
     p.flags = flags;
     const size_t smem = (size_t)kPpoTile * A * 8 + 6 * kPpoTile * 4 + 16;
     cudaStream_t s = (cudaStream_t)stream;
+    // Two schedules (B200RL_K3_STREAM: 0 = this rule, 1 = always the tile kernel, 2 = always try the streaming kernel):
+    // a launch that has the GPU to itself and is large enough to give every CTA slot a few chunks streams through the
+    // persistent ring kernel; small minibatches and launches that overlap others (B200RL_INPUTS_STABLE) keep the tiles.
+    const int impl = env_int("B200RL_K3_STREAM", 0);
+    if (impl == 2 || (impl == 0 && !(flags & B200RL_INPUTS_STABLE))) {
+        const int32_t rc = launch_ppo_stream(p, s);
+        if (rc != 1) return rc;
+    }
     switch (A) {
         case 4: return launch_ppo<4, true>(p, smem, s);
         case 6: return launch_ppo<6, true>(p, smem, s);

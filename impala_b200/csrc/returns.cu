@@ -157,127 +157,11 @@ __global__ void __launch_bounds__(kSmemScanWarps * 32) scan_smem_kernel(const Sc
     }
 }
 
-// Time-major kernel, cluster version (opt-in, B200RL_K2_CLUSTER=1; see launch_scan for why): a thread-block CLUSTER owns 128
-// adjacent columns x all T steps; CTA q of the cluster owns the q-th slice of the time axis (<= kClusterRows
-// steps), staged in its shared memory with 16-byte cp.async (512 contiguous bytes per row and tensor).  A thread
-// owns 4 adjacent columns (16-byte shared-memory reads, 16-byte stores), a warp a sub-slice of the CTA's
-// steps.  Pass 1 composes each warp's affine map, warp 0 folds them into the CTA's map; after one cluster
-// barrier every warp folds the maps of the LATER CTAs (read through distributed shared memory) and of
-// the later warps of its own CTA into its carry-in, then pass 2 re-walks its steps in the reference's
-// operation order.  Every byte crosses HBM once; the time axis is spread over up to 8 SMs per column strip.
-constexpr int kClusterRows = 64, kClusterCols = 128, kClusterWarps = 8, kClusterMax = 8;
+// (A thread-block-cluster version -- the time axis split over the CTAs of a cluster, chunk maps exchanged through
+// distributed shared memory -- was built and measured in round 1: slower than the one-CTA kernels here (T=256, B=8192:
+// 6.8 vs 5.0 us; T=512, B=4096: 9.3 vs 8.7 us; co-scheduling the cluster and its two cluster barriers cost more than the
+// wider rows save).  It was removed from the library in round 2; DESIGN.md keeps the numbers.)
 
-struct F4 {
-    float v[4];
-};
-__device__ __forceinline__ F4 ld_f4(const float *p) {
-    const float4 x = *reinterpret_cast<const float4 *>(p);
-    return F4{{x.x, x.y, x.z, x.w}};
-}
-
-template <int MODE>
-__global__ void __launch_bounds__(kClusterWarps * 32) scan_cluster_kernel(const ScanParams p, int rows_per_cta) {
-    extern __shared__ __align__(16) float smem_scan[];
-    const int T = p.T;
-    const int q = (int)cluster_ctarank(), Q = (int)gridDim.y;
-    const int r0 = q * rows_per_cta, r1 = min(T, r0 + rows_per_cta);
-    const int nrows = max(r1 - r0, 0);
-    const int nv = nrows + (MODE == MODE_GAE ? 1 : 0);       // GAE also needs V[r1]
-    float *sr = smem_scan;                                   // [rows_per_cta][128]
-    float *sd = sr + rows_per_cta * kClusterCols;            // [rows_per_cta][128]
-    float *sv = sd + rows_per_cta * kClusterCols;            // [rows_per_cta + 1][128]
-    float *sA = sv + (rows_per_cta + 1) * kClusterCols;      // [kClusterWarps][128] warp maps
-    float *sB = sA + kClusterWarps * kClusterCols;
-    float *cA = sB + kClusterWarps * kClusterCols;           // [128] this CTA's map
-    float *cB = cA + kClusterCols;
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const int b0 = blockIdx.x * kClusterCols;
-    if (nrows > 0) {
-        for (int ch = threadIdx.x; ch < nv * 32; ch += kClusterWarps * 32) {
-            const int row = ch >> 5, c4 = (ch & 31) * 4;
-            const int remaining = p.B - (b0 + c4);
-            const int bytes = remaining >= 4 ? 16 : (remaining > 0 ? remaining * 4 : 0);
-            const long long col = remaining > 0 ? b0 + c4 : 0;  // keep the address valid when nothing is read
-            if (row < nrows) {
-                cp_async16(sr + row * kClusterCols + c4, p.r + (long long)(r0 + row) * p.st + col, bytes);
-                cp_async16(sd + row * kClusterCols + c4, p.disc + (long long)(r0 + row) * p.st + col, bytes);
-            }
-            cp_async16(sv + row * kClusterCols + c4, p.v + (long long)(r0 + row) * p.vst + col, bytes);
-        }
-    }
-    const int b = b0 + lane * 4, o = lane * 4;
-    float y[4] = {0.f, 0.f, 0.f, 0.f};
-    if (MODE == MODE_LAMBDA_RETURNS) {  // bootstrap v_t[T-1]
-#pragma unroll
-        for (int k = 0; k < 4; ++k) y[k] = (b + k) < p.B ? __ldg(p.v + (long long)(T - 1) * p.vst + b + k) : 0.f;
-    }
-    cp_async_wait_all();
-    __syncthreads();
-    // this warp's steps [t0, t1) in local rows
-    const int Lw = (nrows + kClusterWarps - 1) / kClusterWarps;
-    const int t0 = min(w * Lw, nrows), t1 = min(t0 + Lw, nrows);
-    // pass 1: this warp's map y_in -> B + A * y_in
-    float A[4] = {1.f, 1.f, 1.f, 1.f}, Bm[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int t = t1 - 1; t >= t0; --t) {
-        const F4 r = ld_f4(sr + t * kClusterCols + o), d = ld_f4(sd + t * kClusterCols + o), v0 = ld_f4(sv + t * kClusterCols + o);
-        F4 v1 = v0;
-        if (MODE == MODE_GAE) v1 = ld_f4(sv + (t + 1) * kClusterCols + o);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const float a = p.lambda_ * d.v[k];
-            const float bb = scan_step<MODE>(r.v[k], d.v[k], v0.v[k], v1.v[k], p.lambda_, p.one_minus_lambda, 0.f);
-            Bm[k] = bb + a * Bm[k];
-            A[k] = a * A[k];
-        }
-    }
-    *reinterpret_cast<float4 *>(sA + w * kClusterCols + o) = make_float4(A[0], A[1], A[2], A[3]);
-    *reinterpret_cast<float4 *>(sB + w * kClusterCols + o) = make_float4(Bm[0], Bm[1], Bm[2], Bm[3]);
-    __syncthreads();
-    if (w == 0) {  // the CTA's map: fold the warp maps from the last steps to the first
-        float a4[4] = {1.f, 1.f, 1.f, 1.f}, b4[4] = {0.f, 0.f, 0.f, 0.f};
-        for (int k = kClusterWarps - 1; k >= 0; --k) {
-            const F4 ak = ld_f4(sA + k * kClusterCols + o), bk = ld_f4(sB + k * kClusterCols + o);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                b4[j] = bk.v[j] + ak.v[j] * b4[j];
-                a4[j] = ak.v[j] * a4[j];
-            }
-        }
-        *reinterpret_cast<float4 *>(cA + o) = make_float4(a4[0], a4[1], a4[2], a4[3]);
-        *reinterpret_cast<float4 *>(cB + o) = make_float4(b4[0], b4[1], b4[2], b4[3]);
-    }
-    cluster_sync_all();  // every CTA's map is published (also orders warp 0's writes for this CTA)
-    // carry-in: later CTAs (distributed shared memory), then the later warps of this CTA
-    for (int k = Q - 1; k > q; --k) {
-        const float4 ak = ld_dsmem_f4(cA + o, (uint32_t)k), bk = ld_dsmem_f4(cB + o, (uint32_t)k);
-        y[0] = bk.x + ak.x * y[0]; y[1] = bk.y + ak.y * y[1]; y[2] = bk.z + ak.z * y[2]; y[3] = bk.w + ak.w * y[3];
-    }
-    for (int k = kClusterWarps - 1; k > w; --k) {
-        const F4 ak = ld_f4(sA + k * kClusterCols + o), bk = ld_f4(sB + k * kClusterCols + o);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) y[j] = bk.v[j] + ak.v[j] * y[j];
-    }
-    // pass 2: this warp's steps in the reference's operation order
-    const bool full = b + 3 < p.B;
-    for (int t = t1 - 1; t >= t0; --t) {
-        const F4 r = ld_f4(sr + t * kClusterCols + o), d = ld_f4(sd + t * kClusterCols + o), v0 = ld_f4(sv + t * kClusterCols + o);
-        F4 v1 = v0;
-        if (MODE == MODE_GAE) v1 = ld_f4(sv + (t + 1) * kClusterCols + o);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) y[k] = scan_step<MODE>(r.v[k], d.v[k], v0.v[k], v1.v[k], p.lambda_, p.one_minus_lambda, y[k]);
-        float *dst = p.out + (long long)(r0 + t) * p.st + b;
-        if (full) {
-            __stcs(reinterpret_cast<float4 *>(dst), make_float4(y[0], y[1], y[2], y[3]));
-        } else {
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-                if (b + k < p.B) __stcs(dst + k, y[k]);
-        }
-    }
-    cluster_sync_all();  // no CTA leaves while a peer may still read its map
-}
-
-// Generic layout (batch-major): one thread per column, sequential, reference order.
 template <int MODE>
 __global__ void __launch_bounds__(128) scan_generic_kernel(const ScanParams p) {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -299,37 +183,6 @@ static int32_t launch_scan(const ScanParams &p, cudaStream_t stream) {
     const bool time_major = (p.sb == 1 && p.vsb == 1);
     const bool al16 = ((reinterpret_cast<uintptr_t>(p.r) | reinterpret_cast<uintptr_t>(p.disc) |
                         reinterpret_cast<uintptr_t>(p.v)) % 16 == 0) && p.st % 4 == 0 && p.vst % 4 == 0;
-    const bool out16 = reinterpret_cast<uintptr_t>(p.out) % 16 == 0;
-    // B200RL_K2_CLUSTER=1 selects the cluster / distributed-shared-memory version.  It is OFF by default: measured on
-    // B200 it is slower than the one-CTA kernels below (T=256, B=8192: 6.8 vs 5.0 us; T=512, B=4096: 9.3 vs 8.7 us) --
-    // co-scheduling the cluster and its two cluster barriers cost more than the wider rows save.
-    if (time_major && al16 && out16 && p.T <= kClusterRows * kClusterMax && env_int("B200RL_K2_CLUSTER", 0) == 1) {
-        int Q = 1;
-        while (Q < kClusterMax && (p.T + Q - 1) / Q > kClusterRows) Q *= 2;
-        const int rows = (p.T + Q - 1) / Q;
-        const size_t smem = ((size_t)(3 * rows + 1) + 2 * kClusterWarps + 2) * kClusterCols * 4;
-        static size_t cc[kMaxDevices];
-        if (int32_t rc = ensure_dynamic_smem(scan_cluster_kernel<MODE>, smem, cc, "scan")) return rc;
-        cudaLaunchConfig_t cfg = {};
-        cfg.gridDim = dim3((unsigned)((p.B + kClusterCols - 1) / kClusterCols), (unsigned)Q);
-        cfg.blockDim = dim3(kClusterWarps * 32);
-        cfg.dynamicSmemBytes = smem;
-        cfg.stream = stream;
-        cudaLaunchAttribute attr[1];
-        attr[0].id = cudaLaunchAttributeClusterDimension;
-        attr[0].val.clusterDim.x = 1;
-        attr[0].val.clusterDim.y = (unsigned)Q;
-        attr[0].val.clusterDim.z = 1;
-        cfg.attrs = attr;
-        cfg.numAttrs = 1;
-        cudaError_t e = cudaLaunchKernelEx(&cfg, scan_cluster_kernel<MODE>, p, rows);
-        if (e != cudaSuccess) {
-            set_error("scan_cluster_kernel launch: %s", cudaGetErrorString(e));
-            (void)cudaGetLastError();
-            return (int32_t)e;
-        }
-        return check_launch("scan_cluster_kernel");
-    }
     if (time_major && al16 && p.T <= kSmemScanMaxT && p.T >= 32 && env_int("B200RL_K2_SMEM", 1)) {
         const int TV = p.T + (MODE == MODE_GAE ? 1 : 0);
         const int nw = env_int("B200RL_K2_WARPS", 8);

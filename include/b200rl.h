@@ -35,17 +35,21 @@ extern "C" {
 #define B200RL_DETACH_RHO 2u  /* treat rho as a constant inside V-trace; reference: not detached, learning.py:148 */
 #define B200RL_ORDER_RLAX 4u  /* b200rl_vtrace output order (errors, pg_adv, q) instead of call-site (pg_adv, errors, q) */
 /* Fused losses are launched with programmatic dependent launch (PDL).  By default the kernel waits
- * for the preceding kernel of the stream before it reads anything.  With B200RL_INPUTS_STABLE the
- * caller promises that NO buffer of this call except `workspace` and `scalars` is written or read by
- * the immediately preceding kernel of the stream (e.g. a pipeline over independent rollout batches):
- * loads, arithmetic and gradient stores then overlap the previous launch's tail and only the
- * scalar reduction waits. */
+ * for the preceding kernel of the stream before it reads anything (it may ask L2 to PREFETCH its inputs
+ * earlier -- a hint, never a read).  With B200RL_INPUTS_STABLE the caller promises that NO buffer of
+ * this call except `workspace` and `scalars` is written or read by ANY earlier launch of the stream
+ * that may still be running (every fused loss lets its successor start early, so launch N+2 can
+ * overlap launch N; e.g. a pipeline over independent rollout batches): loads, arithmetic and gradient
+ * stores then overlap the earlier launches' tails and only the scalar reduction waits.  K1 also takes
+ * the flag as "throughput matters, not latency" and runs its many-small-CTAs implementation. */
 #define B200RL_INPUTS_STABLE 8u
-/* Profiling aid (K1): thread 0 of every CTA < 4096 stamps %globaltimer (ns) at 7 phase boundaries into
- * workspace + b200rl_trace_offset_bytes(), layout uint64 [cta][16] (slots 0-7 %globaltimer, 8-15 clock64 of the same points;
- * slot 7/15 = %smid):
- * 0 start, 1 tile landed in shared memory, 2 softmax statistics done, 3 V-trace recursion done,
- * 4 gradients written to shared memory, 5 scalar reduction done, 6 bulk store drained from shared memory. */
+/* Profiling aid (K1): stamps of %globaltimer (ns) at 7 phase boundaries into workspace + b200rl_trace_offset_bytes(),
+ * layout uint64 [row][16] (slots 0-6 %globaltimer, 7 %smid, 8-14 clock64 of the same points).  Tile kernel: one row per
+ * CTA < 4096 (thread 0).  Persistent kernel: one row per warp group (row = CTA * groups + group < 2048, the group's
+ * first thread, first unit): 0 past the dependency wait, 1 chunk landed in shared memory, 2 softmax statistics done,
+ * 3 V-trace recursion done, 4 gradients written and the chunk's bulk store issued, 5 reduction done, 6 bulk stores drained;
+ * plus CTA rows 2048 + 1024 * (launch generation & 1) + CTA: 0 last warp at the reduction, 1 published, 2 kernel entry,
+ * 3 past the dependency wait, 4 thread 0's last instruction (scripts/k1_trace.py prints the timeline). */
 #define B200RL_TRACE 0x80000000u
 
 /* slots of the float[8] `scalars` output of the fused losses */
@@ -60,8 +64,10 @@ extern "C" {
 int32_t b200rl_version(void);
 const char *b200rl_last_error(void);
 
-/* Bytes of zero-initialised device workspace the fused losses need (zero it ONCE;
- * every launch leaves it zeroed again). */
+/* Bytes of zero-initialised device workspace the fused losses need.  Zero it ONCE and never touch it again: it holds
+ * the launch generation the scalar reduction tags its partial sums with.  One workspace per stream.  A reduction that
+ * times out (~1 s without progress: the GPU is wedged) reports NaN scalars and poisons the workspace -- every later launch
+ * on it reports NaN until it is zeroed again. */
 int64_t b200rl_loss_workspace_bytes(void);
 int64_t b200rl_trace_offset_bytes(void);
 

@@ -159,23 +159,6 @@ def test_scans_parity(B, T, lam, time_major):
         assert torch.equal(got_lr.cpu(), want_lr) and torch.equal(got_gae.cpu(), want_gae)
 
 
-@pytest.mark.parametrize("B,T", [(300, 256), (128, 65), (64, 20), (132, 512), (4, 1), (260, 129)])
-def test_scans_cluster_variant(B, T, monkeypatch):
-    """The opt-in thread-block-cluster kernel (B200RL_K2_CLUSTER=1: time axis split over the CTAs of a cluster, chunk maps
-    exchanged through distributed shared memory) against the oracle; time-major, B a multiple of 4 (16-byte rows)."""
-    monkeypatch.setenv("B200RL_K2_CLUSTER", "1")
-    x = synth.returns_rollout(B, T + 1, seed=B + T)
-    r, d, v = x["r"][:, :T], x["discount"][:, :T], x["v"]
-    rg, dg, vg = (t.t().contiguous().cuda() for t in (r, d, v))
-    for lam in (.95, 1.0):
-        got_lr = vtrace.lambda_returns(rg, dg, vg[1:], lam, time_major=True).t()
-        got_gae = vtrace.truncated_generalized_advantage_estimation(rg, dg, lam, vg, time_major=True).t()
-        for name, got, want in (("lambda_returns", got_lr, oracle_returns(r, d, v[:, 1:], lam)),
-                                ("gae", got_gae, oracle_gae(r, d, v, lam))):
-            M = max(1.0, want.abs().max().item())
-            assert_close(got, want, name, rtol=1e-5, atol=1e-6 * M, rel_to_max=2e-6)
-
-
 def test_scans_golden_identity_and_ppo_targets():
     z = np.load(os.path.join(GOLDEN, "returns_small.npz"))
     r, d, v = (torch.from_numpy(z[k]).cuda() for k in ("r", "discount", "v"))
