@@ -28,6 +28,7 @@ SIGNATURES = {
     "b200rl_loss_workspace_bytes": (_i64, []),
     "b200rl_trace_offset_bytes": (_i64, []),
     "b200rl_vtrace_impala_loss_fwdbwd": (_i32, [_vp] * 6 + [_i64] * 6 + [_d] + [_f] * 3 + [_u32] + [_vp] * 5),
+    "b200rl_vtrace_impala_loss_fwdbwd_noalloc": (_i32, [_vp] * 6 + [_i64] * 6 + [_d] + [_f] * 3 + [_u32] + [_vp] * 4),
     "b200rl_vtrace": (_i32, [_vp] * 5 + [_i64] * 4 + [_d] + [_f] * 2 + [_vp] * 4),
     "b200rl_vtrace_bwd": (_i32, [_vp] * 7 + [_i64] * 4 + [_d, _f] + [_vp] * 4),
     "b200rl_lambda_returns": (_i32, [_vp] * 3 + [_i64] * 4 + [_d] + [_vp] * 2),

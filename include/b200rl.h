@@ -86,6 +86,24 @@ int32_t b200rl_vtrace_impala_loss_fwdbwd(
     double lambda_, float clip_rho, float clip_pg_rho, float entropy_coeff, uint32_t flags,
     float *dlogits, float *dvalues, float *scalars, void *workspace, void *stream);
 
+/* K1 without any allocation.  NO counterpart in the reference: added for callers
+ * that cannot call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid it).  Same
+ * arguments, kernels and results as b200rl_vtrace_impala_loss_fwdbwd minus `workspace`: the scalar reduction's scratch is a
+ * static device array inside the library, B200RL_NOALLOC_SCRATCH_BYTES (1 MiB + 256 B) on every GPU that loads the library,
+ * held until the process exits.  Limits (rejected on the host with status -3 and a message): B <= B200RL_NOALLOC_MAX_COLUMNS
+ * batch columns per call; no B200RL_TRACE.  All calls on a device share the scratch and find the previous call's contents:
+ * the entry point itself clears what must start at zero (one 1-thread launch ahead of the loss kernel, in stream order).
+ * Calls that OVERLAP on the GPU (different streams or threads) race on the scratch and get undefined scalars[] -- such
+ * callers use the ordinary entry point with one workspace per stream.  Calls no cudaMalloc / cudaFree / allocating routine. */
+#define B200RL_NOALLOC_SCRATCH_BYTES 1048832
+#define B200RL_NOALLOC_MAX_COLUMNS 16384
+int32_t b200rl_vtrace_impala_loss_fwdbwd_noalloc(
+    const float *logits, const float *pi_ref, const int64_t *actions, const float *rewards,
+    const float *discounts, const float *values,
+    int64_t B, int64_t T, int64_t A, int64_t stride_b, int64_t stride_t, int64_t n_global_b,
+    double lambda_, float clip_rho, float clip_pg_rho, float entropy_coeff, uint32_t flags,
+    float *dlogits, float *dvalues, float *scalars, void *stream);
+
 /* Stand-alone drop-in for batched_vtrace(v_tm1, v_t, r_t, discount_t, rho_tm1)
  * (reference agents/impala/learning.py:18,150-153).  The five inputs are [B,Tm]
  * views sharing (stride_b, stride_t): batch-major (stride_t=1, stride_b>=Tm -- e.g.
