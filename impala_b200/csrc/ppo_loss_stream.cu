@@ -54,17 +54,24 @@ __global__ void __launch_bounds__(kStreamThreads, 2) ppo_loss_stream_kernel(cons
     pdl_launch_dependents();
     const bool late_wait = p.flags & B200RL_INPUTS_STABLE;
     unsigned int gen = 0;
-    if (!late_wait) {
-        pdl_wait();  // inputs may come from the preceding kernel
-        gen = grid_generation(p.workspace);
-    }
-    __syncthreads();
-
     const int b = (int)blockIdx.x;
     const long long c_begin = (long long)b * q.chunks_lo + min(b, q.chunks_rem);
     const int nc = q.chunks_lo + (b < q.chunks_rem ? 1 : 0);
     auto chunk_n0 = [&](int c) { return (c_begin + c) * (long long)kStreamChunk; };
     auto chunk_count = [&](int c) { return (int)min((long long)kStreamChunk, p.N - chunk_n0(c)); };
+    if (!late_wait) {
+        // A HINT, not a read: while the preceding kernel (normally the lambda-return scan that writes v_target) still runs,
+        // ask L2 for the chunks this CTA loads first (cp.async.bulk.prefetch.L2); every value is read after the wait below.
+        if (warp == kStreamConsumers && lane < min(S, nc)) {
+            const size_t g0 = (size_t)chunk_n0(lane) * A;
+            const uint32_t bytes = (uint32_t)(chunk_count(lane) * A * 4);
+            bulk_prefetch_l2(p.logits + g0, bytes);
+            bulk_prefetch_l2(p.pi_ref + g0, bytes);
+        }
+        pdl_wait();  // inputs may come from the preceding kernel
+        gen = grid_generation(p.workspace);
+    }
+    __syncthreads();
 
     if (warp == kStreamConsumers) {
         // ---- producer: one thread drives the ring ------------------------------------------------

@@ -114,6 +114,10 @@ __global__ void __launch_bounds__(kSmemScanWarps * 32) scan_smem_kernel(const Sc
     float *sB = sA + kSmemScanWarps * 32;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     const int b0 = blockIdx.x * 32;
+    // The kernel that consumes the targets (the fused PPO loss, launched with the PDL attribute) may be scheduled while
+    // this one runs: it waits for this grid's completion before it reads anything (griddepcontrol.wait), but its prologue
+    // and its L2 prefetch of the logits overlap this kernel.  A no-op for dependents launched without the attribute.
+    pdl_launch_dependents();
     // ---- stage: chunk = (row, group of 4 columns); rows are st (vst) elements apart in HBM
     for (int ch = threadIdx.x; ch < TV * 8; ch += kSmemScanWarps * 32) {
         const int row = ch >> 3, c4 = (ch & 7) * 4;

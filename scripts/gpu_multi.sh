@@ -1,13 +1,6 @@
-# multi-GPU check (run under gpurun --gpus N): bench workloads under torchrun, as the driver launches them
+# multi-GPU check (run under gpurun --gpus N): the peer test, then bench.py exactly as the driver launches it
 N=${1:-2}
 mkdir -p gpurun_out
-TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
-for wl in impala_loss ppo learner; do
-  timeout 600 $TR bench.py --gpus $N --workload $wl --no-e2e > gpurun_out/bench_${wl}_n$N.log 2>&1
-  grep '^{' gpurun_out/bench_${wl}_n$N.log | tail -1 | python -c "
-import sys,json
-for l in sys.stdin:
-    d=json.loads(l); print('$wl N=$N', '%.4g %s'%(d['value'], d['unit']), 'ms/step %.4f'%d['ms_per_step'], 'frac', d['roofline'] and round(d['roofline']['frac'],3))
-" || tail -5 gpurun_out/bench_${wl}_n$N.log
-done
-timeout 300 python bench.py --workload learner > gpurun_out/bench_learner_n1.log 2>&1; tail -1 gpurun_out/bench_learner_n1.log | cut -c1-400
+timeout 600 python -m pytest tests/test_gpu_peer.py -m gpu -x -q > gpurun_out/pytest_peer_n$N.log 2>&1; tail -2 gpurun_out/pytest_peer_n$N.log
+timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 20 --warmup 3 > gpurun_out/bench_n$N.log 2>&1
+echo "rc=$?"; tail -1 gpurun_out/bench_n$N.log | python scripts/bench_digest.py || tail -30 gpurun_out/bench_n$N.log
