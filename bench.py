@@ -236,13 +236,19 @@ def make_replay(args, device, seed):
     idxs = [torch.empty(n, dtype=torch.int64, device=device) for _ in range(nout)]
     state = {"draws": 0}
 
+    fused = os.environ.get("B200RL_BENCH_REPLAY_FUSED", "1") == "1"
+
     def launch(i):
-        ops.sample_uniform(123, 0, i * n, n, cap, device, out=idxs[i % nout])
-        ops.gather_rows(store, idxs[i % nout], out=outs[i % nout])
+        if fused:       # K4 + K5 in one launch (what ReplayBuffer.sample issues for the uniform sampler)
+            ops.sample_gather_fields([store], 123, 0, i * n, n, cap, outs=[outs[i % nout]], out_idx=idxs[i % nout])
+        else:
+            ops.sample_uniform(123, 0, i * n, n, cap, device, out=idxs[i % nout])
+            ops.gather_rows(store, idxs[i % nout], out=outs[i % nout])
 
     desc = {"workload": "replay uniform sample + gather (BASELINE config 4)", "capacity": cap, "row_bytes": 12288,
             "batch": n, "l2_policy": "12.3 GB storage >> L2; random rows; %d rotating outputs" % nout}
-    return dict(launch=launch, units=n, kernels=2, host=None, e2e_step=None, desc=desc,
+    desc["launches"] = "ONE launch per step: the index draw (K4) happens inside the gather kernel (K5)" if fused else "two launches per step: K4 then K5"
+    return dict(launch=launch, units=n, kernels=1 if fused else 2, host=None, e2e_step=None, desc=desc,
                 check=lambda: idxs[0], state=state)
 
 

@@ -24,16 +24,20 @@ __device__ __forceinline__ void philox4x32_10(uint32_t &c0, uint32_t &c1, uint32
     }
 }
 
+// draw number g of stream (seed, stream_id), reduced to [0, size)
+__device__ __forceinline__ long long uniform_index(uint64_t seed, uint32_t stream_id, uint64_t g, uint64_t size) {
+    uint32_t c0 = (uint32_t)g, c1 = (uint32_t)(g >> 32), c2 = stream_id, c3 = 0u;
+    philox4x32_10(c0, c1, c2, c3, (uint32_t)seed, (uint32_t)(seed >> 32));
+    const uint64_t x = (uint64_t)c0 | ((uint64_t)c1 << 32);
+    return (long long)__umul64hi(x, size);
+}
+
 __global__ void __launch_bounds__(256) sample_uniform_kernel(uint64_t seed, uint32_t stream_id,
                                                              uint64_t draw_offset, long long n,
                                                              uint64_t size, long long *__restrict__ out) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const uint64_t g = draw_offset + (uint64_t)i;
-    uint32_t c0 = (uint32_t)g, c1 = (uint32_t)(g >> 32), c2 = stream_id, c3 = 0u;
-    philox4x32_10(c0, c1, c2, c3, (uint32_t)seed, (uint32_t)(seed >> 32));
-    const uint64_t x = (uint64_t)c0 | ((uint64_t)c1 << 32);
-    out[i] = (long long)__umul64hi(x, size);
+    out[i] = uniform_index(seed, stream_id, draw_offset + (uint64_t)i, size);
 }
 
 // Row copy with a per-row source or destination index.  The work is flattened over
@@ -42,7 +46,7 @@ __global__ void __launch_bounds__(256) sample_uniform_kernel(uint64_t seed, uint
 // independent vectors in flight.
 //   GATHER : dst[i]                    = src[clamp(idx[i])]
 //   RING   : dst[(count + i) % cap]    = src[i]
-enum { COPY_GATHER = 0, COPY_RING = 1 };
+enum { COPY_GATHER = 0, COPY_RING = 1, COPY_SAMPLE_GATHER = 2 };
 constexpr int kCopyThreads = 256, kCopyUnroll = 4;
 
 template <typename V, int MODE>
@@ -149,11 +153,19 @@ struct FieldTable {
     float gamma[kMaxFields];
     long long n, capacity, count;
     const long long *idx;  // gather only
+    // sample + gather in one launch (COPY_SAMPLE_GATHER): row i comes from storage row uniform_index(draw_offset + i)
+    uint64_t seed, draw_offset, size;
+    uint32_t stream_id;
+    long long *idx_out;
     unsigned int cta_end[kMaxFields];  // field f owns CTAs [cta_end[f-1], cta_end[f])
     int n_fields;
 };
 
-// MODE COPY_RING: dst[(count + i) % capacity] = src[i];  COPY_GATHER: dst[i] = src[clamp(idx[i])]
+// MODE COPY_RING: dst[(count + i) % capacity] = src[i];  COPY_GATHER: dst[i] = src[clamp(idx[i])];
+// COPY_SAMPLE_GATHER: dst[i] = src[uniform_index(draw_offset + i)] and idx_out[i] = that index -- K4 and K5 in ONE launch:
+// a CTA first draws the indices of the few rows its 1,024 vectors touch (3 for 12 KB rows) into shared memory, so the
+// sampler's launch (3.4 us of the 19 us sample + gather step at BASELINE config 4) and the index round trip through HBM
+// disappear; the draws are the same Philox stream, bit for bit.
 template <int MODE>
 __global__ void __launch_bounds__(kCopyThreads) fields_copy_kernel(const FieldTable ft) {
     int f = 0;
@@ -163,6 +175,25 @@ __global__ void __launch_bounds__(kCopyThreads) fields_copy_kernel(const FieldTa
     const int vec = ft.vec[f];
     const long long vpr = rb / vec, total = ft.n * vpr;
     const long long base = ((long long)cta * kCopyUnroll) * kCopyThreads + threadIdx.x;
+    __shared__ long long s_idx[MODE == COPY_SAMPLE_GATHER ? kCopyThreads * kCopyUnroll + 1 : 1];
+    long long first_row = 0;
+    if (MODE == COPY_SAMPLE_GATHER) {
+        // launched with the PDL attribute: the draws are pure arithmetic and run while the preceding kernel drains;
+        // nothing in global memory is touched before griddepcontrol.wait (storage may have just been appended to, and
+        // the previous consumer of idx_out may still be reading it)
+        pdl_launch_dependents();
+        const long long k0 = (long long)cta * kCopyUnroll * kCopyThreads;                  // < total: the grid is exact
+        const long long k1 = min(total, k0 + (long long)kCopyUnroll * kCopyThreads) - 1;
+        first_row = k0 / vpr;
+        const long long last_row = k1 / vpr;
+        for (long long r = first_row + threadIdx.x; r <= last_row; r += kCopyThreads)
+            s_idx[r - first_row] = uniform_index(ft.seed, ft.stream_id, ft.draw_offset + (uint64_t)r, ft.size);
+        __syncthreads();
+        pdl_wait();
+        if (f == 0)
+            for (long long r = first_row + threadIdx.x; r <= last_row; r += kCopyThreads)
+                if (r * vpr >= k0) ft.idx_out[r] = s_idx[r - first_row];  // every row starts in exactly one CTA of field 0
+    }
     if (base >= total) return;
     if (MODE == COPY_RING && ft.kind[f] == B200RL_FIELD_DONE_TO_DISCOUNT) {
         const unsigned char *src = static_cast<const unsigned char *>(ft.src[f]);
@@ -195,7 +226,7 @@ __global__ void __launch_bounds__(kCopyThreads) fields_copy_kernel(const FieldTa
                     regs[u] = __ldcs(src + k);
                     d_off[u] = ((ft.count + row) % ft.capacity) * vpr + col;
                 } else {
-                    long long j = __ldg(ft.idx + row);
+                    long long j = MODE == COPY_SAMPLE_GATHER ? s_idx[row - first_row] : __ldg(ft.idx + row);
                     j = j < 0 ? 0 : (j >= ft.capacity ? ft.capacity - 1 : j);
                     regs[u] = __ldcs(src + j * vpr + col);
                     d_off[u] = k;
@@ -273,4 +304,42 @@ extern "C" int32_t b200rl_gather_fields(const b200rl_field_t *fields, int32_t n_
     if (int32_t rc = fill_field_table("gather_fields", fields, n_fields, n, false, ft, max_ctas)) return rc;
     fields_copy_kernel<COPY_GATHER><<<(unsigned)max_ctas, kCopyThreads, 0, (cudaStream_t)stream>>>(ft);
     return check_launch("fields_copy_kernel<gather>");
+}
+
+// K4 + K5 in one launch (the learner's ReplayBuffer.sample with the uniform sampler, reference
+// agents/impala/learning.py:121 / agents/ppo/learning.py:112): draws n indices in [0, size) exactly as
+// b200rl_sample_uniform(seed, stream_id, draw_offset, n, size) does, writes them to out_idx and gathers those rows of every field.
+extern "C" int32_t b200rl_sample_gather_fields(const b200rl_field_t *fields, int32_t n_fields, uint64_t seed,
+                                               uint32_t stream_id, uint64_t draw_offset, int64_t n, int64_t size,
+                                               int64_t nrows, int64_t *out_idx, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(n >= 0, -2, "sample_gather_fields: negative size");
+    B200RL_REQUIRE(n_fields >= 1 && n_fields <= kMaxFields, -2, "sample_gather_fields: 1..%d fields (got %d)", kMaxFields, n_fields);
+    B200RL_REQUIRE(fields, -1, "sample_gather_fields: null field table");
+    if (n == 0) return 0;
+    B200RL_REQUIRE(out_idx, -1, "sample_gather_fields: null index output");
+    B200RL_REQUIRE(size >= 1 && size <= nrows, -2,
+                   "sample_gather_fields: cannot sample %lld of %lld rows (size must be in 1..nrows)", (long long)size, (long long)nrows);
+    FieldTable ft = {};
+    ft.n = n; ft.capacity = nrows; ft.count = 0; ft.idx = nullptr;
+    ft.seed = seed; ft.stream_id = stream_id; ft.draw_offset = draw_offset; ft.size = (uint64_t)size;
+    ft.idx_out = reinterpret_cast<long long *>(out_idx);
+    long long max_ctas;
+    if (int32_t rc = fill_field_table("sample_gather_fields", fields, n_fields, n, false, ft, max_ctas)) return rc;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)max_ctas);
+    cfg.blockDim = dim3(kCopyThreads);
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // PDL: see pdl_wait() in the kernel
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, fields_copy_kernel<COPY_SAMPLE_GATHER>, ft);
+    if (e != cudaSuccess) {
+        set_error("fields_copy_kernel<sample_gather> launch: %s", cudaGetErrorString(e));
+        (void)cudaGetLastError();
+        return (int32_t)e;
+    }
+    return check_launch("fields_copy_kernel<sample_gather>");
 }

@@ -385,6 +385,26 @@ def gather_fields(storages, idx, outs=None):
     return outs
 
 
+def sample_gather_fields(storages, seed, stream_id, draw_offset, n, size, outs=None, out_idx=None):
+    """K4 + K5 in ONE launch: draws the ``n`` indices of ``sample_uniform(seed, stream_id, draw_offset, n, size)`` (same
+    Philox stream, bit for bit) and gathers those rows of every field.  Returns ``(idx, outs)``."""
+    _require_cuda(*storages)
+    nrows, dev = storages[0].shape[0], storages[0].device
+    if out_idx is None:
+        out_idx = torch.empty(n, dtype=torch.int64, device=dev)
+    if outs is None:
+        outs = [torch.empty((n,) + tuple(st.shape[1:]), dtype=st.dtype, device=st.device) for st in storages]
+    table = (_cabi.Field * len(storages))()
+    for i, (st, o) in enumerate(zip(storages, outs)):
+        if not st.is_contiguous() or st.shape[0] != nrows or not o.is_contiguous():
+            raise RuntimeError("sample_gather_fields: field %d must be contiguous with %d rows" % (i, nrows))
+        table[i] = _cabi.Field(st.data_ptr(), o.data_ptr(), (st[0].numel() * st.element_size()) if nrows else 1,
+                               _cabi.FIELD_COPY, 0.0)
+    _cabi.call("b200rl_sample_gather_fields", table, len(storages), seed, stream_id, draw_offset, n, size, nrows,
+               _i64c(out_idx, "out_idx").data_ptr(), _stream())
+    return out_idx, outs
+
+
 def n_step_returns(r_t, discount_t, v_t, n, lambda_=1.0):
     """N4.  ``[B,T]`` views (batch- or time-major) -> n-step bootstrapped returns, same major order."""
     _require_cuda(r_t, discount_t, v_t)

@@ -194,9 +194,16 @@ class ReplayBuffer:
         size = st.size
         if self._prioritized():
             slots, probs = self.sampler.sample(n, size, st.device)
+            batch = st.gather(slots)
+        elif type(self.sampler) is UniformSampler and st.fields is not None and len(st.fields) <= 8:
+            # uniform sampler: the draw happens inside the gather launch (K4 + K5 in one kernel, same Philox stream)
+            probs = None
+            slots, batch = ops.sample_gather_fields(st.fields, self.sampler.seed, self.sampler.stream_id,
+                                                    self.sampler.draws, n, size)
+            self.sampler.draws += n
         else:
             slots, probs = self.sampler.sample(n, size, st.device), None
-        batch = st.gather(slots)
+            batch = st.gather(slots)
         if not self.with_keys:
             return slots, batch, None
         oldest = max(st.count - st.capacity, 0)

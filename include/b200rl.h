@@ -231,6 +231,15 @@ int32_t b200rl_ring_append_fields(
 int32_t b200rl_gather_fields(
     const b200rl_field_t *fields, int32_t n_fields, const int64_t *idx, int64_t n, int64_t nrows, void *stream);
 
+/* K4 + K5 in ONE launch -- replaces ReplayBuffer.sample(n) with the uniform sampler (reference agents/impala/learning.py:121,
+ * agents/ppo/learning.py:112; rlmeta UniformSampler + CircularBuffer built at agents/impala/builder.py:30-36): draws the n
+ * indices of b200rl_sample_uniform(seed, stream_id, draw_offset, n, size) -- the same Philox stream, bit for bit -- writes
+ * them to out_idx and gathers those rows of every field (fields[f].src = storage [nrows, row_bytes], .dst = batch
+ * [n, row_bytes]).  1 <= size <= nrows. */
+int32_t b200rl_sample_gather_fields(const b200rl_field_t *fields, int32_t n_fields, uint64_t seed, uint32_t stream_id,
+                                    uint64_t draw_offset, int64_t n, int64_t size, int64_t nrows, int64_t *out_idx,
+                                    void *stream);
+
 /* N3 -- prioritized sampling (replaces rlmeta PrioritizedSampler, reference agents/dqn/builder.py:83-90;
  * extend/sample/update at agents/dqn/learning.py:54,122,184).  `tree` is a caller-owned, zero-initialised
  * fp64 array of 2*leaves nodes (leaves = power of two >= capacity; node 1 = root, leaf j at leaves + j).

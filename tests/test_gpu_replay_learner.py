@@ -350,3 +350,32 @@ def test_act_epilogue_matches_spec(cuda):
     model.reset_act_rng(3)
     act, lg, v = model.act(torch.zeros(5, 3, 64, 64, dtype=torch.uint8), torch.tensor([False]))
     assert act.shape == (5, 1) and act.dtype == torch.int64 and lg.shape == (5, 15) and v.shape == (5, 1)
+
+
+@pytest.mark.parametrize("shapes", [[(3, 64, 64)], [(20, 3, 8, 8), (20, 1), (20, 1), (20, 15)], [(1,), (5,)], [(7, 3)]])
+def test_sample_gather_in_one_launch_matches_two_launches(cuda, shapes):
+    """b200rl_sample_gather_fields (K4 + K5 fused) == b200rl_sample_uniform then b200rl_gather_fields: same Philox draws,
+    same rows, bit for bit -- incl. rows that straddle CTAs, tiny rows (many rows per CTA) and odd row sizes."""
+    cap, size, n = 997, 613, 777
+    g = torch.Generator(device=cuda).manual_seed(5)
+    dts = [torch.uint8, torch.int64, torch.float32, torch.float32]
+    stores = [(torch.randint(0, 250, (cap,) + sh, generator=g, device=cuda).to(dts[i % 4])) for i, sh in enumerate(shapes)]
+    for call in range(2):
+        off = 1000 * call + 3
+        idx = ops.sample_uniform(99, 2, off, n, size, cuda)
+        want = ops.gather_fields(stores, idx)
+        got_idx, got = ops.sample_gather_fields(stores, 99, 2, off, n, size)
+        torch.cuda.synchronize()
+        assert torch.equal(got_idx, idx)
+        assert int(got_idx.max()) < size
+        for a, b in zip(got, want):
+            assert torch.equal(a, b)
+    # and through the drop-in buffer: keys / batch of the fused path == oracle sampler stream
+    rb = replay.ReplayBuffer(replay.CircularBuffer(64, device=cuda), replay.UniformSampler(stream_id=1))
+    rb.sampler.reset(7)
+    rb.extend((torch.arange(40, device=cuda).reshape(40, 1).float(), torch.arange(40, device=cuda).reshape(40, 1)))
+    keys, batch, probs = rb.sample(16)
+    want_idx = ops.sample_uniform(7, 1, 0, 16, 40, cuda)
+    assert torch.equal(keys, want_idx) and torch.equal(batch[1].reshape(-1), want_idx)
+    keys2, _, _ = rb.sample(16)
+    assert torch.equal(keys2, ops.sample_uniform(7, 1, 16, 16, 40, cuda))
