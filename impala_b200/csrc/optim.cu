@@ -405,9 +405,13 @@ extern "C" int32_t b200rl_peer_allreduce_clip_adam_step(
     float *params, const float *const *peer_buckets, uint32_t *const *peer_flags, float *const *peer_reduced,
     uint32_t *const *peer_cta_flags, const float *mc_buckets, float *mc_reduced, int32_t world, int32_t rank,
     float *grads_out, float *extra_out, int64_t n_extra, float *exp_avg, float *exp_avg_sq, int64_t n, float max_norm,
-    double lr, double beta1, double beta2, double eps, int64_t step, float *total_norm, void *workspace, void *stream) {
+    double lr, double beta1, double beta2, double eps, int64_t step, int64_t flag_generation, float *total_norm,
+    void *workspace, void *stream) {
     using namespace b200rl;
     B200RL_REQUIRE(peer_buckets && peer_flags && grads_out, -1, "peer_allreduce_clip_adam_step: null pointer argument");
+    B200RL_REQUIRE(flag_generation >= 1 && flag_generation < (1ll << 31), -2,
+                   "peer_allreduce_clip_adam_step: flag_generation=%lld (a counter >= 1 that every rank advances by one per call)",
+                   (long long)flag_generation);
     B200RL_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, -2,
                    "peer_allreduce_clip_adam_step: world=%d rank=%d (at most %d ranks)", world, rank, kMaxPeers);
     B200RL_REQUIRE(n_extra >= 0 && n_extra <= kOptThreads && (n_extra == 0 || extra_out), -2,
@@ -444,7 +448,7 @@ extern "C" int32_t b200rl_peer_allreduce_clip_adam_step(
     }
     pp.extra_out = extra_out;
     pp.world = world; pp.rank = rank; pp.n_extra = (int)n_extra;
-    pp.gen = (unsigned int)step;
+    pp.gen = (unsigned int)flag_generation;  // owned by the flag areas (the bucket), NOT the optimizer's step: see b200rl.h
     return launch_clip_adam("peer_allreduce_clip_adam_step", params, grads_out, exp_avg, exp_avg_sq, n, max_norm, lr, beta1,
                             beta2, eps, step, total_norm, workspace, stream, &pp);
 }

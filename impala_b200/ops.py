@@ -291,7 +291,7 @@ def clip_adam_step(params, grads, exp_avg, exp_avg_sq, step, lr, beta1=0.9, beta
 def peer_allreduce_clip_adam_step(params, peer_bucket_ptrs, peer_flag_ptrs, rank, grads_out, extra_out, exp_avg,
                                   exp_avg_sq, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, max_norm=0.0,
                                   total_norm=None, peer_reduced_ptrs=None, peer_cta_flag_ptrs=None, mc_bucket_ptr=0,
-                                  mc_reduced_ptr=0):
+                                  mc_reduced_ptr=0, flag_generation=None):
     """K8.  ``peer_bucket_ptrs`` / ``peer_flag_ptrs``: device addresses (ints) of every rank's bucket and flag area as
     mapped into THIS process (``parallel.PeerGradBucket``).  Returns the 1-element pre-clip norm of the reduced gradient."""
     _require_cuda(params, grads_out, exp_avg, exp_avg_sq)
@@ -314,7 +314,7 @@ def peer_allreduce_clip_adam_step(params, peer_bucket_ptrs, peer_flag_ptrs, rank
                ctypes.addressof(red) if two else 0, ctypes.addressof(cfl) if two else 0, mc_bucket_ptr or 0,
                mc_reduced_ptr or 0, world, rank, grads_out.data_ptr(), 0 if extra_out is None else extra_out.data_ptr(), n_extra,
                exp_avg.data_ptr(), exp_avg_sq.data_ptr(), n, max_norm, lr, beta1, beta2, eps, step,
-               total_norm.data_ptr(), ws.data_ptr(), _stream())
+               step if flag_generation is None else flag_generation, total_norm.data_ptr(), ws.data_ptr(), _stream())
     return total_norm
 
 

@@ -22,7 +22,11 @@ class FusedClipAdam(torch.optim.Optimizer):
 
     def __init__(self, params: Iterable[torch.nn.Parameter], lr: float = 1e-3, betas=(0.9, 0.999),
                  eps: float = 1e-8, max_grad_norm: float = 0.0):
-        super().__init__(params, dict(lr=lr, betas=betas, eps=eps))
+        # torch.optim.Adam's full set of group keys (fixed at its defaults: no weight decay / amsgrad, as the reference),
+        # so that a checkpoint written here loads into torch's Adam and the other way round
+        super().__init__(params, dict(lr=lr, betas=betas, eps=eps, weight_decay=0, amsgrad=False, maximize=False,
+                                      foreach=None, capturable=False, differentiable=False, fused=None,
+                                      decoupled_weight_decay=False))
         if len(self.param_groups) != 1:
             raise RuntimeError("FusedClipAdam: one parameter group only")
         self.max_grad_norm = float(max_grad_norm)
@@ -64,7 +68,45 @@ class FusedClipAdam(torch.optim.Optimizer):
                                                  bucket.extra_reduced, self.exp_avg, self.exp_avg_sq, self.step_count,
                                                  g["lr"], g["betas"][0], g["betas"][1], g["eps"], mgn, self.total_norm,
                                                  bucket.reduced_ptrs, bucket.cta_flag_ptrs, bucket.mc_bucket_ptr,
-                                                 bucket.mc_reduced_ptr)
+                                                 bucket.mc_reduced_ptr, flag_generation=bucket.next_generation())
+
+    # -- checkpoint / resume: the layout torch.optim.Adam uses, so either optimizer loads the other's state ---------------
+    def _moment_views(self):
+        off, out = 0, []
+        for p in self.params:
+            out.append((p, flat_view(self.exp_avg, off, p), flat_view(self.exp_avg_sq, off, p)))
+            off += p.numel()
+        return out
+
+    def state_dict(self):
+        """``torch.optim.Adam``'s format: per-parameter ``step`` / ``exp_avg`` / ``exp_avg_sq`` (copies of the flat moment
+        buffers) -- the base class would otherwise save an EMPTY state and a resumed run would restart the moments and the
+        bias correction."""
+        for p, m, v in self._moment_views():
+            self.state[p] = {"step": torch.tensor(float(self.step_count)), "exp_avg": m.detach().clone(),
+                             "exp_avg_sq": v.detach().clone()}
+        try:
+            return super().state_dict()
+        finally:
+            self.state.clear()
+
+    def load_state_dict(self, state_dict):
+        """Accepts a ``FusedClipAdam`` or a ``torch.optim.Adam`` state dict over the same parameters."""
+        super().load_state_dict(state_dict)
+        steps = set()
+        with torch.no_grad():
+            for p, m, v in self._moment_views():
+                st = self.state.get(p)
+                if not st:
+                    continue
+                m.copy_(st["exp_avg"])
+                v.copy_(st["exp_avg_sq"])
+                steps.add(int(float(st["step"])))
+        if len(steps) > 1:
+            raise RuntimeError("FusedClipAdam.load_state_dict: parameters carry different step counts %s" % sorted(steps))
+        if steps:
+            self.step_count = steps.pop()
+        self.state.clear()
 
     @torch.no_grad()
     def step(self, closure=None):

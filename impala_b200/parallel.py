@@ -156,6 +156,13 @@ class PeerGradBucket(GradBucket):
         if self.world_size > 1:
             dist.barrier(group=group)   # every rank has mapped every bucket before the first kernel touches one
 
+    def next_generation(self) -> int:
+        """The value the cross-rank flags of this bucket carry on the next K8 launch: a monotonic counter owned by the
+        bucket (its flag areas were zeroed when it was created, under a barrier), advanced by one per launch on every rank --
+        NOT the optimizer's step, which a resumed or recreated optimizer may set to anything."""
+        self._generation = getattr(self, "_generation", 0) + 1
+        return self._generation
+
     def allreduce(self, group=None) -> None:
         raise RuntimeError("PeerGradBucket: the allreduce is fused into FusedClipAdam.step_peer (K8)")
 

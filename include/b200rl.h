@@ -279,9 +279,12 @@ int32_t b200rl_clip_adam_step(
  * exchanges "gradients final" flags, reads its chunk from ALL buckets over NVLink with system-scope loads, adds
  * them in rank order (bit-identical on every rank), then norm -> clip -> Adam as K6; grads_out receives the
  * reduced, clipped gradient (must not alias a bucket), extra_out the n_extra tail sums.  The kernel returns only
- * after every peer has finished reading this rank's bucket.  `step` doubles as the flag generation: all ranks
- * must pass the same, strictly increasing value.  A rank that never arrives turns total_norm into NaN after
- * ~18 s instead of hanging.  peer_buckets / peer_flags are HOST arrays of `world` device pointers (<= 8).
+ * after every peer has finished reading this rank's bucket.  `step` is Adam's step (bias correction);
+ * `flag_generation` is the value the cross-rank flags carry: it belongs to the flag areas (zeroed once when they are
+ * created), starts at 1 and every rank advances it by exactly one per call -- independent of the optimizer's step, so an
+ * optimizer that is recreated or resumed from a checkpoint cannot fall behind stale flags.  A rank that never arrives
+ * turns total_norm into NaN after ~18 s instead of hanging, and the NaN propagates into the update (as torch's
+ * clip_grad_norm_ would) instead of applying partial gradients.  peer_buckets / peer_flags are HOST arrays of `world` device pointers (<= 8).
  * Routes: one-shot (every rank reads every bucket in full; default for 2 ranks) and two-shot (reduce-scatter +
  * all-gather through every rank's peer-mapped reduced buffer; default for more ranks).  Two-shot needs
  * peer_reduced (every rank's reduced-gradient buffer of n floats, peer_reduced[rank] == grads_out) and
@@ -295,7 +298,7 @@ int32_t b200rl_peer_allreduce_clip_adam_step(
     float *params, const float *const *peer_buckets, uint32_t *const *peer_flags, float *const *peer_reduced,
     uint32_t *const *peer_cta_flags, const float *mc_buckets, float *mc_reduced, int32_t world, int32_t rank,
     float *grads_out, float *extra_out, int64_t n_extra, float *exp_avg, float *exp_avg_sq, int64_t n,
-    float max_norm, double lr, double beta1, double beta2, double eps, int64_t step,
+    float max_norm, double lr, double beta1, double beta2, double eps, int64_t step, int64_t flag_generation,
     float *total_norm, void *workspace, void *stream);
 
 /* CUDA IPC plumbing for K8.  export: 64-byte handle of the cudaMalloc block `ptr` lives in + its byte offset in

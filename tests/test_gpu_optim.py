@@ -123,3 +123,49 @@ def test_nan_gradient_poisons_the_update_like_torch(cuda):
     q.grad = g.cpu().clone()
     torch.nn.utils.clip_grad_norm_([q], 0.5)
     assert torch.isnan(q.grad).all()
+
+
+def test_state_dict_round_trips_with_torch_adam(cuda):
+    """FusedClipAdam.state_dict() is torch.optim.Adam's format (the base class saved an EMPTY state): a run
+    checkpointed from the fused optimizer resumes in torch's Adam, and back, with the same moments and bias correction."""
+    torch.manual_seed(3)
+    shapes = [(16, 3, 3, 3), (16,), (40, 16)]
+    pf = [torch.nn.Parameter(torch.randn(s, device=cuda)) for s in shapes]
+    pt = [torch.nn.Parameter(p.detach().clone()) for p in pf]
+    fused = optim.FusedClipAdam(pf, lr=1e-2, eps=1e-5)
+    ref = torch.optim.Adam(pt, lr=1e-2, eps=1e-5)
+    g = torch.Generator(device=cuda).manual_seed(1)
+
+    def step_both(opt_a, pa, opt_b, pb):
+        grads = [torch.randn(p.shape, generator=g, device=cuda) for p in pa]
+        for p, q, gr in zip(pa, pb, grads):
+            p.grad, q.grad = gr.clone(), gr.clone()
+        opt_a.step()
+        opt_b.step()
+
+    for _ in range(3):
+        step_both(fused, pf, ref, pt)
+    sd = fused.state_dict()
+    assert len(sd["state"]) == 3 and float(sd["state"][0]["step"]) == 3.0
+    for i, p in enumerate(pt):          # same moments as torch's own state
+        assert_close(sd["state"][i]["exp_avg"], ref.state[p]["exp_avg"], "exp_avg", rtol=1e-5, atol=1e-8)
+    # fused -> torch: a fresh torch Adam resumed from the fused checkpoint continues like the fused one
+    pt2 = [torch.nn.Parameter(p.detach().clone()) for p in pf]
+    ref2 = torch.optim.Adam(pt2, lr=1e-2, eps=1e-5)
+    ref2.load_state_dict(sd)
+    # torch -> fused: a fresh fused optimizer resumed from torch's checkpoint
+    pf2 = [torch.nn.Parameter(p.detach().clone()) for p in pt]
+    fused2 = optim.FusedClipAdam(pf2, lr=1e-2, eps=1e-5)
+    fused2.load_state_dict(ref.state_dict())
+    assert fused2.step_count == 3
+    step_both(fused, pf, ref2, pt2)
+    for p, q in zip(pf, pt2):
+        assert_close(p, q, "fused -> torch resume", rtol=1e-5, atol=1e-6)
+    g = torch.Generator(device=cuda).manual_seed(2)
+    grads = [torch.randn(p.shape, generator=g, device=cuda) for p in pt]
+    for p, q, gr in zip(pt, pf2, grads):
+        p.grad, q.grad = gr.clone(), gr.clone()
+    ref.step()
+    fused2.step()
+    for p, q in zip(pt, pf2):
+        assert_close(q, p, "torch -> fused resume", rtol=1e-5, atol=1e-6)
