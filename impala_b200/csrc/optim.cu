@@ -27,6 +27,11 @@ struct AdamParams {
     float *total_norm;
     unsigned int *gen;
     unsigned long long *words;
+    // CUDA-graph capture: the step-dependent values may not be launch arguments.  counters (nullable, device):
+    // [0] Adam's step, [1] the cross-rank flag generation (K8).  Every CTA reads them at entry, uses value + 1 and CTA 0
+    // stores value + 1 back after the grid barrier; the bias corrections are then formed in the kernel from lr / betas.
+    long long *counters;
+    double lr, beta1, beta2_d;
 };
 
 // ---- K8: the same kernel with the gradient ALLREDUCE fused in (PEER = true) ----------------------------------
@@ -139,13 +144,27 @@ __device__ __forceinline__ float adam_update(float &p, float &g, float &m, float
 constexpr int kResident = 4;
 
 template <bool VEC, bool RESIDENT, bool PEER>
-__global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams a, const PeerParams pp) {
+__global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams a_in, const PeerParams pp_in) {
     __shared__ float red[kOptThreads];
     __shared__ float s_total;
+    __shared__ float s_bias[2];
+    AdamParams a = a_in;
+    PeerParams pp = pp_in;
     const long long lo = (long long)blockIdx.x * a.chunk;
     const long long hi = min(a.n, lo + a.chunk);
     __shared__ unsigned int s_tag;
     __shared__ int s_peer_ok;
+    long long dev_step = 0, dev_gen = 0;
+    if (a.counters) {  // uniform branch: device-resident step / flag generation (graph capture)
+        dev_step = *reinterpret_cast<volatile long long *>(a.counters) + 1;
+        dev_gen = *reinterpret_cast<volatile long long *>(a.counters + 1) + 1;
+        if (PEER) pp.gen = (unsigned int)dev_gen;
+        if (threadIdx.x == 0) {  // torch's bias corrections, in double as Python forms them
+            const double bc1 = 1.0 - pow(a.beta1, (double)dev_step), bc2 = 1.0 - pow(a.beta2_d, (double)dev_step);
+            s_bias[0] = (float)(a.lr / bc1);
+            s_bias[1] = (float)(1.0 / sqrt(bc2));
+        }
+    }
     if (PEER) {
         // "my gradients are final" to every rank (they were written by earlier kernels of this stream), then wait
         // for every rank's word in this rank's flag area
@@ -263,6 +282,14 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams
         *a.total_norm = norm;
         *reinterpret_cast<volatile unsigned int *>(a.gen) = tag;  // every CTA has read the old value (barrier above)
     }
+    if (a.counters) {
+        a.step_size = s_bias[0];      // written before the barriers above
+        a.inv_bc2_sqrt = s_bias[1];
+        if (blockIdx.x == 0 && threadIdx.x == 0) {  // every CTA has read the old values (grid barrier above)
+            *reinterpret_cast<volatile long long *>(a.counters) = dev_step;
+            if (PEER) *reinterpret_cast<volatile long long *>(a.counters + 1) = dev_gen;
+        }
+    }
     // ---- phase 2: clip + Adam ----
     if (RESIDENT) {
         float4 *p4 = reinterpret_cast<float4 *>(a.p), *g4 = reinterpret_cast<float4 *>(a.g);
@@ -307,10 +334,12 @@ __global__ void __launch_bounds__(kOptThreads) clip_adam_kernel(const AdamParams
 // Shared host side of K6 (peer == nullptr) and K8.
 static int32_t launch_clip_adam(const char *who, float *params, float *grads, float *exp_avg, float *exp_avg_sq, int64_t n,
                                 float max_norm, double lr, double beta1, double beta2, double eps, int64_t step,
-                                float *total_norm, void *workspace, void *stream, const PeerParams *peer) {
+                                float *total_norm, void *workspace, void *stream, const PeerParams *peer,
+                                int64_t *device_counters) {
     B200RL_REQUIRE(params && grads && exp_avg && exp_avg_sq && total_norm && workspace, -1, "%s: null pointer argument", who);
     B200RL_REQUIRE(n >= 1, -2, "%s: n=%lld", who, (long long)n);
-    B200RL_REQUIRE(step >= 1, -2, "%s: step must be >= 1 (got %lld)", who, (long long)step);
+    B200RL_REQUIRE(step >= 1 || device_counters, -2, "%s: step must be >= 1 (got %lld) unless device_counters is given", who, (long long)step);
+    if (device_counters) step = 1;  // the host-side value is unused: the kernel forms the bias corrections itself
     B200RL_REQUIRE(lr >= 0 && beta1 >= 0 && beta1 < 1 && beta2 >= 0 && beta2 < 1 && eps >= 0, -2,
                    "%s: invalid hyper-parameters", who);
     static int max_grid_dev[kMaxDevices];      // co-resident CTAs of the streaming kernel, per device
@@ -352,6 +381,8 @@ static int32_t launch_clip_adam(const char *who, float *params, float *grads, fl
     a.step_size = (float)(lr / bc1);
     a.inv_bc2_sqrt = (float)(1.0 / sqrt(bc2));
     a.eps = (float)eps;
+    a.counters = reinterpret_cast<long long *>(device_counters);
+    a.lr = lr; a.beta1 = beta1; a.beta2_d = beta2;
     a.total_norm = total_norm;
     a.gen = reinterpret_cast<unsigned int *>(reinterpret_cast<char *>(workspace) + kOptOffset);
     a.words = reinterpret_cast<unsigned long long *>(reinterpret_cast<char *>(workspace) + kOptOffset + 64);
@@ -395,28 +426,28 @@ static int32_t launch_clip_adam(const char *who, float *params, float *grads, fl
 
 extern "C" int32_t b200rl_clip_adam_step(float *params, float *grads, float *exp_avg, float *exp_avg_sq,
                                          int64_t n, float max_norm, double lr, double beta1, double beta2,
-                                         double eps, int64_t step, float *total_norm, void *workspace,
-                                         void *stream) {
+                                         double eps, int64_t step, int64_t *device_counters, float *total_norm,
+                                         void *workspace, void *stream) {
     return b200rl::launch_clip_adam("clip_adam_step", params, grads, exp_avg, exp_avg_sq, n, max_norm, lr, beta1, beta2, eps,
-                                    step, total_norm, workspace, stream, nullptr);
+                                    step, total_norm, workspace, stream, nullptr, device_counters);
 }
 
 extern "C" int32_t b200rl_peer_allreduce_clip_adam_step(
     float *params, const float *const *peer_buckets, uint32_t *const *peer_flags, float *const *peer_reduced,
     uint32_t *const *peer_cta_flags, const float *mc_buckets, float *mc_reduced, int32_t world, int32_t rank,
     float *grads_out, float *extra_out, int64_t n_extra, float *exp_avg, float *exp_avg_sq, int64_t n, float max_norm,
-    double lr, double beta1, double beta2, double eps, int64_t step, int64_t flag_generation, float *total_norm,
-    void *workspace, void *stream) {
+    double lr, double beta1, double beta2, double eps, int64_t step, int64_t flag_generation,
+    int64_t *device_counters, float *total_norm, void *workspace, void *stream) {
     using namespace b200rl;
     B200RL_REQUIRE(peer_buckets && peer_flags && grads_out, -1, "peer_allreduce_clip_adam_step: null pointer argument");
-    B200RL_REQUIRE(flag_generation >= 1 && flag_generation < (1ll << 31), -2,
+    B200RL_REQUIRE(device_counters || (flag_generation >= 1 && flag_generation < (1ll << 31)), -2,
                    "peer_allreduce_clip_adam_step: flag_generation=%lld (a counter >= 1 that every rank advances by one per call)",
                    (long long)flag_generation);
     B200RL_REQUIRE(world >= 1 && world <= kMaxPeers && rank >= 0 && rank < world, -2,
                    "peer_allreduce_clip_adam_step: world=%d rank=%d (at most %d ranks)", world, rank, kMaxPeers);
     B200RL_REQUIRE(n_extra >= 0 && n_extra <= kOptThreads && (n_extra == 0 || extra_out), -2,
                    "peer_allreduce_clip_adam_step: n_extra=%lld", (long long)n_extra);
-    B200RL_REQUIRE(step >= 1 && step < (1ll << 31), -2, "peer_allreduce_clip_adam_step: step=%lld", (long long)step);
+    B200RL_REQUIRE(device_counters || (step >= 1 && step < (1ll << 31)), -2, "peer_allreduce_clip_adam_step: step=%lld", (long long)step);
     PeerParams pp = {};
     for (int r = 0; r < world; ++r) {
         B200RL_REQUIRE(peer_buckets[r] && peer_flags[r], -1, "peer_allreduce_clip_adam_step: rank %d pointer is null", r);
@@ -450,5 +481,5 @@ extern "C" int32_t b200rl_peer_allreduce_clip_adam_step(
     pp.world = world; pp.rank = rank; pp.n_extra = (int)n_extra;
     pp.gen = (unsigned int)flag_generation;  // owned by the flag areas (the bucket), NOT the optimizer's step: see b200rl.h
     return launch_clip_adam("peer_allreduce_clip_adam_step", params, grads_out, exp_avg, exp_avg_sq, n, max_norm, lr, beta1,
-                            beta2, eps, step, total_norm, workspace, stream, &pp);
+                            beta2, eps, step, total_norm, workspace, stream, &pp, device_counters);
 }

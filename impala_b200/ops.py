@@ -271,9 +271,19 @@ def ring_append(storage, count, rows):
                rows.data_ptr(), rows.shape[0], _stream())
 
 
+def _counters_ptr(device_counters):
+    if device_counters is None:
+        return 0
+    if device_counters.dtype != torch.int64 or device_counters.numel() < 2 or not device_counters.is_cuda or \
+            not device_counters.is_contiguous():
+        raise RuntimeError("device_counters must be a contiguous int64[2] CUDA tensor (Adam step, flag generation)")
+    return device_counters.data_ptr()
+
+
 def clip_adam_step(params, grads, exp_avg, exp_avg_sq, step, lr, beta1=0.9, beta2=0.999, eps=1e-8,
-                   max_norm=0.0, total_norm=None):
-    """K6.  Flat fp32 buffers, updated in place; returns the 1-element ``total_norm`` tensor (pre-clip)."""
+                   max_norm=0.0, total_norm=None, device_counters=None):
+    """K6.  Flat fp32 buffers, updated in place; returns the 1-element ``total_norm`` tensor (pre-clip).  With
+    ``device_counters`` (int64[2] on the device) the step number lives in device memory and the launch is graph-replayable."""
     _require_cuda(params, grads, exp_avg, exp_avg_sq)
     n = params.numel()
     for name, x in (("params", params), ("grads", grads), ("exp_avg", exp_avg), ("exp_avg_sq", exp_avg_sq)):
@@ -283,15 +293,15 @@ def clip_adam_step(params, grads, exp_avg, exp_avg_sq, step, lr, beta1=0.9, beta
         total_norm = torch.empty(1, dtype=torch.float32, device=params.device)
     ws = workspace(params.device)
     _cabi.call("b200rl_clip_adam_step", params.data_ptr(), grads.data_ptr(), exp_avg.data_ptr(),
-               exp_avg_sq.data_ptr(), n, max_norm, lr, beta1, beta2, eps, step, total_norm.data_ptr(),
-               ws.data_ptr(), _stream())
+               exp_avg_sq.data_ptr(), n, max_norm, lr, beta1, beta2, eps, step, _counters_ptr(device_counters),
+               total_norm.data_ptr(), ws.data_ptr(), _stream())
     return total_norm
 
 
 def peer_allreduce_clip_adam_step(params, peer_bucket_ptrs, peer_flag_ptrs, rank, grads_out, extra_out, exp_avg,
                                   exp_avg_sq, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, max_norm=0.0,
                                   total_norm=None, peer_reduced_ptrs=None, peer_cta_flag_ptrs=None, mc_bucket_ptr=0,
-                                  mc_reduced_ptr=0, flag_generation=None):
+                                  mc_reduced_ptr=0, flag_generation=None, device_counters=None):
     """K8.  ``peer_bucket_ptrs`` / ``peer_flag_ptrs``: device addresses (ints) of every rank's bucket and flag area as
     mapped into THIS process (``parallel.PeerGradBucket``).  Returns the 1-element pre-clip norm of the reduced gradient."""
     _require_cuda(params, grads_out, exp_avg, exp_avg_sq)
@@ -314,7 +324,8 @@ def peer_allreduce_clip_adam_step(params, peer_bucket_ptrs, peer_flag_ptrs, rank
                ctypes.addressof(red) if two else 0, ctypes.addressof(cfl) if two else 0, mc_bucket_ptr or 0,
                mc_reduced_ptr or 0, world, rank, grads_out.data_ptr(), 0 if extra_out is None else extra_out.data_ptr(), n_extra,
                exp_avg.data_ptr(), exp_avg_sq.data_ptr(), n, max_norm, lr, beta1, beta2, eps, step,
-               step if flag_generation is None else flag_generation, total_norm.data_ptr(), ws.data_ptr(), _stream())
+               step if flag_generation is None else flag_generation, _counters_ptr(device_counters),
+               total_norm.data_ptr(), ws.data_ptr(), _stream())
     return total_norm
 
 

@@ -47,6 +47,23 @@ class FusedClipAdam(torch.optim.Optimizer):
         self.total_norm = torch.zeros(1, dtype=torch.float32, device=dev)
         self.step_count = 0
         self._own_grads = None
+        # graph-capturable mode (``capturable_()``): Adam's step and K8's flag generation live in device memory
+        self.device_counters = None
+
+    def capturable_(self, bucket=None):
+        """Switch to device-resident counters so that ``step_flat`` / ``step_peer`` can be captured in a CUDA graph and
+        replayed: a step number passed as a launch argument would be frozen into the graph.  Call it outside capture, on
+        every rank at the same point; ``bucket`` (a ``PeerGradBucket``) hands over its flag generation."""
+        if self.device_counters is None:
+            gen = getattr(bucket, "_generation", 0) if bucket is not None else 0
+            self.device_counters = torch.tensor([self.step_count, gen], dtype=torch.int64, device=self.flat.device)
+        return self
+
+    def sync_step_count(self) -> int:
+        """Host copy of the device-resident step (synchronises); keeps ``state_dict()`` truthful in capturable mode."""
+        if self.device_counters is not None:
+            self.step_count = int(self.device_counters[0].item())
+        return self.step_count
 
     def step_flat(self, flat_grads: torch.Tensor, max_grad_norm=None) -> torch.Tensor:
         """One clip + Adam step from a flat gradient buffer laid out like ``self.params``.
@@ -55,7 +72,8 @@ class FusedClipAdam(torch.optim.Optimizer):
         self.step_count += 1
         mgn = self.max_grad_norm if max_grad_norm is None else float(max_grad_norm)
         return ops.clip_adam_step(self.flat, flat_grads, self.exp_avg, self.exp_avg_sq, self.step_count,
-                                  g["lr"], g["betas"][0], g["betas"][1], g["eps"], mgn, self.total_norm)
+                                  g["lr"], g["betas"][0], g["betas"][1], g["eps"], mgn, self.total_norm,
+                                  device_counters=self.device_counters)
 
     def step_peer(self, bucket, max_grad_norm=None) -> torch.Tensor:
         """K8: allreduce (over the peer-mapped buckets of ``parallel.PeerGradBucket``) + clip + Adam in ONE launch, no
@@ -68,7 +86,8 @@ class FusedClipAdam(torch.optim.Optimizer):
                                                  bucket.extra_reduced, self.exp_avg, self.exp_avg_sq, self.step_count,
                                                  g["lr"], g["betas"][0], g["betas"][1], g["eps"], mgn, self.total_norm,
                                                  bucket.reduced_ptrs, bucket.cta_flag_ptrs, bucket.mc_bucket_ptr,
-                                                 bucket.mc_reduced_ptr, flag_generation=bucket.next_generation())
+                                                 bucket.mc_reduced_ptr, flag_generation=bucket.next_generation(),
+                                                 device_counters=self.device_counters)
 
     # -- checkpoint / resume: the layout torch.optim.Adam uses, so either optimizer loads the other's state ---------------
     def _moment_views(self):
@@ -82,6 +101,7 @@ class FusedClipAdam(torch.optim.Optimizer):
         """``torch.optim.Adam``'s format: per-parameter ``step`` / ``exp_avg`` / ``exp_avg_sq`` (copies of the flat moment
         buffers) -- the base class would otherwise save an EMPTY state and a resumed run would restart the moments and the
         bias correction."""
+        self.sync_step_count()
         for p, m, v in self._moment_views():
             self.state[p] = {"step": torch.tensor(float(self.step_count)), "exp_avg": m.detach().clone(),
                              "exp_avg_sq": v.detach().clone()}
@@ -106,6 +126,8 @@ class FusedClipAdam(torch.optim.Optimizer):
             raise RuntimeError("FusedClipAdam.load_state_dict: parameters carry different step counts %s" % sorted(steps))
         if steps:
             self.step_count = steps.pop()
+            if self.device_counters is not None:
+                self.device_counters[0] = self.step_count
         self.state.clear()
 
     @torch.no_grad()

@@ -266,10 +266,14 @@ int32_t b200rl_act_epilogue(
  * scaled by min(1, max_norm / (||g||_2 + 1e-6)) (max_norm <= 0: no clipping), then exp_avg, exp_avg_sq and
  * params take one Adam step; `step` is the 1-based step number (bias correction).  total_norm[0] receives
  * ||g||_2 before clipping.  `workspace` is the zero-initialised loss workspace (a separate region of it).
- * One cooperative launch (grid <= co-resident CTAs; CTAs loop over their chunk, so any n works). */
+ * One cooperative launch (grid <= co-resident CTAs; CTAs loop over their chunk, so any n works).
+ * `device_counters` (nullable; int64[2] in device memory, zeroed once by the caller) makes the launch CUDA-graph
+ * replayable: a step number passed as an argument would be frozen into the graph, so with the pointer given the kernel
+ * uses device_counters[0] + 1 as the step (`step` is then ignored), forms the bias corrections itself and stores the new
+ * step back; K8 does the same with device_counters[1] for its flag generation. */
 int32_t b200rl_clip_adam_step(
     float *params, float *grads, float *exp_avg, float *exp_avg_sq, int64_t n,
-    float max_norm, double lr, double beta1, double beta2, double eps, int64_t step,
+    float max_norm, double lr, double beta1, double beta2, double eps, int64_t step, int64_t *device_counters,
     float *total_norm, void *workspace, void *stream);
 
 /* K8 -- K6 with the gradient allreduce fused in (SURVEY sec 8f N1 "fused with the allreduce epilogue"; replaces the
@@ -299,7 +303,7 @@ int32_t b200rl_peer_allreduce_clip_adam_step(
     uint32_t *const *peer_cta_flags, const float *mc_buckets, float *mc_reduced, int32_t world, int32_t rank,
     float *grads_out, float *extra_out, int64_t n_extra, float *exp_avg, float *exp_avg_sq, int64_t n,
     float max_norm, double lr, double beta1, double beta2, double eps, int64_t step, int64_t flag_generation,
-    float *total_norm, void *workspace, void *stream);
+    int64_t *device_counters, float *total_norm, void *workspace, void *stream);
 
 /* CUDA IPC plumbing for K8.  export: 64-byte handle of the cudaMalloc block `ptr` lives in + its byte offset in
  * that block.  import: map a peer's block (peer access enabled lazily) and return the peer's buffer address.

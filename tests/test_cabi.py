@@ -65,8 +65,8 @@ def test_argument_errors_are_reported_without_a_gpu():
     disc = (_cabi.Field * 1)(_cabi.Field(16, 16, 4, 1, .99))
     assert lib.b200rl_gather_fields(disc, 1, one, 4, 8, None) == -2                  # discount kind is append-only
     assert lib.b200rl_gather_fields(fields, 1, one, 0, 8, None) == 0                 # empty gather is a no-op
-    assert lib.b200rl_clip_adam_step(one, one, one, one, 0, .5, 1e-4, .9, .999, 1e-5, 1, one, one, None) == -2
-    assert lib.b200rl_clip_adam_step(one, one, one, one, 8, .5, 1e-4, .9, .999, 1e-5, 0, one, one, None) == -2
+    assert lib.b200rl_clip_adam_step(one, one, one, one, 0, .5, 1e-4, .9, .999, 1e-5, 1, None, one, one, None) == -2
+    assert lib.b200rl_clip_adam_step(one, one, one, one, 8, .5, 1e-4, .9, .999, 1e-5, 0, None, one, one, None) == -2   # step 0 without device counters
     with pytest.raises(RuntimeError, match="status -2"):
         _cabi.call("b200rl_sample_uniform", 1, 0, 0, 8, 0, 16, None)
 

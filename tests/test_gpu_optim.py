@@ -169,3 +169,41 @@ def test_state_dict_round_trips_with_torch_adam(cuda):
     fused2.step()
     for p, q in zip(pt, pf2):
         assert_close(q, p, "torch -> fused resume", rtol=1e-5, atol=1e-6)
+
+
+def test_device_resident_step_counter_matches_host_steps_and_replays_in_a_graph(cuda):
+    """K6 with `device_counters`: the step number lives in device memory (a launch argument would be frozen into a CUDA
+    graph).  Same parameters as the host-step path after every step, eagerly and as ONE captured launch replayed."""
+    n = 70_000
+    g = torch.Generator(device=cuda).manual_seed(11)
+    p0 = torch.randn(n, generator=g, device=cuda)
+    grads = [torch.randn(n, generator=g, device=cuda) * (1 + k) for k in range(6)]
+    # host-step reference (the eager path tested against torch above)
+    p, m, v = p0.clone(), torch.zeros(n, device=cuda), torch.zeros(n, device=cuda)
+    want = []
+    for k, gk in enumerate(grads):
+        ops.clip_adam_step(p, gk.clone(), m, v, k + 1, 1e-3, eps=1e-5, max_norm=0.5)
+        want.append(p.clone())
+    # device counters, eager
+    p, m, v = p0.clone(), torch.zeros(n, device=cuda), torch.zeros(n, device=cuda)
+    ctr = torch.zeros(2, dtype=torch.int64, device=cuda)
+    for k, gk in enumerate(grads[:3]):
+        ops.clip_adam_step(p, gk.clone(), m, v, 0, 1e-3, eps=1e-5, max_norm=0.5, device_counters=ctr)
+        assert torch.equal(p, want[k]), "step %d" % (k + 1)
+    assert ctr.tolist() == [3, 0]
+    # ... and one captured launch replayed three more times (the gradient buffer is refilled between replays)
+    gbuf = torch.empty(n, device=cuda)
+    side = torch.cuda.Stream(cuda)
+    with torch.cuda.stream(side):
+        ops.workspace(cuda)
+        norm = torch.empty(1, device=cuda)
+    torch.cuda.synchronize()
+    gr = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(gr, stream=side):
+        ops.clip_adam_step(p, gbuf, m, v, 0, 1e-3, eps=1e-5, max_norm=0.5, total_norm=norm, device_counters=ctr)
+    for k in range(3, 6):
+        gbuf.copy_(grads[k])
+        gr.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(p, want[k]), "replayed step %d" % (k + 1)
+    assert ctr.tolist() == [6, 0]
