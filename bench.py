@@ -284,6 +284,9 @@ def make_learner(args, device, seed):
     learner = ImpalaLearner(model, rb, opt, batch_size=B, learning_starts=cap)
     learner.prepare()
     last = {}
+    use_graph = os.environ.get("B200RL_BENCH_LEARNER_GRAPH", "1") == "1"
+    if use_graph:
+        learner.capture_graph()        # the whole step = ONE graph launch (sample -> CNN -> K1 -> CNN bwd -> K6 / K8)
 
     def launch(i):
         last["m"] = learner.train_step()
@@ -294,6 +297,9 @@ def make_learner(args, device, seed):
                      "and its backward in the K9 kernels (convolutions bias-free in cuDNN)" if fused else ""),
             "replay": "%d rollouts device-resident (%.0f MB u8), uniform sample + gather on device" % (cap, cap * T * 12288 / 1e6),
             "l2_policy": "gathered batch 63 MB + activations >> per-step reuse; buffer 246 MB > 126 MB L2"}
+    desc["step_launch"] = ("ONE CUDA-graph launch per step (ImpalaLearner.capture_graph: sample -> CNN fwd -> K1 -> CNN bwd -> K6/K8; "
+                           "step number, flag generation and draw count in device memory)") if use_graph else "eager: one Python pass per step"
+
     def grad_exchange():
         from impala_b200 import parallel
         if not dist.is_initialized() or dist.get_world_size() == 1:
@@ -307,6 +313,7 @@ def make_learner(args, device, seed):
     def breakdown():
         """Per-phase device time of the learner step (mean of 5 profiled steps after the timed region)."""
         learner.profile = True
+        saved_graph, learner._graph = learner._graph, None      # the phases are timed on the eager path
         tot, names = {}, []
         for _ in range(5):
             t0 = torch.cuda.Event(enable_timing=True)
@@ -320,15 +327,18 @@ def make_learner(args, device, seed):
             for k, v in bd.items():
                 tot[k] = tot.get(k, 0.0) + v / 5
         learner.profile = False
+        learner._graph = saved_graph
         return {k: round(v, 4) for k, v in tot.items()}
 
     def launches_per_step():
-        """Kernel launches of one learner step, counted by the profiler (one profiled step after the timed region)."""
+        """Kernels of one learner step, counted by the profiler (one profiled step after the timed region); with the
+        captured step they are the nodes of ONE graph launch."""
         from torch.profiler import profile, ProfilerActivity
         with profile(activities=[ProfilerActivity.CUDA]) as prof:
             launch(0)
             torch.cuda.synchronize()
-        return int(sum(e.count for e in prof.key_averages() if e.device_type == torch.autograd.DeviceType.CUDA))
+        n = int(sum(e.count for e in prof.key_averages() if e.device_type == torch.autograd.DeviceType.CUDA))
+        return "1 graph launch (%d kernel nodes)" % n if use_graph else n
 
     return dict(launch=launch, units=B * T, kernels=0, host=None, e2e_step=None, desc=desc, graph=False,
                 check=lambda: last["m"]["train/loss"], breakdown=breakdown, learner=learner, grad_exchange=grad_exchange,
@@ -784,7 +794,8 @@ def main():
         line["config"]["breakdown_ms"] = w["breakdown"]()
         line["config"]["grad_exchange"] = w["grad_exchange"]()
         line["config"]["launches_per_step"] = w["launches_per_step"]()
-        launches += line["config"]["launches_per_step"] * steps * res["timing"]["repeats"]
+        lps = line["config"]["launches_per_step"]
+        launches += (int(str(lps).split("(")[1].split()[0]) if isinstance(lps, str) else lps) * steps * res["timing"]["repeats"]
     if not args.no_e2e and w["e2e_step"] is not None:
         e_steps = min(steps, 500)
         dt, h2d, d2h, est = time_e2e(w, e_steps, min(warmup, 20), device, world_size)
@@ -825,7 +836,8 @@ def main():
                 entry["breakdown_ms"] = w3["breakdown"]()
                 entry["grad_exchange"] = w3["grad_exchange"]()
                 entry["launches_per_step"] = w3["launches_per_step"]()
-                launches += entry["launches_per_step"] * r3["steps"] * r3["timing"]["repeats"]
+                lps = entry["launches_per_step"]
+                launches += (int(str(lps).split("(")[1].split()[0]) if isinstance(lps, str) else lps) * r3["steps"] * r3["timing"]["repeats"]
             line["config"]["other_workloads"][name] = entry
             if hasattr(w3.get("learner", None), "_bucket") and hasattr(w3["learner"]._bucket, "close"):
                 w3["learner"]._bucket.close()

@@ -41,7 +41,8 @@ SIGNATURES = {
     "b200rl_ring_append": (_i32, [_vp, _i64, _i64, _i64, _vp, _i64, _vp]),
     "b200rl_ring_append_fields": (_i32, [ctypes.POINTER(Field), _i32, _i64, _i64, _i64, _vp]),
     "b200rl_gather_fields": (_i32, [ctypes.POINTER(Field), _i32, _vp, _i64, _i64, _vp]),
-    "b200rl_sample_gather_fields": (_i32, [ctypes.POINTER(Field), _i32, _u64, _u32, _u64, _i64, _i64, _i64, _vp, _vp]),
+    "b200rl_sample_gather_fields": (_i32, [ctypes.POINTER(Field), _i32, _u64, _u32, _u64, _vp, _i64, _i64, _i64, _vp, _vp]),
+    "b200rl_counter_add": (_i32, [_vp, _i64, _vp]),
     "b200rl_sumtree_update": (_i32, [_vp, _i64, _vp, _vp, _i64, _vp]),
     "b200rl_sumtree_sample": (_i32, [_vp, _i64, _i64, _u64, _u32, _u64, _i64, _vp, _vp, _vp]),
     "b200rl_quantile_huber_fwdbwd": (_i32, [_vp] * 3 + [_i64] * 3 + [_f] + [_vp] * 3),

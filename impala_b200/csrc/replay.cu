@@ -157,6 +157,7 @@ struct FieldTable {
     uint64_t seed, draw_offset, size;
     uint32_t stream_id;
     long long *idx_out;
+    const unsigned long long *draw_counter;  // nullable, device: added to draw_offset (CUDA-graph replay, see b200rl.h)
     unsigned int cta_end[kMaxFields];  // field f owns CTAs [cta_end[f-1], cta_end[f])
     int n_fields;
 };
@@ -186,10 +187,15 @@ __global__ void __launch_bounds__(kCopyThreads) fields_copy_kernel(const FieldTa
         const long long k1 = min(total, k0 + (long long)kCopyUnroll * kCopyThreads) - 1;
         first_row = k0 / vpr;
         const long long last_row = k1 / vpr;
+        uint64_t off = ft.draw_offset;
+        if (ft.draw_counter) {  // the counter is advanced by a preceding launch of this stream: read it after the wait
+            pdl_wait();
+            off += *reinterpret_cast<const volatile unsigned long long *>(ft.draw_counter);
+        }
         for (long long r = first_row + threadIdx.x; r <= last_row; r += kCopyThreads)
-            s_idx[r - first_row] = uniform_index(ft.seed, ft.stream_id, ft.draw_offset + (uint64_t)r, ft.size);
+            s_idx[r - first_row] = uniform_index(ft.seed, ft.stream_id, off + (uint64_t)r, ft.size);
         __syncthreads();
-        pdl_wait();
+        if (!ft.draw_counter) pdl_wait();
         if (f == 0)
             for (long long r = first_row + threadIdx.x; r <= last_row; r += kCopyThreads)
                 if (r * vpr >= k0) ft.idx_out[r] = s_idx[r - first_row];  // every row starts in exactly one CTA of field 0
@@ -310,8 +316,8 @@ extern "C" int32_t b200rl_gather_fields(const b200rl_field_t *fields, int32_t n_
 // agents/impala/learning.py:121 / agents/ppo/learning.py:112): draws n indices in [0, size) exactly as
 // b200rl_sample_uniform(seed, stream_id, draw_offset, n, size) does, writes them to out_idx and gathers those rows of every field.
 extern "C" int32_t b200rl_sample_gather_fields(const b200rl_field_t *fields, int32_t n_fields, uint64_t seed,
-                                               uint32_t stream_id, uint64_t draw_offset, int64_t n, int64_t size,
-                                               int64_t nrows, int64_t *out_idx, void *stream) {
+                                               uint32_t stream_id, uint64_t draw_offset, const uint64_t *draw_counter,
+                                               int64_t n, int64_t size, int64_t nrows, int64_t *out_idx, void *stream) {
     using namespace b200rl;
     B200RL_REQUIRE(n >= 0, -2, "sample_gather_fields: negative size");
     B200RL_REQUIRE(n_fields >= 1 && n_fields <= kMaxFields, -2, "sample_gather_fields: 1..%d fields (got %d)", kMaxFields, n_fields);
@@ -324,6 +330,7 @@ extern "C" int32_t b200rl_sample_gather_fields(const b200rl_field_t *fields, int
     ft.n = n; ft.capacity = nrows; ft.count = 0; ft.idx = nullptr;
     ft.seed = seed; ft.stream_id = stream_id; ft.draw_offset = draw_offset; ft.size = (uint64_t)size;
     ft.idx_out = reinterpret_cast<long long *>(out_idx);
+    ft.draw_counter = reinterpret_cast<const unsigned long long *>(draw_counter);
     long long max_ctas;
     if (int32_t rc = fill_field_table("sample_gather_fields", fields, n_fields, n, false, ft, max_ctas)) return rc;
     cudaLaunchConfig_t cfg = {};
@@ -342,4 +349,17 @@ extern "C" int32_t b200rl_sample_gather_fields(const b200rl_field_t *fields, int
         return (int32_t)e;
     }
     return check_launch("fields_copy_kernel<sample_gather>");
+}
+
+namespace b200rl {
+__global__ void counter_add_kernel(unsigned long long *counter, long long delta) { *counter += (unsigned long long)delta; }
+}  // namespace b200rl
+
+// *counter += delta in stream order (one thread).  The device-resident draw counter of a sampler whose launches are replayed
+// from a CUDA graph: the sampling launch reads it, this launch advances it for the next replay.
+extern "C" int32_t b200rl_counter_add(uint64_t *counter, int64_t delta, void *stream) {
+    using namespace b200rl;
+    B200RL_REQUIRE(counter, -1, "counter_add: null counter");
+    counter_add_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(reinterpret_cast<unsigned long long *>(counter), (long long)delta);
+    return check_launch("counter_add_kernel");
 }

@@ -396,7 +396,15 @@ def gather_fields(storages, idx, outs=None):
     return outs
 
 
-def sample_gather_fields(storages, seed, stream_id, draw_offset, n, size, outs=None, out_idx=None):
+def counter_add(counter, delta):
+    """``counter[0] += delta`` in stream order (device-resident counters of graph-replayed launches)."""
+    _require_cuda(counter)
+    if counter.dtype != torch.int64 or not counter.is_contiguous():
+        raise RuntimeError("counter_add: int64 CUDA tensor expected")
+    _cabi.call("b200rl_counter_add", counter.data_ptr(), delta, _stream())
+
+
+def sample_gather_fields(storages, seed, stream_id, draw_offset, n, size, outs=None, out_idx=None, draw_counter=None):
     """K4 + K5 in ONE launch: draws the ``n`` indices of ``sample_uniform(seed, stream_id, draw_offset, n, size)`` (same
     Philox stream, bit for bit) and gathers those rows of every field.  Returns ``(idx, outs)``."""
     _require_cuda(*storages)
@@ -411,7 +419,8 @@ def sample_gather_fields(storages, seed, stream_id, draw_offset, n, size, outs=N
             raise RuntimeError("sample_gather_fields: field %d must be contiguous with %d rows" % (i, nrows))
         table[i] = _cabi.Field(st.data_ptr(), o.data_ptr(), (st[0].numel() * st.element_size()) if nrows else 1,
                                _cabi.FIELD_COPY, 0.0)
-    _cabi.call("b200rl_sample_gather_fields", table, len(storages), seed, stream_id, draw_offset, n, size, nrows,
+    _cabi.call("b200rl_sample_gather_fields", table, len(storages), seed, stream_id, draw_offset,
+               0 if draw_counter is None else _i64c(draw_counter, "draw_counter").data_ptr(), n, size, nrows,
                _i64c(out_idx, "out_idx").data_ptr(), _stream())
     return out_idx, outs
 

@@ -24,9 +24,19 @@ class UniformSampler:
 
     def __init__(self, stream_id: int = 0):
         self.seed, self.stream_id, self.draws = 0, int(stream_id), 0
+        self.draw_counter = None      # device-resident copy of `draws` (capturable_): for CUDA-graph replay
 
     def reset(self, seed: int) -> None:
         self.seed, self.draws = int(seed), 0
+        if self.draw_counter is not None:
+            self.draw_counter.zero_()
+
+    def capturable_(self, device):
+        """Keep the draw count in device memory so that ``ReplayBuffer.sample`` can be captured in a CUDA graph and replayed
+        (a draw offset passed as a launch argument would be frozen into the graph).  Call outside capture."""
+        if self.draw_counter is None:
+            self.draw_counter = torch.tensor([self.draws], dtype=torch.int64, device=device)
+        return self
 
     def sample(self, n: int, size: int, device, out=None) -> torch.Tensor:
         if size <= 0:
@@ -198,8 +208,11 @@ class ReplayBuffer:
         elif type(self.sampler) is UniformSampler and st.fields is not None and len(st.fields) <= 8:
             # uniform sampler: the draw happens inside the gather launch (K4 + K5 in one kernel, same Philox stream)
             probs = None
+            ctr = self.sampler.draw_counter
             slots, batch = ops.sample_gather_fields(st.fields, self.sampler.seed, self.sampler.stream_id,
-                                                    self.sampler.draws, n, size)
+                                                    0 if ctr is not None else self.sampler.draws, n, size, draw_counter=ctr)
+            if ctr is not None:
+                ops.counter_add(ctr, n)       # in stream order, after the draw: the next (replayed) sample continues the stream
             self.sampler.draws += n
         else:
             slots, probs = self.sampler.sample(n, size, st.device), None

@@ -237,8 +237,13 @@ int32_t b200rl_gather_fields(
  * them to out_idx and gathers those rows of every field (fields[f].src = storage [nrows, row_bytes], .dst = batch
  * [n, row_bytes]).  1 <= size <= nrows. */
 int32_t b200rl_sample_gather_fields(const b200rl_field_t *fields, int32_t n_fields, uint64_t seed, uint32_t stream_id,
-                                    uint64_t draw_offset, int64_t n, int64_t size, int64_t nrows, int64_t *out_idx,
-                                    void *stream);
+                                    uint64_t draw_offset, const uint64_t *draw_counter, int64_t n, int64_t size,
+                                    int64_t nrows, int64_t *out_idx, void *stream);
+
+/* `draw_counter` above (nullable, device memory) is added to draw_offset inside the kernel: a draw offset passed as an
+ * argument would be frozen into a CUDA graph.  b200rl_counter_add(counter, delta) advances such a counter in stream order
+ * (one thread); a captured learner step is sample_gather_fields(draw_counter) -> counter_add(counter, n) -> ... */
+int32_t b200rl_counter_add(uint64_t *counter, int64_t delta, void *stream);
 
 /* N3 -- prioritized sampling (replaces rlmeta PrioritizedSampler, reference agents/dqn/builder.py:83-90;
  * extend/sample/update at agents/dqn/learning.py:54,122,184).  `tree` is a caller-owned, zero-initialised

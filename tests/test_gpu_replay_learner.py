@@ -379,3 +379,53 @@ def test_sample_gather_in_one_launch_matches_two_launches(cuda, shapes):
     assert torch.equal(keys, want_idx) and torch.equal(batch[1].reshape(-1), want_idx)
     keys2, _, _ = rb.sample(16)
     assert torch.equal(keys2, ops.sample_uniform(7, 1, 16, 16, 40, cuda))
+
+
+@pytest.mark.parametrize("body,kw", [("impala", dict(channels_last=True, fused_glue=True)), ("impala", {})])
+def test_learner_step_as_one_cuda_graph_matches_eager_steps(cuda, body, kw):
+    """ImpalaLearner.capture_graph: the whole step (sample -> CNN -> K1 -> CNN bwd -> clip + Adam) replayed as ONE graph
+    launch follows the eager learner step for step: the sampler's draw count and Adam's step live in device memory, so
+    every replay draws new rollouts and uses the next bias correction."""
+    T, A, Bsz, steps = 20, 15, 8, 5
+
+    def make():
+        torch.manual_seed(0)
+        model = models.ActorCritic((3, 64, 64), A, body=body, **kw).to(cuda)
+        if kw.get("channels_last"):
+            model = model.to(memory_format=torch.channels_last)
+        rb = replay.ReplayBuffer(replay.CircularBuffer(32, device=cuda), replay.UniformSampler())
+        rb.sampler.reset(123)
+        _fill_impala_replay(rb, 32, T, A, seed=5)
+        # eps = 1e-2: with Adam's usual eps a gradient element at rounding-noise level still moves its parameter by +-lr
+        # (m / sqrt(v) = +-1), so two runs whose convolutions round differently (cuDNN picks its algorithm per stream and
+        # workspace) could not be compared elementwise; a large eps makes the update proportional to the gradient
+        opt = optim.FusedClipAdam(model.parameters(), lr=1e-3, eps=1e-2)
+        learner = ImpalaLearner(model, rb, opt, batch_size=Bsz, learning_starts=10)
+        learner.prepare()
+        return model, rb, opt, learner
+
+    model_e, rb_e, opt_e, eager = make()
+    want = []
+    for _ in range(steps):
+        m = eager.train_step()
+        want.append(({k: float(m[k]) for k in ("train/loss", "train/td", "train/grad_norm")}, opt_e.flat.clone()))
+    model_g, rb_g, opt_g, graphed = make()
+    graphed.capture_graph(warmup=2)                     # two real (eager) steps, then the capture (which executes nothing)
+    torch.cuda.synchronize()
+    assert_close(opt_g.flat, want[1][1], "parameters after the 2 warm-up steps", rtol=1e-4, atol=2e-5)
+    losses_seen = []
+    for k in range(2, steps):
+        m = graphed.train_step()                        # ONE graph launch
+        torch.cuda.synchronize()
+        losses_seen.append(float(m["train/loss"]))
+        # the first replay starts from (numerically) the same state as eager step 3: tight.  Later steps: two TF32 training
+        # runs drift apart step by step, so only their agreement to a few percent is meaningful; what the graph must get
+        # right -- a NEW batch and the NEXT Adam step on every replay -- is asserted directly below and, bit for bit, in
+        # tests/test_gpu_optim.py::test_device_resident_step_counter... and test_sample_gather_in_one_launch...
+        rel, atol = (2e-3, 2e-5) if k == 2 else (5e-2, 5e-4)
+        for name, v in want[k][0].items():
+            assert float(m[name]) == pytest.approx(v, rel=rel, abs=1e-6), (k, name)
+        assert_close(opt_g.flat, want[k][1], "parameters after step %d" % (k + 1), rtol=1e-3, atol=atol)
+    assert len(set(losses_seen)) == len(losses_seen), "every replay must draw a new batch"
+    assert opt_g.sync_step_count() == steps
+    assert int(rb_g.sampler.draw_counter.item()) == steps * Bsz == rb_e.sampler.draws
