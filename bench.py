@@ -285,6 +285,8 @@ def make_learner(args, device, seed):
     learner.prepare()
     last = {}
     use_graph = os.environ.get("B200RL_BENCH_LEARNER_GRAPH", "1") == "1"
+    if dist.is_initialized() and dist.get_world_size() > 1 and os.environ.get("B200RL_PEER_ALLREDUCE", "auto") == "0":
+        use_graph = False              # the NCCL-allreduce route is not captured (capture_graph says so); K8 is
     if use_graph:
         learner.capture_graph()        # the whole step = ONE graph launch (sample -> CNN -> K1 -> CNN bwd -> K6 / K8)
 
@@ -710,6 +712,8 @@ def k8_check(args, device, rank, world_size):
     from impala_b200 import parallel
     out = {}
     flats = {}
+    saved = os.environ.get("B200RL_BENCH_LEARNER_GRAPH")
+    os.environ["B200RL_BENCH_LEARNER_GRAPH"] = "0"      # both routes eagerly, step for step
     for route, env in (("k8_peer", "auto"), ("nccl", "0")):
         os.environ["B200RL_PEER_ALLREDUCE"] = env
         a = copy.copy(args)
@@ -732,6 +736,10 @@ def k8_check(args, device, rank, world_size):
         del w, learner
         torch.cuda.empty_cache()
     os.environ.pop("B200RL_PEER_ALLREDUCE", None)
+    if saved is None:
+        os.environ.pop("B200RL_BENCH_LEARNER_GRAPH", None)
+    else:
+        os.environ["B200RL_BENCH_LEARNER_GRAPH"] = saved
     d = (flats["k8_peer"] - flats["nccl"]).abs().max().item()
     out["max_abs_diff_vs_nccl_route"] = d
     out["max_rel_diff_vs_nccl_route"] = d / max(flats["nccl"].abs().max().item(), 1e-30)
