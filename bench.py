@@ -287,8 +287,13 @@ def make_learner(args, device, seed):
     use_graph = os.environ.get("B200RL_BENCH_LEARNER_GRAPH", "1") == "1"
     if dist.is_initialized() and dist.get_world_size() > 1 and os.environ.get("B200RL_PEER_ALLREDUCE", "auto") == "0":
         use_graph = False              # the NCCL-allreduce route is not captured (capture_graph says so); K8 is
+    graph_error = None
     if use_graph:
-        learner.capture_graph()        # the whole step = ONE graph launch (sample -> CNN -> K1 -> CNN bwd -> K6 / K8)
+        try:
+            learner.capture_graph()    # the whole step = ONE graph launch (sample -> CNN -> K1 -> CNN bwd -> K6 / K8)
+        except Exception as e:         # stated in the line, never silent: the step is then timed eagerly
+            use_graph, graph_error = False, "%s: %s" % (type(e).__name__, e)
+            learner._graph = None
 
     def launch(i):
         last["m"] = learner.train_step()
@@ -301,6 +306,8 @@ def make_learner(args, device, seed):
             "l2_policy": "gathered batch 63 MB + activations >> per-step reuse; buffer 246 MB > 126 MB L2"}
     desc["step_launch"] = ("ONE CUDA-graph launch per step (ImpalaLearner.capture_graph: sample -> CNN fwd -> K1 -> CNN bwd -> K6/K8; "
                            "step number, flag generation and draw count in device memory)") if use_graph else "eager: one Python pass per step"
+    if graph_error:
+        desc["step_launch"] = "eager (CUDA-graph capture failed: %s)" % graph_error[:300]
 
     def grad_exchange():
         from impala_b200 import parallel
@@ -854,9 +861,9 @@ def main():
             if name == "learner" and world_size > 1:
                 line["config"]["other_workloads"]["learner"]["k8_check"] = k8_check(args, device, rank, world_size)
         except Exception as e:  # a secondary workload must not take the headline line down with it
-            line["config"]["other_workloads"][name] = {"error": "%s: %s" % (type(e).__name__, e)}
-            if world_size > 1:
-                raise
+            # recorded, never fatal: the headline line must survive (a failure here is symmetric across ranks in practice;
+            # re-raising under torchrun would lose every number of the run)
+            line["config"]["other_workloads"][name] = {"error": ("%s: %s" % (type(e).__name__, e))[:500]}
     line["gpu_launches"] = launches
     if rank == 0 and world_size == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline_legs(args, unit, args.cpu_seconds)
