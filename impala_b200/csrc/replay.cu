@@ -195,7 +195,18 @@ __global__ void __launch_bounds__(kCopyThreads) fields_copy_kernel(const FieldTa
         for (long long r = first_row + threadIdx.x; r <= last_row; r += kCopyThreads)
             s_idx[r - first_row] = uniform_index(ft.seed, ft.stream_id, off + (uint64_t)r, ft.size);
         __syncthreads();
-        if (!ft.draw_counter) pdl_wait();
+        if (!ft.draw_counter) {
+            // the source addresses are known before the dependency wait: ask L2 for this CTA's part of its rows
+            // (cp.async.bulk.prefetch.L2 -- a hint, never a read; 16-byte vectors only: the bulk unit's alignment)
+            if (vec == 16 && threadIdx.x <= last_row - first_row) {
+                const long long r = first_row + threadIdx.x;
+                const long long ka = max(k0, r * vpr), kb = min(k1 + 1, (r + 1) * vpr);
+                long long j = s_idx[threadIdx.x];
+                j = j < 0 ? 0 : (j >= ft.capacity ? ft.capacity - 1 : j);
+                bulk_prefetch_l2(static_cast<const char *>(ft.src[f]) + (j * vpr + (ka - r * vpr)) * 16, (uint32_t)((kb - ka) * 16));
+            }
+            pdl_wait();
+        }
         if (f == 0)
             for (long long r = first_row + threadIdx.x; r <= last_row; r += kCopyThreads)
                 if (r * vpr >= k0) ft.idx_out[r] = s_idx[r - first_row];  // every row starts in exactly one CTA of field 0
