@@ -118,6 +118,17 @@ __global__ void __launch_bounds__(kSmemScanWarps * 32) scan_smem_kernel(const Sc
     // this one runs: it waits for this grid's completion before it reads anything (griddepcontrol.wait), but its prologue
     // and its L2 prefetch of the logits overlap this kernel.  A no-op for dependents launched without the attribute.
     pdl_launch_dependents();
+    // Launched with the PDL attribute itself (in the PPO pipeline it follows the previous step's loss kernel): before the
+    // dependency wait it may only HINT -- one L2 prefetch per 128-byte row segment of its three inputs -- then it waits.
+    for (int row = threadIdx.x; row < TV; row += kSmemScanWarps * 32) {
+        const long long col = b0 < p.B ? b0 : 0;
+        if (row < T) {
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p.r + (long long)row * p.st + col));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(p.disc + (long long)row * p.st + col));
+        }
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(p.v + (long long)row * p.vst + col));
+    }
+    pdl_wait();
     // ---- stage: chunk = (row, group of 4 columns); rows are st (vst) elements apart in HBM
     for (int ch = threadIdx.x; ch < TV * 8; ch += kSmemScanWarps * 32) {
         const int row = ch >> 3, c4 = (ch & 7) * 4;
@@ -200,12 +211,29 @@ static int32_t launch_scan(const ScanParams &p, cudaStream_t stream) {
             default: rc = ensure_dynamic_smem(scan_smem_kernel<MODE, 8>, smem, c8, "scan"); break;
         }
         if (rc) return rc;
-        const unsigned grid = (unsigned)((p.B + 31) / 32);
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)((p.B + 31) / 32));
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = stream;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;  // PDL: see pdl_wait() in the kernel
+        attr[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = attr;
+        // measured A/B on one box (T=256, K2 + K3 per step): early launch + prefetch is -2 % at 8,192 columns (75.2 -> 73.6 us)
+        // but +4 % at 1,024 / 2,048 (16.0 -> 16.6, 23.7 -> 24.3 us): only when the scan fills the machine (>= 1 CTA per SM)
+        const int k2_pdl = env_int("B200RL_K2_PDL", -1);
+        cfg.numAttrs = (env_int("B200RL_PDL", 1) && (k2_pdl == 1 || (k2_pdl < 0 && cfg.gridDim.x >= 148))) ? 1 : 0;
+        cudaError_t e;
         switch (nw) {
-            case 1: scan_smem_kernel<MODE, 1><<<grid, 32, smem, stream>>>(p); break;
-            case 2: scan_smem_kernel<MODE, 2><<<grid, 64, smem, stream>>>(p); break;
-            case 4: scan_smem_kernel<MODE, 4><<<grid, 128, smem, stream>>>(p); break;
-            default: scan_smem_kernel<MODE, 8><<<grid, 256, smem, stream>>>(p); break;
+            case 1: cfg.blockDim = dim3(32); e = cudaLaunchKernelEx(&cfg, scan_smem_kernel<MODE, 1>, p); break;
+            case 2: cfg.blockDim = dim3(64); e = cudaLaunchKernelEx(&cfg, scan_smem_kernel<MODE, 2>, p); break;
+            case 4: cfg.blockDim = dim3(128); e = cudaLaunchKernelEx(&cfg, scan_smem_kernel<MODE, 4>, p); break;
+            default: cfg.blockDim = dim3(256); e = cudaLaunchKernelEx(&cfg, scan_smem_kernel<MODE, 8>, p); break;
+        }
+        if (e != cudaSuccess) {
+            set_error("scan_smem_kernel launch: %s", cudaGetErrorString(e));
+            (void)cudaGetLastError();
+            return (int32_t)e;
         }
         return check_launch("scan_smem_kernel");
     }

@@ -1,5 +1,4 @@
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_replay_learner.py -m gpu -q -x -k "sample_gather or replay or ring or gather" > gpurun_out/pytest_gpu.log 2>&1; tail -2 gpurun_out/pytest_gpu.log
-for f in 1 0; do
-echo "replay fused=$f: $(B200RL_BENCH_REPLAY_FUSED=$f timeout 600 python bench.py --workload replay --steps 100 --warmup 3 --repeats 10 --no-cpu-baseline --no-e2e --others= 2>&1 | tail -1 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('ms/step %.5f frac %.3f' % (d['ms_per_step'], d['roofline']['frac']))")"
-done
+for rep in 1 2 3; do for pdl in 1 0; do for B in 1024 2048 8192; do
+echo "K2_PDL=$pdl B=$B: $(B200RL_K2_PDL=$pdl timeout 600 python bench.py --workload ppo --B $B --steps 50 --warmup 3 --repeats 10 --no-cpu-baseline --no-e2e --others= 2>&1 | tail -1 | python -c "import json,sys; d=json.loads(sys.stdin.read()); print('ms/step %.5f' % d['ms_per_step'])")"
+done; done; done
