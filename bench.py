@@ -817,8 +817,10 @@ def main():
         launches += e_steps * w["kernels"] * est["repeats"]
         line["e2e"] = {"value": w["units"] * e_steps * world_size / dt, "unit": unit, "h2d_bytes_per_step": h2d,
                        "d2h_bytes_per_step": d2h, "steps": e_steps, "timing": est,
+                       "h2d_gb_per_s_achieved": h2d * e_steps / dt / 1e9,
                        "note": "pinned host arena -> ONE H2D copy -> fused kernel -> D2H of the 8 loss/metric scalars, every step; "
-                               "wall clock, median of the repeats, max over ranks"}
+                               "wall clock, median of the repeats, max over ranks; PCIe-bound: the value is the box's pinned H2D rate "
+                               "(h2d_gb_per_s_achieved; 16 to 53 GB/s across the boxes of this pool) divided by 140 B/sample"}
     elif not args.no_e2e:
         line["e2e"] = None
     del w
