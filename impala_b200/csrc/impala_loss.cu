@@ -86,7 +86,8 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
     float *scratch = smem + (size_t)NSTAGE * 2 * chunk_words + (size_t)grp * 4 * ns4;
     uint64_t *bars = reinterpret_cast<uint64_t *>(smem + (size_t)NSTAGE * 2 * chunk_words + (size_t)G * 4 * ns4);
     int *done = reinterpret_cast<int *>(bars + NSTAGE);  // [NSTAGE] groups that finished the stage's chunk
-    float *red = reinterpret_cast<float *>(done + NSTAGE);  // [5][nwarps]
+    int *issued = done + NSTAGE;                         // [NSTAGE] highest round whose load has been issued into the stage
+    float *red = reinterpret_cast<float *>(issued + NSTAGE);  // [5][nwarps]
     int *ctl = reinterpret_cast<int *>(red + 5 * nwarps);   // [0] warps arrived at the reduction
 
     const bool trace = TRACE && i == 0 && (int)(blockIdx.x * G + grp) < kMaxTraceCtas;
@@ -96,7 +97,7 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
     if (trace) { unsigned int smid; asm volatile("mov.u32 %0, %%smid;" : "=r"(smid)); tr[7] = smid; }
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < NSTAGE; ++s) { mbar_init(bars + s, 1); done[s] = 0; }
+        for (int s = 0; s < NSTAGE; ++s) { mbar_init(bars + s, 1); done[s] = 0; issued[s] = 0; }
         ctl[0] = 0;
         fence_mbar_init();
     }
@@ -237,6 +238,13 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
         const int b0 = (ustart + j) * C, ucols = min(C, p.B - b0), nsu = ucols * T;
         const size_t n0 = (size_t)b0 * T;
 
+        // Ring rounds: a chunk is completed -- and its stage refilled -- by the GPC groups that own its units only, so a group
+        // can be TWO rounds ahead of the groups that still work on the stage's round-0 chunk.  A parity wait alone would then
+        // match the long-completed round 0 instead of round 2.  So: first wait until the load of THIS round has been issued
+        // (a shared-memory counter written after the issue), then the phase wait is unambiguous -- round r+1 cannot be issued
+        // before this group has finished its unit of round r.
+        if (round > 0)
+            while (*reinterpret_cast<volatile int *>(issued + st_i) < round) {}
         mbar_wait(bars + st_i, (uint32_t)round & 1u);  // the unit's chunk has landed
         if (first) K1_STAMP(1);
 
@@ -333,6 +341,8 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
                 if (c + NSTAGE < n_chunks) {  // refill the stage once the store has read it
                     bulk_wait_read0();
                     issue_chunk(c + NSTAGE);
+                    __threadfence_block();
+                    *reinterpret_cast<volatile int *>(issued + st_i) = round + 1;
                 }
             }
         }
@@ -471,7 +481,7 @@ static int32_t launch_k1(const ImpalaArgs &a, cudaStream_t stream) {
     p.debug = env_int("B200RL_K1_DEBUG", 0);
     p.prefetch = env_int("B200RL_K1_PREFETCH", 1);
     const int threads = G * W * 32;
-    const size_t smem = (size_t)NSTAGE * 2 * GPC * unit_bytes + (size_t)G * 4 * p.ns4 * 4 + (size_t)NSTAGE * 12 +
+    const size_t smem = (size_t)NSTAGE * 2 * GPC * unit_bytes + (size_t)G * 4 * p.ns4 * 4 + (size_t)NSTAGE * 16 +
                         5 * (size_t)(threads / 32) * 4 + 16 + 128;
     // the reference's shape class (T = 20 rollouts, procgen's 15 actions): compile-time T / W / C / GPC
     if constexpr (AT == 15 && EXACT) {

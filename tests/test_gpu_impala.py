@@ -251,3 +251,31 @@ def test_trace_flag_stamps_phases(cuda):
     assert (tr[:, 0] > 0).all()
     assert ((tr[:, 9:15] - tr[:, 8:14]) >= 0).all()                                # clock64 monotone per CTA
     ops.workspace(cuda)[off:off + 8 * 16 * 8].zero_()
+
+
+@pytest.mark.parametrize("B,T,A,stages", [(32768, 20, 15, None), (20000, 20, 6, None), (3000, 128, 15, None),
+                                            (4096, 20, 15, "2"), (1500, 20, 15, "3"), (65536, 20, 15, None)])
+def test_persistent_kernel_ring_refill_matches_tile_kernel(cuda, B, T, A, stages, monkeypatch):
+    """Large batches: a CTA of the persistent kernel owns more chunks than fit in shared memory, so stages are refilled
+    after their bulk store has drained (mbarrier phase flips, per-stage completion counts).  The tile kernel computes every
+    sample with the same code: gradients bit for bit, scalars to the tolerance (another summation order); plus the oracle
+    on a column sample through the sharding identity (columns are independent).  `stages` forces a short ring
+    (B200RL_K1_STAGES) so that small batches go through many rounds too.  Regression test for a round-aliasing bug: a group
+    two rounds ahead on a stage matched the parity of the long-completed round 0 (fixed by the per-stage `issued` counter)."""
+    if stages:
+        monkeypatch.setenv("B200RL_K1_STAGES", stages)
+    g = to_cuda(synth.impala_rollout(B, T, A, seed=B + T))
+    outs = {}
+    for impl in ("1", "2"):
+        monkeypatch.setenv("B200RL_K1_TILE", impl)
+        outs[impl] = [x.clone() for x in ops.impala_loss_fwdbwd(g["logits"], g["values"], g["a"], g["r"], g["discount"], g["pi_ref"])]
+        torch.cuda.synchronize()
+    assert torch.equal(outs["1"][1], outs["2"][1]) and torch.equal(outs["1"][2], outs["2"][2])
+    torch.testing.assert_close(outs["1"][0][:6], outs["2"][0][:6], rtol=1e-5, atol=1e-6)
+    # the oracle on the first and last 64 columns (n_global_b = B keeps the scaling of the full launch)
+    for sl in (slice(0, 64), slice(B - 64, B)):
+        d = {k: v[sl].cpu() for k, v in g.items()}
+        _, _, dl_ref, dv_ref = oracle_impala(d)
+        scale = 64.0 / B
+        assert_close(outs["2"][1][sl], dl_ref * scale, "dlogits (column sample)", rel_to_max=2e-6)
+        assert_close(outs["2"][2][sl], dv_ref * scale, "dvalues (column sample)", rel_to_max=2e-6)
