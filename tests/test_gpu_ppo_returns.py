@@ -360,3 +360,17 @@ def test_ppo_is_full_size_properties():
         assert_close(a[0][slot], m[k], k, rtol=1e-5, atol=1e-6)
     assert_close(a[1], dl_ref, "dlogits", rel_to_max=2e-6)
     assert_close(a[2], dv_ref, "dv", rel_to_max=2e-6)
+
+
+@pytest.mark.parametrize("N,A", [(200_004, 15), (151_556, 6), (1_000_000, 15), (262_144 + 252, 18)])
+def test_ppo_streaming_kernel_matches_tile_kernel_on_ragged_large_minibatches(cuda, N, A, monkeypatch):
+    """The persistent ring kernel (B200RL_K3_STREAM=2) against the tile kernel (=1) where the minibatch does not end on a
+    256-sample chunk: gradients bit for bit (same per-sample code), scalars to the tolerance (another summation order)."""
+    d = to_cuda(synth.ppo_minibatch(N, A, seed=N % 1000))
+    outs = {}
+    for impl in ("1", "2"):
+        monkeypatch.setenv("B200RL_K3_STREAM", impl)
+        outs[impl] = [x.clone() for x in ops.ppo_loss_fwdbwd(d["logits"], d["v"].reshape(-1), d["a"], d["v_target"], d["pi_ref"])]
+        torch.cuda.synchronize()
+    assert torch.equal(outs["1"][1], outs["2"][1]) and torch.equal(outs["1"][2], outs["2"][2])
+    torch.testing.assert_close(outs["1"][0][:7], outs["2"][0][:7], rtol=1e-5, atol=1e-6)
