@@ -7,7 +7,7 @@ c = d["config"]
 print("headline %s: %.3e %s, %.3f us/step, roofline frac %.3f (streams %s, pipeline %s)" % (
     c.get("workload", "?")[:40], d["value"], d["unit"], d["ms_per_step"] * 1e3, (d.get("roofline") or {}).get("frac", float("nan")),
     c.get("streams"), c.get("pipeline")))
-for k in ("serial_single_stream", "overlapped_6_streams"):
+for k in sorted(k for k in c if k == "serial_single_stream" or (k.startswith("overlapped_") and k.endswith("_streams"))):
     if k in c:
         print("  %s: %.3f us/step, frac %.3f" % (k, c[k]["ms_per_step"] * 1e3, c[k]["frac"]))
 if d.get("e2e"):

@@ -1,2 +1,5 @@
 mkdir -p gpurun_out
-timeout 300 python -m pytest tests/test_gpu_ppo_returns.py -m gpu -q -x -k "ragged_large" -o faulthandler_timeout=90 > gpurun_out/pytest_gpu.log 2>&1; tail -2 gpurun_out/pytest_gpu.log; grep -n "^E " gpurun_out/pytest_gpu.log | head -5
+for i in 1 2 3; do timeout 250 python -m pytest tests -m gpu -q -x -o faulthandler_timeout=120 -p no:cacheprovider 2>&1 | tail -1; done
+for shape in "4096 20 15" "256 20 15" "8192 20 6" "1366 20 15" "100 64 18"; do
+  echo "stress $shape: $(timeout 120 python scripts/k1_stress.py $shape 60 2>&1 | awk '/grads equal/{n++; if ($5=="True") t++} /FAIL/{print} END{print t"/"n" iterations bit-equal"}')"
+done
