@@ -243,7 +243,8 @@ __device__ __forceinline__ void st_volatile_u32(unsigned int *p, unsigned int v)
 // partial as one 64-bit word (launch tag << 32 | float bits) with a single store: the tag travels with
 // the data, so no fence is needed and the CTA retires immediately.  The tag is the workspace's launch
 // generation + 1 (never 0): words are never cleared, a word of an older launch can not be mistaken for
-// this launch's.  One collector CTA (the highest blockIdx: normally dispatched last, so it rarely waits)
+// this launch's (the 31-bit tag wraps after 2^31 launches on one workspace: a stale word could alias only if
+// its CTA index had gone unused for exactly that many launches and the grid then grew back).  One collector CTA (the highest blockIdx: normally dispatched last, so it rarely waits)
 // polls the words until every one carries this launch's tag, sums them in a fixed order --
 // deterministic, bit-reproducible scalars -- hands the totals to `finalize(sums)` (one thread) and
 // bumps the generation.

@@ -347,7 +347,16 @@ int32_t launch_impala_tile(const ImpalaArgs &a, cudaStream_t s) {
     auto smem_for = [&](int c) { return (size_t)c * T * (2 * A + 4) * 4 + 5 * (size_t)threads_for(c) * 4 + 16 + 256; };
     while (C > 1 && smem_for(C) > 200 * 1024) C = (C > 4) ? ((C / 2) & ~3) : C - 1;
     B200RL_REQUIRE(smem_for(C) <= 226 * 1024, -3, "impala_loss: T*A too large for one CTA tile");
-    B200RL_REQUIRE((B + C - 1) / C <= kMaxPartialCtas, -3, "impala_loss: B too large for the partials workspace");
+    if ((B + C - 1) / C > kMaxPartialCtas) {
+        // very wide batches of long rollouts: the grid may not exceed the partials the workspace holds, so a CTA takes
+        // more columns than the tuned tile (found by tests/test_gpu_fuzz.py: T=128 used to stop at B=16384)
+        int need = (int)((B + kMaxPartialCtas - 1) / kMaxPartialCtas);
+        if (need >= 4 && time_major && !batch_major) need = (need + 3) & ~3;
+        B200RL_REQUIRE((long long)need * T <= max_threads && smem_for(need) <= 226 * 1024, -3,
+                       "impala_loss: B=%lld columns of T=%lld need %d columns per CTA to fit the %d partial sums of the workspace, "
+                       "which one CTA cannot hold -- split the batch", (long long)B, (long long)T, need, kMaxPartialCtas);
+        C = need;
+    }
     p.C = C;
     {   // alignment of the bulk copies: row start, row size, row strides (time-major), base pointers
         const bool tm = p.time_major != 0;

@@ -229,7 +229,13 @@ extern "C" int32_t b200rl_ppo_is_loss_fwdbwd(
     auto smem_for = [&](int c) { return (size_t)c * T * (2 * A + 3) * 4 + 5 * (size_t)threads_for(c) * 4 + 16; };
     while (C > 1 && smem_for(C) > 200 * 1024) --C;
     B200RL_REQUIRE(smem_for(C) <= 226 * 1024, -3, "ppo_is_loss: T*A too large for one CTA tile");
-    B200RL_REQUIRE((B + C - 1) / C <= kMaxPartialCtas, -3, "ppo_is_loss: B too large for the partials workspace");
+    if ((B + C - 1) / C > kMaxPartialCtas) {  // wide batches of long rollouts: wider CTA tiles so the grid fits the workspace's partial sums
+        const int need = (int)((B + kMaxPartialCtas - 1) / kMaxPartialCtas);
+        B200RL_REQUIRE((long long)need * T <= max_threads && smem_for(need) <= 226 * 1024, -3,
+                       "ppo_is_loss: B=%lld columns of T=%lld need %d columns per CTA to fit the %d partial sums of the workspace, "
+                       "which one CTA cannot hold -- split the batch", (long long)B, (long long)T, need, kMaxPartialCtas);
+        C = need;
+    }
     p.C = C;
     const bool ptrs = ((reinterpret_cast<uintptr_t>(logits) | reinterpret_cast<uintptr_t>(pi_ref) |
                         reinterpret_cast<uintptr_t>(dlogits)) % 16) == 0;

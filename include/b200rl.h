@@ -78,7 +78,10 @@ int64_t b200rl_trace_offset_bytes(void);
  * the GLOBAL batch (== B unless sharded along B across ranks): means are taken
  * over n_global_b*(T-1) resp. n_global_b*T, so per-rank scalars and gradients sum
  * to the single-GPU result.  Outputs: dlogits [B,T,A], dvalues [B,T] =
- * d loss / d logits, d loss / d values; scalars[8] (B200RL_S_*). */
+ * d loss / d logits, d loss / d values; scalars[8] (B200RL_S_*).
+ * Limits (status -3 and a message, nothing launched): A <= 32; T <= 640 (256 when A > 16); and, for the tile kernel
+ * (time-major inputs, B200RL_INPUTS_STABLE), B <= 16384 * floor(640 / T) columns per call (256 / T when A > 16) -- a CTA
+ * holds one thread per sample and the workspace one partial sum per CTA for 16384 CTAs. */
 int32_t b200rl_vtrace_impala_loss_fwdbwd(
     const float *logits, const float *pi_ref, const int64_t *actions, const float *rewards,
     const float *discounts, const float *values,

@@ -254,7 +254,9 @@ def test_trace_flag_stamps_phases(cuda):
 
 
 @pytest.mark.parametrize("B,T,A,stages", [(32768, 20, 15, None), (20000, 20, 6, None), (3000, 128, 15, None),
-                                            (4096, 20, 15, "2"), (1500, 20, 15, "3"), (65536, 20, 15, None)])
+                                            (4096, 20, 15, "2"), (1500, 20, 15, "3"), (65536, 20, 15, None),
+                                            # beyond 16384 CTAs of the tuned tile: the tile kernel widens its tiles (fuzz find)
+                                            (20421, 128, 15, None), (42594, 64, 6, None), (17000, 128, 18, None)])
 def test_persistent_kernel_ring_refill_matches_tile_kernel(cuda, B, T, A, stages, monkeypatch):
     """Large batches: a CTA of the persistent kernel owns more chunks than fit in shared memory, so stages are refilled
     after their bulk store has drained (mbarrier phase flips, per-stage completion counts).  The tile kernel computes every

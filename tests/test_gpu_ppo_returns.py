@@ -274,6 +274,23 @@ def oracle_ppo_is(d, **kw):
     return m, lg.grad, v.grad
 
 
+def test_ppo_is_wide_batch_of_long_rollouts_widens_its_tiles(cuda):
+    """B / (columns per tuned CTA tile) > 16384 partial sums of the workspace: the launch takes wider tiles instead of
+    refusing.  Columns are independent, so a launch on a column slice (tuned tiles) must give the same gradients."""
+    B, T, A = 40000, 128, 6
+    d = to_cuda(synth.ppo_is_rollout(B, T, A, seed=9))
+    args = lambda sl: (d["logits"][sl], d["values"][sl], d["v_boot"][sl], d["a"][sl], d["r"][sl], d["done"][sl], d["pi_ref"][sl])
+    full = [x.clone() for x in ops.ppo_is_loss_fwdbwd(*args(slice(0, B)))]
+    for sl in (slice(0, 96), slice(B - 96, B), slice(20000, 20096)):
+        part = ops.ppo_is_loss_fwdbwd(*[x.contiguous() for x in args(sl)], n_global_b=B)
+        torch.cuda.synchronize()
+        assert torch.equal(full[1][sl], part[1]) and torch.equal(full[2][sl], part[2])
+    assert torch.isfinite(full[0][:7]).all()
+    with pytest.raises(RuntimeError, match="split the batch"):
+        ops.ppo_is_loss_fwdbwd(*[x[:, :1].expand(-1, 600, *x.shape[2:]).contiguous() if x.dim() > 1 else x
+                                 for x in args(slice(0, 20000))])
+
+
 @pytest.mark.parametrize("B,T,A", [(12, 20, 15), (1, 1, 1), (7, 1, 6), (33, 20, 15), (5, 33, 8), (9, 64, 17), (3, 256, 4),
                                    (300, 20, 32), (64, 7, 18)])
 @pytest.mark.parametrize("kw", [{}, dict(entropy_cost=0., clip_coeff=.3, lambda_=1., gamma=.9)])
