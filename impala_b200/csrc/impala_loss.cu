@@ -300,7 +300,9 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
                 if (t < T - 2) {
                     const float e1 = s_e[i + 1];
                     const float tgt1 = ((e1 + u_vn) - u_vn) + u_vn;
-                    qb = p.lambda_ * tgt1 + p.one_minus_lambda * u_vn;
+                    // two rounded products and a rounded sum, as the reference's tensor expression evaluates it: never contracted
+                    // into an FMA (which of the two products the compiler fuses differed between kernels -- tests/test_gpu_fuzz.py)
+                    qb = __fadd_rn(__fmul_rn(p.lambda_, tgt1), __fmul_rn(p.one_minus_lambda, u_vn));
                 }
                 const float q = u_rew + u_disc * qb;
                 const float qmv = q - u_v;
@@ -310,8 +312,8 @@ __global__ void __launch_bounds__(k1_max_threads<AT>(), 1) impala_loss_kernel(co
                 float dpg_dlp = adv;  // d(lp*adv)/dlp, adv's own dependence on lp via rho below
                 if (!detach_adv && !detach_rho && st.rho <= p.clip_pg_rho) dpg_dlp += st.lp * st.rho * qmv;
                 g_lp = -dpg_dlp * p.inv_n_pg;
-                dv = -2.f * err * p.inv_n_pg;
-                if (!detach_adv) dv += st.lp * c_pg * p.inv_n_pg;
+                dv = __fmul_rn(-2.f * err, p.inv_n_pg);  // explicit roundings: both K1 kernels give the same bits
+                if (!detach_adv) dv = __fmaf_rn(st.lp * c_pg, p.inv_n_pg, dv);
             }
             if (t > 0) dv += s_nx[i - 1];
             sums[2] += st.H;

@@ -200,7 +200,9 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_tile_kernel
             if (t < T - 2) {
                 const float e1 = e_t1;
                 const float tgt1 = ((e1 + v_next) - v_next) + v_next;
-                qb = p.lambda_ * tgt1 + p.one_minus_lambda * v_next;
+                // two rounded products and a rounded sum, as the reference's tensor expression evaluates it: never contracted
+                // into an FMA (which of the two products the compiler fuses differed between kernels -- tests/test_gpu_fuzz.py)
+                qb = __fadd_rn(__fmul_rn(p.lambda_, tgt1), __fmul_rn(p.one_minus_lambda, v_next));
             }
             const float q = rew + disc * qb;
             const float qmv = q - v;
@@ -210,8 +212,8 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) impala_loss_tile_kernel
             float dpg_dlp = adv;  // d(lp*adv)/dlp, adv's own dependence on lp via rho below
             if (!detach_adv && !detach_rho && st.rho <= p.clip_pg_rho) dpg_dlp += st.lp * st.rho * qmv;
             g_lp = -dpg_dlp * p.inv_n_pg;
-            dv = -2.f * err * p.inv_n_pg;
-            if (!detach_adv) dv += st.lp * c_pg * p.inv_n_pg;
+            dv = __fmul_rn(-2.f * err, p.inv_n_pg);  // explicit roundings: both K1 kernels give the same bits
+            if (!detach_adv) dv = __fmaf_rn(st.lp * c_pg, p.inv_n_pg, dv);
         }
         if (t > 0) dv += s_nx[s - st_local];
         p.dvalues[n] = dv;

@@ -117,7 +117,9 @@ __global__ void __launch_bounds__(AT <= 16 ? 1024 : 256) ppo_is_loss_kernel(cons
         float qb = v_next;
         if (!last) {
             const float tgt1 = ((s_e[s + 1] + v_next) - v_next) + v_next;
-            qb = p.lambda_ * tgt1 + p.one_minus_lambda * v_next;
+            // two rounded products and a rounded sum, as the reference's tensor expression evaluates it: never contracted
+            // into an FMA (which of the two products the compiler fuses differed between kernels -- tests/test_gpu_fuzz.py)
+            qb = __fadd_rn(__fmul_rn(p.lambda_, tgt1), __fmul_rn(p.one_minus_lambda, v_next));
         }
         const float q = rew + disc * qb;
         const float adv = (fminf(st.rho, p.clip_pg_rho) * (q - v)) * mask;  // (adv * mask).detach(), :75

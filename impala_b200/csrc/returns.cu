@@ -387,7 +387,9 @@ extern "C" int32_t b200rl_gae(const float *r_t, const float *discount_t, const f
     if (int32_t rc = check_scan_layout("gae", B, T, stride_b, stride_t)) return rc;
     B200RL_REQUIRE((vstride_t == 1 && vstride_b >= T + 1) || (vstride_b == 1 && vstride_t >= B), -4,
                    "gae: value strides (%lld,%lld) unsupported", (long long)vstride_b, (long long)vstride_t);
-    B200RL_REQUIRE((stride_b == 1) == (vstride_b == 1), -4, "gae: values and rewards must share the major order");
+    // with one step or one column a [B,T] view is both batch- and time-major (strides (1,1)): nothing to compare then
+    B200RL_REQUIRE((stride_b == 1) == (vstride_b == 1) || T == 1 || B == 1, -4,
+                   "gae: values and rewards must share the major order");
     ScanParams p{r_t, discount_t, values, out, (int)B, (int)T, stride_b, stride_t, vstride_b, vstride_t, (float)lambda_,
                  (float)(1.0 - lambda_)};
     return launch_scan<MODE_GAE>(p, (cudaStream_t)stream);

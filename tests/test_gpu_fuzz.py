@@ -102,3 +102,104 @@ def test_fused_sample_gather_random_cases_equal_two_launches(cuda, cap, size, dr
     assert int(idx.max()) < size and int(idx.min()) >= 0
     for a, b in zip(got, want):
         assert torch.equal(a, b)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# single-implementation kernels against the oracle at drawn shapes (the comparators of the hand-picked tests)
+def _scan_cases(n, seed):
+    rng = random.Random(seed)
+    out = []
+    for _ in range(n):
+        T = rng.choice([1, 2, 3, 31, 32, 33, 64, 127, 128, 256, 257, 511, 700]) if rng.random() < 0.6 else rng.randint(1, 700)
+        B = rng.randint(1, 4096) if rng.random() < 0.7 else rng.randint(1, 40)
+        out.append((B, T, rng.choice([0.0, 0.5, 0.95, 1.0]), rng.random() < 0.5))
+    return out
+
+
+@pytest.mark.parametrize("B,T,lam,time_major", _scan_cases(24 * _MORE, seed=5))
+def test_k2_random_shapes_against_the_oracle(cuda, B, T, lam, time_major):
+    from impala_b200 import vtrace
+    from oracle import rlego_ref
+    x = synth.returns_rollout(B, T + 1, seed=B * 7 + T)
+    r, d, v = x["r"][:, :T], x["discount"][:, :T], x["v"]
+    want_lr = rlego_ref.batched(rlego_ref.lambda_returns, lambda_=lam)(r, d, v[:, 1:])
+    want_gae = rlego_ref.batched(lambda a, b, c: rlego_ref.truncated_generalized_advantage_estimation(a, b, lam, c))(r, d, v)
+    if time_major:
+        rg, dg, vg = (t.t().contiguous().cuda() for t in (r, d, v))
+        got_lr = vtrace.lambda_returns(rg, dg, vg[1:], lam, time_major=True).t()
+        got_gae = vtrace.truncated_generalized_advantage_estimation(rg, dg, lam, vg, time_major=True).t()
+    else:
+        rg, dg, vg = r.cuda(), d.cuda(), v.cuda()
+        got_lr = vtrace.lambda_returns(rg, dg, vg[:, 1:], lam)
+        got_gae = vtrace.truncated_generalized_advantage_estimation(rg, dg, lam, vg)
+    for name, got, want in (("lambda_returns", got_lr, want_lr), ("gae", got_gae, want_gae)):
+        M = max(1.0, want.abs().max().item())   # fp32 recursion: rounding error ~ eps * magnitude (test_scans_parity)
+        assert_close(got, want, name, rtol=1e-5, atol=1e-6 * M, rel_to_max=2e-6)
+    if not time_major:
+        assert torch.equal(got_lr.cpu(), want_lr) and torch.equal(got_gae.cpu(), want_gae)
+
+
+def _nstep_cases(n, seed):
+    rng = random.Random(seed)
+    out = []
+    for _ in range(n):
+        T = rng.randint(1, 300)
+        out.append((rng.randint(1, 300), T, rng.randint(1, min(T + 1, 12)), rng.choice([1.0, 0.9, 0.0]), rng.random() < 0.5))
+    return out
+
+
+@pytest.mark.parametrize("B,T,n,lam,time_major", _nstep_cases(16 * _MORE, seed=6))
+def test_n4_random_shapes_bit_exact(cuda, B, T, n, lam, time_major):
+    from impala_b200 import vtrace
+    from oracle import rlego_ref
+    d = synth.returns_rollout(B, T, seed=B * 100 + T + n)
+    want = rlego_ref.batched_loop(rlego_ref.n_step_bootstrapped_returns, d["r"], d["discount"], d["v"], n=n, lambda_t=lam)
+    g = {k: v.cuda() for k, v in d.items()}
+    if time_major:
+        got = vtrace.n_step_bootstrapped_returns(g["r"].t().contiguous(), g["discount"].t().contiguous(),
+                                                 g["v"].t().contiguous(), n, lam, time_major=True).t()
+    else:
+        got = vtrace.n_step_bootstrapped_returns(g["r"], g["discount"], g["v"], n, lam)
+    assert torch.equal(got.cpu(), want)
+
+
+def _k1_layout_cases(n, seed):
+    rng = random.Random(seed)
+    return [(rng.randint(1, 6000), rng.choice([2, 5, 20, 20, 33, 64]), rng.choice([1, 4, 6, 15, 18, 32]),
+             rng.choice([0.0, 0.9, 1.0])) for _ in range(n)]
+
+
+@pytest.mark.parametrize("B,T,A,lam", _k1_layout_cases(16 * _MORE, seed=7))
+def test_k1_random_shapes_time_major_and_stable_flag_equal_batch_major(cuda, B, T, A, lam):
+    """[T,B,...] storage (the reference learner's layout before its transpose) and the B200RL_INPUTS_STABLE contract run
+    other load paths of the same per-sample code: gradients bit for bit."""
+    g = to_cuda(synth.impala_rollout(B, T, A, seed=B + 13 * T))
+    base = [x.clone() for x in ops.impala_loss_fwdbwd(g["logits"], g["values"], g["a"], g["r"], g["discount"], g["pi_ref"],
+                                                      lambda_=lam)]
+    stable = ops.impala_loss_fwdbwd(g["logits"], g["values"], g["a"], g["r"], g["discount"], g["pi_ref"], lambda_=lam,
+                                    flags=ops.INPUTS_STABLE)
+    torch.cuda.synchronize()
+    assert torch.equal(base[1], stable[1]) and torch.equal(base[2], stable[2])
+    tm = {k: v.transpose(0, 1).contiguous() for k, v in g.items()}                      # [T,B,...] storage
+    got = ops.impala_loss_fwdbwd(tm["logits"], tm["values"], tm["a"], tm["r"], tm["discount"], tm["pi_ref"], lambda_=lam,
+                                 time_major=True)
+    torch.cuda.synchronize()
+    assert torch.equal(base[1], got[1].transpose(0, 1)) and torch.equal(base[2], got[2].transpose(0, 1))
+    torch.testing.assert_close(base[0][:6], got[0][:6], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("n", [random.Random(8).randint(1, 3_000_000) for _ in range(6 * _MORE)])
+def test_k6_random_sizes_match_torch(cuda, n):
+    g = torch.Generator(device=cuda).manual_seed(n)
+    p0, g0 = torch.randn(n, generator=g, device=cuda), torch.randn(n, generator=g, device=cuda) * 0.01
+    ref = torch.nn.Parameter(p0.clone())
+    opt = torch.optim.Adam([ref], lr=1e-4, eps=1e-5)
+    p, m, v = p0.clone(), torch.zeros_like(p0), torch.zeros_like(p0)
+    for k in range(2):
+        ref.grad = g0 * (k + 1)
+        want_norm = torch.nn.utils.clip_grad_norm_([ref], 0.05)
+        opt.step()
+        norm = ops.clip_adam_step(p, g0 * (k + 1), m, v, k + 1, 1e-4, 0.9, 0.999, 1e-5, 0.05)
+        assert_close(norm[0], want_norm, "norm", rtol=1e-5, atol=0)
+    assert_close(p, ref.detach(), "params", rtol=1e-6, atol=1e-7)
+    assert_close(m, opt.state[ref]["exp_avg"], "exp_avg", rtol=2e-5, atol=1e-8)
