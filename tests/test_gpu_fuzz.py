@@ -203,3 +203,70 @@ def test_k6_random_sizes_match_torch(cuda, n):
         assert_close(norm[0], want_norm, "norm", rtol=1e-5, atol=0)
     assert_close(p, ref.detach(), "params", rtol=1e-6, atol=1e-7)
     assert_close(m, opt.state[ref]["exp_avg"], "exp_avg", rtol=2e-5, atol=1e-8)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# pointers that are only 4-byte aligned (views one element into an allocation): the bulk-copy / float4 paths must
+# step aside for the scalar ones and give the same bits
+def _off1(x):
+    """Same values in storage that starts one element (4 or 8 bytes) into a fresh allocation."""
+    buf = torch.empty(x.numel() + 1, dtype=x.dtype, device=x.device)
+    v = buf[1:].view(x.shape)
+    v.copy_(x)
+    return v
+
+
+def _misaligned_k1(n, seed):
+    rng = random.Random(seed)
+    return [(rng.randint(1, 3000), rng.choice([2, 7, 20, 20, 33]), rng.choice([1, 3, 6, 15, 18]), rng.random() < 0.5)
+            for _ in range(n)]
+
+
+@pytest.mark.parametrize("B,T,A,time_major", _misaligned_k1(12 * _MORE, seed=9))
+def test_k1_misaligned_pointers_equal_aligned(cuda, B, T, A, time_major):
+    g = to_cuda(synth.impala_rollout(B, T, A, seed=3 * B + T))
+    if time_major:
+        g = {k: v.transpose(0, 1).contiguous() for k, v in g.items()}
+    order = ("logits", "values", "a", "r", "discount", "pi_ref")
+    want = [x.clone() for x in ops.impala_loss_fwdbwd(*[g[k] for k in order], time_major=time_major)]
+    out = (torch.empty(8, device=cuda), _off1(torch.empty_like(g["logits"])), _off1(torch.empty_like(g["values"])))
+    got = ops.impala_loss_fwdbwd(*[_off1(g[k]) for k in order], time_major=time_major, out=out)
+    torch.cuda.synchronize()
+    assert torch.equal(want[1], got[1]) and torch.equal(want[2], got[2])
+    torch.testing.assert_close(want[0][:6], got[0][:6], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("N,A", [(random.Random(10 + i).randint(1, 400_000), random.Random(20 + i).choice([1, 3, 6, 15, 18]))
+                                 for i in range(8 * _MORE)])
+def test_k3_misaligned_pointers_equal_aligned(cuda, N, A):
+    d = to_cuda(synth.ppo_minibatch(N, A, seed=N % 977))
+    args = (d["logits"], d["v"].reshape(-1), d["a"], d["v_target"], d["pi_ref"])
+    want = [x.clone() for x in ops.ppo_loss_fwdbwd(*args)]
+    got = ops.ppo_loss_fwdbwd(*[_off1(x) for x in args])
+    torch.cuda.synchronize()
+    assert torch.equal(want[1], got[1]) and torch.equal(want[2], got[2])
+    torch.testing.assert_close(want[0][:7], got[0][:7], rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("B,T,time_major", [(random.Random(30 + i).randint(1, 3000), random.Random(40 + i).choice([1, 5, 32, 64, 256, 300]),
+                                             i % 2 == 0) for i in range(8 * _MORE)])
+def test_k2_misaligned_pointers_equal_aligned(cuda, B, T, time_major):
+    from impala_b200 import vtrace
+    x = synth.returns_rollout(B, T + 1, seed=B + T)
+    r, d, v = (t.cuda() for t in (x["r"][:, :T].contiguous(), x["discount"][:, :T].contiguous(), x["v"]))
+    if time_major:
+        r, d, v = (t.t().contiguous() for t in (r, d, v))
+        f = lambda r, d, v: (vtrace.lambda_returns(r, d, v[1:], 0.95, time_major=True),
+                             vtrace.truncated_generalized_advantage_estimation(r, d, 0.95, v, time_major=True))
+    else:
+        f = lambda r, d, v: (vtrace.lambda_returns(r, d, v[:, 1:], 0.95),
+                             vtrace.truncated_generalized_advantage_estimation(r, d, 0.95, v))
+    want = [y.clone() for y in f(r, d, v)]
+    got = f(_off1(r), _off1(d), _off1(v))
+    torch.cuda.synchronize()
+    for a, b in zip(want, got):
+        if time_major:   # the staged (16-byte aligned) and the chunked scan compose the steps in another order
+            M = max(1.0, a.abs().max().item())
+            assert_close(b, a, "scan", rtol=1e-5, atol=1e-6 * M, rel_to_max=2e-6)
+        else:
+            assert torch.equal(a, b)
