@@ -87,6 +87,10 @@ template <int AT, bool EXACT>
 __device__ __forceinline__ void write_dlogits(const SampleStats<AT> &st, float *srow, int A_rt,
                                               float g_lp, float c_ent) {
     const int A = EXACT ? AT : A_rt;
+    if (!EXACT && A == 1) {  // one action: p = 1, every term cancels; exactly 0 instead of the factored form's rounding residue
+        srow[0] = 0.f;
+        return;
+    }
     const float c1 = c_ent * st.inv_se;
     const float k1 = -fmaf(c_ent, st.dbar, g_lp) * st.inv_se;
 #pragma unroll

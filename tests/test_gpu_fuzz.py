@@ -270,3 +270,76 @@ def test_k2_misaligned_pointers_equal_aligned(cuda, B, T, time_major):
             assert_close(b, a, "scan", rtol=1e-5, atol=1e-6 * M, rel_to_max=2e-6)
         else:
             assert torch.equal(a, b)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# the rows beyond K1-K5 at drawn shapes
+@pytest.mark.parametrize("cap,seed", [(random.Random(50 + i).choice([1, 2, 3, 17, 255, 256, 257, 1023, 4097, 70_001, 300_000]), i)
+                                      for i in range(6 * _MORE)])
+def test_sumtree_random_update_sequences_bit_exact(cuda, cap, seed):
+    import numpy as np
+    from oracle import replay_ref
+    rng = np.random.default_rng(seed)
+    ot = replay_ref.SumTree(cap)
+    tree = torch.zeros(2 * ot.leaves, dtype=torch.float64, device=cuda)
+    for _ in range(5):
+        n = int(rng.integers(1, min(cap, 20_000) + 1))
+        idx = rng.choice(cap, size=n, replace=False).astype(np.int64)
+        val = rng.random(n) ** 3 + 1e-3
+        if rng.random() < 0.3:
+            val[: n // 3] = 0.0                                   # zero-priority leaves are never drawn
+        ot.update(idx, val)
+        ops.sumtree_update(tree, torch.from_numpy(idx).to(cuda), torch.from_numpy(val).to(cuda))
+        assert np.array_equal(tree.cpu().numpy(), ot.tree)
+        if ot.tree[1] > 0:
+            off, draws = int(rng.integers(0, 2 ** 40)), int(rng.integers(1, 5000))
+            want_idx, want_p = ot.sample(77, 1, off, draws, cap)
+            got_idx, got_p = ops.sumtree_sample(tree, cap, 77, 1, off, draws)
+            assert np.array_equal(got_idx.cpu().numpy(), want_idx) and np.array_equal(got_p.cpu().numpy(), want_p)
+
+
+def _k9_cases(n, seed):
+    rng = random.Random(seed)
+    return [(rng.randint(1, 400), rng.choice([1, 2, 7, 20, 33, 128]), rng.choice([1, 4, 6, 15, 18, 32]),
+             rng.choice([0.0, 0.9, 0.95, 1.0]), rng.choice([0.9, 0.99])) for _ in range(n)]
+
+
+@pytest.mark.parametrize("B,T,A,lam,gamma", _k9_cases(10 * _MORE, seed=11))
+def test_k9_random_shapes_against_the_oracle(cuda, B, T, A, lam, gamma):
+    """As test_ppo_is_parity, minus the samples whose probability ratio sits within 1e-5 of a clip boundary (0.9, 1, 1.1):
+    the gradient is discontinuous there and a last-bit difference of the ratio legitimately picks the other branch
+    (one such sample in ~2.4 M drawn ones is what this test met before the mask)."""
+    from oracle import losses_ref
+    from impala_b200 import losses
+    d = synth.ppo_is_rollout(B, T, A, seed=B * 3 + T)
+    kw = dict(lambda_=lam, gamma=gamma)
+    lg0, v0 = d["logits"].clone().requires_grad_(True), d["values"].clone().requires_grad_(True)
+    loss0, m0 = losses_ref.ppo_is_loss_from_outputs(lg0, v0, d["v_boot"], d["a"], d["r"], d["done"], d["pi_ref"], **kw)
+    loss0.backward()
+    g = to_cuda(d)
+    lg, v = g["logits"].requires_grad_(True), g["values"].requires_grad_(True)
+    loss, m = losses.ppo_is_loss_from_outputs(lg, v, g["v_boot"], g["a"], g["r"], g["done"], g["pi_ref"], **kw)
+    loss.backward()
+    for k in m0:
+        assert_close(m[k], m0[k], k, rtol=1e-5, atol=1e-6)
+    lp = torch.log_softmax(d["logits"].double(), -1).gather(-1, d["a"].unsqueeze(-1)).squeeze(-1)
+    lpr = torch.log_softmax(d["pi_ref"].double(), -1).gather(-1, d["a"].unsqueeze(-1)).squeeze(-1)
+    ratio = (lp - lpr).exp()
+    near = ((ratio - 0.9).abs() < 1e-5) | ((ratio - 1.0).abs() < 1e-5) | ((ratio - 1.1).abs() < 1e-5)
+    if A == 1:
+        near[:] = False       # ratio == 1 everywhere and every gradient w.r.t. the single logit is 0
+    assert int(near.sum()) <= 5 + B * T // 2000        # ~6e-5 of the samples fall in the three windows
+    keep = (~near).unsqueeze(-1).float()
+    assert_close(lg.grad.cpu() * keep, lg0.grad * keep, "dlogits", rel_to_max=2e-6)
+    # the V-trace target of step t-1 carries rho_t: a flipped branch at t also moves dv there -- compare the columns without any
+    cols = ~near.any(dim=1)
+    assert_close(v.grad.cpu()[cols], v0.grad[cols], "dv", rel_to_max=2e-6)
+
+
+@pytest.mark.parametrize("B,N,M,kappa", [(random.Random(60 + i).randint(1, 300), random.Random(70 + i).randint(1, 200),
+                                          random.Random(80 + i).randint(1, 200), random.Random(90 + i).choice([0.0, 0.3, 1.0]))
+                                         for i in range(8 * _MORE)])
+def test_quantile_huber_random_shapes(cuda, B, N, M, kappa):
+    import importlib
+    t = importlib.import_module("test_gpu_ppo_returns")
+    t.test_quantile_huber_fwd_bwd(B, N, M, kappa)
