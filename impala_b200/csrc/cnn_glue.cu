@@ -43,6 +43,21 @@ __global__ void __launch_bounds__(kGlueThreads) obs_u8_to_f32_nhwc3_kernel(const
                                 __fmul_rn((float)c.w, d)));
 }
 
+// frames whose H*W is not a multiple of 4 (or unaligned buffers): one thread per pixel, same arithmetic
+__global__ void __launch_bounds__(kGlueThreads) obs_u8_to_f32_nhwc3_pixel_kernel(const uint8_t *__restrict__ obs,
+                                                                                 float *__restrict__ out, long long n_pixels,
+                                                                                 long long plane, float divisor) {
+    const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n_pixels) return;
+    const long long img = q / plane, pi = q - img * plane;
+    const uint8_t *src = obs + img * 3 * plane + pi;
+    const float d = 1.0f / divisor;
+    float *dst = out + q * 3;
+    dst[0] = __fmul_rn((float)__ldg(src), d);
+    dst[1] = __fmul_rn((float)__ldg(src + plane), d);
+    dst[2] = __fmul_rn((float)__ldg(src + 2 * plane), d);
+}
+
 // torch's rule (max_pool_forward_nhwc): scan kh, kw ascending, take v if (v > best) || isnan(v) -> first maximum wins
 __device__ __forceinline__ void pool_take(float v, int pos, float &best, uint32_t &arg) {
     if (v > best || v != v) { best = v; arg = (uint32_t)pos; }
@@ -248,10 +263,13 @@ extern "C" int32_t b200rl_obs_u8_to_f32_nhwc(const uint8_t *obs, float *out, int
     if (N == 0) return 0;
     B200RL_REQUIRE(obs && out, -1, "obs_u8_to_f32_nhwc: null pointer argument");
     B200RL_REQUIRE(C == 3, -2, "obs_u8_to_f32_nhwc: C=%lld (3 colour planes only)", (long long)C);
-    B200RL_REQUIRE((H * W) % 4 == 0, -2, "obs_u8_to_f32_nhwc: H*W=%lld must be a multiple of 4", (long long)(H * W));
-    B200RL_REQUIRE((reinterpret_cast<uintptr_t>(obs) & 3u) == 0 && aligned16(out), -3,
-                   "obs_u8_to_f32_nhwc: obs must be 4-byte and out 16-byte aligned");
     B200RL_REQUIRE(divisor != 0.f, -2, "obs_u8_to_f32_nhwc: divisor 0");
+    if ((H * W) % 4 != 0 || (reinterpret_cast<uintptr_t>(obs) & 3u) != 0 || !aligned16(out)) {
+        const long long plane = H * W, np = N * plane;
+        obs_u8_to_f32_nhwc3_pixel_kernel<<<(unsigned)((np + kGlueThreads - 1) / kGlueThreads), kGlueThreads, 0,
+                                           (cudaStream_t)stream>>>(obs, out, np, plane, divisor);
+        return check_launch("obs_u8_to_f32_nhwc3_pixel_kernel");
+    }
     const long long qpi = H * W / 4, nq = N * qpi;
     obs_u8_to_f32_nhwc3_kernel<<<(unsigned)((nq + kGlueThreads - 1) / kGlueThreads), kGlueThreads, 0,
                                  (cudaStream_t)stream>>>(obs, out, nq, qpi, divisor);

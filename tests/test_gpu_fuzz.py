@@ -343,3 +343,66 @@ def test_quantile_huber_random_shapes(cuda, B, N, M, kappa):
     import importlib
     t = importlib.import_module("test_gpu_ppo_returns")
     t.test_quantile_huber_fwd_bwd(B, N, M, kappa)
+
+
+def _cnn_shapes(n, seed):
+    rng = random.Random(seed)
+    return [((rng.randint(1, 40), rng.choice([4, 8, 16, 32, 64]), rng.randint(1, 70), rng.randint(1, 70)),
+             rng.choice([None, 1, 2, 3]), rng.random() < 0.5) for _ in range(n)]
+
+
+@pytest.mark.parametrize("shape,levels,with_bias", _cnn_shapes(10 * _MORE, seed=12))
+def test_k9_pool_random_shapes_match_torch(cuda, shape, levels, with_bias):
+    import importlib
+    importlib.import_module("test_gpu_cnn_glue").test_maxpool_forward_and_backward_match_torch(cuda, shape, levels, with_bias)
+
+
+@pytest.mark.parametrize("shape,levels,_", _cnn_shapes(8 * _MORE, seed=13))
+def test_k9_bias_act_random_shapes_match_torch(cuda, shape, levels, _):
+    import importlib
+    importlib.import_module("test_gpu_cnn_glue").test_bias_act_and_relu_bwd_add_match_torch(cuda, shape)
+
+
+@pytest.mark.parametrize("shape", [(random.Random(100 + i).randint(1, 300), 3, random.Random(110 + i).randint(1, 90),
+                                    random.Random(120 + i).randint(1, 90)) for i in range(6 * _MORE)])
+def test_k9_obs_conversion_random_shapes(cuda, shape):
+    g = torch.Generator(device=cuda).manual_seed(shape[0])
+    obs = torch.randint(0, 256, shape, device=cuda, dtype=torch.uint8, generator=g)
+    got = ops.obs_to_f32_nhwc(obs)
+    assert got.is_contiguous(memory_format=torch.channels_last) and torch.equal(got, obs.float() / 255.)
+
+
+@pytest.mark.parametrize("cap,seed", [(random.Random(130 + i).choice([1, 2, 7, 37, 64, 100, 1000]), i) for i in range(8 * _MORE)])
+def test_ring_buffer_random_extend_sequences_match_the_oracle(cuda, cap, seed):
+    """Random extend sizes (wraps, exact fills, more rows than the capacity) then a sample: storage, keys, rows and
+    probabilities as oracle/replay_ref.py (the rlmeta CircularBuffer + UniformSampler semantics)."""
+    import numpy as np
+    from impala_b200 import replay
+    from oracle import replay_ref
+    rng = random.Random(seed)
+    rb = replay.ReplayBuffer(replay.CircularBuffer(cap, device=cuda), replay.UniformSampler())
+    ob = replay_ref.ReplayBuffer(replay_ref.CircularBuffer(cap), replay_ref.UniformSampler())
+    rb.sampler.reset(seed)
+    ob.sampler.reset(seed)
+    g = torch.Generator().manual_seed(seed)
+    for step in range(8):
+        n = rng.choice([1, 1, 2, cap, cap + 1, 2 * cap + 3, rng.randint(1, 3 * cap)])
+        obs = torch.randint(0, 255, (n, 5, 3), generator=g, dtype=torch.uint8)
+        act = torch.randint(0, 15, (n, 1), generator=g)
+        rew = torch.randn(n, 2, generator=g)
+        rb.extend((obs, act, rew))
+        if n <= cap:
+            ob.extend([obs.numpy(), act.numpy(), rew.numpy()])
+        else:                                                       # oracle: only the survivors matter
+            ob.storage.count += n - cap
+            ob.extend([obs[n - cap:].numpy(), act[n - cap:].numpy(), rew[n - cap:].numpy()])
+        assert rb.size == ob.storage.size and rb.info() == (cap, ob.storage.size)
+        occupied = min(rb.storage.count, cap)
+        for f, of in zip(rb.storage.fields, ob.storage.fields):
+            assert np.array_equal(f.cpu().numpy()[:occupied], of[:occupied])
+        draws = rng.randint(1, 200)
+        keys, batch, probs = rb.sample(draws)
+        okeys, obatch, oprobs = ob.sample(draws)
+        assert np.array_equal(keys.cpu().numpy(), okeys)
+        assert all(np.array_equal(b.cpu().numpy(), o) for b, o in zip(batch, obatch))
+        assert np.allclose(probs.cpu().numpy(), oprobs)
