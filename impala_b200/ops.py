@@ -588,8 +588,18 @@ WGRAD_MAX_CTAS = 148              # one persistent CTA (24 warps, double-buffere
 
 
 def conv3x3_wgrad_supported(x_shape, cout):
-    """Shapes ``b200rl_conv3x3_wgrad`` takes (the IMPALA-CNN's): 3x3/s1/p1, Cin 3/16/32, Cout 16/32, W in 8/16/32/64."""
-    return len(x_shape) == 4 and x_shape[1] in (3, 16, 32) and cout in (16, 32) and x_shape[3] in (8, 16, 32, 64)
+    """Shapes ``b200rl_conv3x3_wgrad`` / ``_fwd`` take (the IMPALA-CNN's): 3x3/s1/p1, Cin 3/16/32, Cout 16/32, W in 8/16/32/64
+    (W = 64: see ``_conv3x3_shape_ok``)."""
+    return len(x_shape) == 4 and _conv3x3_shape_ok(x_shape[1], cout, x_shape[3])
+
+
+def _conv3x3_shape_ok(cin, cout, W):
+    """Channel counts and image widths K10/K11 are instantiated for AND whose tiles fit one CTA's shared memory: at
+    W = 64 only the layers the IMPALA-CNN has there (3 -> 16/32 and 16 -> 16); the wider 64-column layers would need
+    290-375 KB (the library refuses them with status -2) and stay on cuDNN."""
+    if cin not in (3, 16, 32) or cout not in (16, 32) or W not in (8, 16, 32, 64):
+        return False
+    return W < 64 or cin == 3 or (cin, cout) == (16, 16)
 
 
 def conv3x3_wgrad(x, dy):
@@ -637,7 +647,7 @@ def conv3x3_dgrad(dy, weight):
     w = _w_cl(weight)
     N, O, H, W = dy.shape
     I = w.shape[1]
-    if w.shape[0] != O or O not in (16, 32) or I not in (16, 32) or W not in (8, 16, 32, 64):
+    if w.shape[0] != O or I == 3 or not _conv3x3_shape_ok(I, O, W):
         raise RuntimeError("conv3x3_dgrad: unsupported shapes dy %s weight %s" % (tuple(dy.shape), tuple(w.shape)))
     dx = _empty_nhwc(N, I, H, W, dy.device)
     _cabi.call("b200rl_conv3x3_fwd", dy.data_ptr(), w.data_ptr(), dx.data_ptr(), N, H, W, O, I, 1, _stream())

@@ -113,8 +113,11 @@ def test_autograd_pieces_match_torch_block(cuda):
         torch.backends.cudnn.allow_tf32 = tf32
 
 
-def test_fused_model_matches_eager_model(cuda):
-    """ActorCritic(body='impala', fused_glue=True) vs the eager channels_last model with the same parameters.  Both
+@pytest.mark.parametrize("frame,n", [(64, 24), (128, 6), (84, 10), (50, 10)])
+def test_fused_model_matches_eager_model(cuda, frame, n):
+    """ActorCritic(body='impala', fused_glue=True) vs the eager channels_last model with the same parameters; 64x64 is
+    procgen's frame (every convolution on K10/K11 or cuDNN's tcgen05 kernels), 128 / 84 / 50 put some or all layers outside
+    the widths K10/K11 are built for -- those must route to cuDNN, with the K9 glue around them.  Both
     multiply their convolutions in TF32 (torch's default), so neither is "the" answer: an fp64 copy of the eager
     model is, and the fused model must be as close to it as the eager TF32 model is (within x8: the two carry
     different random rounding errors, here maxima over up to 9,216 elements), for outputs and for every parameter gradient."""
@@ -122,15 +125,15 @@ def test_fused_model_matches_eager_model(cuda):
     torch.backends.cudnn.allow_tf32 = True
     try:
         torch.manual_seed(0)
-        eager = models.ActorCritic((3, 64, 64), 15, body="impala", channels_last=True).to(cuda).to(memory_format=CL)
+        eager = models.ActorCritic((3, frame, frame), 15, body="impala", channels_last=True).to(cuda).to(memory_format=CL)
         for p in eager.body.parameters():                           # biases are zero-initialised: make them matter
             if p.dim() == 1:
                 torch.nn.init.normal_(p, std=0.1)
-        fused = models.ActorCritic((3, 64, 64), 15, body="impala", channels_last=True, fused_glue=True).to(cuda).to(memory_format=CL)
+        fused = models.ActorCritic((3, frame, frame), 15, body="impala", channels_last=True, fused_glue=True).to(cuda).to(memory_format=CL)
         fused.load_state_dict(copy.deepcopy(eager.state_dict()))
         assert [n for n, _ in fused.named_parameters()] == [n for n, _ in eager.named_parameters()]
         exact = copy.deepcopy(eager).double()
-        obs = torch.randint(0, 256, (24, 3, 64, 64), device=cuda, dtype=torch.uint8)
+        obs = torch.randint(0, 256, (n, 3, frame, frame), device=cuda, dtype=torch.uint8)
         outs = []
         for m in (exact, eager, fused):
             if m is exact:

@@ -406,3 +406,29 @@ def test_ring_buffer_random_extend_sequences_match_the_oracle(cuda, cap, seed):
         assert np.array_equal(keys.cpu().numpy(), okeys)
         assert all(np.array_equal(b.cpu().numpy(), o) for b, o in zip(batch, obatch))
         assert np.allclose(probs.cpu().numpy(), oprobs)
+
+
+def _conv_cases(n, seed):
+    rng = random.Random(seed)
+    out = []
+    for _ in range(n):
+        W = rng.choice([8, 16, 32, 64])
+        H = rng.choice([1, 2, 3, 7, 8, 9, 15, 16, 17, 31, 33, 64]) if rng.random() < 0.7 else rng.randint(1, 70)
+        N = rng.randint(1, max(1, min(400, 600_000 // (H * W))))
+        cin, cout = rng.choice([3, 16, 16, 32]), rng.choice([16, 32])
+        if not ops.conv3x3_wgrad_supported((N, cin, H, W), cout):   # 64 columns x many channels: stays on cuDNN
+            W = 32
+        out.append((N, cin, cout, H, W))
+    return out
+
+
+@pytest.mark.parametrize("N,Cin,Cout,H,W", _conv_cases(12 * _MORE, seed=14))
+def test_k10_k11_random_shapes(cuda, N, Cin, Cout, H, W):
+    """K10 / K11 (plain and fused epilogue) at drawn image counts and heights: TF32 tolerance vs cuDNN fp32, bit-identical on
+    TF32-exact integer data vs fp64 -- the comparators of tests/test_gpu_cnn_glue.py."""
+    import importlib
+    t = importlib.import_module("test_gpu_cnn_glue")
+    t.test_conv3x3_forward_and_dgrad_match_cudnn_fp32(cuda, N, Cin, Cout, H, W)
+    t.test_conv3x3_fused_epilogue_exact_on_integers(cuda, N, Cin, Cout, H, W)
+    # the wgrad test ends with a W = 4 refusal built by slicing the last axis: it needs W >= 8, which every draw has
+    t.test_conv3x3_wgrad_matches_cudnn_fp32(cuda, N, Cin, Cout, H, W)
