@@ -140,8 +140,12 @@ class FusedClipAdam(torch.optim.Optimizer):
         for p in self.params:
             n = p.numel()
             if p.grad is not None and p.grad.data_ptr() != self._own_grads[off:off + n].data_ptr():
-                self._own_grads[off:off + n].copy_(p.grad.reshape(-1))
+                # through the parameter's own strides: a channels_last weight sits in the flat buffers in its physical
+                # order, so a logical-order flatten of the gradient would pair the wrong elements
+                flat_view(self._own_grads, off, p).copy_(p.grad)
             elif p.grad is None:
+                # a zero gradient (the moments still decay), where torch.optim.Adam would skip the parameter; the
+                # reference's learners produce every gradient on every step
                 self._own_grads[off:off + n].zero_()
             off += n
         self.step_flat(self._own_grads)

@@ -432,3 +432,59 @@ def test_k10_k11_random_shapes(cuda, N, Cin, Cout, H, W):
     t.test_conv3x3_fused_epilogue_exact_on_integers(cuda, N, Cin, Cout, H, W)
     # the wgrad test ends with a W = 4 refusal built by slicing the last axis: it needs W >= 8, which every draw has
     t.test_conv3x3_wgrad_matches_cudnn_fp32(cuda, N, Cin, Cout, H, W)
+
+
+def _param_sets(n, seed):
+    rng = random.Random(seed)
+    out = []
+    for _ in range(n):
+        shapes = []
+        for _ in range(rng.randint(1, 9)):
+            kind = rng.random()
+            if kind < 0.35:
+                shapes.append((rng.choice([16, 32]), rng.choice([3, 16, 32]), 3, 3, rng.random() < 0.7))     # conv weight (+ channels_last?)
+            elif kind < 0.6:
+                shapes.append((rng.randint(1, 64),))
+            elif kind < 0.7:
+                shapes.append(())
+            else:
+                shapes.append((rng.randint(1, 300), rng.randint(1, 700)))
+        out.append((tuple(shapes), rng.choice([0.0, 0.5, 40.0])))
+    return out
+
+
+@pytest.mark.parametrize("shapes,max_norm", _param_sets(8 * _MORE, seed=15))
+def test_fused_clip_adam_class_random_parameter_sets_match_torch(cuda, shapes, max_norm):
+    """FusedClipAdam.step() over drawn parameter lists (scalars, vectors, matrices, channels_last convolution weights whose
+    gradients arrive in either memory format) == clip_grad_norm_ + torch.optim.Adam on copies."""
+    from impala_b200 import optim
+    g = torch.Generator(device=cuda).manual_seed(len(shapes))
+    mine, ref = [], []
+    for sh in shapes:
+        cl = len(sh) == 5 and sh[4]
+        t = torch.randn(sh[:4] if len(sh) == 5 else sh, device=cuda, generator=g)
+        if cl:
+            t = t.contiguous(memory_format=torch.channels_last)
+        mine.append(torch.nn.Parameter(t.clone(memory_format=torch.preserve_format)))
+        ref.append(torch.nn.Parameter(t.clone(memory_format=torch.preserve_format)))
+    opt = optim.FusedClipAdam(mine, lr=1e-3, eps=1e-5, max_grad_norm=max_norm)
+    ropt = torch.optim.Adam(ref, lr=1e-3, eps=1e-5)
+    for k in range(3):
+        for i, (a, b) in enumerate(zip(mine, ref)):
+            gr = torch.randn(a.shape, device=cuda, generator=g) * (0.1 + k)
+            if a.dim() == 4 and (i + k) % 2 == 0:
+                gr = gr.contiguous(memory_format=torch.channels_last)
+            a.grad, b.grad = gr.clone(memory_format=torch.preserve_format), gr.clone(memory_format=torch.preserve_format)
+        if max_norm > 0:
+            want_norm = torch.nn.utils.clip_grad_norm_(ref, max_norm)
+        ropt.step()
+        opt.step()
+        if max_norm > 0:
+            assert_close(opt.total_norm[0], want_norm, "norm", rtol=1e-5, atol=0)
+    for i, (a, b) in enumerate(zip(mine, ref)):
+        assert a.shape == b.shape and a.stride() == b.stride()
+        assert_close(a, b, "param %d %s" % (i, tuple(a.shape)), rtol=1e-5, atol=1e-6)
+    sd = opt.state_dict()                       # and the checkpoint carries the moments in the parameters' own layout
+    rsd = ropt.state_dict()
+    for i in range(len(mine)):
+        assert_close(sd["state"][i]["exp_avg"], rsd["state"][i]["exp_avg"], "exp_avg %d" % i, rtol=2e-5, atol=1e-7)

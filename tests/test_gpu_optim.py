@@ -66,9 +66,14 @@ def test_clip_adam_unaligned_and_deterministic(cuda):
     assert_close(norm[0], want_norms[0], "norm", rtol=1e-5, atol=0)
 
 
-def test_fused_optimizer_class_matches_adam_on_model(cuda):
+@pytest.mark.parametrize("body,channels_last", [("nature", False), ("impala", True)])
+def test_fused_optimizer_class_matches_adam_on_model(cuda, body, channels_last):
+    """Plain ``zero_grad() / backward() / step()`` use.  With channels_last convolution weights the flat buffers hold a
+    weight in its physical order: step() must gather p.grad through the same strides."""
     torch.manual_seed(0)
-    model = models.ActorCritic((3, 64, 64), 15, body="nature").to(cuda)
+    model = models.ActorCritic((3, 64, 64), 15, body=body, channels_last=channels_last).to(cuda)
+    if channels_last:
+        model = model.to(memory_format=torch.channels_last)
     ref = copy.deepcopy(model)
     opt = optim.FusedClipAdam(model.parameters(), lr=1e-4, eps=1e-5, max_grad_norm=0.5)
     ropt = torch.optim.Adam(ref.parameters(), lr=1e-4, eps=1e-5)
@@ -81,8 +86,12 @@ def test_fused_optimizer_class_matches_adam_on_model(cuda):
             if o is ropt:
                 torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.5)
             o.step()
+    # IMPALA-CNN: cuDNN's TF32 weight-gradient kernels are not run-to-run reproducible and Adam's m / sqrt(v) turns that
+    # noise into up to ~4 % of a step for small gradients (3.6e-6 seen); wrongly paired elements would be off by the whole
+    # motion (3 steps x lr = 3e-4)
+    atol = 1e-5 if body == "impala" else 2e-7
     for (n1, a), (_, b) in zip(model.named_parameters(), ref.named_parameters()):
-        assert_close(a, b, n1, rtol=1e-5, atol=2e-7)
+        assert_close(a, b, n1, rtol=1e-5, atol=atol)
 
 
 def test_golden_next_rows(cuda):
