@@ -593,13 +593,16 @@ def conv3x3_wgrad_supported(x_shape, cout):
     return len(x_shape) == 4 and _conv3x3_shape_ok(x_shape[1], cout, x_shape[3])
 
 
-def _conv3x3_shape_ok(cin, cout, W):
-    """Channel counts and image widths K10/K11 are instantiated for AND whose tiles fit one CTA's shared memory: at
-    W = 64 only the layers the IMPALA-CNN has there (3 -> 16/32 and 16 -> 16); the wider 64-column layers would need
-    290-375 KB (the library refuses them with status -2) and stay on cuDNN."""
+def _conv3x3_shape_ok(cin, cout, W, wgrad=True):
+    """Channel counts and image widths K10/K11 are instantiated for AND whose tiles fit one CTA's shared memory.  At
+    W = 64 the weight gradient (K10) fits for the layers the IMPALA-CNN has there (3 -> 16/32 and 16 -> 16; the others
+    would need 290-375 KB), the forward / input-gradient form (K11) for everything but 32 -> 32 (236 KB); the library
+    refuses the rest with status -2 and they stay on cuDNN."""
     if cin not in (3, 16, 32) or cout not in (16, 32) or W not in (8, 16, 32, 64):
         return False
-    return W < 64 or cin == 3 or (cin, cout) == (16, 16)
+    if W < 64:
+        return True
+    return (cin == 3 or (cin, cout) == (16, 16)) if wgrad else (cin, cout) != (32, 32)
 
 
 def conv3x3_wgrad(x, dy):
@@ -633,7 +636,7 @@ def conv3x3_fwd(x, weight):
     w = _w_cl(weight)
     N, Cin, H, W = x.shape
     Cout = w.shape[0]
-    if w.shape[1] != Cin or not conv3x3_wgrad_supported(x.shape, Cout):
+    if w.shape[1] != Cin or not _conv3x3_shape_ok(Cin, Cout, W, wgrad=False):
         raise RuntimeError("conv3x3_fwd: unsupported shapes x %s weight %s" % (tuple(x.shape), tuple(w.shape)))
     y = _empty_nhwc(N, Cout, H, W, x.device)
     _cabi.call("b200rl_conv3x3_fwd", x.data_ptr(), w.data_ptr(), y.data_ptr(), N, H, W, Cin, Cout, 0, _stream())
@@ -647,7 +650,7 @@ def conv3x3_dgrad(dy, weight):
     w = _w_cl(weight)
     N, O, H, W = dy.shape
     I = w.shape[1]
-    if w.shape[0] != O or I == 3 or not _conv3x3_shape_ok(I, O, W):
+    if w.shape[0] != O or I == 3 or not _conv3x3_shape_ok(O, I, W, wgrad=False):   # runs as a forward O -> I
         raise RuntimeError("conv3x3_dgrad: unsupported shapes dy %s weight %s" % (tuple(dy.shape), tuple(w.shape)))
     dx = _empty_nhwc(N, I, H, W, dy.device)
     _cabi.call("b200rl_conv3x3_fwd", dy.data_ptr(), w.data_ptr(), dx.data_ptr(), N, H, W, O, I, 1, _stream())
@@ -662,7 +665,7 @@ def conv3x3_fwd_fused(x, weight, bias, res=None, want_y=True, want_r=False):
     w = _w_cl(weight)
     N, Cin, H, W = x.shape
     Cout = w.shape[0]
-    if w.shape[1] != Cin or not conv3x3_wgrad_supported(x.shape, Cout) or not (want_y or want_r):
+    if w.shape[1] != Cin or not _conv3x3_shape_ok(Cin, Cout, W, wgrad=False) or not (want_y or want_r):
         raise RuntimeError("conv3x3_fwd_fused: unsupported shapes x %s weight %s" % (tuple(x.shape), tuple(w.shape)))
     if res is not None:
         _nhwc(res, "conv3x3_fwd_fused res")

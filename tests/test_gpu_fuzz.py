@@ -488,3 +488,38 @@ def test_fused_clip_adam_class_random_parameter_sets_match_torch(cuda, shapes, m
     rsd = ropt.state_dict()
     for i in range(len(mine)):
         assert_close(sd["state"][i]["exp_avg"], rsd["state"][i]["exp_avg"], "exp_avg %d" % i, rtol=2e-5, atol=1e-7)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+def test_empty_inputs_are_no_ops_or_clean_errors(cuda):
+    """Zero rows / zero draws / zero columns through the public surface: replay calls are no-ops (rlmeta's extend([]) is),
+    the losses and scans refuse with the library's message -- never a CUDA launch error that would poison the context."""
+    from impala_b200 import replay, vtrace
+    rb = replay.ReplayBuffer(replay.CircularBuffer(16, device=cuda), replay.UniformSampler())
+    rb.sampler.reset(1)
+    assert len(rb.extend([])) == 0
+    rb.extend((torch.arange(5, device=cuda).reshape(5, 1).float(), torch.arange(5, device=cuda).reshape(5, 1)))
+    assert len(rb.extend((torch.empty(0, 1, device=cuda), torch.empty(0, 1, dtype=torch.int64, device=cuda)))) == 0
+    assert rb.size == 5
+    keys, batch, probs = rb.sample(0)
+    assert keys.numel() == 0 and batch[0].shape == (0, 1) and probs.numel() == 0
+    keys, batch, _ = rb.sample(3)                                   # the stream is where it was: draw offset 0
+    assert torch.equal(keys, ops.sample_uniform(1, 0, 0, 3, 5, cuda))
+    assert ops.sample_uniform(1, 0, 0, 0, 5, cuda).numel() == 0
+    assert ops.gather_rows(torch.zeros(4, 3, device=cuda), torch.empty(0, dtype=torch.int64, device=cuda)).shape == (0, 3)
+    tree = torch.zeros(16, dtype=torch.float64, device=cuda)
+    ops.sumtree_update(tree, torch.empty(0, dtype=torch.int64, device=cuda), torch.empty(0, dtype=torch.float64, device=cuda))
+    assert float(tree.sum()) == 0.0
+    assert ops.act_epilogue(torch.empty(0, 6, device=cuda), torch.tensor([False]), 1, 0, 0).numel() == 0
+    z = lambda *s: torch.zeros(*s, device=cuda)
+    zi = lambda *s: torch.zeros(*s, dtype=torch.int64, device=cuda)
+    for call in (lambda: ops.impala_loss_fwdbwd(z(0, 20, 6), z(0, 20), zi(0, 20), z(0, 20), z(0, 20), z(0, 20, 6)),
+                 lambda: ops.impala_loss_fwdbwd(z(4, 1, 6), z(4, 1), zi(4, 1), z(4, 1), z(4, 1), z(4, 1, 6)),     # T = 1
+                 lambda: ops.ppo_loss_fwdbwd(z(0, 6), z(0), zi(0), z(0), z(0, 6)),
+                 lambda: vtrace.lambda_returns(z(0, 8), z(0, 8), z(0, 8), 0.9),
+                 lambda: ops.clip_adam_step(z(0), z(0), z(0), z(0), 1, 1e-3)):
+        with pytest.raises(RuntimeError):
+            call()
+    # the context is intact
+    torch.cuda.synchronize()
+    assert float(ops.impala_loss_fwdbwd(z(2, 3, 4), z(2, 3), zi(2, 3), z(2, 3), z(2, 3), z(2, 3, 4))[0][1]) > 0   # entropy = ln 4

@@ -86,12 +86,18 @@ def test_fused_optimizer_class_matches_adam_on_model(cuda, body, channels_last):
             if o is ropt:
                 torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.5)
             o.step()
-    # IMPALA-CNN: cuDNN's TF32 weight-gradient kernels are not run-to-run reproducible and Adam's m / sqrt(v) turns that
-    # noise into up to ~4 % of a step for small gradients (3.6e-6 seen); wrongly paired elements would be off by the whole
-    # motion (3 steps x lr = 3e-4)
-    atol = 1e-5 if body == "impala" else 2e-7
+    if body == "nature":
+        for (n1, a), (_, b) in zip(model.named_parameters(), ref.named_parameters()):
+            assert_close(a, b, n1, rtol=1e-5, atol=2e-7)
+        return
+    # IMPALA-CNN: the two copies' TF32 convolution gradients differ in their last bits from the second step on, and Adam's
+    # m / sqrt(v) turns that into up to ~6 % of the motion for the smallest gradients (1.8e-5 seen on 6 of 2,304 elements).
+    # Wrongly paired elements (a logical-order gather into the physical-order flat buffer) would move nearly EVERY element
+    # of a 4-D weight by the whole motion, 3 steps x lr = 3e-4.
     for (n1, a), (_, b) in zip(model.named_parameters(), ref.named_parameters()):
-        assert_close(a, b, n1, rtol=1e-5, atol=atol)
+        err = (a.detach() - b.detach()).abs()
+        assert err.max().item() < 1e-4, (n1, err.max().item())
+        assert (err > 1e-5).float().mean().item() < 0.02, (n1, (err > 1e-5).float().mean().item())
 
 
 def test_golden_next_rows(cuda):
