@@ -5,6 +5,7 @@ from typing import Dict, Optional
 import torch
 
 from .. import ops, optim, parallel
+from ._graph import GraphedStepMixin
 
 
 def make_discount(done: torch.Tensor, gamma: float = 0.99) -> torch.Tensor:
@@ -12,7 +13,7 @@ def make_discount(done: torch.Tensor, gamma: float = 0.99) -> torch.Tensor:
     return torch.logical_not(done) * gamma
 
 
-class ImpalaLearner:
+class ImpalaLearner(GraphedStepMixin):
     """Same constructor, ``prepare()``, ``train_step()`` and ``_train_step(batch)`` as the reference.
 
     Differences, all on the hot path: the replay buffer is device-resident (``impala_b200.replay``),
@@ -46,55 +47,17 @@ class ImpalaLearner:
     def prepare(self):
         self._replay_buffer.warm_up(self._learning_starts)
 
-    # -- the whole step as ONE CUDA graph -------------------------------------------------------------------------------
-    _graph = None
-
-    def capture_graph(self, warmup: int = 3) -> None:
-        """Capture ``sample -> model forward -> K1 -> model backward -> (allreduce +) clip + Adam`` once; ``train_step`` then
-        replays ONE graph launch per step instead of ~180 kernel launches (reference ``agents/impala/learning.py:119-177`` is
-        one Python pass per step).  Needs ``FusedClipAdam`` (K6, or K8 across ranks: its step number and flag generation move to
-        device memory) and the uniform device sampler (its draw count moves to device memory); the replay buffer must not
-        change SIZE between replays (a full ring may keep being appended to).  Every rank must call it at the same point."""
-        if self._graph is not None:
-            return
-        if not isinstance(self._optimizer, optim.FusedClipAdam):
-            raise RuntimeError("capture_graph needs impala_b200.optim.FusedClipAdam (a launch-argument step number cannot be replayed)")
-        from .. import replay as _replay
-        sampler = self._replay_buffer.sampler
-        if type(sampler) is not _replay.UniformSampler:
-            raise RuntimeError("capture_graph supports the uniform device sampler")
-        dev = self.device()
-        if self._bucket is None:
-            self._bucket = parallel.make_bucket(self._model.parameters(), self._group, True)
-        if not isinstance(self._bucket, parallel.PeerGradBucket) and parallel.world(self._group)[1] > 1:
-            raise RuntimeError("capture_graph across ranks needs the peer-memory gradient bucket (K8); an NCCL allreduce is not captured here")
-        self._optimizer.capturable_(self._bucket if isinstance(self._bucket, parallel.PeerGradBucket) else None)
-        sampler.capturable_(dev)
-        self.profile = False
-        side = torch.cuda.Stream(dev)
-        side.wait_stream(torch.cuda.current_stream(dev))
-        with torch.cuda.stream(side):
-            ops.workspace(dev)                      # the capture stream's loss workspace must exist before capture
-            for _ in range(max(1, warmup)):         # cuDNN plans, allocator pools, lazy module loads
-                self._step_body()
-        side.synchronize()
-        graph = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(graph, stream=side):
-            self._graph_metrics = self._step_body()
-        torch.cuda.current_stream(dev).wait_stream(side)
-        self._graph = graph
-
-    def _step_body(self):
-        _, batch, _ = self._replay_buffer.sample(self._batch_size)
-        return self._train_step(batch)
-
     def train_step(self):
-        if self._graph is not None:
+        if self._graph is not None:                 # capture_graph(): ONE launch per step (agents/_graph.py)
             t0 = time.perf_counter()
-            self._graph.replay()
-            self._step_count += 1
-            metrics = dict(self._graph_metrics)     # static device tensors, rewritten by every replay
+            metrics, dt = self._replay_step()
+            update_time = self._push_model()
+            # same keys as the eager path; sampling and the gradient step are one launch here, so they share its host time
+            n_samples = self._batch_size * self._batch_shape[1]
+            metrics["debug/replay_sample_per_second"] = metrics["debug/gradient_per_second"] = n_samples / max(dt * 1000, 1e-9)
             metrics["debug/total_time"] = (time.perf_counter() - t0) * 1000
+            metrics["debug/forward_dt"] = dt * 1000 / self._batch_size
+            metrics["debug/update_time"] = update_time
             return metrics
         t0 = time.perf_counter()
         _, batch, _ = self._replay_buffer.sample(self._batch_size)
@@ -102,12 +65,7 @@ class ImpalaLearner:
         t1 = time.perf_counter()
         metrics = self._train_step(batch)
         t2 = time.perf_counter()
-        update_time = 0
-        self._step_count += 1
-        if self._step_count % self._model_push_period == 0 and hasattr(self._model, "push"):
-            start = time.perf_counter()
-            self._model.push()
-            update_time = time.perf_counter() - start
+        update_time = self._push_model()
         metrics["debug/replay_sample_per_second"] = n_samples / max((t1 - t0) * 1000, 1e-9)
         metrics["debug/gradient_per_second"] = n_samples / max((t2 - t1) * 1000, 1e-9)
         metrics["debug/total_time"] = (time.perf_counter() - t0) * 1000

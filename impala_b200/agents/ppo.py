@@ -6,6 +6,7 @@ from typing import Dict, Optional
 import torch
 
 from .. import ops, optim, parallel, vtrace
+from ._graph import GraphedStepMixin
 
 
 def make_targets(r, done, v, gamma: float = 0.99, lambda_: float = 0.95, time_major: bool = False):
@@ -18,7 +19,10 @@ def make_targets(r, done, v, gamma: float = 0.99, lambda_: float = 0.95, time_ma
     return vtrace.lambda_returns(r[:, :-1], discount[:, :-1], v[:, 1:], lambda_)
 
 
-class PPOLearner:
+class PPOLearner(GraphedStepMixin):
+    """Same constructor, ``prepare()``, ``train_step()`` and ``_train_step(batch)`` as the reference; ``capture_graph()``
+    (``agents/_graph.py``) turns the step into one CUDA graph launch."""
+
     def __init__(self, model, replay_buffer, optimizer: torch.optim.Optimizer, batch_size: int = 256,
                  max_grad_norm: float = 0.5, entropy_coeff: float = 0.01,
                  learning_starts: Optional[int] = None, model_push_period: int = 8,
@@ -34,9 +38,13 @@ class PPOLearner:
         self._clip_coeff = clip_coeff
         self._group = process_group
         self._device = None
-        self._step_counter = 0
+        self._step_count = 0
         self._bucket = None
         self.can_train = False
+
+    @property
+    def _step_counter(self) -> int:                 # the reference's name for it (agents/ppo/learning.py:98)
+        return self._step_count
 
     def device(self) -> torch.device:
         if self._device is None:
@@ -50,17 +58,17 @@ class PPOLearner:
 
     def train_step(self):
         t0 = time.perf_counter()
-        _, batch, _ = self._replay_buffer.sample(self._batch_size)
-        t1 = time.perf_counter()
-        metrics = self._train_step(batch)
-        t2 = time.perf_counter()
-        self._step_counter += 1
-        update_time = 0
-        if self._step_counter % self._model_push_period == 0 and hasattr(self._model, "push"):
-            start = time.perf_counter()
-            self._model.push()
-            update_time = (time.perf_counter() - start) * 1000
-        metrics["debug/replay_sample_per_second"] = self._batch_size / max((t1 - t0) * 1000, 1e-9)
+        if self._graph is not None:                 # capture_graph(): ONE launch per step
+            metrics, dt = self._replay_step()
+            t1 = t0
+            t2 = t0 + dt
+        else:
+            _, batch, _ = self._replay_buffer.sample(self._batch_size)
+            t1 = time.perf_counter()
+            metrics = self._train_step(batch)
+            t2 = time.perf_counter()
+        update_time = self._push_model() * 1000                            # :108-112
+        metrics["debug/replay_sample_per_second"] = self._batch_size / max(((t1 - t0) or (t2 - t0)) * 1000, 1e-9)
         metrics["debug/gradient_per_second"] = self._batch_size / max((t2 - t1) * 1000, 1e-9)
         metrics["debug/total_time"] = (time.perf_counter() - t0) * 1000
         metrics["debug/forward_dt"] = (t2 - t1) * 1000

@@ -400,8 +400,10 @@ def test_learner_step_as_one_cuda_graph_matches_eager_steps(cuda, body, kw):
         # (m / sqrt(v) = +-1), so two runs whose convolutions round differently (cuDNN picks its algorithm per stream and
         # workspace) could not be compared elementwise; a large eps makes the update proportional to the gradient
         opt = optim.FusedClipAdam(model.parameters(), lr=1e-3, eps=1e-2)
-        learner = ImpalaLearner(model, rb, opt, batch_size=Bsz, learning_starts=10)
+        learner = ImpalaLearner(model, rb, opt, batch_size=Bsz, learning_starts=10, model_push_period=2)
         learner.prepare()
+        model.pushes = []
+        model.push = lambda: model.pushes.append(learner._step_count)       # the reference's RemotableModel.push
         return model, rb, opt, learner
 
     model_e, rb_e, opt_e, eager = make()
@@ -428,4 +430,52 @@ def test_learner_step_as_one_cuda_graph_matches_eager_steps(cuda, body, kw):
         assert_close(opt_g.flat, want[k][1], "parameters after step %d" % (k + 1), rtol=1e-3, atol=atol)
     assert len(set(losses_seen)) == len(losses_seen), "every replay must draw a new batch"
     assert opt_g.sync_step_count() == steps
+    assert model_g.pushes == model_e.pushes == [2, 4]                       # warm-up steps count; replays push too
+    assert set(m) >= {"debug/replay_sample_per_second", "debug/gradient_per_second", "debug/total_time", "debug/forward_dt",
+                      "debug/update_time"}
     assert int(rb_g.sampler.draw_counter.item()) == steps * Bsz == rb_e.sampler.draws
+
+
+def test_ppo_learner_step_as_one_cuda_graph_matches_eager_steps(cuda):
+    """PPOLearner.capture_graph (agents/_graph.py): sample -> model -> K3 -> backward -> clip + Adam as ONE graph launch per
+    step follows the eager learner (same seeds): new minibatch and next Adam step on every replay."""
+    A, N, steps = 15, 256, 5
+
+    def make():
+        torch.manual_seed(0)
+        model = models.ActorCritic((3, 64, 64), A).to(cuda)
+        rb = replay.ReplayBuffer(replay.CircularBuffer(1000, collate_fn=torch.cat, device=cuda), replay.UniformSampler())
+        rb.sampler.reset(7)
+        g = torch.Generator().manual_seed(1)
+        rb.extend((torch.randint(0, 255, (600, 3, 64, 64), generator=g, dtype=torch.uint8),
+                   torch.randint(0, A, (600,), generator=g), torch.randn(600, generator=g), torch.randn(600, A, generator=g)))
+        opt = optim.FusedClipAdam(model.parameters(), lr=1e-3, eps=1e-2)      # eps: see the IMPALA graph test above
+        learner = PPOLearner(model, rb, opt, batch_size=N, model_push_period=2)
+        learner.prepare()
+        model.pushes = []
+        model.push = lambda: model.pushes.append(learner._step_counter)
+        return model, rb, opt, learner
+
+    model_e, rb_e, opt_e, eager = make()
+    want = []
+    for _ in range(steps):
+        m = eager.train_step()
+        want.append(({k: float(m[k]) for k in ("train/loss", "train/td", "train/target", "train_step/grad_norm")}, opt_e.flat.clone()))
+    model_g, rb_g, opt_g, graphed = make()
+    graphed.capture_graph(warmup=2)
+    torch.cuda.synchronize()
+    assert_close(opt_g.flat, want[1][1], "parameters after the 2 warm-up steps", rtol=1e-4, atol=2e-5)
+    targets_seen = []
+    for k in range(2, steps):
+        m = graphed.train_step()
+        torch.cuda.synchronize()
+        targets_seen.append(float(m["train/target"]))
+        rel, atol = (2e-3, 2e-5) if k == 2 else (5e-2, 5e-4)
+        for name, v in want[k][0].items():
+            assert float(m[name]) == pytest.approx(v, rel=rel, abs=1e-5), (k, name)
+        assert_close(opt_g.flat, want[k][1], "parameters after step %d" % (k + 1), rtol=1e-3, atol=atol)
+    assert len(set(targets_seen)) == len(targets_seen), "every replay must draw a new minibatch"
+    assert [float(t) for t in targets_seen] == pytest.approx([w[0]["train/target"] for w in want[2:]], rel=1e-5)   # mean(v_target): data only
+    assert opt_g.sync_step_count() == steps and graphed._step_counter == steps
+    assert model_g.pushes == model_e.pushes == [2, 4]
+    assert int(rb_g.sampler.draw_counter.item()) == steps * N == rb_e.sampler.draws
