@@ -523,3 +523,14 @@ def test_empty_inputs_are_no_ops_or_clean_errors(cuda):
     # the context is intact
     torch.cuda.synchronize()
     assert float(ops.impala_loss_fwdbwd(z(2, 3, 4), z(2, 3), zi(2, 3), z(2, 3), z(2, 3), z(2, 3, 4))[0][1]) > 0   # entropy = ln 4
+
+
+@pytest.mark.parametrize("B,T,lam", [(random.Random(200 + i).randint(1, 600), random.Random(210 + i).randint(2, 300),
+                                      random.Random(220 + i).choice([0.0, 0.5, 0.9, 1.0])) for i in range(8 * _MORE)])
+def test_stand_alone_vtrace_random_shapes(cuda, B, T, lam):
+    """batched_vtrace (forward, backward, output orders, per-sequence form) and its time-major storage path at drawn
+    shapes -- the comparators of tests/test_gpu_ppo_returns.py."""
+    import importlib
+    t = importlib.import_module("test_gpu_ppo_returns")
+    t.test_batched_vtrace_dropin_forward_backward(B, T, lam)
+    t.test_vtrace_forward_time_major(B, T)
