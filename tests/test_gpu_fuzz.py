@@ -534,3 +534,27 @@ def test_stand_alone_vtrace_random_shapes(cuda, B, T, lam):
     t = importlib.import_module("test_gpu_ppo_returns")
     t.test_batched_vtrace_dropin_forward_backward(B, T, lam)
     t.test_vtrace_forward_time_major(B, T)
+
+
+def _k1_switch_cases(n, seed):
+    rng = random.Random(seed)
+    out = []
+    for _ in range(n):
+        lam, crho, cpg, ent = rng.choice([0.0, 0.5, 0.9, 1.0]), rng.choice([0.7, 1.0, 1.3]), rng.choice([0.8, 1.0, 1.5]), rng.choice([0.0, 0.01, 0.2])
+        da, dr = rng.random() < 0.3, rng.random() < 0.3
+        out.append((rng.randint(1, 400), rng.choice([2, 3, 11, 20, 20, 40]), rng.choice([1, 2, 6, 15, 18, 32]), rng.random() < 0.4,
+                    rng.choice(["0", "1", "2"]), lam, crho, cpg, ent, da, dr))
+    return out
+
+
+@pytest.mark.parametrize("B,T,A,time_major,impl,lam,crho,cpg,ent,da,dr", _k1_switch_cases(16 * _MORE, seed=16))
+def test_k1_random_semantic_switches_against_the_oracle(cuda, B, T, A, time_major, impl, lam, crho, cpg, ent, da, dr, monkeypatch):
+    """Every K1 argument drawn at once (lambda, both clip thresholds, entropy coefficient, detach flags, layout, kernel):
+    metrics and gradients against the fp32 oracle, fp64-arbitrated (tests/test_gpu_impala.py::check)."""
+    import importlib
+    monkeypatch.setenv("B200RL_K1_TILE", impl)
+    t = importlib.import_module("test_gpu_impala")
+    okw = dict(lambda_=lam, clip_rho_threshold=crho, clip_pg_rho_threshold=cpg, entropy_coeff=ent, detach_adv=da, detach_rho=dr)
+    kkw = dict(lambda_=lam, clip_rho=crho, clip_pg_rho=cpg, entropy_coeff=ent,
+               flags=(ops.DETACH_ADV if da else 0) | (ops.DETACH_RHO if dr else 0))
+    t.check(synth.impala_rollout(B, T, A, seed=B * 31 + T), okw, kkw, time_major=time_major)
