@@ -558,3 +558,28 @@ def test_k1_random_semantic_switches_against_the_oracle(cuda, B, T, A, time_majo
     kkw = dict(lambda_=lam, clip_rho=crho, clip_pg_rho=cpg, entropy_coeff=ent,
                flags=(ops.DETACH_ADV if da else 0) | (ops.DETACH_RHO if dr else 0))
     t.check(synth.impala_rollout(B, T, A, seed=B * 31 + T), okw, kkw, time_major=time_major)
+
+
+def _sampler_cases(n, seed):
+    rng = random.Random(seed)
+    out = []
+    for _ in range(n):
+        off = rng.choice([0, 2 ** 32 - rng.randint(1, 2000), 2 ** 32, 2 ** 33 + rng.randint(0, 10 ** 6), rng.randint(0, 2 ** 62),
+                          2 ** 62 - rng.randint(1, 5000)])
+        size = rng.choice([1, 2, 3, rng.randint(1, 10 ** 6), 2 ** 31 - 1, 2 ** 31, 2 ** 32 + 1, rng.randint(1, 2 ** 62)])
+        out.append((rng.randint(0, 2 ** 63 - 1), rng.randint(0, 2 ** 31 - 1), off, rng.randint(1, 5000), size))
+    return out
+
+
+@pytest.mark.parametrize("seed,stream,off,n,size", _sampler_cases(16 * _MORE, seed=17))
+def test_k4_random_streams_offsets_and_sizes_bit_exact(cuda, seed, stream, off, n, size):
+    """Draw offsets across the 2^32 counter-word boundary, 63-bit seeds, buffer sizes beyond 2^32: numpy and C oracles."""
+    import numpy as np
+    from oracle import c_oracle, replay_ref
+    got = ops.sample_uniform(seed, stream, off, n, size, cuda).cpu().numpy()
+    assert np.array_equal(got, replay_ref.sample_uniform(seed, stream, off, n, size))
+    assert np.array_equal(got, c_oracle.sample_uniform(seed, stream, off, n, size))
+    if size <= 5000:                                           # the fused draw + gather uses the same stream
+        store = torch.arange(size, device=cuda).reshape(size, 1)
+        idx, (rows,) = ops.sample_gather_fields([store], seed, stream, off, n, size)
+        assert np.array_equal(idx.cpu().numpy(), got) and torch.equal(rows.reshape(-1), idx)
