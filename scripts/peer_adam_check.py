@@ -20,8 +20,10 @@ def main():
     dev = torch.device("cuda", torch.cuda.current_device())
     dist.init_process_group("nccl", device_id=dev)
     results = {}
-    for route, n in [(r, n) for r in ("one_shot", "two_shot", "nvls") for n in (630_352, 1001, 3_000_000)]:
-        # the reference model, a ragged tiny one, a streaming-path one; every exchange route
+    timed_sizes, check_only = (630_352, 1001, 3_000_000), (9, 4099, 70_001)
+    for route, n in [(r, n) for r in ("one_shot", "two_shot", "nvls") for n in timed_sizes + check_only]:
+        # the reference model, a ragged tiny one, a streaming-path one (timed); fewer elements than one CTA / than the
+        # ranks' two-shot slices, sizes that are no multiple of 4 (checked only); every exchange route
         os.environ["B200RL_K8_TWO_SHOT"] = "0" if route == "one_shot" else "1"
         os.environ["B200RL_K8_NVLS"] = "1" if route == "nvls" else "0"
         os.environ["B200RL_PEER_TRANSPORT"] = "auto" if route == "nvls" else "ipc"
@@ -84,6 +86,10 @@ def main():
             dist.all_reduce(ref.flat)
             opt_b.step_flat(ref.grads, 0.5)
 
+        if n in check_only:
+            dist.barrier()
+            bucket.close()
+            continue
         results["%s n=%d" % (route, n)] = {"k8_us": round(timed(lambda: opt_a.step_peer(bucket, 0.5)), 2), "nccl_plus_k6_us": round(timed(nccl_route), 2)}
         dist.barrier()
         bucket.close()
