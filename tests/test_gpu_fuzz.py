@@ -298,14 +298,14 @@ def test_sumtree_random_update_sequences_bit_exact(cuda, cap, seed):
             assert np.array_equal(got_idx.cpu().numpy(), want_idx) and np.array_equal(got_p.cpu().numpy(), want_p)
 
 
-def _k9_cases(n, seed):
+def _k7_cases(n, seed):
     rng = random.Random(seed)
     return [(rng.randint(1, 400), rng.choice([1, 2, 7, 20, 33, 128]), rng.choice([1, 4, 6, 15, 18, 32]),
              rng.choice([0.0, 0.9, 0.95, 1.0]), rng.choice([0.9, 0.99])) for _ in range(n)]
 
 
-@pytest.mark.parametrize("B,T,A,lam,gamma", _k9_cases(10 * _MORE, seed=11))
-def test_k9_random_shapes_against_the_oracle(cuda, B, T, A, lam, gamma):
+@pytest.mark.parametrize("B,T,A,lam,gamma", _k7_cases(10 * _MORE, seed=11))
+def test_k7_random_shapes_against_the_oracle(cuda, B, T, A, lam, gamma):
     """As test_ppo_is_parity, minus the samples whose probability ratio sits within 1e-5 of a clip boundary (0.9, 1, 1.1):
     the gradient is discontinuous there and a last-bit difference of the ratio legitimately picks the other branch
     (one such sample in ~2.4 M drawn ones is what this test met before the mask)."""
