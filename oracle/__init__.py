@@ -30,6 +30,11 @@ reference's own files with import shims for the absent third-party names
 checked in ``tests/test_reference_golden.py``) -- ``losses.ppo_loss``,
 ``quantile_regression_loss``, the whole of ``ImpalaLearner._train_step`` around
 the rlego call (slices, means, signs, no-detach, clip, Adam) and
-``losses.impala_loss`` as committed.  The rlego recursions themselves are
-covered by hand-derived known-answer cases in ``tests/`` only.
+``losses.impala_loss`` as committed.  The rlego recursions themselves cannot be
+checked against rlego (unobtainable): they are covered by hand-derived known-answer
+cases and -- an EXTERNAL pin of the algorithms they restate -- by the known answers
+of rlax's own unit tests for V-trace (TD errors, policy-gradient advantages),
+lambda-returns and GAE (``tests/rlax_vectors.py``, which states how those vectors
+got here; ``tests/test_oracle.py::test_rlax_published_vectors``).  That rlego
+computes what rlax computes remains the assumption its function names invite.
 """

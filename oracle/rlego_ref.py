@@ -1,6 +1,7 @@
 """Restatement of the ``rlego`` functions the reference calls (TEST ORACLE, CPU).
 
-``rlego`` is absent and unpinned (see ``oracle/__init__.py``): PARITY UNPINNED.
+``rlego`` is absent and unpinned (see ``oracle/__init__.py``): PARITY UNPINNED against rlego itself; the rlax algorithms
+restated here reproduce the known answers of rlax's own unit tests (``tests/rlax_vectors.py``).
 Per-sequence ``[T]`` functions with a Python loop over time, exactly the shape
 the reference feeds to ``functorch.vmap`` (``agents/impala/learning.py:18``).
 Algorithms follow DeepMind rlax (the package rlego mirrors name-for-name).

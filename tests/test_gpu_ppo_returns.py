@@ -391,3 +391,38 @@ def test_ppo_streaming_kernel_matches_tile_kernel_on_ragged_large_minibatches(cu
         torch.cuda.synchronize()
     assert torch.equal(outs["1"][1], outs["2"][1]) and torch.equal(outs["1"][2], outs["2"][2])
     torch.testing.assert_close(outs["1"][0][:7], outs["2"][0][:7], rtol=1e-5, atol=1e-6)
+
+
+def test_rlax_published_vectors_on_the_kernels(cuda):
+    """The stand-alone V-trace kernel, the K2 scans and (through its td / pg metrics) the fused K1 kernel against the known
+    answers of rlax's own unit tests (tests/rlax_vectors.py states the provenance)."""
+    import rlax_vectors as rv
+    C = lambda x: torch.from_numpy(np.ascontiguousarray(x)).to(cuda)
+    rho, v_t = rv.rho_tm1(), rv.v_t()
+    adv, err, q = vtrace.batched_vtrace(C(rv.VALUES), C(v_t), C(rv.REWARDS), C(rv.DISCOUNTS), C(rho), **rv.VTRACE_KW)
+    np.testing.assert_allclose(err.cpu().numpy(), rv.EXPECTED_TD, rtol=1e-6, atol=1e-10)
+    np.testing.assert_allclose(adv.cpu().numpy(), rv.EXPECTED_PG, rtol=1e-6, atol=1e-10)
+    for tm in (False, True):
+        f = (lambda x: C(x.T)) if tm else C
+        got = vtrace.lambda_returns(f(rv.MS_R), f(rv.MS_DISCOUNT), f(rv.MS_V), rv.MS_LAMBDA, time_major=tm)
+        np.testing.assert_allclose((got.t() if tm else got).cpu().numpy(), rv.EXPECTED_LAMBDA_RETURNS, rtol=1e-6)
+        for lam, want in rv.EXPECTED_GAE.items():
+            got = vtrace.truncated_generalized_advantage_estimation(f(rv.GAE_R), f(rv.GAE_DISCOUNT), lam, f(rv.GAE_V), time_major=tm)
+            np.testing.assert_allclose((got.t() if tm else got).cpu().numpy(), want, atol=1e-3)
+    # K1: the same rollouts as [B, T=5] learner inputs (values carry the bootstrap as their last step; the last step's
+    # logits / reward / discount do not enter V-trace).  train/td = mean(err^2), train/pg = mean(log pi(a) * adv), :155-156
+    pad = lambda x, fill: np.concatenate([x, np.full_like(x[:, :1], fill)], axis=1)
+    logits, pi_ref = pad(rv.TARGET_LOGITS, 0.5), pad(rv.BEHAVIOR_LOGITS, 0.25)
+    a = pad(rv.ACTIONS, 0)
+    values = np.concatenate([rv.VALUES, rv.BOOTSTRAP[:, None]], axis=1)
+    for impl in ("1", "2"):
+        os.environ["B200RL_K1_TILE"] = impl
+        try:
+            sc, _, _ = ops.impala_loss_fwdbwd(C(logits), C(values), C(a), C(pad(rv.REWARDS, 7.0)), C(pad(rv.DISCOUNTS, 0.9)), C(pi_ref))
+        finally:
+            os.environ.pop("B200RL_K1_TILE")
+        lp = torch.log_softmax(torch.from_numpy(rv.TARGET_LOGITS).double(), -1).gather(-1, torch.from_numpy(rv.ACTIONS)[..., None])[..., 0]
+        want_td = float((rv.EXPECTED_TD.astype(np.float64) ** 2).mean())
+        want_pg = float((lp.numpy() * rv.EXPECTED_PG.astype(np.float64)).mean())
+        assert float(sc[ops.S_TD]) == pytest.approx(want_td, rel=2e-6)
+        assert float(sc[ops.S_PG]) == pytest.approx(want_pg, rel=5e-6)      # rlax prints EXPECTED_PG to 8 digits; fp32 mean of 8 products

@@ -308,3 +308,26 @@ def test_ppo_loss_is_restatement():
     l2, _ = losses_ref.ppo_loss_is((s, d["a"][..., None], d["r"][..., None], s, done, d["pi_ref"]), model)
     l3, _ = losses_ref.ppo_is_loss_from_outputs(d["logits"], d["values"], d["v_boot"], d["a"], d["r"], done, d["pi_ref"])
     assert l2.item() == l3.item()
+
+
+def test_rlax_published_vectors():
+    """The recursions against the known answers of rlax's own unit tests (tests/rlax_vectors.py states the provenance):
+    V-trace TD errors to the last printed digit, policy-gradient advantages and lambda-returns to 1e-6, GAE to the
+    rlax test's own atol.  This is an EXTERNAL pin of what `rlego_ref` restates."""
+    import rlax_vectors as rv
+    T = torch.from_numpy
+    rho, v_t = rv.rho_tm1(), rv.v_t()
+    for i in range(2):
+        adv, err, q = rlego_ref.vtrace_td_error_and_advantage(T(rv.VALUES[i]), T(v_t[i]), T(rv.REWARDS[i]), T(rv.DISCOUNTS[i]),
+                                                              T(rho[i]), **rv.VTRACE_KW)
+        np.testing.assert_allclose(err.numpy(), rv.EXPECTED_TD[i], rtol=2e-7, atol=1e-11)
+        np.testing.assert_allclose(adv.numpy(), rv.EXPECTED_PG[i], rtol=1e-6, atol=1e-10)
+        got = rlego_ref.lambda_returns(T(rv.MS_R[i]), T(rv.MS_DISCOUNT[i]), T(rv.MS_V[i]), lambda_=rv.MS_LAMBDA)
+        np.testing.assert_allclose(got.numpy(), rv.EXPECTED_LAMBDA_RETURNS[i], rtol=1e-6)
+        for lam, want in rv.EXPECTED_GAE.items():
+            got = rlego_ref.truncated_generalized_advantage_estimation(T(rv.GAE_R[i]), T(rv.GAE_DISCOUNT[i]), lam, T(rv.GAE_V[i]))
+            np.testing.assert_allclose(got.numpy(), want[i], atol=1e-3)
+    # batched form (what the reference vmaps) and the C restatement of the scans
+    adv, err, q = rlego_ref.batched(rlego_ref.vtrace_td_error_and_advantage, **rv.VTRACE_KW)(
+        T(rv.VALUES), T(v_t), T(rv.REWARDS), T(rv.DISCOUNTS), T(rho))
+    np.testing.assert_allclose(err.numpy(), rv.EXPECTED_TD, rtol=2e-7, atol=1e-11)
