@@ -409,6 +409,10 @@ def test_rlax_published_vectors_on_the_kernels(cuda):
         for lam, want in rv.EXPECTED_GAE.items():
             got = vtrace.truncated_generalized_advantage_estimation(f(rv.GAE_R), f(rv.GAE_DISCOUNT), lam, f(rv.GAE_V), time_major=tm)
             np.testing.assert_allclose((got.t() if tm else got).cpu().numpy(), want, atol=1e-3)
+    # rlax's test_lambda_q_estimate on the kernel: vs = v + min(1, rho) (q - v) at lambda = 0.8 (fixes the q bootstrap)
+    adv8, err8, q8 = vtrace.batched_vtrace(C(rv.VALUES), C(v_t), C(rv.REWARDS), C(rv.DISCOUNTS), C(rho), lambda_=0.8)
+    vs_from_q = C(rv.VALUES) + torch.clamp(C(rho), max=1.0) * (q8 - C(rv.VALUES))
+    np.testing.assert_allclose((err8 + C(rv.VALUES)).cpu().numpy(), vs_from_q.cpu().numpy(), rtol=1e-5, atol=1e-5)
     # K1: the same rollouts as [B, T=5] learner inputs (values carry the bootstrap as their last step; the last step's
     # logits / reward / discount do not enter V-trace).  train/td = mean(err^2), train/pg = mean(log pi(a) * adv), :155-156
     pad = lambda x, fill: np.concatenate([x, np.full_like(x[:, :1], fill)], axis=1)

@@ -331,3 +331,17 @@ def test_rlax_published_vectors():
     adv, err, q = rlego_ref.batched(rlego_ref.vtrace_td_error_and_advantage, **rv.VTRACE_KW)(
         T(rv.VALUES), T(v_t), T(rv.REWARDS), T(rv.DISCOUNTS), T(rho))
     np.testing.assert_allclose(err.numpy(), rv.EXPECTED_TD, rtol=2e-7, atol=1e-11)
+
+
+def test_rlax_lambda_q_estimate_identity():
+    """rlax's `test_lambda_q_estimate` (vtrace_test.py), on its data: at lambda = 0.8 and clip_rho = 1 the V-trace targets
+    satisfy vs = v + min(1, rho) * (q_estimate - v).  This is what fixes the q bootstrap as lambda * vs' + (1 - lambda) * v'
+    (the lambda = 1 vectors above cannot tell)."""
+    import rlax_vectors as rv
+    T = torch.from_numpy
+    rho, v_t = rv.rho_tm1(), rv.v_t()
+    adv, err, q = rlego_ref.batched(rlego_ref.vtrace_td_error_and_advantage, lambda_=0.8, clip_rho_threshold=1.0)(
+        T(rv.VALUES), T(v_t), T(rv.REWARDS), T(rv.DISCOUNTS), T(rho))
+    vs = err + T(rv.VALUES)
+    vs_from_q = T(rv.VALUES) + torch.clamp(T(rho), max=1.0) * (q - T(rv.VALUES))
+    np.testing.assert_allclose(vs.numpy(), vs_from_q.numpy(), rtol=1e-5, atol=1e-5)
