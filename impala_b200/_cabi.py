@@ -46,6 +46,7 @@ SIGNATURES = {
     "b200rl_sumtree_update": (_i32, [_vp, _i64, _vp, _vp, _i64, _vp]),
     "b200rl_sumtree_sample": (_i32, [_vp, _i64, _i64, _u64, _u32, _u64, _i64, _vp, _vp, _vp]),
     "b200rl_quantile_huber_fwdbwd": (_i32, [_vp] * 3 + [_i64] * 3 + [_f] + [_vp] * 3),
+    "b200rl_per_td_loss_fwdbwd": (_i32, [_vp] * 4 + [_i64] * 2 + [_f] + [_vp] * 6),
     "b200rl_act_epilogue": (_i32, [_vp, _i64, _i64, _vp, _i64, _u64, _u32, _u64, _vp, _vp]),
     "b200rl_clip_adam_step": (_i32, [_vp] * 4 + [_i64, _f] + [_d] * 4 + [_i64] + [_vp] * 4),
     "b200rl_peer_allreduce_clip_adam_step": (_i32, [_vp] * 7 + [_i32] * 2 + [_vp] * 2 + [_i64] + [_vp] * 2 + [_i64, _f] +

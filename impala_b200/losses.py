@@ -178,3 +178,18 @@ def quantile_regression_loss(dist_src, tau_src, dist_target, huber_param: float 
     """Drop-in for reference ``models/quantile_layers.py:83-93`` (per-sample loss ``[B]``, differentiable w.r.t.
     ``dist_src``; ``tau_src`` enters only through the detached weights, ``dist_target`` is a target)."""
     return _QuantileHuber.apply(dist_src, tau_src, dist_target, float(huber_param))
+
+
+def per_td_loss(q, action, target, probabilities, importance_sampling_exponent: float):
+    """The loss block of ``ApexLearner._train_step`` (reference ``agents/dqn/learning.py:161-172``) on the Q network's
+    output ``q [N,A]``: ``loss = 0.5 * mean((target - q.gather(1, action))^2 * w)``, ``w`` = the prioritized sampler's
+    probabilities turned into max-normalised importance weights.  Returns ``(loss, priorities, metrics)``:
+    ``loss.backward()`` reaches the Q network, ``priorities = |target - q|`` go back to ``ReplayBuffer.update`` (``:184``),
+    ``metrics`` carry the reference's ``train_step/*`` keys as device scalars.  One kernel launch (N3b)."""
+    scalars, dq, priorities, _ = ops.per_td_loss_fwdbwd(_as_input(q, "q"), _as_input(action, "action", torch.int64),
+                                                        _as_input(target, "target"), _as_input(probabilities, "probabilities"),
+                                                        importance_sampling_exponent)
+    loss = _attach(scalars[0], (q,), (dq,))
+    metrics = {"train_step/q": scalars[1], "train_step/target": scalars[2], "train_step/priorities": scalars[3],
+               "train_step/loss": scalars[0]}
+    return loss, priorities, metrics

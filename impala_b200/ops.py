@@ -475,6 +475,27 @@ def quantile_huber_fwdbwd(dist_src, tau_src, dist_target, huber_param=1.0):
     return loss, d_src
 
 
+def per_td_loss_fwdbwd(q, actions, target, probabilities, importance_sampling_exponent, want_weights=False):
+    """N3b (reference ``agents/dqn/learning.py:161-172``).  ``q [N,A]``, ``actions, target, probabilities [N]`` ->
+    ``(scalars[8], dq [N,A], priorities [N], weights [N] or None)``; ``scalars`` = loss, mean q, mean target, mean
+    priority, the weight normaliser."""
+    _require_cuda(q, actions, target, probabilities)
+    q, target, probabilities = _f32c(q.detach(), "q"), _f32c(target.detach(), "target"), _f32c(probabilities, "probabilities")
+    actions = _i64c(actions, "actions")
+    if q.dim() != 2 or any(tuple(x.shape) != (q.shape[0],) for x in (actions, target, probabilities)):
+        raise RuntimeError("per_td_loss: expected q [N,A] and actions / target / probabilities [N], got %s %s %s %s"
+                           % (tuple(q.shape), tuple(actions.shape), tuple(target.shape), tuple(probabilities.shape)))
+    N, A = q.shape
+    scalars = torch.empty(8, dtype=torch.float32, device=q.device)
+    dq, priorities = torch.empty_like(q), torch.empty_like(target)
+    weights = torch.empty_like(target) if want_weights else None
+    ws = workspace(q.device)
+    _cabi.call("b200rl_per_td_loss_fwdbwd", q.data_ptr(), actions.data_ptr(), target.data_ptr(), probabilities.data_ptr(),
+               N, A, float(importance_sampling_exponent), dq.data_ptr(), priorities.data_ptr(), _cabi.ptr(weights),
+               scalars.data_ptr(), ws.data_ptr(), _stream())
+    return scalars, dq, priorities, weights
+
+
 def act_epilogue(logits, deterministic, seed, stream_id, draw_offset):
     """N5.  ``logits [n,A]`` -> int64 actions ``[n,1]``; ``deterministic``: bool tensor of 1 or n elements."""
     _require_cuda(logits)

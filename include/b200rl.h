@@ -161,6 +161,18 @@ int32_t b200rl_quantile_huber_fwdbwd(
     const float *dist_src, const float *tau_src, const float *dist_target, int64_t B, int64_t N, int64_t M,
     float huber_param, float *loss, float *d_src, void *stream);
 
+/* N3b -- the prioritized-replay-weighted TD loss of ApexLearner._train_step after q = model(obs) (reference
+ * agents/dqn/learning.py:161-170) with its backward w.r.t. q (:169) and the new priorities (:172), one launch:
+ * q [N,A], actions / target / probabilities [N] (the probabilities the PER sampler returned, N3);
+ * w_i = p_i^(-exponent) / max_j p_j^(-exponent); loss = 0.5 mean((target - q[i,a_i])^2 w_i);
+ * dq [N,A] = d loss / d q (one non-zero per row), priorities [N] = |target - q[i,a_i]|, weights [N] (may be NULL);
+ * scalars[8] = loss, mean q (:188), mean target (:189), mean priority (:190), max_j p_j^(-exponent), 0, 0, 0.
+ * `workspace` as for the fused losses. */
+int32_t b200rl_per_td_loss_fwdbwd(
+    const float *q, const int64_t *actions, const float *target, const float *probabilities, int64_t N, int64_t A,
+    float importance_sampling_exponent, float *dq, float *priorities, float *weights, float *scalars, void *workspace,
+    void *stream);
+
 /* K3 -- replaces losses.ppo_loss after model(s) + backward w.r.t. model outputs
  * (reference losses.py:134-155, caller agents/ppo/learning.py:132-134).
  * Flat minibatch: logits, pi_ref [N,A]; actions, v_target, v [N].

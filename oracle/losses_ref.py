@@ -209,3 +209,18 @@ def act_epilogue(logits, deterministic, seed, stream_id, draw_offset):
     det = np.broadcast_to(np.asarray(deterministic, dtype=bool).reshape(-1), (n,))
     a = np.where(det, x.argmax(1), a)
     return a, u, cum / cum[:, -1:]
+
+
+def apex_td_loss(q_all, action, target, probabilities, importance_sampling_exponent):
+    """Reference ``ApexLearner._train_step`` lines ``agents/dqn/learning.py:161-172,188-191`` on the Q network's output:
+    ``(loss, priorities, metrics)``."""
+    q = q_all.gather(1, action.unsqueeze(-1)).squeeze(-1)                       # :161-162
+    probabilities = probabilities.to(dtype=q.dtype)                             # :164
+    weight = probabilities.pow(-importance_sampling_exponent)                   # :165
+    weight = weight / weight.max()                                              # :166 (div_ in place there)
+    err = target - q                                                            # :167
+    loss = 0.5 * (err.pow(2) * weight).mean()                                   # :168
+    priorities = err.detach().abs()                                             # :172
+    metrics = {"train_step/q": q.mean().detach(), "train_step/target": target.mean(),
+               "train_step/priorities": priorities.mean(), "train_step/loss": loss.detach()}   # :188-191
+    return loss, priorities, metrics

@@ -132,3 +132,32 @@ vs = [[torch.randn(Bv, Tv, device=dev) for _ in range(4)] + [torch.rand(Bv, Tv, 
 report("A1 stand-alone V-trace fwd B=4096 T-1=19 (batch-major)", timed(lambda i: ops.vtrace_fwd(*vs[i % 60])), 32 * Bv * Tv,
        "20 B read + 12 B written per step; 2.5 MB per launch: launch-bound")
 del vs
+
+# N3b: PER-weighted TD loss (agents/dqn/learning.py:161-172): Ape-X batch 512 x 18 actions, and a large batch; next to
+# the eager torch ops of the reference's lines on the same tensors
+for Np, Ap in ((512, 18), (65536, 18)):
+    per = [(torch.randn(Np, Ap, device=dev), torch.randint(0, Ap, (Np,), device=dev), torch.randn(Np, device=dev),
+            torch.rand(Np, device=dev) * 0.01 + 1e-5) for _ in range(20)]
+    us = timed(lambda i: ops.per_td_loss_fwdbwd(*per[i % 20], 0.4), n_streams=1)
+    nbytes = Np * (32 + 8 + 4 + 4 + 4 * Ap + 4)     # one sector of q, action, target, probability in; dq row + priority out
+    report("N3b PER TD loss N=%d A=%d" % (Np, Ap), us, nbytes, "dependent chain on one stream")
+
+    def eager(i):
+        q, a, tg, p = per[i % 20]
+        q = q.clone().requires_grad_(True)
+        qa = q.gather(1, a.unsqueeze(-1)).squeeze(-1)
+        w = p.pow(-0.4)
+        w = w / w.max()
+        err = tg - qa
+        (0.5 * (err.pow(2) * w).mean()).backward()
+        return err.detach().abs()
+    for _ in range(5):
+        eager(0)
+    torch.cuda.synchronize()
+    a0, b0 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record()
+    for i in range(100):
+        eager(i)
+    b0.record(); torch.cuda.synchronize()
+    report("   the reference's eager torch ops for the same lines N=%d" % Np, a0.elapsed_time(b0) * 10, nbytes, "eager, host-launched")
+    del per

@@ -583,3 +583,10 @@ def test_k4_random_streams_offsets_and_sizes_bit_exact(cuda, seed, stream, off, 
         store = torch.arange(size, device=cuda).reshape(size, 1)
         idx, (rows,) = ops.sample_gather_fields([store], seed, stream, off, n, size)
         assert np.array_equal(idx.cpu().numpy(), got) and torch.equal(rows.reshape(-1), idx)
+
+
+@pytest.mark.parametrize("N,A,beta", [(random.Random(300 + i).randint(1, 20000), random.Random(310 + i).choice([1, 2, 4, 6, 18, 33, 51, 200]),
+                                       random.Random(320 + i).choice([0.0, 0.4, 0.6, 1.0])) for i in range(8 * _MORE)])
+def test_per_td_loss_random_shapes(cuda, N, A, beta):
+    import importlib
+    importlib.import_module("test_gpu_replay_learner").test_per_td_loss_matches_the_reference_lines(cuda, N, A, beta)

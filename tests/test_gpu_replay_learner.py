@@ -9,7 +9,7 @@ import torch
 
 from conftest import GOLDEN
 from gpu_util import assert_close
-from impala_b200 import models, ops, optim, replay, synth
+from impala_b200 import losses, models, ops, optim, replay, synth
 from impala_b200.agents import ImpalaLearner, PPOLearner
 from oracle import c_oracle, losses_ref, replay_ref
 
@@ -479,3 +479,45 @@ def test_ppo_learner_step_as_one_cuda_graph_matches_eager_steps(cuda):
     assert opt_g.sync_step_count() == steps and graphed._step_counter == steps
     assert model_g.pushes == model_e.pushes == [2, 4]
     assert int(rb_g.sampler.draw_counter.item()) == steps * N == rb_e.sampler.draws
+
+
+@pytest.mark.parametrize("N,A,beta", [(512, 18, 0.4), (1, 1, 0.4), (33, 6, 0.0), (4096, 4, 1.0), (100_000, 15, 0.6), (257, 51, 0.4)])
+def test_per_td_loss_matches_the_reference_lines(cuda, N, A, beta):
+    """N3b: the PER-weighted TD loss of ApexLearner._train_step (reference agents/dqn/learning.py:161-172) in one launch:
+    loss, the gradient the Q network receives, the new priorities and the logged means against the oracle; then the whole
+    prioritized loop on the device -- sample (N3) -> loss -> update(keys, priorities)."""
+    g = torch.Generator().manual_seed(N + A)
+    q = torch.randn(N, A, generator=g)
+    a = torch.randint(0, A, (N,), generator=g)
+    tgt = torch.randn(N, generator=g) * 2
+    p = (torch.rand(N, generator=g) ** 3) * 0.01 + 1e-6
+    qc = q.clone().requires_grad_(True)
+    want_loss, want_pri, want_m = losses_ref.apex_td_loss(qc, a, tgt, p, beta)
+    want_loss.backward()
+    qg = q.to(cuda).requires_grad_(True)
+    loss, pri, m = losses.per_td_loss(qg, a.to(cuda), tgt.to(cuda), p.to(cuda), beta)
+    loss.backward()
+    assert_close(loss, want_loss, "loss", rtol=1e-5, atol=1e-6)
+    for k in want_m:
+        assert_close(m[k], want_m[k], k, rtol=1e-5, atol=1e-6)
+    assert_close(pri, want_pri, "priorities", rtol=1e-6, atol=1e-7)
+    assert_close(qg.grad * N, qc.grad * N, "dq x N", rtol=1e-5, atol=1e-6)
+    assert int((qg.grad != 0).sum()) <= N                                    # one element per row at most
+    sc, dq, pr2, w = ops.per_td_loss_fwdbwd(q.to(cuda), a.to(cuda), tgt.to(cuda), p.to(cuda), beta, want_weights=True)
+    wref = p.pow(-beta)
+    assert_close(w, wref / wref.max(), "weights", rtol=1e-5, atol=1e-7)
+    sc2, dq2, _, _ = ops.per_td_loss_fwdbwd(q.to(cuda), a.to(cuda), tgt.to(cuda), p.to(cuda), beta)
+    assert torch.equal(sc, sc2) and torch.equal(dq, dq2)                      # deterministic
+    if N != 512:
+        return
+    rb = replay.ReplayBuffer(replay.CircularBuffer(2048, collate_fn=torch.cat, device=cuda), replay.PrioritizedSampler(0.6))
+    rb.sampler.reset(3)
+    rb.extend((torch.randn(2048, 8), torch.randint(0, A, (2048,)), torch.randn(2048)), priorities=torch.rand(2048) + 0.1)
+    keys, (obs, act, target), probs = rb.sample(N)
+    net = torch.nn.Linear(8, A).to(cuda)
+    loss, priorities, metrics = losses.per_td_loss(net(obs), act, target, probs, 0.4)
+    loss.backward()
+    assert net.weight.grad is not None and torch.isfinite(net.weight.grad).all()
+    before = rb.sampler.tree[1].item()
+    rb.update(keys, priorities)                                               # :184
+    assert rb.sampler.tree[1].item() != before

@@ -345,3 +345,24 @@ def test_rlax_lambda_q_estimate_identity():
     vs = err + T(rv.VALUES)
     vs_from_q = T(rv.VALUES) + torch.clamp(T(rho), max=1.0) * (q - T(rv.VALUES))
     np.testing.assert_allclose(vs.numpy(), vs_from_q.numpy(), rtol=1e-5, atol=1e-5)
+
+
+def test_apex_td_loss_restatement():
+    """N3b oracle (reference agents/dqn/learning.py:161-172): weights are max-normalised importance weights of the
+    sampler's probabilities, constants for autograd; d loss / d q is -err * w / N at the taken action only."""
+    g = torch.Generator().manual_seed(0)
+    N, A, beta = 64, 6, 0.4
+    q = torch.randn(N, A, generator=g, dtype=torch.float64, requires_grad=True)
+    a = torch.randint(0, A, (N,), generator=g)
+    tgt = torch.randn(N, generator=g, dtype=torch.float64)
+    p = torch.rand(N, generator=g, dtype=torch.float64) * 0.01 + 1e-4
+    loss, pri, m = losses_ref.apex_td_loss(q, a, tgt, p, beta)
+    loss.backward()
+    w = p.pow(-beta)
+    w = w / w.max()
+    err = tgt - q.detach().gather(1, a[:, None])[:, 0]
+    want = torch.zeros(N, A, dtype=torch.float64)
+    want[torch.arange(N), a] = -err * w / N
+    assert torch.allclose(q.grad, want, rtol=1e-12, atol=1e-15)
+    assert torch.equal(pri, err.abs()) and float(w.max()) == 1.0 and float(m["train_step/loss"]) == float(loss.detach())
+    assert float(loss) == pytest.approx(float(0.5 * (err ** 2 * w).mean()), rel=1e-12)
