@@ -365,4 +365,4 @@ def test_apex_td_loss_restatement():
     want[torch.arange(N), a] = -err * w / N
     assert torch.allclose(q.grad, want, rtol=1e-12, atol=1e-15)
     assert torch.equal(pri, err.abs()) and float(w.max()) == 1.0 and float(m["train_step/loss"]) == float(loss.detach())
-    assert float(loss) == pytest.approx(float(0.5 * (err ** 2 * w).mean()), rel=1e-12)
+    assert float(loss.detach()) == pytest.approx(float(0.5 * (err ** 2 * w).mean()), rel=1e-12)
