@@ -261,6 +261,9 @@ def make_learner(args, device, seed):
     from impala_b200.agents.impala import ImpalaLearner
     B, T, A = args.B or 256, args.T or 20, args.A
     torch.manual_seed(seed)
+    # the reference's own setting (main.py:59): cuDNN picks its algorithm for the remaining (32 -> 32 channel) layers by
+    # measurement during the warm-up steps; B200RL_BENCH_CUDNN_BENCHMARK=0 for torch's default heuristics
+    torch.backends.cudnn.benchmark = os.environ.get("B200RL_BENCH_CUDNN_BENCHMARK", "1") == "1"
     cl = os.environ.get("B200RL_BENCH_CHANNELS_LAST", "1") == "1"
     fused = cl and os.environ.get("B200RL_BENCH_FUSED_GLUE", "1") == "1"
     model = models.ActorCritic((3, 64, 64), A, body="impala", channels_last=cl, fused_glue=fused).to(device)
