@@ -9,6 +9,7 @@ from impala_b200 import ops
 dev = torch.device("cuda", 0)
 CL = torch.channels_last
 N = int(os.environ.get("N", 5120))
+torch.backends.cudnn.benchmark = os.environ.get("CUDNN_BENCHMARK", "0") == "1"     # the reference sets it (main.py:59)
 LAYERS = [("s1.conv", 3, 16, 64), ("s1.res", 16, 16, 32), ("s2.conv", 16, 32, 32), ("s2.res", 32, 32, 16),
           ("s3.conv", 32, 32, 16), ("s3.res", 32, 32, 8)]
 
