@@ -327,6 +327,11 @@ def make_learner(args, device, seed):
         learner.profile = True
         saved_graph, learner._graph = learner._graph, None      # the phases are timed on the eager path
         tot, names = {}, []
+        learner.profile = False
+        for _ in range(2):                                       # eager path on THIS stream: cuDNN's autotuning (cudnn.benchmark)
+            learner._train_step(rb.sample(B)[1])                 # and workspace allocation stay out of the profiled steps
+        torch.cuda.synchronize()
+        learner.profile = True
         for _ in range(5):
             t0 = torch.cuda.Event(enable_timing=True)
             t0.record()
