@@ -752,6 +752,9 @@ def k8_check(args, device, rank, world_size):
     flats = {}
     saved = os.environ.get("B200RL_BENCH_LEARNER_GRAPH")
     os.environ["B200RL_BENCH_LEARNER_GRAPH"] = "0"      # both routes eagerly, step for step
+    saved_cb = os.environ.get("B200RL_BENCH_CUDNN_BENCHMARK")
+    os.environ["B200RL_BENCH_CUDNN_BENCHMARK"] = "0"    # the two learners must run the SAME convolution algorithms: autotuning
+    #                                                     picks per learner, and Adam turns the rounding differences into 4e-5
     for route, env in (("k8_peer", "auto"), ("nccl", "0")):
         os.environ["B200RL_PEER_ALLREDUCE"] = env
         a = copy.copy(args)
@@ -774,6 +777,11 @@ def k8_check(args, device, rank, world_size):
         del w, learner
         torch.cuda.empty_cache()
     os.environ.pop("B200RL_PEER_ALLREDUCE", None)
+    if saved_cb is None:
+        os.environ.pop("B200RL_BENCH_CUDNN_BENCHMARK", None)
+    else:
+        os.environ["B200RL_BENCH_CUDNN_BENCHMARK"] = saved_cb
+    torch.backends.cudnn.benchmark = os.environ.get("B200RL_BENCH_CUDNN_BENCHMARK", "1") == "1"
     if saved is None:
         os.environ.pop("B200RL_BENCH_LEARNER_GRAPH", None)
     else:
